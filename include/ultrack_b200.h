@@ -1,0 +1,140 @@
+/*
+ * ultrack_b200.h -- C ABI of the B200-native candidate-generation path.
+ *
+ * ultrack (the reference) has no FFI layer on this path: segment() and link() are Python
+ * functions whose arithmetic lives in numba / higra / scipy.  This library sits UNDER the
+ * same two Python entry points (ultrack_b200.segment / ultrack_b200.link mirror
+ * ultrack/core/segmentation/processing.py:393 and ultrack/core/linking/processing.py:294)
+ * and replaces, per timepoint, the bodies of
+ *
+ *   ulk_segment_frame*   <- core/segmentation/processing.py:160-340   (_process: threshold,
+ *                           create_hierarchies, Hierarchy.nodes, ids / overlaps)
+ *                           core/segmentation/hierarchy.py:33-90, vendored/hierarchy.py:125-365,
+ *                           vendored/node.py:27-141, node.py:229-233
+ *   ulk_link_frames      <- core/linking/processing.py:172-291        (compute_spatial_neighbors:
+ *                           KD-tree k-NN, IoU, top-k) and core/segmentation/node.py:23-118
+ *   ulk_labels_to_contours <- utils/edge.py:18-96                      (labels_to_contours)
+ *
+ * Conventions: every function returns 0 on success and a negative code on failure and never
+ * throws; ulk_last_error() gives the message of the calling thread's last failure.  Code -10
+ * is the reference's RuntimeError("Region too small...") (vendored/hierarchy.py:161-162).
+ * Frames are C-contiguous [D,H,W] (2-D frames: D = 1).  Device pointers unless the name
+ * says _host.  Results are owned by the library until the matching ulk_*_free.
+ */
+#ifndef ULTRACK_B200_H
+#define ULTRACK_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ULK_API __attribute__((visibility("default")))
+
+/* element types of foreground / contours / labels */
+enum { ULK_DT_U8 = 0, ULK_DT_I8 = 1, ULK_DT_U16 = 2, ULK_DT_I16 = 3, ULK_DT_F16 = 4, ULK_DT_F32 = 5,
+       ULK_DT_F64 = 6, ULK_DT_I32 = 7, ULK_DT_U32 = 8, ULK_DT_I64 = 9, ULK_DT_U64 = 10 };
+
+/* SegmentationConfig fields _process reads (config/segmentationconfig.py:19-57).
+ * `threshold` must already be rounded to the foreground dtype when that is a float type
+ * (numpy compares `foreground > threshold` in the array's own precision). */
+typedef struct ulk_seg_params {
+    double threshold;
+    double min_area;
+    double max_area;
+    double min_area_factor;
+    double min_frontier;
+    int32_t ws_hierarchy;      /* 0 = area, 1 = dynamics (hg.watershed_hierarchy_by_*) */
+    int32_t reserved;
+} ulk_seg_params;
+
+typedef struct ulk_seg_stats {
+    int64_t n_basins, n_rag_edges, plateau_voxels;
+    int32_t flow_rounds, k3_rounds;
+} ulk_seg_stats;
+
+/* Candidate nodes of one frame, device-resident struct of arrays.  Node order is the
+ * reference's emission order (t_node_id = index + 1). */
+typedef struct ulk_frame_nodes {
+    int32_t n_nodes, n_overlaps, n_hier, fix_shift;
+    int32_t shape[3];
+    int32_t pad0;
+    int64_t mask_words;
+    int32_t *bbox;        /* [n,6]  z0,y0,x0,z1,y1,x1 (max exclusive), frame coordinates        */
+    int32_t *centroid;    /* [n,3]  z,y,x (node.py:229-233)                                     */
+    int32_t *area;        /* [n]                                                                */
+    double *frontier;     /* [n]    hg.attribute_contour_strength, -1 for the root fallback     */
+    double *height;       /* [n]    hg.attribute_height,           -1 for the root fallback     */
+    int32_t *hier_id;     /* [n]    t_hier_id (1-based region index)                            */
+    int32_t *parent;      /* [n]    node index of the hierarchy parent, -1 if none emitted      */
+    int32_t *hidx;        /* [n]    Node._h_node_index                                          */
+    int64_t *mask_off;    /* [n+1]  offset of each node's mask in 32-bit words                  */
+    uint32_t *mask;       /* bit-packed masks: rows of ceil(bw/32) words over the bbox          */
+    int32_t *overlaps;    /* [m,2]  (node index, ancestor index) rows of the overlaps table     */
+    int32_t *labels;      /* [D,H,W] region labels after oversegmentation, or NULL              */
+    ulk_seg_stats stats;
+} ulk_frame_nodes;
+
+/* LinkingConfig fields compute_spatial_neighbors reads (config/config.py:23-49) */
+typedef struct ulk_link_params {
+    double max_distance;
+    double distance_weight;
+    int32_t max_neighbors;
+    int32_t has_scale;
+    double scale[3];          /* z,y,x, applied to both centroids when has_scale != 0            */
+} ulk_link_params;
+
+typedef struct ulk_links {
+    int64_t n_links;
+    int32_t *source;          /* [n] node index in the source frame                             */
+    int32_t *target;          /* [n] node index in the target frame                             */
+    double *weight;           /* [n] IoU - distance_weight * distance                           */
+    int64_t n_pairs;          /* candidate pairs evaluated (for the byte model)                 */
+} ulk_links;
+
+ULK_API const char *ulk_last_error(void);
+ULK_API int ulk_device_count(void);
+/* kernels launched by this library on the calling process so far */
+ULK_API int64_t ulk_launch_count(void);
+
+/* stream: a cudaStream_t (0 = default stream); all work of a call is ordered on it and the
+ * call returns after the results are complete. */
+ULK_API int ulk_segment_frame(const void *foreground, int fg_dtype, const void *contours, int ct_dtype,
+                      const int64_t shape[3], const ulk_seg_params *params, int keep_labels,
+                      void *stream, ulk_frame_nodes **out);
+/* same, inputs in (ideally pinned) host memory: the copies are part of the call */
+ULK_API int ulk_segment_frame_host(const void *foreground, int fg_dtype, const void *contours, int ct_dtype,
+                           const int64_t shape[3], const ulk_seg_params *params, int keep_labels,
+                           void *stream, ulk_frame_nodes **out);
+ULK_API void ulk_frame_nodes_free(ulk_frame_nodes *nodes);
+/* copies the device arrays into caller-provided host buffers (any may be NULL) */
+ULK_API int ulk_frame_nodes_to_host(const ulk_frame_nodes *nodes, int32_t *bbox, int32_t *centroid, int32_t *area,
+                            double *frontier, double *height, int32_t *hier_id, int32_t *parent,
+                            int32_t *hidx, int64_t *mask_off, uint32_t *mask, int32_t *overlaps,
+                            int32_t *labels, void *stream);
+/* builds a device node table from host arrays (a boundary frame received from another rank,
+ * or nodes loaded back from the database) */
+ULK_API int ulk_frame_nodes_from_host(int32_t n_nodes, const int32_t shape[3], const int32_t *bbox,
+                              const int32_t *centroid, const int32_t *area, const int64_t *mask_off,
+                              const uint32_t *mask, void *stream, ulk_frame_nodes **out);
+
+/* dst_shift: host [n_dst,3] float64 (z,y,x shifts of the target nodes) or NULL */
+ULK_API int ulk_link_frames(const ulk_frame_nodes *src, const ulk_frame_nodes *dst, const double *dst_shift_host,
+                    const ulk_link_params *params, void *stream, ulk_links **out);
+ULK_API int ulk_links_to_host(const ulk_links *links, int32_t *source, int32_t *target, double *weight, void *stream);
+ULK_API void ulk_links_free(ulk_links *links);
+
+/* utils/edge.py:18-96 for one frame: n_sets label images [n_sets,D,H,W] (int32, device) ->
+ * foreground uint8 [D,H,W] and contours float32 [D,H,W] (sigma = None path) */
+ULK_API int ulk_labels_to_contours(const int32_t *labels, int32_t n_sets, const int64_t shape[3],
+                           uint8_t *foreground, float *contours, void *stream);
+
+/* seeded synthetic frame on the device (ultrack_b200/synth.py recipe, variant "S"):
+ * foreground float32 and contours float32 [D,H,W] */
+ULK_API int ulk_synth_frame(const int64_t shape[3], int32_t t, uint64_t seed, double radius, double fill,
+                    double motion, double noise, float *foreground, float *contours, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,165 @@
+"""ctypes binding of the C ABI declared in include/ultrack_b200.h.
+
+The product path loads ONLY ultrack_b200/csrc/libultrack_b200.so (hand-written sm_100a
+CUDA) and raises if it is missing or no CUDA device is visible: there is no CPU fallback.
+`bind()` is also used by tests/emu to bind the host-emulation test harness.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+from typing import Dict, Optional
+
+import numpy as np
+
+HERE = Path(__file__).resolve().parent
+LIB_PATH = HERE / "csrc" / "libultrack_b200.so"
+
+DTYPE_CODES = {
+    np.dtype(np.bool_): 0, np.dtype(np.uint8): 0, np.dtype(np.int8): 1, np.dtype(np.uint16): 2,
+    np.dtype(np.int16): 3, np.dtype(np.float16): 4, np.dtype(np.float32): 5, np.dtype(np.float64): 6,
+    np.dtype(np.int32): 7, np.dtype(np.uint32): 8, np.dtype(np.int64): 9, np.dtype(np.uint64): 10,
+}
+WS_HIERARCHY_CODES = {"area": 0, "dynamics": 1}
+
+
+class SegParams(C.Structure):
+    _fields_ = [("threshold", C.c_double), ("min_area", C.c_double), ("max_area", C.c_double),
+                ("min_area_factor", C.c_double), ("min_frontier", C.c_double),
+                ("ws_hierarchy", C.c_int32), ("reserved", C.c_int32)]
+
+
+class SegStats(C.Structure):
+    _fields_ = [("n_basins", C.c_int64), ("n_rag_edges", C.c_int64), ("plateau_voxels", C.c_int64),
+                ("flow_rounds", C.c_int32), ("k3_rounds", C.c_int32)]
+
+
+class FrameNodes(C.Structure):
+    _fields_ = [("n_nodes", C.c_int32), ("n_overlaps", C.c_int32), ("n_hier", C.c_int32),
+                ("fix_shift", C.c_int32), ("shape", C.c_int32 * 3), ("pad0", C.c_int32),
+                ("mask_words", C.c_int64),
+                ("bbox", C.c_void_p), ("centroid", C.c_void_p), ("area", C.c_void_p),
+                ("frontier", C.c_void_p), ("height", C.c_void_p), ("hier_id", C.c_void_p),
+                ("parent", C.c_void_p), ("hidx", C.c_void_p), ("mask_off", C.c_void_p),
+                ("mask", C.c_void_p), ("overlaps", C.c_void_p), ("labels", C.c_void_p),
+                ("stats", SegStats)]
+
+
+class LinkParams(C.Structure):
+    _fields_ = [("max_distance", C.c_double), ("distance_weight", C.c_double),
+                ("max_neighbors", C.c_int32), ("has_scale", C.c_int32), ("scale", C.c_double * 3)]
+
+
+class Links(C.Structure):
+    _fields_ = [("n_links", C.c_int64), ("source", C.c_void_p), ("target", C.c_void_p),
+                ("weight", C.c_void_p), ("n_pairs", C.c_int64)]
+
+
+EXPORTS = [
+    "ulk_last_error", "ulk_device_count", "ulk_launch_count", "ulk_segment_frame",
+    "ulk_segment_frame_host", "ulk_frame_nodes_free", "ulk_frame_nodes_to_host",
+    "ulk_frame_nodes_from_host", "ulk_link_frames", "ulk_links_to_host", "ulk_links_free",
+    "ulk_labels_to_contours", "ulk_synth_frame",
+]
+
+
+def bind(lib: C.CDLL) -> C.CDLL:
+    vp, i32, i64, dbl = C.c_void_p, C.c_int32, C.c_int64, C.c_double
+    PF, PL = C.POINTER(FrameNodes), C.POINTER(Links)
+    lib.ulk_last_error.restype = C.c_char_p
+    lib.ulk_last_error.argtypes = []
+    lib.ulk_device_count.restype = C.c_int
+    lib.ulk_launch_count.restype = i64
+    seg_args = [vp, C.c_int, vp, C.c_int, C.POINTER(i64), C.POINTER(SegParams), C.c_int, vp, C.POINTER(PF)]
+    lib.ulk_segment_frame.argtypes = seg_args
+    lib.ulk_segment_frame_host.argtypes = seg_args
+    lib.ulk_frame_nodes_free.argtypes = [PF]
+    lib.ulk_frame_nodes_free.restype = None
+    lib.ulk_frame_nodes_to_host.argtypes = [PF] + [vp] * 12 + [vp]
+    lib.ulk_frame_nodes_from_host.argtypes = [i32, C.POINTER(i32), vp, vp, vp, vp, vp, vp, C.POINTER(PF)]
+    lib.ulk_link_frames.argtypes = [PF, PF, vp, C.POINTER(LinkParams), vp, C.POINTER(PL)]
+    lib.ulk_links_to_host.argtypes = [PL, vp, vp, vp, vp]
+    lib.ulk_links_free.argtypes = [PL]
+    lib.ulk_links_free.restype = None
+    lib.ulk_labels_to_contours.argtypes = [vp, i32, C.POINTER(i64), vp, vp, vp]
+    lib.ulk_synth_frame.argtypes = [C.POINTER(i64), i32, C.c_uint64, dbl, dbl, dbl, dbl, vp, vp, vp]
+    return lib
+
+
+_LIB: Optional[C.CDLL] = None
+
+
+def get_lib() -> C.CDLL:
+    """The CUDA library.  Raises (never falls back) when it cannot run."""
+    global _LIB
+    if _LIB is None:
+        if not LIB_PATH.exists():
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -m ultrack_b200.csrc.build` "
+                "(nvcc, sm_100a). ultrack_b200 has no CPU fallback.")
+        lib = bind(C.CDLL(str(LIB_PATH)))
+        if lib.ulk_device_count() <= 0:
+            raise RuntimeError("ultrack_b200 needs a CUDA device (B200, sm_100a); none is visible "
+                               "and there is no CPU fallback.")
+        _LIB = lib
+    return _LIB
+
+
+class UlkError(RuntimeError):
+    pass
+
+
+def check(lib: C.CDLL, rc: int) -> None:
+    if rc == 0:
+        return
+    msg = (lib.ulk_last_error() or b"").decode("utf-8", "replace")
+    if rc == -10:
+        # vendored/hierarchy.py:161-162 raises RuntimeError for tiny regions
+        raise RuntimeError(msg)
+    if rc == -1:
+        raise ValueError(msg)
+    raise UlkError(f"ultrack_b200 native call failed ({rc}): {msg}")
+
+
+def dtype_code(dt) -> int:
+    dt = np.dtype(dt)
+    if dt not in DTYPE_CODES:
+        raise TypeError(f"unsupported array dtype {dt}")
+    return DTYPE_CODES[dt]
+
+
+def nodes_to_host(lib: C.CDLL, handle, stream: int = 0, with_labels: bool = False) -> Dict[str, np.ndarray]:
+    """Copies a device node table into numpy arrays."""
+    f = handle.contents
+    n, m = int(f.n_nodes), int(f.n_overlaps)
+    out = dict(
+        bbox=np.zeros((n, 6), np.int32), centroid=np.zeros((n, 3), np.int32), area=np.zeros(n, np.int32),
+        frontier=np.zeros(n, np.float64), height=np.zeros(n, np.float64), hier_id=np.zeros(n, np.int32),
+        parent=np.zeros(n, np.int32), hidx=np.zeros(n, np.int32), mask_off=np.zeros(n + 1, np.int64),
+        mask=np.zeros(int(f.mask_words), np.uint32), overlaps=np.zeros((m, 2), np.int32),
+    )
+    labels = None
+    if with_labels and f.labels:
+        labels = np.zeros(tuple(f.shape), np.int32)
+    p = lambda a: a.ctypes.data_as(C.c_void_p) if a is not None else None  # noqa: E731
+    check(lib, lib.ulk_frame_nodes_to_host(
+        handle, p(out["bbox"]), p(out["centroid"]), p(out["area"]), p(out["frontier"]), p(out["height"]),
+        p(out["hier_id"]), p(out["parent"]), p(out["hidx"]), p(out["mask_off"]), p(out["mask"]),
+        p(out["overlaps"]), p(labels), C.c_void_p(stream)))
+    out["n_hier"] = int(f.n_hier)
+    out["shape"] = tuple(int(s) for s in f.shape)
+    out["stats"] = {k: int(getattr(f.stats, k)) for k, _ in SegStats._fields_}
+    if labels is not None:
+        out["labels"] = labels
+    return out
+
+
+def unpack_mask(nodes: Dict[str, np.ndarray], i: int, ndim: int = 3) -> np.ndarray:
+    """Bool mask of node i over its bbox (the reference's Node.mask)."""
+    bb = nodes["bbox"][i]
+    d, h, w = int(bb[3] - bb[0]), int(bb[4] - bb[1]), int(bb[5] - bb[2])
+    wpr = (w + 31) // 32
+    words = nodes["mask"][int(nodes["mask_off"][i]):int(nodes["mask_off"][i + 1])]
+    bits = np.unpackbits(words.view(np.uint8), bitorder="little").reshape(d, h, wpr * 32)[:, :, :w]
+    m = bits.astype(bool)
+    return m[0] if ndim == 2 else m

@@ -1,0 +1,165 @@
+// ulk_api.cu -- the extern "C" boundary (include/ultrack_b200.h).
+#include "ulk_seg.h"
+#include "ulk_common.h"
+
+extern long long g_ulk_launches;
+
+#define API_CHK(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
+
+extern "C" {
+
+const char *ulk_last_error(void) { return ulk_error_cstr(); }
+
+int ulk_device_count(void)
+{
+#ifdef ULK_EMU
+    return 0;
+#else
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+#endif
+}
+
+int64_t ulk_launch_count(void) { return (int64_t)g_ulk_launches; }
+
+int ulk_segment_frame(const void *foreground, int fg_dtype, const void *contours, int ct_dtype,
+                      const int64_t shape[3], const ulk_seg_params *params, int keep_labels,
+                      void *stream, ulk_frame_nodes **out)
+{
+    if (!foreground || !contours || !shape || !params || !out) ULK_FAIL(-1, "null argument");
+    ulk_stream_t st = (ulk_stream_t)stream;
+    ulk_set_alloc_stream(st);
+    *out = nullptr;
+    int rc = ulk_segment_frame_impl(st, foreground, fg_dtype, contours, ct_dtype, shape, params, keep_labels, out);
+    if (rc) { ulk_frame_nodes_free_impl(*out); *out = nullptr; ulk_sync(st); }
+    return rc;
+}
+
+int ulk_segment_frame_host(const void *foreground, int fg_dtype, const void *contours, int ct_dtype,
+                           const int64_t shape[3], const ulk_seg_params *params, int keep_labels,
+                           void *stream, ulk_frame_nodes **out)
+{
+    if (!foreground || !contours || !shape || !params || !out) ULK_FAIL(-1, "null argument");
+    ulk_stream_t st = (ulk_stream_t)stream;
+    ulk_set_alloc_stream(st);
+    i64 V = shape[0] * shape[1] * shape[2];
+    UlkArena A;
+    u8 *dfg = A.get<u8>(V * ulk_dtype_size(fg_dtype));
+    u8 *dct = A.get<u8>(V * ulk_dtype_size(ct_dtype));
+    if (A.failed) ULK_FAIL(-3, "device allocation failed");
+    API_CHK(ulk_h2d(dfg, foreground, (size_t)V * ulk_dtype_size(fg_dtype), st));
+    API_CHK(ulk_h2d(dct, contours, (size_t)V * ulk_dtype_size(ct_dtype), st));
+    return ulk_segment_frame(dfg, fg_dtype, dct, ct_dtype, shape, params, keep_labels, stream, out);
+}
+
+void ulk_frame_nodes_free(ulk_frame_nodes *nodes) { ulk_frame_nodes_free_impl(nodes); }
+
+int ulk_frame_nodes_to_host(const ulk_frame_nodes *f, int32_t *bbox, int32_t *centroid, int32_t *area,
+                            double *frontier, double *height, int32_t *hier_id, int32_t *parent,
+                            int32_t *hidx, int64_t *mask_off, uint32_t *mask, int32_t *overlaps,
+                            int32_t *labels, void *stream)
+{
+    if (!f) ULK_FAIL(-1, "null argument");
+    ulk_stream_t st = (ulk_stream_t)stream;
+    i64 n = f->n_nodes;
+    if (n > 0) {
+        if (bbox) API_CHK(ulk_d2h(bbox, f->bbox, (size_t)n * 6 * 4, st));
+        if (centroid) API_CHK(ulk_d2h(centroid, f->centroid, (size_t)n * 3 * 4, st));
+        if (area) API_CHK(ulk_d2h(area, f->area, (size_t)n * 4, st));
+        if (frontier) API_CHK(ulk_d2h(frontier, f->frontier, (size_t)n * 8, st));
+        if (height) API_CHK(ulk_d2h(height, f->height, (size_t)n * 8, st));
+        if (hier_id && f->hier_id) API_CHK(ulk_d2h(hier_id, f->hier_id, (size_t)n * 4, st));
+        if (parent && f->parent) API_CHK(ulk_d2h(parent, f->parent, (size_t)n * 4, st));
+        if (hidx && f->hidx) API_CHK(ulk_d2h(hidx, f->hidx, (size_t)n * 4, st));
+        if (mask_off) API_CHK(ulk_d2h(mask_off, f->mask_off, (size_t)(n + 1) * 8, st));
+        if (mask && f->mask_words > 0) API_CHK(ulk_d2h(mask, f->mask, (size_t)f->mask_words * 4, st));
+        if (overlaps && f->n_overlaps > 0) API_CHK(ulk_d2h(overlaps, f->overlaps, (size_t)f->n_overlaps * 2 * 4, st));
+    }
+    if (labels && f->labels)
+        API_CHK(ulk_d2h(labels, f->labels, (size_t)f->shape[0] * f->shape[1] * f->shape[2] * 4, st));
+    return 0;
+}
+
+int ulk_frame_nodes_from_host(int32_t n_nodes, const int32_t shape[3], const int32_t *bbox,
+                              const int32_t *centroid, const int32_t *area, const int64_t *mask_off,
+                              const uint32_t *mask, void *stream, ulk_frame_nodes **out)
+{
+    if (!shape || !out || n_nodes < 0) ULK_FAIL(-1, "bad argument");
+    ulk_stream_t st = (ulk_stream_t)stream;
+    ulk_set_alloc_stream(st);
+    ulk_frame_nodes *F = new ulk_frame_nodes();
+    memset(F, 0, sizeof(*F));
+    *out = F;
+    F->n_nodes = n_nodes;
+    for (int d = 0; d < 3; ++d) F->shape[d] = shape[d];
+    if (n_nodes == 0) return 0;
+    i64 n = n_nodes;
+    i64 words = mask_off[n];
+    F->mask_words = words;
+    void *p;
+    int rc = 0;
+    rc |= ulk_dev_alloc(&p, (size_t)n * 6 * 4); F->bbox = (i32 *)p;
+    rc |= ulk_dev_alloc(&p, (size_t)n * 3 * 4); F->centroid = (i32 *)p;
+    rc |= ulk_dev_alloc(&p, (size_t)n * 4); F->area = (i32 *)p;
+    rc |= ulk_dev_alloc(&p, (size_t)(n + 1) * 8); F->mask_off = (i64 *)p;
+    rc |= ulk_dev_alloc(&p, (size_t)(words > 0 ? words : 1) * 4); F->mask = (u32 *)p;
+    if (rc) { ulk_frame_nodes_free_impl(F); *out = nullptr; ULK_FAIL(-3, "device allocation failed"); }
+    API_CHK(ulk_h2d(F->bbox, bbox, (size_t)n * 6 * 4, st));
+    API_CHK(ulk_h2d(F->centroid, centroid, (size_t)n * 3 * 4, st));
+    API_CHK(ulk_h2d(F->area, area, (size_t)n * 4, st));
+    API_CHK(ulk_h2d(F->mask_off, mask_off, (size_t)(n + 1) * 8, st));
+    if (words > 0) API_CHK(ulk_h2d(F->mask, mask, (size_t)words * 4, st));
+    API_CHK(ulk_sync(st));
+    return 0;
+}
+
+int ulk_link_frames(const ulk_frame_nodes *src, const ulk_frame_nodes *dst, const double *dst_shift_host,
+                    const ulk_link_params *params, void *stream, ulk_links **out)
+{
+    if (!src || !dst || !params || !out) ULK_FAIL(-1, "null argument");
+    ulk_stream_t st = (ulk_stream_t)stream;
+    ulk_set_alloc_stream(st);
+    *out = nullptr;
+    int rc = ulk_link_frames_impl(st, src, dst, dst_shift_host, params, out);
+    if (rc && *out) { ulk_links_free(*out); *out = nullptr; }
+    return rc;
+}
+
+int ulk_links_to_host(const ulk_links *l, int32_t *source, int32_t *target, double *weight, void *stream)
+{
+    if (!l) ULK_FAIL(-1, "null argument");
+    ulk_stream_t st = (ulk_stream_t)stream;
+    if (l->n_links <= 0) return 0;
+    if (source) API_CHK(ulk_d2h(source, l->source, (size_t)l->n_links * 4, st));
+    if (target) API_CHK(ulk_d2h(target, l->target, (size_t)l->n_links * 4, st));
+    if (weight) API_CHK(ulk_d2h(weight, l->weight, (size_t)l->n_links * 8, st));
+    return 0;
+}
+
+void ulk_links_free(ulk_links *l)
+{
+    if (!l) return;
+    ulk_dev_free(l->source); ulk_dev_free(l->target); ulk_dev_free(l->weight);
+    delete l;
+}
+
+int ulk_labels_to_contours(const int32_t *labels, int32_t n_sets, const int64_t shape[3],
+                           uint8_t *foreground, float *contours, void *stream)
+{
+    if (!labels || !shape || !foreground || !contours || n_sets <= 0) ULK_FAIL(-1, "bad argument");
+    ulk_stream_t st = (ulk_stream_t)stream;
+    ulk_set_alloc_stream(st);
+    return ulk_labels_to_contours_impl(st, labels, n_sets, shape, foreground, contours);
+}
+
+int ulk_synth_frame(const int64_t shape[3], int32_t t, uint64_t seed, double radius, double fill,
+                    double motion, double noise, float *foreground, float *contours, void *stream)
+{
+    if (!shape || !foreground || !contours) ULK_FAIL(-1, "null argument");
+    ulk_stream_t st = (ulk_stream_t)stream;
+    ulk_set_alloc_stream(st);
+    return ulk_synth_frame_impl(st, shape, t, seed, radius, fill, motion, noise, foreground, contours);
+}
+
+}  // extern "C"

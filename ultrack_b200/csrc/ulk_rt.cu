@@ -1,0 +1,147 @@
+// ulk_rt.cu -- runtime layer implementation (see ulk_rt.h).
+#include "ulk_rt.h"
+#include <cstdarg>
+#include <string>
+
+static thread_local std::string g_err;
+long long g_ulk_launches = 0;
+
+void ulk_set_error(const char *fmt, ...)
+{
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+}
+const char *ulk_error_cstr() { return g_err.c_str(); }
+
+#ifdef ULK_EMU
+// ------------------------------------------------------------------ host emulation
+void ulk_set_alloc_stream(ulk_stream_t) {}
+int ulk_dev_alloc(void **p, size_t bytes) { *p = malloc(bytes ? bytes : 1); return *p ? 0 : -3; }
+void ulk_dev_free(void *p) { free(p); }
+int ulk_memset(void *p, int byte, size_t bytes, ulk_stream_t) { memset(p, byte, bytes); return 0; }
+int ulk_d2h(void *dst, const void *src, size_t bytes, ulk_stream_t) { memcpy(dst, src, bytes); return 0; }
+int ulk_h2d(void *dst, const void *src, size_t bytes, ulk_stream_t) { memcpy(dst, src, bytes); return 0; }
+int ulk_d2d(void *dst, const void *src, size_t bytes, ulk_stream_t) { memmove(dst, src, bytes); return 0; }
+int ulk_sync(ulk_stream_t) { return 0; }
+
+int ulk_exclusive_scan_i32(const i32 *in, i32 *out, i64 n, ulk_stream_t)
+{
+    i32 acc = 0;
+    for (i64 i = 0; i < n; ++i) { i32 v = in[i]; out[i] = acc; acc += v; }
+    return 0;
+}
+int ulk_exclusive_scan_i64(const i64 *in, i64 *out, i64 n, ulk_stream_t)
+{
+    i64 acc = 0;
+    for (i64 i = 0; i < n; ++i) { i64 v = in[i]; out[i] = acc; acc += v; }
+    return 0;
+}
+template <class K>
+static int emu_sort(const K *ki, K *ko, const u32 *vi, u32 *vo, i64 n)
+{
+    std::vector<i64> idx((size_t)n);
+    std::iota(idx.begin(), idx.end(), (i64)0);
+    std::stable_sort(idx.begin(), idx.end(), [&](i64 a, i64 b) { return ki[a] < ki[b]; });
+    std::vector<K> k2((size_t)n);
+    std::vector<u32> v2((size_t)n);
+    for (i64 i = 0; i < n; ++i) { k2[i] = ki[idx[i]]; v2[i] = vi[idx[i]]; }
+    for (i64 i = 0; i < n; ++i) { ko[i] = k2[i]; vo[i] = v2[i]; }
+    return 0;
+}
+int ulk_sort_pairs_u64(const u64 *ki, u64 *ko, const u32 *vi, u32 *vo, i64 n, ulk_stream_t) { return emu_sort(ki, ko, vi, vo, n); }
+int ulk_sort_pairs_u32(const u32 *ki, u32 *ko, const u32 *vi, u32 *vo, i64 n, ulk_stream_t) { return emu_sort(ki, ko, vi, vo, n); }
+
+#else
+// ------------------------------------------------------------------ CUDA
+// stream-ordered allocator: frame-scoped buffers come from the default memory pool, whose
+// release threshold is raised so that freed blocks stay cached between frames
+static cudaStream_t g_alloc_stream = 0;
+static bool g_pool_ready = false;
+void ulk_set_alloc_stream(ulk_stream_t s)
+{
+    g_alloc_stream = s;
+    if (!g_pool_ready) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+            unsigned long long thr = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+        }
+        g_pool_ready = true;
+    }
+}
+int ulk_dev_alloc(void **p, size_t bytes)
+{
+    ULK_CUDA(cudaMallocAsync(p, bytes ? bytes : 1, g_alloc_stream));
+    return 0;
+}
+void ulk_dev_free(void *p) { if (p) cudaFreeAsync(p, g_alloc_stream); }
+int ulk_memset(void *p, int byte, size_t bytes, ulk_stream_t s) { ULK_CUDA(cudaMemsetAsync(p, byte, bytes, s)); return 0; }
+int ulk_d2h(void *dst, const void *src, size_t bytes, ulk_stream_t s)
+{
+    ULK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s));
+    ULK_CUDA(cudaStreamSynchronize(s));
+    return 0;
+}
+int ulk_h2d(void *dst, const void *src, size_t bytes, ulk_stream_t s) { ULK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s)); return 0; }
+int ulk_d2d(void *dst, const void *src, size_t bytes, ulk_stream_t s) { ULK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, s)); return 0; }
+int ulk_sync(ulk_stream_t s) { ULK_CUDA(cudaStreamSynchronize(s)); return 0; }
+
+// CUB temp storage: one growable scratch buffer per process (calls are stream-ordered
+// and the library is used from one host thread per device).
+static void *g_cub_tmp = nullptr;
+static size_t g_cub_cap = 0;
+static int cub_tmp(size_t need)
+{
+    if (need <= g_cub_cap) return 0;
+    if (g_cub_tmp) { cudaDeviceSynchronize(); cudaFree(g_cub_tmp); }
+    g_cub_cap = need + (need >> 2) + 256;
+    ULK_CUDA(cudaMalloc(&g_cub_tmp, g_cub_cap));
+    return 0;
+}
+int ulk_exclusive_scan_i32(const i32 *in, i32 *out, i64 n, ulk_stream_t s)
+{
+    if (n <= 0) return 0;
+    size_t need = 0;
+    ULK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, need, in, out, (int)n, s));
+    if (cub_tmp(need)) return -2;
+    ULK_CUDA(cub::DeviceScan::ExclusiveSum(g_cub_tmp, need, in, out, (int)n, s));
+    ++g_ulk_launches;
+    return 0;
+}
+int ulk_exclusive_scan_i64(const i64 *in, i64 *out, i64 n, ulk_stream_t s)
+{
+    if (n <= 0) return 0;
+    size_t need = 0;
+    ULK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, need, in, out, (int)n, s));
+    if (cub_tmp(need)) return -2;
+    ULK_CUDA(cub::DeviceScan::ExclusiveSum(g_cub_tmp, need, in, out, (int)n, s));
+    ++g_ulk_launches;
+    return 0;
+}
+int ulk_sort_pairs_u64(const u64 *ki, u64 *ko, const u32 *vi, u32 *vo, i64 n, ulk_stream_t s)
+{
+    if (n <= 0) return 0;
+    size_t need = 0;
+    ULK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, need, ki, ko, vi, vo, (int)n, 0, 64, s));
+    if (cub_tmp(need)) return -2;
+    ULK_CUDA(cub::DeviceRadixSort::SortPairs(g_cub_tmp, need, ki, ko, vi, vo, (int)n, 0, 64, s));
+    ++g_ulk_launches;
+    return 0;
+}
+int ulk_sort_pairs_u32(const u32 *ki, u32 *ko, const u32 *vi, u32 *vo, i64 n, ulk_stream_t s)
+{
+    if (n <= 0) return 0;
+    size_t need = 0;
+    ULK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, need, ki, ko, vi, vo, (int)n, 0, 32, s));
+    if (cub_tmp(need)) return -2;
+    ULK_CUDA(cub::DeviceRadixSort::SortPairs(g_cub_tmp, need, ki, ko, vi, vo, (int)n, 0, 32, s));
+    ++g_ulk_launches;
+    return 0;
+}
+#endif

@@ -1,0 +1,150 @@
+// ulk_rt.h -- thin runtime layer under the ultrack_b200 kernels.
+//
+// Product build: nvcc, sm_100a; kernels are functor structs launched through
+// ulk_launch<> (named kernels, 256-thread CTAs), device-wide sort / scan come
+// from CUB (CUDA toolkit headers), memory from the stream-ordered allocator.
+//
+// ULK_EMU build (tests/emu only, never loaded by the package): the same functor
+// bodies are compiled by g++ and executed thread by thread on the host so the
+// kernel LOGIC can be checked against the oracle in the CPU-only test tier.
+// It is a test harness, not a fallback: ultrack_b200/_lib.py only ever loads the
+// CUDA library and raises when it is missing.
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#ifdef ULK_EMU
+#include <algorithm>
+#include <numeric>
+#include <vector>
+#include <cmath>
+#define ULK_HD
+#define ULK_D
+#define ULK_INLINE inline
+typedef void *ulk_stream_t;
+#else
+#include <cuda_runtime.h>
+#include <cub/cub.cuh>
+#define ULK_HD __host__ __device__
+#define ULK_D __device__
+#define ULK_INLINE __forceinline__
+typedef cudaStream_t ulk_stream_t;
+#endif
+
+typedef int64_t i64;
+typedef uint64_t u64;
+typedef uint32_t u32;
+typedef int32_t i32;
+typedef uint8_t u8;
+
+// ---------------------------------------------------------------- errors
+void ulk_set_error(const char *fmt, ...);
+#define ULK_FAIL(code, ...) do { ulk_set_error(__VA_ARGS__); return (code); } while (0)
+
+#ifndef ULK_EMU
+#define ULK_CUDA(call)                                                              \
+    do {                                                                            \
+        cudaError_t e__ = (call);                                                   \
+        if (e__ != cudaSuccess) {                                                   \
+            ulk_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call,              \
+                          cudaGetErrorString(e__));                                 \
+            return -2;                                                              \
+        }                                                                           \
+    } while (0)
+#else
+#define ULK_CUDA(call) do { (void)0; } while (0)
+#endif
+
+// ---------------------------------------------------------------- atomics
+#ifdef ULK_EMU
+template <class T> ULK_INLINE T ulk_atomic_min(T *p, T v) { T o = *p; if (v < o) *p = v; return o; }
+template <class T> ULK_INLINE T ulk_atomic_max(T *p, T v) { T o = *p; if (v > o) *p = v; return o; }
+template <class T> ULK_INLINE T ulk_atomic_add(T *p, T v) { T o = *p; *p = o + v; return o; }
+template <class T> ULK_INLINE T ulk_atomic_or(T *p, T v) { T o = *p; *p = o | v; return o; }
+template <class T> ULK_INLINE T ulk_atomic_cas(T *p, T c, T v) { T o = *p; if (o == c) *p = v; return o; }
+template <class T> ULK_INLINE T ulk_atomic_exch(T *p, T v) { T o = *p; *p = v; return o; }
+ULK_INLINE int ulk_popc(u32 x) { return __builtin_popcount(x); }
+ULK_INLINE u32 ulk_funnel_r(u32 lo, u32 hi, u32 s) { return s ? (lo >> s) | (hi << (32 - s)) : lo; }
+#else
+ULK_D ULK_INLINE i32 ulk_atomic_min(i32 *p, i32 v) { return atomicMin(p, v); }
+ULK_D ULK_INLINE u32 ulk_atomic_min(u32 *p, u32 v) { return atomicMin(p, v); }
+ULK_D ULK_INLINE u64 ulk_atomic_min(u64 *p, u64 v) { return atomicMin((unsigned long long *)p, (unsigned long long)v); }
+ULK_D ULK_INLINE i32 ulk_atomic_max(i32 *p, i32 v) { return atomicMax(p, v); }
+ULK_D ULK_INLINE u32 ulk_atomic_max(u32 *p, u32 v) { return atomicMax(p, v); }
+ULK_D ULK_INLINE u64 ulk_atomic_max(u64 *p, u64 v) { return atomicMax((unsigned long long *)p, (unsigned long long)v); }
+ULK_D ULK_INLINE i32 ulk_atomic_add(i32 *p, i32 v) { return atomicAdd(p, v); }
+ULK_D ULK_INLINE u32 ulk_atomic_add(u32 *p, u32 v) { return atomicAdd(p, v); }
+ULK_D ULK_INLINE u64 ulk_atomic_add(u64 *p, u64 v) { return atomicAdd((unsigned long long *)p, (unsigned long long)v); }
+ULK_D ULK_INLINE i64 ulk_atomic_add(i64 *p, i64 v) { return (i64)atomicAdd((unsigned long long *)p, (unsigned long long)v); }
+ULK_D ULK_INLINE u32 ulk_atomic_or(u32 *p, u32 v) { return atomicOr(p, v); }
+ULK_D ULK_INLINE i32 ulk_atomic_cas(i32 *p, i32 c, i32 v) { return atomicCAS(p, c, v); }
+ULK_D ULK_INLINE u32 ulk_atomic_cas(u32 *p, u32 c, u32 v) { return atomicCAS(p, c, v); }
+ULK_D ULK_INLINE u64 ulk_atomic_cas(u64 *p, u64 c, u64 v) { return atomicCAS((unsigned long long *)p, (unsigned long long)c, (unsigned long long)v); }
+ULK_D ULK_INLINE i32 ulk_atomic_exch(i32 *p, i32 v) { return atomicExch(p, v); }
+ULK_D ULK_INLINE int ulk_popc(u32 x) { return __popc(x); }
+ULK_D ULK_INLINE u32 ulk_funnel_r(u32 lo, u32 hi, u32 s) { return __funnelshift_r(lo, hi, s); }
+#endif
+
+// ---------------------------------------------------------------- launch
+#ifdef ULK_EMU
+template <class F> void ulk_launch(i64 n, ulk_stream_t, const F &f) { for (i64 i = 0; i < n; ++i) f(i); }
+#else
+template <class F> __global__ void __launch_bounds__(256) ulk_kernel(i64 n, F f)
+{
+    i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) f(i);
+}
+extern long long g_ulk_launches;
+template <class F> void ulk_launch(i64 n, ulk_stream_t s, const F &f)
+{
+    if (n <= 0) return;
+    i64 grid = (n + 255) / 256;
+    ulk_kernel<F><<<(unsigned)grid, 256, 0, s>>>(n, f);
+    ++g_ulk_launches;
+}
+#endif
+
+// ---------------------------------------------------------------- memory
+struct UlkArena;  // growable pool of device buffers, see ulk_rt.cu
+void ulk_set_alloc_stream(ulk_stream_t s);
+int ulk_dev_alloc(void **p, size_t bytes);
+void ulk_dev_free(void *p);
+int ulk_memset(void *p, int byte, size_t bytes, ulk_stream_t s);
+int ulk_d2h(void *dst, const void *src, size_t bytes, ulk_stream_t s);  // synchronises
+int ulk_h2d(void *dst, const void *src, size_t bytes, ulk_stream_t s);
+int ulk_d2d(void *dst, const void *src, size_t bytes, ulk_stream_t s);
+int ulk_sync(ulk_stream_t s);
+
+// ---------------------------------------------------------------- primitives
+// exclusive prefix sum of n int32 -> int32 (out may alias in); returns total via *total (host)
+int ulk_exclusive_scan_i32(const i32 *in, i32 *out, i64 n, ulk_stream_t s);
+int ulk_exclusive_scan_i64(const i64 *in, i64 *out, i64 n, ulk_stream_t s);
+// stable LSD radix sort of (key, value) pairs; results land in keys_out / vals_out
+int ulk_sort_pairs_u64(const u64 *keys_in, u64 *keys_out, const u32 *vals_in, u32 *vals_out,
+                       i64 n, ulk_stream_t s);
+int ulk_sort_pairs_u32(const u32 *keys_in, u32 *keys_out, const u32 *vals_in, u32 *vals_out,
+                       i64 n, ulk_stream_t s);
+
+// ---------------------------------------------------------------- numerics
+// order-preserving map float32 -> uint32 (handles negatives)
+ULK_HD ULK_INLINE u32 ulk_f2ord(float f)
+{
+    u32 b;
+    memcpy(&b, &f, 4);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+ULK_HD ULK_INLINE float ulk_ord2f(u32 o)
+{
+    u32 b = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+    float f;
+    memcpy(&f, &b, 4);
+    return f;
+}
+ULK_HD ULK_INLINE u64 ulk_d2ord(double d)
+{
+    u64 b;
+    memcpy(&b, &d, 8);
+    return (b & 0x8000000000000000ull) ? ~b : (b | 0x8000000000000000ull);
+}

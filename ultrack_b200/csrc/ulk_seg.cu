@@ -1,0 +1,579 @@
+// ulk_seg.cu -- per-frame segmentation pipeline (host orchestration + kernel launches).
+//
+// Replaces, for one timepoint, ultrack's
+//   core/segmentation/processing.py:160-340  (_process)
+//   core/segmentation/hierarchy.py:33-90     (create_hierarchies)
+//   core/segmentation/vendored/hierarchy.py  (Hierarchy, oversegment_components)
+//   core/segmentation/vendored/node.py       (bbox / mask)
+// with voxel-scale kernels (ulk_voxel.h) that collapse the frame into watershed basins
+// and a basin-scale hierarchy builder (ulk_hier.h).
+#include "ulk_seg.h"
+#include "ulk_hier.h"
+#include "ulk_voxel.h"
+#include <cmath>
+
+#define CHK(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
+#define CHKA(a) do { if ((a).failed) ULK_FAIL(-3, "device allocation failed"); } while (0)
+
+// ------------------------------------------------------------------ hierarchy kernels
+struct K_HierStage1 {
+    const i32 *bs, *es; UlkBasins B; UlkEdges E; UlkHierScratch S;
+    ULK_D void operator()(i64 h) const { ulk_hier_stage1((i32)h, bs, es, B, E, S); }
+};
+struct K_HierCut {
+    const i32 *bs, *es; UlkBasins B; UlkEdges E; UlkHierScratch S; double max_area;
+    i32 *region_of; u64 *rkey_w, *rkey_k;
+    ULK_D void operator()(i64 h) const { ulk_hier_cut((i32)h, bs, es, B, E, S, max_area, region_of, rkey_w, rkey_k); }
+};
+struct K_HierFull {
+    const i32 *bs, *es; UlkBasins B; UlkEdges E; UlkHierScratch S; UlkHierParams P; UlkNodeOut O;
+    ULK_D void operator()(i64 h) const { ulk_hier_full((i32)h, bs, es, B, E, S, P, O); }
+};
+
+// ------------------------------------------------------------------ node finalisation kernels
+struct K_NodeGather {
+    const i32 *bs; const i32 *noff; UlkNodeOut O;
+    i32 *bbox, *centroid, *area, *hier_id, *parent, *hidx; double *frontier, *height; i64 *mwords;
+    i32 *err;
+    ULK_D void operator()(i64 hh) const
+    {
+        i32 h = (i32)hh;
+        i32 o = 2 * bs[h];
+        i32 cnt = O.count[h];
+        i32 base = noff[h];
+        for (i32 s = 0; s < cnt; ++s) {
+            i32 g = o + s, n = base + s;
+            i32 a = O.area[g];
+            area[n] = a;
+            frontier[n] = O.frontier[g];
+            height[n] = O.height[g];
+            hier_id[n] = h + 1;
+            parent[n] = O.parent[g] >= 0 ? base + O.parent[g] : -1;
+            hidx[n] = O.rsize[h] + O.hidx[g];
+            i64 ext[3];
+            for (int d = 0; d < 3; ++d) {
+                i32 lo = O.bbmin[3 * g + d], hi = O.bbmax[3 * g + d] + 1;
+                bbox[6 * n + d] = lo;
+                bbox[6 * n + 3 + d] = hi;
+                ext[d] = hi - lo;
+                // core/segmentation/node.py:229-233: mean of the bbox-relative coordinates,
+                // plus the bbox origin, rounded half to even
+                i64 srel = O.csum[3 * g + d] - (i64)a * lo;
+                double m = (double)srel / (double)a;
+                centroid[3 * n + d] = (i32)rint(m + (double)lo);
+            }
+            mwords[n] = ext[0] * ext[1] * ((ext[2] + 31) / 32);
+        }
+    }
+};
+// vendored/hierarchy.py:161-162: a region whose bounding box holds fewer than 8 elements
+// raises RuntimeError in the reference; report the first one back to the host.
+struct K_RegionSizeCheck {
+    const i32 *bs; UlkHierScratch S; i32 *err;
+    ULK_D void operator()(i64 hh) const
+    {
+        i32 h = (i32)hh;
+        i32 o = 2 * bs[h], b = bs[h + 1] - bs[h];
+        i32 root = o + 2 * b - 2;
+        i64 vol = 1;
+        for (int d = 0; d < 3; ++d) vol *= (i64)(S.nbbmax[3 * root + d] - S.nbbmin[3 * root + d] + 1);
+        if (vol < 8) ulk_atomic_max(err, (i32)(8 - vol));
+    }
+};
+struct K_BasinNodeGlobal {
+    const i32 *g_lab; const i32 *noff; const i32 *basin_node; i32 *bnode;
+    ULK_D void operator()(i64 b) const
+    {
+        i32 s = basin_node[b];
+        bnode[b] = s < 0 ? -1 : noff[g_lab[b] - 1] + s;
+    }
+};
+struct K_MaskPaint {
+    const i32 *bas; const i32 *bnode; const i32 *parent; const i32 *bbox; const i64 *moff; UlkDims dm;
+    u32 *mask;
+    ULK_D void operator()(i64 vv) const
+    {
+        i32 v = (i32)vv;
+        i32 b = bas[v];
+        if (b < 0) return;
+        i32 z, y, x;
+        dm.coords(v, z, y, x);
+        for (i32 n = bnode[b]; n >= 0; n = parent[n]) {
+            const i32 *bb = bbox + 6 * n;
+            i64 bh = bb[4] - bb[1], wpr = (bb[5] - bb[2] + 31) / 32;
+            i32 rx = x - bb[2];
+            i64 word = moff[n] + ((i64)(z - bb[0]) * bh + (y - bb[1])) * wpr + (rx >> 5);
+            ulk_atomic_or(&mask[word], 1u << (rx & 31));
+        }
+    }
+};
+struct K_AncestorCount {
+    const i32 *parent; i32 *depth;
+    ULK_D void operator()(i64 n) const
+    {
+        i32 d = 0;
+        for (i32 a = parent[n]; a >= 0; a = parent[a]) ++d;
+        depth[n] = d;
+    }
+};
+struct K_OverlapWrite {
+    const i32 *parent; const i32 *ooff; i32 *ov;
+    ULK_D void operator()(i64 n) const
+    {
+        i32 k = ooff[n];
+        for (i32 a = parent[n]; a >= 0; a = parent[a]) { ov[2 * k] = (i32)n; ov[2 * k + 1] = a; ++k; }
+    }
+};
+struct K_LabelSmallOnly {
+    const i32 *P; const i32 *ccpre; i32 *lab2;
+    ULK_D void operator()(i64 v) const { i32 r = P[v]; lab2[v] = r < 0 ? 0 : ccpre[r] + 1; }
+};
+struct K_Iota { u32 *p; ULK_D void operator()(i64 i) const { p[i] = (u32)i; } };
+struct K_Valid { const u32 *c; i32 *f; ULK_D void operator()(i64 i) const { f[i] = c[i] != ULK_NONE32; } };
+
+// ------------------------------------------------------------------ voxel stage
+struct VoxelStage {
+    i32 *bas = nullptr; i32 B = 0; i32 Eg = 0;
+    i32 *g_root = nullptr, *g_lab = nullptr; u32 *g_L = nullptr;
+    i32 *b_size = nullptr; u64 *b_top = nullptr; u32 *b_k3 = nullptr;
+    i32 *bbmin = nullptr, *bbmax = nullptr; i64 *csum = nullptr;
+    i32 *bs = nullptr, *es = nullptr;
+    i32 *ea = nullptr, *eb = nullptr; u64 *wk = nullptr; u32 *k3 = nullptr, *cnt = nullptr; u64 *shi = nullptr, *slo = nullptr;
+    u32 *mw = nullptr, *jk = nullptr;
+};
+
+static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const UlkCt &ct, const i32 *lab,
+                       i32 R, bool need_join, bool need_k3, bool need_stats, double fixscale,
+                       VoxelStage &out, ulk_seg_stats *stats)
+{
+    const i64 V = dm.V;
+    u32 *mw = A.get<u32>(V), *pk = A.get<u32>(V);
+    i32 *bp = A.get<i32>(V);
+    u8 *state = A.get<u8>(V + 4);
+    u32 *Lr = A.get<u32>(V), *best = A.get<u32>(V), *flowkey = A.get<u32>(V);
+    u8 *fmark = A.get<u8>(V + 8);
+    i32 *cand = A.get<i32>(V), *cand2 = A.get<i32>(V);
+    i32 *groots = A.get<i32>(V), *groots2 = A.get<i32>(V), *tgt = A.get<i32>(V);
+    i32 *ctr = A.get<i32>(8);
+    CHKA(A);
+    CHK(ulk_memset(fmark, 0, (size_t)V + 8, st));
+    CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
+    ulk_launch(V, st, K_MinEdge{lab, ct, dm, mw, pk});
+    ulk_launch(V, st, K_Hook1{lab, mw, pk, dm, bp, state, Lr, best, flowkey});
+    ulk_launch(V, st, K_Compress{bp});
+    ulk_launch(V, st, K_CandInit{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1});
+    i32 hc[8];
+    CHK(ulk_read(hc, ctr, 8, st));
+    i32 ncand = hc[0], ng = hc[1];
+    int rounds = 0;
+    while (ng > 0) {
+        CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
+        ulk_launch(ncand, st, K_FindFlow{cand, lab, bp, mw, Lr, state, ct, dm, best, cand2, ctr + 0});
+        ulk_launch(ng, st, K_Decide1{groots, bp, best, dm, tgt});
+        ulk_launch(ng, st, K_Decide2{groots, tgt, bp, state, best, flowkey, fmark, groots2, ctr + 1});
+        CHK(ulk_read(hc, ctr, 8, st));
+        ncand = hc[0]; ng = hc[1];
+        i32 *t = cand; cand = cand2; cand2 = t;
+        t = groots; groots = groots2; groots2 = t;
+        if (++rounds > 100000) ULK_FAIL(-4, "flow rounds did not converge");
+    }
+    if (stats) stats->flow_rounds += rounds;
+    ulk_launch(V, st, K_Compress{bp});
+    A.release(cand); A.release(cand2); A.release(groots); A.release(groots2); A.release(tgt);
+
+    // ---- basin ids, grouped by region label
+    i32 *flag = A.get<i32>(V + 1), *pre = A.get<i32>(V + 1);
+    CHKA(A);
+    ulk_launch(V, st, K_FlagRoots{bp, flag});
+    CHK(ulk_memset(flag + V, 0, sizeof(i32), st));
+    CHK(ulk_exclusive_scan_i32(flag, pre, V + 1, st));
+    i32 B = 0;
+    CHK(ulk_read(&B, pre + V, 1, st));
+    out.B = B;
+    i32 *b_root = A.get<i32>(B);
+    u32 *b_labkey = A.get<u32>(B), *b_labsorted = A.get<u32>(B), *iota = A.get<u32>(B), *sorted_pre = A.get<u32>(B);
+    i32 *gid_of_pre = A.get<i32>(B);
+    out.g_root = A.get<i32>(B); out.g_lab = A.get<i32>(B); out.g_L = A.get<u32>(B);
+    out.bs = A.get<i32>(R + 1);
+    i32 *lab_hist = A.get<i32>(R + 1);
+    CHKA(A);
+    CHK(ulk_memset(lab_hist, 0, (size_t)(R + 1) * sizeof(i32), st));
+    ulk_launch(V, st, K_BasinRootInfo{bp, lab, Lr, pre, b_root, b_labkey});
+    ulk_launch(B, st, K_Iota{iota});
+    CHK(ulk_sort_pairs_u32(b_labkey, b_labsorted, iota, sorted_pre, B, st));
+    ulk_launch(B, st, K_BasinRegroup{sorted_pre, b_root, lab, Lr, gid_of_pre, out.g_root, out.g_lab, out.g_L, lab_hist});
+    CHK(ulk_exclusive_scan_i32(lab_hist, out.bs, R + 1, st));
+    out.bas = A.get<i32>(V);
+    CHKA(A);
+    ulk_launch(V, st, K_AssignBasin{bp, pre, gid_of_pre, out.bas});
+    A.release(flag); A.release(pre);
+
+    // ---- per-basin accumulators
+    out.b_size = A.get<i32>(B); out.b_top = A.get<u64>(B);
+    u64 *ncross = A.get<u64>(1);
+    if (need_stats) { out.bbmin = A.get<i32>(3 * (i64)B); out.bbmax = A.get<i32>(3 * (i64)B); out.csum = A.get<i64>(3 * (i64)B); }
+    CHKA(A);
+    CHK(ulk_memset(out.b_size, 0, (size_t)B * sizeof(i32), st));
+    CHK(ulk_memset(out.b_top, 0, (size_t)B * sizeof(u64), st));
+    CHK(ulk_memset(ncross, 0, sizeof(u64), st));
+    if (need_stats) {
+        ulk_fill<i32>(out.bbmin, 0x7fffffff, 3 * (i64)B, st);
+        ulk_fill<i32>(out.bbmax, -0x7fffffff, 3 * (i64)B, st);
+        CHK(ulk_memset(out.csum, 0, (size_t)B * 3 * sizeof(i64), st));
+    }
+    ulk_launch(V, st, K_BasinAccum{out.bas, lab, mw, pk, flowkey, ct, dm, out.b_size, out.b_top, ncross,
+                                   need_stats ? 1 : 0, out.bbmin, out.bbmax, out.csum});
+    u64 h_ncross = 0;
+    CHK(ulk_read(&h_ncross, ncross, 1, st));
+
+    // ---- join keys for the area attribute
+    out.mw = mw;
+    if (need_join) {
+        out.jk = A.get<u32>(V);
+        i32 *hp = A.get<i32>(V);
+        CHKA(A);
+        CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
+        ulk_launch(V, st, K_JoinKey{out.bas, mw, pk, out.g_L, dm, out.jk, hp, ctr + 0});
+        CHK(ulk_read(hc, ctr, 8, st));
+        i32 nhp = hc[0];
+        if (stats) stats->plateau_voxels += nhp;
+        int it = 0;
+        while (nhp > 0) {
+            CHK(ulk_memset(ctr + 2, 0, sizeof(i32), st));
+            ulk_launch(nhp, st, K_PlateauRelax{hp, lab, mw, pk, fmark, ct, dm, out.jk, ctr + 2});
+            CHK(ulk_read(hc, ctr, 8, st));
+            if (!hc[2]) break;
+            if (++it > 1000000) ULK_FAIL(-4, "plateau relaxation did not converge");
+        }
+        A.release(hp);
+    }
+
+    // ---- region adjacency graph (hash of basin pairs)
+    u64 cap = 1024;
+    while (cap < 2 * h_ncross + 16) cap <<= 1;
+    UlkRagTable T;
+    T.key = A.get<u64>((i64)cap); T.wk = A.get<u64>((i64)cap); T.k3 = A.get<u32>((i64)cap);
+    T.cnt = A.get<u32>((i64)cap); T.shi = A.get<u64>((i64)cap); T.slo = A.get<u64>((i64)cap);
+    T.mask = cap - 1;
+    CHKA(A);
+    CHK(ulk_memset(T.key, 0xff, cap * 8, st));
+    CHK(ulk_memset(T.wk, 0xff, cap * 8, st));
+    CHK(ulk_memset(T.k3, 0xff, cap * 4, st));
+    CHK(ulk_memset(T.cnt, 0, cap * 4, st));
+    CHK(ulk_memset(T.shi, 0, cap * 8, st));
+    CHK(ulk_memset(T.slo, 0, cap * 8, st));
+    ulk_launch(V, st, K_RagInsert{out.bas, lab, ct, dm, T, fixscale});
+    i32 *eflag = A.get<i32>((i64)cap + 1), *epre = A.get<i32>((i64)cap + 1);
+    CHKA(A);
+    ulk_launch((i64)cap, st, K_RagFlag{T.key, eflag});
+    CHK(ulk_memset(eflag + cap, 0, sizeof(i32), st));
+    CHK(ulk_exclusive_scan_i32(eflag, epre, (i64)cap + 1, st));
+    i32 Eg = 0;
+    CHK(ulk_read(&Eg, epre + cap, 1, st));
+    out.Eg = Eg;
+    i32 *ea0 = A.get<i32>(Eg), *eb0 = A.get<i32>(Eg);
+    u64 *wk0 = A.get<u64>(Eg), *shi0 = A.get<u64>(Eg), *slo0 = A.get<u64>(Eg);
+    u32 *k30 = A.get<u32>(Eg), *cnt0 = A.get<u32>(Eg), *elab0 = A.get<u32>(Eg), *eidx0 = A.get<u32>(Eg);
+    CHKA(A);
+    ulk_launch((i64)cap, st, K_RagGather{T, epre, out.g_lab, ea0, eb0, wk0, k30, cnt0, shi0, slo0, elab0, eidx0});
+    A.release(T.key); A.release(T.wk); A.release(T.k3); A.release(T.cnt); A.release(T.shi); A.release(T.slo);
+    A.release(eflag); A.release(epre);
+    // sort by (label, (w,key)): LSD, two stable passes
+    u64 *wk1 = A.get<u64>(Eg);
+    u32 *perm1 = A.get<u32>(Eg), *elab1 = A.get<u32>(Eg), *elab2 = A.get<u32>(Eg), *perm2 = A.get<u32>(Eg);
+    CHKA(A);
+    CHK(ulk_sort_pairs_u64(wk0, wk1, eidx0, perm1, Eg, st));
+    ulk_launch(Eg, st, K_Gather<u32>{elab0, perm1, elab1});
+    CHK(ulk_sort_pairs_u32(elab1, elab2, perm1, perm2, Eg, st));
+    out.ea = A.get<i32>(Eg); out.eb = A.get<i32>(Eg); out.wk = A.get<u64>(Eg); out.k3 = A.get<u32>(Eg);
+    out.cnt = A.get<u32>(Eg); out.shi = A.get<u64>(Eg); out.slo = A.get<u64>(Eg);
+    out.es = A.get<i32>(R + 1);
+    i32 *ehist = A.get<i32>(R + 1);
+    CHKA(A);
+    ulk_launch(Eg, st, K_Gather<i32>{ea0, perm2, out.ea});
+    ulk_launch(Eg, st, K_Gather<i32>{eb0, perm2, out.eb});
+    ulk_launch(Eg, st, K_Gather<u64>{wk0, perm2, out.wk});
+    ulk_launch(Eg, st, K_Gather<u32>{k30, perm2, out.k3});
+    ulk_launch(Eg, st, K_Gather<u32>{cnt0, perm2, out.cnt});
+    ulk_launch(Eg, st, K_Gather<u64>{shi0, perm2, out.shi});
+    ulk_launch(Eg, st, K_Gather<u64>{slo0, perm2, out.slo});
+    CHK(ulk_memset(ehist, 0, (size_t)(R + 1) * sizeof(i32), st));
+    ulk_launch(Eg, st, K_Hist{elab2, ehist});
+    CHK(ulk_exclusive_scan_i32(ehist, out.es, R + 1, st));
+    A.release(ea0); A.release(eb0); A.release(wk0); A.release(shi0); A.release(slo0);
+    A.release(k30); A.release(cnt0); A.release(elab0); A.release(eidx0);
+    A.release(wk1); A.release(perm1); A.release(elab1); A.release(elab2); A.release(perm2);
+
+    // ---- raster-key bottleneck per basin
+    if (need_k3) {
+        out.b_k3 = A.get<u32>(B);
+        i32 *P3 = bp;          // basin forest no longer needed
+        i32 *nroot = A.get<i32>(B);
+        CHKA(A);
+        CHK(ulk_memset(out.b_k3, 0, (size_t)B * sizeof(u32), st));
+        ulk_launch(V, st, K_MinKeyInBasin{out.bas, dm, out.b_k3});
+        ulk_launch(V, st, K_K3Init{out.bas, P3});
+        ulk_launch(V, st, K_K3Union{out.bas, dm, out.b_k3, P3});
+        ulk_launch(V, st, K_Flatten{P3});
+        int it = 0;
+        for (;;) {
+            CHK(ulk_memset(nroot, 0, (size_t)B * sizeof(i32), st));
+            CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
+            ulk_launch(V, st, K_K3CountRoots{out.bas, P3, nroot, ctr + 0});
+            CHK(ulk_read(hc, ctr, 8, st));
+            if (hc[0] == 0) break;
+            if (stats) stats->k3_rounds += 1;
+            ulk_fill<u32>(best, ULK_NONE32, V, st);
+            ulk_launch(V, st, K_K3FindBest{out.bas, dm, nroot, P3, best});
+            ulk_launch(V, st, K_K3Hook{out.bas, dm, P3, best, out.b_k3});
+            ulk_launch(V, st, K_Flatten{P3});
+            if (++it > 100000) ULK_FAIL(-4, "bottleneck rounds did not converge");
+        }
+        A.release(nroot);
+    }
+    A.release(pk); A.release(state); A.release(Lr); A.release(best); A.release(flowkey); A.release(fmark);
+    A.release(bp);
+    if (stats) { stats->n_basins += B; stats->n_rag_edges += Eg; }
+    return 0;
+}
+
+static int alloc_scratch(UlkArena &A, i32 B, i32 Eg, UlkHierScratch &S)
+{
+    i64 N2 = 2 * (i64)B + 2;
+    i64 M = (Eg > B ? Eg : B) + 2;
+    S.Ipar = A.get<i32>(N2); S.Ic0 = A.get<i32>(N2); S.Ic1 = A.get<i32>(N2);
+    S.Iwk = A.get<u64>(N2); S.IminL = A.get<u32>(N2); S.attach = A.get<i32>(N2);
+    S.acc1 = A.get<i32>(B + 2); S.wprime = A.get<double>(N2);
+    S.par = A.get<i32>(N2); S.c0 = A.get<i32>(N2); S.c1 = A.get<i32>(N2);
+    S.alt = A.get<double>(N2); S.alt1 = A.get<double>(N2); S.par1 = A.get<i32>(N2);
+    S.acc = A.get<i32>(B + 2); S.uf = A.get<i32>(B + 2); S.rootnode = A.get<i32>(B + 2);
+    S.ord = A.get<i32>(M); S.sal = A.get<double>(M);
+    S.area = A.get<i32>(N2); S.Xhi = A.get<u64>(N2); S.Xlo = A.get<u64>(N2); S.Xc = A.get<i64>(N2);
+    S.fp = A.get<i32>(N2); S.surv = A.get<u8>(N2); S.fin = A.get<i32>(N2);
+    S.fr = A.get<double>(N2); S.low = A.get<double>(N2); S.emit_idx = A.get<i32>(N2);
+    S.nbbmin = A.get<i32>(3 * N2); S.nbbmax = A.get<i32>(3 * N2); S.ncsum = A.get<i64>(3 * N2);
+    return A.failed ? -3 : 0;
+}
+
+void ulk_frame_nodes_free_impl(ulk_frame_nodes *f)
+{
+    if (!f) return;
+    ulk_dev_free(f->bbox); ulk_dev_free(f->centroid); ulk_dev_free(f->area); ulk_dev_free(f->frontier);
+    ulk_dev_free(f->height); ulk_dev_free(f->hier_id); ulk_dev_free(f->parent); ulk_dev_free(f->hidx);
+    ulk_dev_free(f->mask_off); ulk_dev_free(f->mask); ulk_dev_free(f->overlaps); ulk_dev_free(f->labels);
+    delete f;
+}
+
+template <class T> static T *keep_alloc(i64 n)
+{
+    void *p = nullptr;
+    if (ulk_dev_alloc(&p, (size_t)(n > 0 ? n : 1) * sizeof(T))) return nullptr;
+    return (T *)p;
+}
+
+int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const void *ctp, int ct_dtype,
+                           const int64_t shape[3], const ulk_seg_params *prm, int keep_labels,
+                           ulk_frame_nodes **result)
+{
+    UlkDims dm;
+    dm.D = (i32)shape[0]; dm.H = (i32)shape[1]; dm.W = (i32)shape[2];
+    dm.V = (i64)dm.D * dm.H * dm.W;
+    if (dm.V <= 0) ULK_FAIL(-1, "empty frame");
+    if (dm.V > 1431655000ll) ULK_FAIL(-1, "frame too large: %lld voxels (edge keys are 32-bit)", (long long)dm.V);
+    if (prm->ws_hierarchy != 0 && prm->ws_hierarchy != 1)
+        ULK_FAIL(-1, "ws_hierarchy=%d is not supported (0 area, 1 dynamics)", prm->ws_hierarchy);
+    const i64 V = dm.V;
+    ulk_seg_stats stats_local;
+    memset(&stats_local, 0, sizeof(stats_local));
+    UlkArena A;
+    ulk_frame_nodes *F = new ulk_frame_nodes();
+    memset(F, 0, sizeof(*F));
+    F->shape[0] = dm.D; F->shape[1] = dm.H; F->shape[2] = dm.W;
+    *result = F;
+
+    // ---- K1 threshold, contour staging
+    UlkCt ct;
+    ct.f = nullptr; ct.d = nullptr;
+    float *ctf = nullptr; double *ctd = nullptr;
+    if (ulk_ct_is_f32(ct_dtype)) { ctf = A.get<float>(V); ct.f = ctf; } else { ctd = A.get<double>(V); ct.d = ctd; }
+    i32 *P = A.get<i32>(V);
+    u32 *cmax = A.get<u32>(1);
+    CHKA(A);
+    CHK(ulk_memset(cmax, 0, 4, st));
+    ulk_launch(V, st, K_Threshold{fg, fg_dtype, prm->threshold, ctp, ct_dtype, ctf, ctd, P, cmax});
+    // ---- connected components (4/6-connected), small-object removal
+    ulk_launch(V, st, K_CclUnion{P, dm});
+    ulk_launch(V, st, K_Flatten{P});
+    i32 *cnt = A.get<i32>(V);
+    i32 *ctr = A.get<i32>(4);
+    CHKA(A);
+    CHK(ulk_memset(cnt, 0, (size_t)V * sizeof(i32), st));
+    CHK(ulk_memset(ctr, 0, 4 * sizeof(i32), st));
+    ulk_launch(V, st, K_CountByRoot{P, cnt});
+    const i32 max_area_i = prm->max_area > 2147483646.0 ? 2147483646 : (i32)prm->max_area;
+    ulk_launch(V, st, K_CcStats{P, cnt, max_area_i, ctr});
+    i32 hc[4];
+    u32 h_cmax = 0;
+    CHK(ulk_read(hc, ctr, 4, st));
+    CHK(ulk_read(&h_cmax, cmax, 1, st));
+    i32 n_cc = hc[0], n_big = hc[1];
+    if (n_cc > 1) {
+        i32 max_size = (i32)(prm->min_area / prm->min_area_factor) - 1;
+        if (max_size >= 1) {
+            u8 *drop = A.get<u8>(V);
+            CHKA(A);
+            ulk_launch(V, st, K_RemoveSmall{P, cnt, max_size, drop});
+            ulk_launch(V, st, K_ApplyDrop{P, drop});
+            A.release(drop);
+            CHK(ulk_memset(ctr, 0, 4 * sizeof(i32), st));
+            ulk_launch(V, st, K_CcStats{P, cnt, max_area_i, ctr});
+            CHK(ulk_read(hc, ctr, 4, st));
+            n_cc = hc[0]; n_big = hc[1];
+        }
+    }
+    float cmaxf;
+    memcpy(&cmaxf, &h_cmax, 4);
+    int e2 = 0;
+    while (ldexp(1.0, e2) <= (double)cmaxf + 1.0) ++e2;
+    const int fix_shift = 62 - e2;
+    const double fixscale = ldexp(1.0, fix_shift);
+    F->fix_shift = fix_shift;
+    if (n_cc == 0) { F->n_nodes = 0; F->stats = stats_local; return 0; }
+
+    // ---- region labels: components, oversegmented where area > max_area
+    i32 *flag = A.get<i32>(V + 1), *ccpre = A.get<i32>(V + 1);
+    i32 *lab2 = A.get<i32>(V);
+    CHKA(A);
+    ulk_launch(V, st, K_FlagRoots{P, flag});
+    CHK(ulk_memset(flag + V, 0, sizeof(i32), st));
+    CHK(ulk_exclusive_scan_i32(flag, ccpre, V + 1, st));
+    i32 R = n_cc;
+    if (n_big == 0) {
+        ulk_launch(V, st, K_LabelSmallOnly{P, ccpre, lab2});
+    } else {
+        UlkArena AA;
+        i32 *bigpre = AA.get<i32>(V + 1), *labA = AA.get<i32>(V);
+        CHKA(AA);
+        ulk_launch(V, st, K_FlagBigRoots{P, cnt, max_area_i, flag});
+        CHK(ulk_memset(flag + V, 0, sizeof(i32), st));
+        CHK(ulk_exclusive_scan_i32(flag, bigpre, V + 1, st));
+        ulk_launch(V, st, K_LabelBigCc{P, cnt, bigpre, max_area_i, labA});
+        VoxelStage va;
+        CHK(voxel_stage(st, AA, dm, ct, labA, n_big, true, false, false, fixscale, va, &stats_local));
+        UlkHierScratch S;
+        CHK(alloc_scratch(AA, va.B, va.Eg, S));
+        UlkBasins Bv{va.b_size, va.g_L, va.b_top, nullptr, nullptr, nullptr, nullptr};
+        UlkEdges Ev{va.ea, va.eb, va.wk, va.k3, va.cnt, va.shi, va.slo};
+        ulk_launch(n_big, st, K_HierStage1{va.bs, va.es, Bv, Ev, S});
+        ulk_launch(V, st, K_Attach{va.bas, va.mw, va.jk, va.g_lab, va.bs, S.Ipar, S.Iwk, S.attach});
+        i32 *region_of = AA.get<i32>(va.B);
+        u64 *rkey_w = AA.get<u64>(va.B), *rkey_k = AA.get<u64>(va.B);
+        CHKA(AA);
+        ulk_launch(n_big, st, K_HierCut{va.bs, va.es, Bv, Ev, S, prm->max_area, region_of, rkey_w, rkey_k});
+        i64 nrec = (i64)n_cc + va.B;
+        u32 *rec_cc = AA.get<u32>(nrec), *perm0 = AA.get<u32>(nrec), *perm1 = AA.get<u32>(nrec);
+        u64 *rec_w = AA.get<u64>(nrec), *rec_k = AA.get<u64>(nrec), *k0 = AA.get<u64>(nrec), *k1 = AA.get<u64>(nrec);
+        u32 *c0 = AA.get<u32>(nrec), *c1 = AA.get<u32>(nrec);
+        i32 *label_of_rec = AA.get<i32>(nrec);
+        CHKA(AA);
+        ulk_launch(V, st, K_SmallCcRecords{P, cnt, ccpre, max_area_i, rec_cc, rec_w, rec_k});
+        ulk_launch(va.B, st, K_RegionRecords{region_of, rkey_w, rkey_k, va.g_root, P, ccpre, n_cc, rec_cc, rec_w, rec_k});
+        ulk_launch(nrec, st, K_Iota{perm0});
+        CHK(ulk_sort_pairs_u64(rec_k, k1, perm0, perm1, nrec, st));           // by tie key
+        ulk_launch(nrec, st, K_Gather<u64>{rec_w, perm1, k0});
+        CHK(ulk_sort_pairs_u64(k0, k1, perm1, perm0, nrec, st));              // then by altitude
+        ulk_launch(nrec, st, K_Gather<u32>{rec_cc, perm0, c0});
+        CHK(ulk_sort_pairs_u32(c0, c1, perm0, perm1, nrec, st));              // then by component
+        ulk_launch(nrec, st, K_RankToLabel{perm1, c1, label_of_rec});
+        ulk_launch(V, st, K_WriteLabels{P, cnt, ccpre, max_area_i, n_cc, va.bas, region_of, label_of_rec, lab2});
+        // number of valid records = regions
+        i32 *nvalid = AA.get<i32>(nrec + 1), *nvpre = AA.get<i32>(nrec + 1);
+        CHKA(AA);
+        ulk_launch(nrec, st, K_Valid{rec_cc, nvalid});
+        CHK(ulk_memset(nvalid + nrec, 0, sizeof(i32), st));
+        CHK(ulk_exclusive_scan_i32(nvalid, nvpre, nrec + 1, st));
+        CHK(ulk_read(&R, nvpre + nrec, 1, st));
+        CHK(ulk_sync(st));
+    }
+    A.release(flag); A.release(ccpre); A.release(cnt); A.release(P);
+    if (keep_labels) {
+        F->labels = keep_alloc<i32>(V);
+        if (!F->labels) return -3;
+        CHK(ulk_d2d(F->labels, lab2, (size_t)V * sizeof(i32), st));
+    }
+    F->n_hier = R;
+
+    // ---- pass B: the configured hierarchy on every region
+    const bool area_mode = prm->ws_hierarchy == 0;
+    VoxelStage vb;
+    CHK(voxel_stage(st, A, dm, ct, lab2, R, area_mode, true, true, fixscale, vb, &stats_local));
+    UlkHierScratch S;
+    CHK(alloc_scratch(A, vb.B, vb.Eg, S));
+    UlkBasins Bv{vb.b_size, vb.g_L, vb.b_top, vb.b_k3, vb.bbmin, vb.bbmax, vb.csum};
+    UlkEdges Ev{vb.ea, vb.eb, vb.wk, vb.k3, vb.cnt, vb.shi, vb.slo};
+    ulk_launch(R, st, K_HierStage1{vb.bs, vb.es, Bv, Ev, S});
+    if (area_mode)
+        ulk_launch(V, st, K_Attach{vb.bas, vb.mw, vb.jk, vb.g_lab, vb.bs, S.Ipar, S.Iwk, S.attach});
+    i64 N2 = 2 * (i64)vb.B + 2;
+    UlkNodeOut O;
+    O.count = A.get<i32>(R + 1); O.nsurv = A.get<i32>(R + 1); O.rsize = A.get<i32>(R + 1);
+    O.area = A.get<i32>(N2); O.frontier = A.get<double>(N2); O.height = A.get<double>(N2);
+    O.bbmin = A.get<i32>(3 * N2); O.bbmax = A.get<i32>(3 * N2); O.csum = A.get<i64>(3 * N2);
+    O.parent = A.get<i32>(N2); O.hidx = A.get<i32>(N2); O.basin_node = A.get<i32>(vb.B);
+    i32 *err = A.get<i32>(1);
+    CHKA(A);
+    CHK(ulk_memset(err, 0, sizeof(i32), st));
+    CHK(ulk_memset(O.count + R, 0, sizeof(i32), st));
+    UlkHierParams HP;
+    HP.kind = prm->ws_hierarchy; HP.min_area = prm->min_area; HP.max_area = prm->max_area;
+    HP.min_frontier = prm->min_frontier; HP.fix_shift = fix_shift;
+    ulk_launch(R, st, K_HierFull{vb.bs, vb.es, Bv, Ev, S, HP, O});
+    ulk_launch(R, st, K_RegionSizeCheck{vb.bs, S, err});
+    i32 h_err = 0;
+    CHK(ulk_read(&h_err, err, 1, st));
+    if (h_err > 0) ULK_FAIL(-10, "Region too small. Size of %d found.", 8 - h_err);
+
+    // ---- node table
+    i32 *noff = A.get<i32>(R + 1);
+    CHKA(A);
+    CHK(ulk_exclusive_scan_i32(O.count, noff, R + 1, st));
+    i32 N = 0;
+    CHK(ulk_read(&N, noff + R, 1, st));
+    F->n_nodes = N;
+    F->bbox = keep_alloc<i32>(6 * (i64)N); F->centroid = keep_alloc<i32>(3 * (i64)N);
+    F->area = keep_alloc<i32>(N); F->frontier = keep_alloc<double>(N); F->height = keep_alloc<double>(N);
+    F->hier_id = keep_alloc<i32>(N); F->parent = keep_alloc<i32>(N); F->hidx = keep_alloc<i32>(N);
+    F->mask_off = keep_alloc<i64>(N + 1);
+    i64 *mwords = A.get<i64>(N + 1);
+    i32 *bnode = A.get<i32>(vb.B);
+    CHKA(A);
+    if (!F->bbox || !F->centroid || !F->area || !F->frontier || !F->height || !F->hier_id || !F->parent || !F->hidx || !F->mask_off)
+        ULK_FAIL(-3, "device allocation failed");
+    ulk_launch(R, st, K_NodeGather{vb.bs, noff, O, F->bbox, F->centroid, F->area, F->hier_id, F->parent, F->hidx,
+                                   F->frontier, F->height, mwords, err});
+    CHK(ulk_memset(mwords + N, 0, sizeof(i64), st));
+    CHK(ulk_exclusive_scan_i64(mwords, F->mask_off, (i64)N + 1, st));
+    i64 total_words = 0;
+    CHK(ulk_read(&total_words, F->mask_off + N, 1, st));
+    F->mask_words = total_words;
+    F->mask = keep_alloc<u32>(total_words);
+    if (!F->mask) ULK_FAIL(-3, "device allocation failed");
+    CHK(ulk_memset(F->mask, 0, (size_t)total_words * 4, st));
+    ulk_launch(vb.B, st, K_BasinNodeGlobal{vb.g_lab, noff, O.basin_node, bnode});
+    ulk_launch(V, st, K_MaskPaint{vb.bas, bnode, F->parent, F->bbox, F->mask_off, dm, F->mask});
+    // ---- overlaps: (node, emitted proper ancestor) pairs, processing.py:289-296
+    i32 *depth = A.get<i32>(N + 1), *ooff = A.get<i32>(N + 1);
+    CHKA(A);
+    ulk_launch(N, st, K_AncestorCount{F->parent, depth});
+    CHK(ulk_memset(depth + N, 0, sizeof(i32), st));
+    CHK(ulk_exclusive_scan_i32(depth, ooff, (i64)N + 1, st));
+    i32 M = 0;
+    CHK(ulk_read(&M, ooff + N, 1, st));
+    F->n_overlaps = M;
+    F->overlaps = keep_alloc<i32>(2 * (i64)M);
+    if (!F->overlaps) ULK_FAIL(-3, "device allocation failed");
+    ulk_launch(N, st, K_OverlapWrite{F->parent, ooff, F->overlaps});
+    CHK(ulk_sync(st));
+    F->stats = stats_local;
+    return 0;
+}

@@ -1,0 +1,17 @@
+// ulk_seg.h -- internal declarations shared by the pipeline files.
+#pragma once
+#include "../../include/ultrack_b200.h"
+#include "ulk_rt.h"
+
+int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const void *ct, int ct_dtype,
+                           const int64_t shape[3], const ulk_seg_params *prm, int keep_labels,
+                           ulk_frame_nodes **result);
+void ulk_frame_nodes_free_impl(ulk_frame_nodes *f);
+int ulk_link_frames_impl(ulk_stream_t st, const ulk_frame_nodes *src, const ulk_frame_nodes *dst,
+                         const double *dst_shift_host, const ulk_link_params *prm, ulk_links **out);
+int ulk_labels_to_contours_impl(ulk_stream_t st, const int32_t *labels, int32_t n_sets, const int64_t shape[3],
+                                uint8_t *foreground, float *contours);
+int ulk_synth_frame_impl(ulk_stream_t st, const int64_t shape[3], int32_t t, uint64_t seed, double radius,
+                         double fill, double motion, double noise, float *fg, float *ct);
+const char *ulk_error_cstr();
+void ulk_set_alloc_stream(ulk_stream_t s);

@@ -1,0 +1,616 @@
+// ulk_voxel.h -- voxel-scale kernels of the segmentation path (functor bodies).
+//
+// Every kernel is a functor launched one thread per voxel (or per list entry)
+// through ulk_launch<>.  Vocabulary follows ultrack / higra: a *region* is one
+// hierarchy's support (core/segmentation/hierarchy.py:89-90), a *basin* is a
+// catchment basin of the watershed cut of a region (altitude-0 node of
+// hg.watershed_hierarchy_by_*), the *RAG* is the basin adjacency graph.
+#pragma once
+#include "ulk_common.h"
+
+#define ULK_JK_CORE 0xFFFFFFFEu   // join key of voxels inside the regional minimum
+
+// ------------------------------------------------------------------ union-find on voxels
+ULK_D ULK_INLINE i32 ulk_vfind(const i32 *P, i32 x)
+{
+    i32 p = P[x];
+    while (p != x) { x = p; p = P[x]; }
+    return x;
+}
+ULK_D ULK_INLINE void ulk_vunion(i32 *P, i32 a, i32 b)
+{
+    for (;;) {
+        a = ulk_vfind(P, a);
+        b = ulk_vfind(P, b);
+        if (a == b) return;
+        if (a < b) { i32 t = a; a = b; b = t; }
+        i32 old = ulk_atomic_min(&P[a], b);   // hook the larger root under the smaller
+        if (old == a) return;
+        a = old;
+    }
+}
+
+// ------------------------------------------------------------------ K1: threshold + contour staging
+// processing.py:212 `foreground[time] > threshold`; vendored/hierarchy.py:158-159,350 up-casts.
+struct K_Threshold {
+    const void *fg; int fgt; double thr;
+    const void *ct; int ctt;
+    float *ctf; double *ctd;
+    i32 *P; u32 *cmax;
+    ULK_D void operator()(i64 v) const
+    {
+        double f = ulk_load_as_double(fg, fgt, v);
+        P[v] = f > thr ? (i32)v : -1;
+        double c = ulk_load_as_double(ct, ctt, v);
+        if (ctf) ctf[v] = (float)c; else ctd[v] = c;
+        float a = (float)(c < 0 ? -c : c);
+        if (a == a && a <= 3.0e38f) {
+            u32 bits;
+            memcpy(&bits, &a, 4);
+            if (bits > *cmax) ulk_atomic_max(cmax, bits);
+        }
+    }
+};
+
+// ------------------------------------------------------------------ connected components (ndi.label)
+struct K_CclUnion {
+    i32 *P; UlkDims dm;
+    ULK_D void operator()(i64 vv) const
+    {
+        i32 v = (i32)vv;
+        if (P[v] < 0) return;
+        i32 z, y, x;
+        dm.coords(v, z, y, x);
+        for (int d = 0; d < 3; ++d) {
+            if (!dm.bwd(d, z, y, x)) continue;
+            i32 u = v - dm.stride(d);
+            if (P[u] >= 0) ulk_vunion(P, v, u);
+        }
+    }
+};
+struct K_Flatten {
+    i32 *P;
+    ULK_D void operator()(i64 v) const { if (P[v] >= 0) P[v] = ulk_vfind(P, (i32)v); }
+};
+struct K_CountByRoot {
+    const i32 *P; i32 *cnt;
+    ULK_D void operator()(i64 v) const { if (P[v] >= 0) ulk_atomic_add(&cnt[P[v]], 1); }
+};
+// counts components and components above max_area
+struct K_CcStats {
+    const i32 *P; const i32 *cnt; i32 max_area; i32 *out;   // out[0]=n_cc out[1]=n_big out[2]=n_fg
+    ULK_D void operator()(i64 v) const
+    {
+        if (P[v] != (i32)v) return;
+        ulk_atomic_add(&out[0], 1);
+        if (cnt[v] > max_area) ulk_atomic_add(&out[1], 1);
+    }
+};
+// morphology.remove_small_objects(labels, max_size=m): drop components with count <= m
+struct K_RemoveSmall {
+    i32 *P; const i32 *cnt; i32 max_size; u8 *drop;
+    ULK_D void operator()(i64 v) const
+    {
+        i32 r = P[v];
+        drop[v] = (r >= 0 && cnt[r] <= max_size) ? 1 : 0;
+    }
+};
+struct K_ApplyDrop {
+    i32 *P; const u8 *drop;
+    ULK_D void operator()(i64 v) const { if (drop[v]) P[v] = -1; }
+};
+struct K_FlagRoots {
+    const i32 *P; i32 *flag;
+    ULK_D void operator()(i64 v) const { flag[v] = P[v] == (i32)v ? 1 : 0; }
+};
+
+// ------------------------------------------------------------------ voxel stage: steepest edges
+// For every active voxel the minimum incident edge by (weight, edge key); edge key =
+// 3*source + direction reproduces the enumeration order of edges_from_mask
+// (vendored/graph.py:41-57), i.e. higra's stable tie-break.
+struct K_MinEdge {
+    const i32 *lab; UlkCt ct; UlkDims dm;
+    u32 *mw, *pk;
+    ULK_D void operator()(i64 vv) const
+    {
+        i32 v = (i32)vv;
+        i32 l = lab[v];
+        if (l <= 0) { mw[v] = ULK_NONE32; pk[v] = ULK_NONE32; return; }
+        i32 z, y, x;
+        dm.coords(v, z, y, x);
+        u64 best = ULK_NONE64;
+        for (int d = 0; d < 3; ++d) {
+            i32 st = dm.stride(d);
+            if (dm.bwd(d, z, y, x)) {
+                i32 u = v - st;
+                if (lab[u] == l) {
+                    u64 k = ((u64)ulk_f2ord(ct.w(u, v)) << 32) | (u32)(3u * (u32)u + d);
+                    if (k < best) best = k;
+                }
+            }
+            if (dm.fwd(d, z, y, x)) {
+                i32 u = v + st;
+                if (lab[u] == l) {
+                    u64 k = ((u64)ulk_f2ord(ct.w(v, u)) << 32) | (u32)(3u * (u32)v + d);
+                    if (k < best) best = k;
+                }
+            }
+        }
+        mw[v] = (u32)(best >> 32);
+        pk[v] = (u32)best;
+    }
+};
+ULK_HD ULK_INLINE i32 ulk_edge_other(u32 key, i32 v, const UlkDims &dm)
+{
+    i32 a = (i32)(key / 3u);
+    i32 b = a + dm.stride((int)(key % 3u));
+    return a == v ? b : a;
+}
+// first Boruvka round: every voxel hooks along its steepest edge; mutual pairs keep the
+// smaller voxel as root.  state: 0 growing, 1 minimum (basin seed)
+struct K_Hook1 {
+    const i32 *lab; const u32 *mw, *pk; UlkDims dm;
+    i32 *bp; u8 *state; u32 *Lr; u32 *best; u32 *flowkey;
+    ULK_D void operator()(i64 vv) const
+    {
+        i32 v = (i32)vv;
+        best[v] = ULK_NONE32;
+        flowkey[v] = ULK_NONE32;
+        state[v] = 0;
+        if (lab[v] <= 0) { bp[v] = -1; return; }
+        u32 k = pk[v];
+        if (k == ULK_NONE32) { bp[v] = v; state[v] = 1; Lr[v] = ULK_NONE32; return; }
+        i32 u = ulk_edge_other(k, v, dm);
+        if (pk[u] == k && v < u) { bp[v] = v; Lr[v] = mw[v]; }
+        else bp[v] = u;
+    }
+};
+struct K_Compress {
+    i32 *bp;
+    ULK_D void operator()(i64 v) const { if (bp[v] >= 0) bp[v] = ulk_vfind(bp, (i32)v); }
+};
+// candidates of the flow rounds: voxels whose steepest weight equals their supervertex level
+struct K_CandInit {
+    const i32 *bp; const u32 *mw; const u32 *Lr; const u8 *state;
+    i32 *cand; i32 *ncand; i32 *groots; i32 *ngroots;
+    ULK_D void operator()(i64 vv) const
+    {
+        i32 v = (i32)vv;
+        i32 r = bp[v];
+        if (r < 0) return;
+        if (r == v && state[v] == 0) groots[ulk_atomic_add(ngroots, 1)] = v;
+        if (state[r] == 0 && mw[v] == Lr[r]) cand[ulk_atomic_add(ncand, 1)] = v;
+    }
+};
+// a growing supervertex looks for its minimum-key outgoing edge at its own level
+struct K_FindFlow {
+    const i32 *cand; const i32 *lab; const i32 *bp; const u32 *mw; const u32 *Lr; const u8 *state;
+    UlkCt ct; UlkDims dm;
+    u32 *best; i32 *cand2; i32 *ncand2;
+    ULK_D void operator()(i64 i) const
+    {
+        i32 v = cand[i];
+        i32 r = ulk_vfind(bp, v);
+        if (state[r] != 0 || mw[v] != Lr[r]) return;
+        cand2[ulk_atomic_add(ncand2, 1)] = v;
+        i32 l = lab[v];
+        u32 lv = Lr[r];
+        i32 z, y, x;
+        dm.coords(v, z, y, x);
+        u32 b = ULK_NONE32;
+        for (int d = 0; d < 3; ++d) {
+            i32 st = dm.stride(d);
+            if (dm.bwd(d, z, y, x)) {
+                i32 u = v - st;
+                if (lab[u] == l && ulk_f2ord(ct.w(u, v)) == lv && ulk_vfind(bp, u) != r) {
+                    u32 k = 3u * (u32)u + d;
+                    if (k < b) b = k;
+                }
+            }
+            if (dm.fwd(d, z, y, x)) {
+                i32 u = v + st;
+                if (lab[u] == l && ulk_f2ord(ct.w(v, u)) == lv && ulk_vfind(bp, u) != r) {
+                    u32 k = 3u * (u32)v + d;
+                    if (k < b) b = k;
+                }
+            }
+        }
+        if (b != ULK_NONE32) ulk_atomic_min(&best[r], b);
+    }
+};
+// decide, read-only part: target root of every growing supervertex (-1: becomes a minimum,
+// -2: stays root as the winner of a mutual pair)
+struct K_Decide1 {
+    const i32 *groots; const i32 *bp; const u32 *best; UlkDims dm;
+    i32 *tgt;
+    ULK_D void operator()(i64 i) const
+    {
+        i32 r = groots[i];
+        u32 k = best[r];
+        if (k == ULK_NONE32) { tgt[i] = -1; return; }
+        i32 a = (i32)(k / 3u), b = a + dm.stride((int)(k % 3u));
+        i32 ra = ulk_vfind(bp, a), rb = ulk_vfind(bp, b);
+        i32 t = ra == r ? rb : ra;
+        if (best[t] == k && r < t) { tgt[i] = -2; return; }
+        tgt[i] = t;
+    }
+};
+struct K_Decide2 {
+    const i32 *groots; const i32 *tgt;
+    i32 *bp; u8 *state; u32 *best; u32 *flowkey; u8 *fmark;
+    i32 *groots2; i32 *ngroots2;
+    ULK_D void operator()(i64 i) const
+    {
+        i32 r = groots[i];
+        i32 t = tgt[i];
+        u32 k = best[r];
+        best[r] = ULK_NONE32;
+        if (t == -1) { state[r] = 1; return; }
+        if (t == -2) { groots2[ulk_atomic_add(ngroots2, 1)] = r; return; }
+        bp[r] = t;
+        flowkey[r] = k;
+        u32 a = k / 3u, d = k % 3u;
+        ulk_atomic_or((u32 *)(fmark + (a & ~3u)), (1u << d) << (8u * (a & 3u)));
+    }
+};
+
+// ------------------------------------------------------------------ basins
+struct K_BasinRootInfo {     // per basin root: label and level
+    const i32 *bp; const i32 *lab; const u32 *Lr; const i32 *pre;   // pre: exclusive scan of root flags
+    i32 *b_root; u32 *b_labkey;
+    ULK_D void operator()(i64 vv) const
+    {
+        i32 v = (i32)vv;
+        if (bp[v] != v) return;
+        i32 i = pre[v];
+        b_root[i] = v;
+        b_labkey[i] = (u32)lab[v];
+    }
+};
+struct K_BasinRegroup {      // sorted position -> global basin id
+    const u32 *sorted_pre; const i32 *b_root; const i32 *lab; const u32 *Lr;
+    i32 *gid_of_pre; i32 *g_root; i32 *g_lab; u32 *g_L; i32 *lab_hist;
+    ULK_D void operator()(i64 g) const
+    {
+        i32 p = (i32)sorted_pre[g];
+        gid_of_pre[p] = (i32)g;
+        i32 v = b_root[p];
+        g_root[g] = v;
+        g_lab[g] = lab[v];
+        g_L[g] = Lr[v];
+        ulk_atomic_add(&lab_hist[lab[v] - 1], 1);
+    }
+};
+struct K_AssignBasin {
+    const i32 *bp; const i32 *pre; const i32 *gid_of_pre;
+    i32 *bas;
+    ULK_D void operator()(i64 v) const { i32 r = bp[v]; bas[v] = r < 0 ? -1 : gid_of_pre[pre[r]]; }
+};
+// per-basin size, spanning-tree top key, crossing-edge count, optional statistics
+struct K_BasinAccum {
+    const i32 *bas; const i32 *lab; const u32 *mw, *pk; const u32 *flowkey; UlkCt ct; UlkDims dm;
+    i32 *b_size; u64 *b_top; u64 *ncross;
+    int want_stats; i32 *bbmin, *bbmax; i64 *csum;
+    ULK_D void operator()(i64 vv) const
+    {
+        i32 v = (i32)vv;
+        i32 b = bas[v];
+        if (b < 0) return;
+        ulk_atomic_add(&b_size[b], 1);
+        if (pk[v] != ULK_NONE32) ulk_atomic_max(&b_top[b], ((u64)mw[v] << 32) | pk[v]);
+        u32 fk = flowkey[v];
+        if (fk != ULK_NONE32) {
+            i32 a = (i32)(fk / 3u), c = a + dm.stride((int)(fk % 3u));
+            ulk_atomic_max(&b_top[b], ((u64)ulk_f2ord(ct.w(a, c)) << 32) | fk);
+        }
+        i32 z, y, x;
+        dm.coords(v, z, y, x);
+        i32 l = lab[v];
+        u32 nc = 0;
+        for (int d = 0; d < 3; ++d)
+            if (dm.fwd(d, z, y, x)) { i32 u = v + dm.stride(d); if (lab[u] == l && bas[u] != b) ++nc; }
+        if (nc) ulk_atomic_add(ncross, (u64)nc);
+        if (want_stats) {
+            i32 c[3] = {z, y, x};
+            for (int d = 0; d < 3; ++d) {
+                ulk_atomic_min(&bbmin[3 * b + d], c[d]);
+                ulk_atomic_max(&bbmax[3 * b + d], c[d]);
+                ulk_atomic_add(&csum[3 * b + d], (i64)c[d]);
+            }
+        }
+    }
+};
+
+// ------------------------------------------------------------------ join keys (area hierarchy)
+// J(v) = (mw[v], jk[v]): the Kruskal position at which voxel v joins a component that
+// holds a regional minimum.  Core voxels (mw == basin level) belong to the minimum.
+struct K_JoinKey {
+    const i32 *bas; const u32 *mw, *pk; const u32 *b_L; UlkDims dm;
+    u32 *jk; i32 *hp; i32 *nhp;
+    ULK_D void operator()(i64 vv) const
+    {
+        i32 v = (i32)vv;
+        i32 b = bas[v];
+        if (b < 0) { jk[v] = ULK_JK_CORE; return; }
+        if (mw[v] == b_L[b] || pk[v] == ULK_NONE32) { jk[v] = ULK_JK_CORE; return; }
+        i32 u = ulk_edge_other(pk[v], v, dm);
+        if (mw[u] < mw[v]) jk[v] = pk[v];
+        else { jk[v] = ULK_NONE32; hp[ulk_atomic_add(nhp, 1)] = v; }
+    }
+};
+// plateau voxels above the basin level: minimax relaxation along spanning-tree edges
+struct K_PlateauRelax {
+    const i32 *hp; const i32 *lab; const u32 *mw, *pk; const u8 *fmark; UlkCt ct; UlkDims dm;
+    u32 *jk; i32 *changed;
+    ULK_D void operator()(i64 i) const
+    {
+        i32 v = hp[i];
+        i32 l = lab[v];
+        u32 lv = mw[v];
+        u32 cur = jk[v];
+        i32 z, y, x;
+        dm.coords(v, z, y, x);
+        u32 bestc = cur;
+        for (int d = 0; d < 3; ++d) {
+            i32 st = dm.stride(d);
+            for (int s = 0; s < 2; ++s) {
+                i32 u, src;
+                if (s == 0) { if (!dm.bwd(d, z, y, x)) continue; u = v - st; src = u; }
+                else { if (!dm.fwd(d, z, y, x)) continue; u = v + st; src = v; }
+                if (lab[u] != l) continue;
+                u32 k = 3u * (u32)src + d;
+                bool tree = pk[v] == k || pk[u] == k || ((fmark[src] >> d) & 1);
+                if (!tree) continue;
+                if (ulk_f2ord(ct.w(src, src + st)) != lv) continue;
+                u32 c;
+                if (mw[u] < lv) c = k;
+                else { u32 ju = jk[u]; c = ju > k ? ju : k; }
+                if (c < bestc) bestc = c;
+            }
+        }
+        if (bestc < cur) { jk[v] = bestc; *changed = 1; }
+    }
+};
+// late joiners climb the basin BPT: a voxel attaches to the highest ancestor of its basin
+// whose merge precedes its join key
+struct K_Attach {
+    const i32 *bas; const u32 *mw, *jk; const i32 *b_lab; const i32 *bs;
+    const i32 *Ipar; const u64 *Iwk; i32 *attach;
+    ULK_D void operator()(i64 v) const
+    {
+        i32 b = bas[v];
+        if (b < 0) return;
+        u32 j = jk[v];
+        if (j == ULK_JK_CORE) return;
+        u64 J = ((u64)mw[v] << 32) | j;
+        i32 h = b_lab[b] - 1;
+        i32 s = bs[h];
+        i32 o = 2 * s;
+        i32 node = b - s;
+        i32 start = node;
+        for (;;) {
+            i32 p = Ipar[o + node];
+            if (p == node || !(Iwk[o + p] < J)) break;
+            node = p;
+        }
+        if (node != start) {
+            ulk_atomic_add(&attach[o + start], -1);
+            ulk_atomic_add(&attach[o + node], 1);
+        }
+    }
+};
+
+// ------------------------------------------------------------------ region adjacency graph
+struct UlkRagTable {
+    u64 *key; u64 *wk; u32 *k3; u32 *cnt; u64 *shi; u64 *slo;
+    u64 mask;
+};
+ULK_HD ULK_INLINE u64 ulk_hash64(u64 x)
+{
+    x ^= x >> 33; x *= 0xff51afd7ed558ccdull; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull; x ^= x >> 33;
+    return x;
+}
+struct K_RagInsert {
+    const i32 *bas; const i32 *lab; UlkCt ct; UlkDims dm; UlkRagTable T; double fixscale;
+    ULK_D void operator()(i64 vv) const
+    {
+        i32 v = (i32)vv;
+        i32 b = bas[v];
+        if (b < 0) return;
+        i32 l = lab[v];
+        i32 z, y, x;
+        dm.coords(v, z, y, x);
+        for (int d = 0; d < 3; ++d) {
+            if (!dm.fwd(d, z, y, x)) continue;
+            i32 u = v + dm.stride(d);
+            if (lab[u] != l) continue;
+            i32 c = bas[u];
+            if (c == b) continue;
+            u64 key = b < c ? ((u64)(u32)b << 32) | (u32)c : ((u64)(u32)c << 32) | (u32)b;
+            float w = ct.w(v, u);
+            u32 ek = 3u * (u32)v + d;
+            u64 h = ulk_hash64(key) & T.mask;
+            for (;;) {
+                u64 old = ulk_atomic_cas(&T.key[h], ULK_NONE64, key);
+                if (old == ULK_NONE64 || old == key) break;
+                h = (h + 1) & T.mask;
+            }
+            ulk_atomic_min(&T.wk[h], ((u64)ulk_f2ord(w) << 32) | ek);
+            ulk_atomic_min(&T.k3[h], ek);
+            ulk_atomic_add(&T.cnt[h], 1u);
+            i64 fx = (i64)((double)w * fixscale);
+            ulk_atomic_add(&T.shi[h], (u64)(fx >> 32));
+            ulk_atomic_add(&T.slo[h], (u64)(fx & 0xffffffffll));
+        }
+    }
+};
+struct K_RagFlag {
+    const u64 *key; i32 *flag;
+    ULK_D void operator()(i64 i) const { flag[i] = key[i] != ULK_NONE64 ? 1 : 0; }
+};
+struct K_RagGather {
+    UlkRagTable T; const i32 *pre; const i32 *g_lab;
+    i32 *ea, *eb; u64 *wk; u32 *k3, *cnt; u64 *shi, *slo; u32 *elab; u32 *eidx;
+    ULK_D void operator()(i64 i) const
+    {
+        u64 k = T.key[i];
+        if (k == ULK_NONE64) return;
+        i32 j = pre[i];
+        ea[j] = (i32)(k >> 32); eb[j] = (i32)(u32)k;
+        wk[j] = T.wk[i]; k3[j] = T.k3[i]; cnt[j] = T.cnt[i]; shi[j] = T.shi[i]; slo[j] = T.slo[i];
+        elab[j] = (u32)g_lab[(i32)(k >> 32)];
+        eidx[j] = (u32)j;
+    }
+};
+template <class T> struct K_Gather {
+    const T *src; const u32 *idx; T *dst;
+    ULK_D void operator()(i64 i) const { dst[i] = src[idx[i]]; }
+};
+struct K_Hist {
+    const u32 *lab; i32 *hist;
+    ULK_D void operator()(i64 i) const { ulk_atomic_add(&hist[lab[i] - 1], 1); }
+};
+
+// ------------------------------------------------------------------ raster-key bottleneck of a basin
+// hg.filter_small_nodes_from_tree re-binarises the tree with bpt_canonical(leaf_graph,
+// saliency); inside a basin every edge has saliency 0, so Kruskal runs there by edge index
+// alone and the basin's altitude-0 node is created by the LAST edge it accepts: the
+// bottleneck of the raster-key MST.  K0 = max over voxels of their smallest in-basin edge
+// key is a lower bound that is tight whenever edges <= K0 already connect the basin.
+struct K_MinKeyInBasin {
+    const i32 *bas; UlkDims dm; u32 *K0;
+    ULK_D void operator()(i64 vv) const
+    {
+        i32 v = (i32)vv;
+        i32 b = bas[v];
+        if (b < 0) return;
+        i32 z, y, x;
+        dm.coords(v, z, y, x);
+        u32 k = ULK_NONE32;
+        for (int d = 0; d < 3; ++d) {
+            if (dm.bwd(d, z, y, x)) { i32 u = v - dm.stride(d); if (bas[u] == b) { u32 kk = 3u * (u32)u + d; if (kk < k) k = kk; } }
+            if (dm.fwd(d, z, y, x)) { i32 u = v + dm.stride(d); if (bas[u] == b) { u32 kk = 3u * (u32)v + d; if (kk < k) k = kk; } }
+        }
+        if (k != ULK_NONE32 && k > K0[b]) ulk_atomic_max(&K0[b], k);
+    }
+};
+struct K_K3Init {
+    const i32 *bas; i32 *P;
+    ULK_D void operator()(i64 v) const { P[v] = bas[v] < 0 ? -1 : (i32)v; }
+};
+struct K_K3Union {
+    const i32 *bas; UlkDims dm; const u32 *K0; i32 *P;
+    ULK_D void operator()(i64 vv) const
+    {
+        i32 v = (i32)vv;
+        i32 b = bas[v];
+        if (b < 0) return;
+        i32 z, y, x;
+        dm.coords(v, z, y, x);
+        u32 kmax = K0[b];
+        for (int d = 0; d < 3; ++d) {
+            if (!dm.bwd(d, z, y, x)) continue;
+            i32 u = v - dm.stride(d);
+            if (bas[u] == b && 3u * (u32)u + d <= kmax) ulk_vunion(P, v, u);
+        }
+    }
+};
+struct K_K3CountRoots {
+    const i32 *bas; const i32 *P; i32 *nroot; i32 *nmulti;
+    ULK_D void operator()(i64 v) const
+    {
+        if (bas[v] < 0 || P[v] != (i32)v) return;
+        i32 old = ulk_atomic_add(&nroot[bas[v]], 1);
+        if (old == 1) ulk_atomic_add(nmulti, 1);
+    }
+};
+struct K_K3FindBest {     // Boruvka step on the basins that are still split
+    const i32 *bas; UlkDims dm; const i32 *nroot; const i32 *P; u32 *best;
+    ULK_D void operator()(i64 vv) const
+    {
+        i32 v = (i32)vv;
+        i32 b = bas[v];
+        if (b < 0 || nroot[b] <= 1) return;
+        i32 r = ulk_vfind(P, v);
+        i32 z, y, x;
+        dm.coords(v, z, y, x);
+        u32 k = ULK_NONE32;
+        for (int d = 0; d < 3; ++d) {
+            i32 st = dm.stride(d);
+            if (dm.bwd(d, z, y, x)) { i32 u = v - st; if (bas[u] == b && ulk_vfind(P, u) != r) { u32 kk = 3u * (u32)u + d; if (kk < k) k = kk; } }
+            if (dm.fwd(d, z, y, x)) { i32 u = v + st; if (bas[u] == b && ulk_vfind(P, u) != r) { u32 kk = 3u * (u32)v + d; if (kk < k) k = kk; } }
+        }
+        if (k != ULK_NONE32) ulk_atomic_min(&best[r], k);
+    }
+};
+struct K_K3Hook {
+    const i32 *bas; UlkDims dm; i32 *P; u32 *best; u32 *K0;
+    ULK_D void operator()(i64 vv) const
+    {
+        i32 v = (i32)vv;
+        if (bas[v] < 0) return;
+        u32 k = best[v];
+        if (k == ULK_NONE32) return;
+        best[v] = ULK_NONE32;
+        i32 a = (i32)(k / 3u), c = a + dm.stride((int)(k % 3u));
+        ulk_vunion(P, a, c);
+        ulk_atomic_max(&K0[bas[v]], k);
+    }
+};
+
+// ------------------------------------------------------------------ label writing (pass A -> pass B)
+struct K_SmallCcRecords {   // one region record per component that is not oversegmented
+    const i32 *P; const i32 *cnt; const i32 *ccpre; i32 max_area;
+    u32 *rec_cc; u64 *rec_w; u64 *rec_k;
+    ULK_D void operator()(i64 vv) const
+    {
+        i32 v = (i32)vv;
+        if (P[v] != v) return;
+        i32 c = ccpre[v];
+        bool big = cnt[v] > max_area;
+        rec_cc[c] = big ? ULK_NONE32 : (u32)c;
+        rec_w[c] = 0; rec_k[c] = 0;
+    }
+};
+struct K_RegionRecords {    // one record per cut region of an oversegmented component
+    const i32 *region_of; const u64 *rkey_w, *rkey_k; const i32 *g_root; const i32 *P; const i32 *ccpre; i32 ncc;
+    u32 *rec_cc; u64 *rec_w; u64 *rec_k;
+    ULK_D void operator()(i64 g) const
+    {
+        i32 i = ncc + (i32)g;
+        if (region_of[g] != (i32)g) { rec_cc[i] = ULK_NONE32; rec_w[i] = 0; rec_k[i] = 0; return; }
+        rec_cc[i] = (u32)ccpre[P[g_root[g]]];
+        rec_w[i] = rkey_w[g]; rec_k[i] = rkey_k[g];
+    }
+};
+struct K_RankToLabel {
+    const u32 *perm; const u32 *rec_cc_sorted; i32 *label_of_rec;
+    ULK_D void operator()(i64 i) const
+    {
+        label_of_rec[perm[i]] = rec_cc_sorted[i] == ULK_NONE32 ? 0 : (i32)i + 1;
+    }
+};
+struct K_WriteLabels {
+    const i32 *P; const i32 *cnt; const i32 *ccpre; i32 max_area; i32 ncc;
+    const i32 *basA; const i32 *region_of; const i32 *label_of_rec;
+    i32 *lab2;
+    ULK_D void operator()(i64 v) const
+    {
+        i32 r = P[v];
+        if (r < 0) { lab2[v] = 0; return; }
+        if (cnt[r] > max_area) lab2[v] = label_of_rec[ncc + region_of[basA[v]]];
+        else lab2[v] = label_of_rec[ccpre[r]];
+    }
+};
+struct K_LabelBigCc {       // pass A works only on the oversize components
+    const i32 *P; const i32 *cnt; const i32 *bigpre; i32 max_area; i32 *labA;
+    ULK_D void operator()(i64 v) const
+    {
+        i32 r = P[v];
+        labA[v] = (r >= 0 && cnt[r] > max_area) ? bigpre[r] + 1 : 0;
+    }
+};
+struct K_FlagBigRoots {
+    const i32 *P; const i32 *cnt; i32 max_area; i32 *flag;
+    ULK_D void operator()(i64 v) const { flag[v] = (P[v] == (i32)v && cnt[v] > max_area) ? 1 : 0; }
+};
