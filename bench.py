@@ -1,0 +1,361 @@
+#!/usr/bin/env python
+"""bench.py -- voxels/s of segment+link (and links/s) on N B200s of one node.
+
+A step = one pass of the hot path over one frame: `ulk_segment_frame` on a synthetic frame
+plus `ulk_link_frames` of the previous frame's node table against the new one.  Frames are
+sharded by timepoint across ranks with no data-path collective (weak scaling: every rank
+runs the same number of steps on its own frames); the shard-boundary exchange of link() is a
+per-shard constant that bench_boundary() reports separately.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c5|c4|c3|c2] [--impl reference]
+
+`--impl reference` times the CPU restatement of the reference's path (oracle/, the reference
+itself is not installable here: it needs higra) on the box's host cores on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+WORKLOADS = {
+    # name: (frame shape, cell radius, BASELINE.json config it is the per-GPU unit of)
+    "c5": ((448, 1536, 1536), 8.0, "configs[4] Zebrahub-scale 3D 448x1536x1536 frame, max_distance=15"),
+    "c4": ((256, 1024, 1024), 8.0, "configs[3]-sized 3D 256x1024x1024 frame"),
+    "c3": ((128, 512, 512), 8.0, "configs[2] 3D 128x512x512 frame, min_area=100 max_area=10000"),
+    "c2": ((1, 2048, 2048), 12.0, "configs[1] 2D 2048x2048 frame, max_neighbors=5"),
+}
+SEG = dict(threshold=0.5, min_area=100, max_area=10000, min_area_factor=4.0, min_frontier=0.0, ws_hierarchy="area")
+LINK = dict(max_distance=15.0, max_neighbors=5, distance_weight=0.0)
+SYNTH = dict(seed=7, fill=0.3, motion=3.0, noise=1e-3)
+METRIC = "voxels_per_sec_segment_link"
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index),
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- CPU arm
+def _cpu_frame(args):
+    """One sample frame through the oracle: segmentation of frame t and its link to t-1's twin."""
+    t, shape, radius = args
+    from oracle.link_oracle import link_pair
+    from oracle.segment_oracle import SegParams, segment_frame
+    from ultrack_b200 import synth
+    prm = SegParams(threshold=SEG["threshold"], min_area=SEG["min_area"], max_area=SEG["max_area"],
+                    min_area_factor=SEG["min_area_factor"], min_frontier=SEG["min_frontier"],
+                    ws_hierarchy=SEG["ws_hierarchy"])
+    out = []
+    for tt in (t, t + 1):
+        fg, ct, _ = synth.make_frame(shape, t=tt, seed=SYNTH["seed"], variant="S", radius=radius, fill=SYNTH["fill"],
+                                     motion=SYNTH["motion"], noise=SYNTH["noise"])
+        t0 = time.perf_counter()
+        out.append((segment_frame(fg, ct, prm, time=tt), time.perf_counter() - t0))
+    t0 = time.perf_counter()
+    links = link_pair(out[0][0]["nodes"], out[1][0]["nodes"], LINK["max_distance"], LINK["max_neighbors"],
+                      LINK["distance_weight"], time=t)
+    t_link = time.perf_counter() - t0
+    # one step = one frame segmented + one pair linked (the second frame's segmentation is the step)
+    return out[1][1] + t_link, 0 if links is None else len(links)
+
+
+def cpu_sample_shape(shape):
+    """Bounded sample of the workload for the CPU arm: a sub-volume of the same synthetic recipe."""
+    if shape[0] == 1:
+        return (384, 384)
+    return (40, 128, 128)
+
+
+def run_cpu_arm(shape, radius, steps: int, warmup: int, max_workers: int = 0):
+    """The restated reference path under a process pool over frames on the host cores (the
+    reference's own parallelism: multiprocessing over timepoints, utils/multiprocessing.py:26-56)."""
+    import multiprocessing as mp
+    from oracle.build import build as build_oracle
+    build_oracle()
+    cores = max_workers or min(os.cpu_count() or 1, 64)
+    sshape = cpu_sample_shape(shape)
+    vox = 1
+    for s in sshape:
+        vox *= s
+    ctx = mp.get_context("spawn")
+    with ctx.pool.Pool(cores) if hasattr(ctx, "pool") else ctx.Pool(cores) as pool:
+        for _ in range(min(warmup, 1)):
+            pool.map(_cpu_frame, [(2 * i, sshape, radius) for i in range(cores)])
+        t0 = time.perf_counter()
+        n_links = 0
+        for k in range(steps):
+            res = pool.map(_cpu_frame, [(2 * (k * cores + i), sshape, radius) for i in range(cores)])
+            n_links += sum(r[1] for r in res)
+        wall = time.perf_counter() - t0
+    return {"voxels_per_sec": vox * cores * steps / wall, "links_per_sec": n_links / wall, "cores": cores,
+            "sample": f"{steps} step(s) x {cores} worker(s), each one {'x'.join(map(str, sshape))} sub-volume of the "
+                      f"workload's synthetic recipe (segment one frame + link it to its predecessor); wall {wall:.1f}s",
+            "ms_per_step": wall * 1e3 / steps}
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=4)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default=os.environ.get("ULK_BENCH_WORKLOAD", "auto"))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        name = "c5" if args.workload == "auto" else args.workload
+        shape, radius, desc = WORKLOADS[name]
+        res = run_cpu_arm(shape, radius, max(args.steps, 1), args.warmup)
+        line = {
+            "impl": "reference", "metric": METRIC, "value": res["voxels_per_sec"], "unit": "voxels/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": res["ms_per_step"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": desc, "frame_shape": list(shape), "segmentation": SEG, "linking": LINK},
+            "links_per_sec": res["links_per_sec"],
+            "cpu_baseline": {"value": res["voxels_per_sec"], "unit": "voxels/s", "cores": res["cores"], "kind": "port",
+                             "sample": res["sample"]},
+            "e2e": {"value": res["voxels_per_sec"], "unit": "voxels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        }
+        print(json.dumps(line))
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from tests.emu_harness import seg_params
+    from ultrack_b200 import _lib, bytes_model
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    lib = _lib.get_lib()
+    _lib.check(lib, lib.ulk_set_device(local_rank))
+    dev = torch.device("cuda", local_rank)
+
+    name = args.workload
+    if name == "auto":
+        free, _ = torch.cuda.mem_get_info()
+        name = "c5" if free > 150e9 else "c4"
+    shape, radius, desc = WORKLOADS[name]
+    V = shape[0] * shape[1] * shape[2]
+    shp = (C.c_int64 * 3)(*shape)
+    stream = torch.cuda.Stream()
+    sp = C.c_void_p(stream.cuda_stream)
+
+    # two device-resident synthetic frames per rank (cells move between them); every rank owns
+    # its own timepoints (t = 2*rank, 2*rank+1): the inputs are far larger than L2 (126 MB)
+    frames_in = []
+    for j in range(2):
+        fg = torch.empty(shape, dtype=torch.float32, device=dev)
+        ct = torch.empty(shape, dtype=torch.float32, device=dev)
+        _lib.check(lib, lib.ulk_synth_frame(shp, 2 * rank + j, SYNTH["seed"], radius, SYNTH["fill"], SYNTH["motion"],
+                                            SYNTH["noise"], C.c_void_p(fg.data_ptr()), C.c_void_p(ct.data_ptr()), sp))
+        frames_in.append((fg, ct))
+    prm = seg_params(fg_dtype=np.float32, **SEG)
+    lprm = _lib.LinkParams(LINK["max_distance"], LINK["distance_weight"], LINK["max_neighbors"], 0,
+                           (C.c_double * 3)(1, 1, 1))
+
+    def seg(j, host=None):
+        h = C.POINTER(_lib.FrameNodes)()
+        if host is None:
+            fg, ct = frames_in[j]
+            rc = lib.ulk_segment_frame(C.c_void_p(fg.data_ptr()), 5, C.c_void_p(ct.data_ptr()), 5, shp, C.byref(prm),
+                                       0, sp, C.byref(h))
+        else:
+            fg, ct = host[j]
+            rc = lib.ulk_segment_frame_host(C.c_void_p(fg.data_ptr()), 5, C.c_void_p(ct.data_ptr()), 5, shp,
+                                            C.byref(prm), 0, sp, C.byref(h))
+        _lib.check(lib, rc)
+        return h
+
+    def lnk(a, b):
+        out = C.POINTER(_lib.Links)()
+        _lib.check(lib, lib.ulk_link_frames(a, b, None, C.byref(lprm), sp, C.byref(out)))
+        return out
+
+    def step(i, prev, host=None, fetch=False):
+        cur = seg(i % 2, host)
+        links = lnk(prev, cur)
+        n_links, n_pairs = int(links.contents.n_links), int(links.contents.n_pairs)
+        d2h = 0
+        if fetch:   # the result a user reads back: node table + links
+            nodes = _lib.nodes_to_host(lib, cur, stream.cuda_stream)
+            s = np.zeros(n_links, np.int32); t = np.zeros(n_links, np.int32); w = np.zeros(n_links, np.float64)
+            p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+            _lib.check(lib, lib.ulk_links_to_host(links, p(s), p(t), p(w), sp))
+            d2h = sum(v.nbytes for v in nodes.values() if isinstance(v, np.ndarray)) + s.nbytes + t.nbytes + w.nbytes
+        lib.ulk_links_free(links)
+        lib.ulk_frame_nodes_free(prev)
+        return cur, n_links, n_pairs, d2h
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.cuda.stream(stream):
+        prev = seg(1)
+        for i in range(args.warmup):
+            prev, *_ = step(i, prev)
+        # ---- timed region: K steps, device-resident inputs, per-kernel events on
+        lib.ulk_profile_reset()
+        lib.ulk_profile_enable(1)
+        launches0 = lib.ulk_launch_count()
+        clocks = ClockSampler(local_rank)
+        clocks.start()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        tot_links = tot_pairs = 0
+        for i in range(args.steps):
+            prev, nl, npairs, _ = step(i, prev)
+            tot_links += nl
+            tot_pairs += npairs
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        clk = clocks.stop()
+        lib.ulk_profile_enable(0)
+        launches = lib.ulk_launch_count() - launches0
+        prof = _lib.profile_report(lib)
+        f = prev.contents
+        stats = dict(n_nodes=int(f.n_nodes), n_overlaps=int(f.n_overlaps), mask_words=int(f.mask_words),
+                     n_hier=int(f.n_hier), n_basins=int(f.stats.n_basins), n_rag_edges=int(f.stats.n_rag_edges))
+        n_fg = int((frames_in[(args.steps - 1) % 2][0] > SEG["threshold"]).sum().item())
+
+        # ---- e2e: the same steps through the C-ABI host entry point, pinned host buffers
+        e2e = None
+        if not args.no_e2e:
+            host = [(fg.cpu().pin_memory(), ct.cpu().pin_memory()) for fg, ct in frames_in]
+            ke = max(1, min(args.steps, 3))
+            prev, *_ = step(0, prev, host, True)
+            barrier()
+            e0.record(stream)
+            d2h_tot = 0
+            for i in range(ke):
+                prev, _, _, d2h = step(i + 1, prev, host, True)
+                d2h_tot += d2h
+            e1.record(stream)
+            barrier()
+            ems = e0.elapsed_time(e1)
+            e2e = (ke, ems, d2h_tot // ke)
+            del host
+    lib.ulk_frame_nodes_free(prev)
+
+    t = torch.tensor([ms, e2e[1] if e2e else 0.0], dtype=torch.float64, device=dev)
+    cnt = torch.tensor([tot_links], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    ms_max, ems_max = float(t[0]), float(t[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks = {}
+    pk = ROOT / "MEASURED_PEAKS.json"
+    if pk.exists():
+        peaks = json.loads(pk.read_text())
+    peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if pk.exists() else "B200_PROFILING.md fallback 6650 GB/s (of fallback)"
+
+    value = V * args.steps * world / (ms_max * 1e-3)
+    kern_ms = sum(v[1] for v in prof.values())
+    top = sorted(prof.items(), key=lambda kv: -kv[1][1])
+    dom_name, (dom_cnt, dom_ms) = top[0]
+    dom_bytes = bytes_model.kernel_bytes(dom_name, V)
+    dom_avg_ms = dom_ms / dom_cnt
+    roofline = {
+        "bound": "hbm", "kernel": dom_name, "launches": dom_cnt, "avg_ms": dom_avg_ms,
+        "share_of_kernel_time": dom_ms / kern_ms if kern_ms else None,
+        "achieved": (dom_bytes / (dom_avg_ms * 1e-3) / 1e9) if dom_bytes else None, "peak": peak_gbs, "unit": "GB/s",
+        "frac": (dom_bytes / (dom_avg_ms * 1e-3) / 1e9 / peak_gbs) if dom_bytes else None,
+        "algorithmic_bytes_per_launch": dom_bytes, "traffic": None, "peak_source": peak_src,
+    }
+    b_frame = bytes_model.frame_bytes(V, 4, 4, n_fg, stats["n_nodes"], stats["mask_words"], stats["n_overlaps"])
+    b_link = bytes_model.link_bytes(tot_links // max(args.steps, 1), tot_pairs // max(args.steps, 1),
+                                    stats["mask_words"] / max(stats["n_nodes"], 1))
+    pipe_gbs = (b_frame + b_link) * args.steps / (ms * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": "voxels/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": desc, "frame_shape": list(shape), "segmentation": SEG, "linking": LINK,
+                   "synthetic": dict(SYNTH, radius=radius), "l2": "inputs larger than L2 (no flush needed)",
+                   "parallelism": f"timepoint shards x{world}", "frame_stats": stats},
+        "links_per_sec": float(cnt[0]) / (ms_max * 1e-3),
+        "gpu_launches": int(launches),
+        "clocks": clk,
+        "roofline": roofline,
+        "pipeline_roofline": {"algorithmic_bytes_per_step": b_frame + b_link, "achieved": pipe_gbs, "peak": peak_gbs,
+                              "unit": "GB/s", "frac": pipe_gbs / peak_gbs,
+                              "kernel_time_ms_per_step": kern_ms / args.steps,
+                              "top_kernels_ms_per_step": {k: round(v[1] / args.steps, 3) for k, v in top[:12]}},
+    }
+    if e2e:
+        ke = e2e[0]
+        line["e2e"] = {"value": V * ke * world / (ems_max * 1e-3), "unit": "voxels/s", "steps": ke,
+                       "ms_per_step": ems_max / ke, "h2d_bytes_per_step": 2 * 4 * V, "d2h_bytes_per_step": e2e[2],
+                       "api": "ulk_segment_frame_host + ulk_frame_nodes_to_host + ulk_link_frames + ulk_links_to_host, pinned host buffers"}
+    if not args.no_cpu_baseline and world == 1:
+        res = run_cpu_arm(shape, radius, 1, 0)
+        line["cpu_baseline"] = {"value": res["voxels_per_sec"], "unit": "voxels/s", "cores": res["cores"], "kind": "port",
+                                "sample": res["sample"], "links_per_sec": res["links_per_sec"]}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -94,8 +94,17 @@ typedef struct ulk_links {
 
 ULK_API const char *ulk_last_error(void);
 ULK_API int ulk_device_count(void);
+/* binds the calling thread to a device (one process per GPU: LOCAL_RANK) */
+ULK_API int ulk_set_device(int device);
 /* kernels launched by this library on the calling process so far */
 ULK_API int64_t ulk_launch_count(void);
+
+/* per-kernel timing for bench.py's roofline line: when enabled every launch is bracketed by a
+ * CUDA event pair on its own stream.  report: "kernel name\tlaunches\ttotal ms\n" per kernel;
+ * returns the buffer size the full report needs. */
+ULK_API void ulk_profile_enable(int on);
+ULK_API void ulk_profile_reset(void);
+ULK_API int ulk_profile_report(char *buf, int64_t cap);
 
 /* stream: a cudaStream_t (0 = default stream); all work of a call is ordered on it and the
  * call returns after the results are complete. */
@@ -118,7 +127,16 @@ ULK_API int ulk_frame_nodes_from_host(int32_t n_nodes, const int32_t shape[3], c
                               const int32_t *centroid, const int32_t *area, const int64_t *mask_off,
                               const uint32_t *mask, void *stream, ulk_frame_nodes **out);
 
-/* dst_shift: host [n_dst,3] float64 (z,y,x shifts of the target nodes) or NULL */
+/* same two, for device-resident buffers owned by the caller (a torch tensor received over
+ * NCCL from the rank that owns the next timepoint shard): d2d copies, no host round trip */
+ULK_API int ulk_frame_nodes_to_device(const ulk_frame_nodes *nodes, int32_t *bbox, int32_t *centroid, int32_t *area,
+                              int64_t *mask_off, uint32_t *mask, void *stream);
+ULK_API int ulk_frame_nodes_from_device(int32_t n_nodes, const int32_t shape[3], const int32_t *bbox,
+                                const int32_t *centroid, const int32_t *area, const int64_t *mask_off,
+                                int64_t mask_words, const uint32_t *mask, void *stream, ulk_frame_nodes **out);
+
+/* dst_shift: host [n_dst,3] float64 (z,y,x shifts of the target nodes) or NULL; for 2-D
+ * frames the z column must be 0 (the reference slices `shift[:, -ndim:]`) */
 ULK_API int ulk_link_frames(const ulk_frame_nodes *src, const ulk_frame_nodes *dst, const double *dst_shift_host,
                     const ulk_link_params *params, void *stream, ulk_links **out);
 ULK_API int ulk_links_to_host(const ulk_links *links, int32_t *source, int32_t *target, double *weight, void *stream);

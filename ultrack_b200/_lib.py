@@ -56,9 +56,10 @@ class Links(C.Structure):
 
 
 EXPORTS = [
-    "ulk_last_error", "ulk_device_count", "ulk_launch_count", "ulk_segment_frame",
+    "ulk_last_error", "ulk_device_count", "ulk_set_device", "ulk_launch_count",
+    "ulk_profile_enable", "ulk_profile_reset", "ulk_profile_report", "ulk_segment_frame",
     "ulk_segment_frame_host", "ulk_frame_nodes_free", "ulk_frame_nodes_to_host",
-    "ulk_frame_nodes_from_host", "ulk_link_frames", "ulk_links_to_host", "ulk_links_free",
+    "ulk_frame_nodes_from_host", "ulk_frame_nodes_to_device", "ulk_frame_nodes_from_device", "ulk_link_frames", "ulk_links_to_host", "ulk_links_free",
     "ulk_labels_to_contours", "ulk_synth_frame",
 ]
 
@@ -69,7 +70,12 @@ def bind(lib: C.CDLL) -> C.CDLL:
     lib.ulk_last_error.restype = C.c_char_p
     lib.ulk_last_error.argtypes = []
     lib.ulk_device_count.restype = C.c_int
+    lib.ulk_set_device.argtypes = [C.c_int]
     lib.ulk_launch_count.restype = i64
+    lib.ulk_profile_enable.argtypes = [C.c_int]
+    lib.ulk_profile_enable.restype = None
+    lib.ulk_profile_reset.restype = None
+    lib.ulk_profile_report.argtypes = [C.c_char_p, i64]
     seg_args = [vp, C.c_int, vp, C.c_int, C.POINTER(i64), C.POINTER(SegParams), C.c_int, vp, C.POINTER(PF)]
     lib.ulk_segment_frame.argtypes = seg_args
     lib.ulk_segment_frame_host.argtypes = seg_args
@@ -77,6 +83,8 @@ def bind(lib: C.CDLL) -> C.CDLL:
     lib.ulk_frame_nodes_free.restype = None
     lib.ulk_frame_nodes_to_host.argtypes = [PF] + [vp] * 12 + [vp]
     lib.ulk_frame_nodes_from_host.argtypes = [i32, C.POINTER(i32), vp, vp, vp, vp, vp, vp, C.POINTER(PF)]
+    lib.ulk_frame_nodes_to_device.argtypes = [PF, vp, vp, vp, vp, vp, vp]
+    lib.ulk_frame_nodes_from_device.argtypes = [i32, C.POINTER(i32), vp, vp, vp, vp, i64, vp, vp, C.POINTER(PF)]
     lib.ulk_link_frames.argtypes = [PF, PF, vp, C.POINTER(LinkParams), vp, C.POINTER(PL)]
     lib.ulk_links_to_host.argtypes = [PL, vp, vp, vp, vp]
     lib.ulk_links_free.argtypes = [PL]
@@ -103,6 +111,18 @@ def get_lib() -> C.CDLL:
                                "and there is no CPU fallback.")
         _LIB = lib
     return _LIB
+
+
+def profile_report(lib: C.CDLL) -> Dict[str, tuple]:
+    """{kernel name: (launches, total ms)} accumulated since the last ulk_profile_reset."""
+    need = lib.ulk_profile_report(None, 0)
+    buf = C.create_string_buffer(int(need) + 16)
+    lib.ulk_profile_report(buf, len(buf))
+    out = {}
+    for line in buf.value.decode("utf-8", "replace").splitlines():
+        name, cnt, ms = line.rsplit("\t", 2)
+        out[name] = (int(cnt), float(ms))
+    return out
 
 
 class UlkError(RuntimeError):

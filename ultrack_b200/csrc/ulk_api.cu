@@ -23,6 +23,20 @@ int ulk_device_count(void)
 
 int64_t ulk_launch_count(void) { return (int64_t)g_ulk_launches; }
 
+void ulk_profile_enable(int on) { ulk_prof_enable(on); }
+void ulk_profile_reset(void) { ulk_prof_reset(); }
+int ulk_profile_report(char *buf, int64_t cap) { return ulk_prof_report(buf, cap); }
+
+int ulk_set_device(int device)
+{
+#ifndef ULK_EMU
+    ULK_CUDA(cudaSetDevice(device));
+#else
+    (void)device;
+#endif
+    return 0;
+}
+
 int ulk_segment_frame(const void *foreground, int fg_dtype, const void *contours, int ct_dtype,
                       const int64_t shape[3], const ulk_seg_params *params, int keep_labels,
                       void *stream, ulk_frame_nodes **out)
@@ -55,37 +69,65 @@ int ulk_segment_frame_host(const void *foreground, int fg_dtype, const void *con
 
 void ulk_frame_nodes_free(ulk_frame_nodes *nodes) { ulk_frame_nodes_free_impl(nodes); }
 
-int ulk_frame_nodes_to_host(const ulk_frame_nodes *f, int32_t *bbox, int32_t *centroid, int32_t *area,
-                            double *frontier, double *height, int32_t *hier_id, int32_t *parent,
-                            int32_t *hidx, int64_t *mask_off, uint32_t *mask, int32_t *overlaps,
-                            int32_t *labels, void *stream)
+// copies between a node table and caller buffers; `dev` selects device-resident caller
+// buffers (d2d) over host buffers
+static int copy_out(void *dst, const void *src, size_t bytes, ulk_stream_t st, int dev)
+{
+    return dev ? ulk_d2d(dst, src, bytes, st) : ulk_d2h(dst, src, bytes, st);
+}
+static int copy_in(void *dst, const void *src, size_t bytes, ulk_stream_t st, int dev)
+{
+    return dev ? ulk_d2d(dst, src, bytes, st) : ulk_h2d(dst, src, bytes, st);
+}
+
+static int frame_nodes_export(const ulk_frame_nodes *f, int32_t *bbox, int32_t *centroid, int32_t *area,
+                              double *frontier, double *height, int32_t *hier_id, int32_t *parent,
+                              int32_t *hidx, int64_t *mask_off, uint32_t *mask, int32_t *overlaps,
+                              int32_t *labels, void *stream, int dev)
 {
     if (!f) ULK_FAIL(-1, "null argument");
     ulk_stream_t st = (ulk_stream_t)stream;
     i64 n = f->n_nodes;
     if (n > 0) {
-        if (bbox) API_CHK(ulk_d2h(bbox, f->bbox, (size_t)n * 6 * 4, st));
-        if (centroid) API_CHK(ulk_d2h(centroid, f->centroid, (size_t)n * 3 * 4, st));
-        if (area) API_CHK(ulk_d2h(area, f->area, (size_t)n * 4, st));
-        if (frontier) API_CHK(ulk_d2h(frontier, f->frontier, (size_t)n * 8, st));
-        if (height) API_CHK(ulk_d2h(height, f->height, (size_t)n * 8, st));
-        if (hier_id && f->hier_id) API_CHK(ulk_d2h(hier_id, f->hier_id, (size_t)n * 4, st));
-        if (parent && f->parent) API_CHK(ulk_d2h(parent, f->parent, (size_t)n * 4, st));
-        if (hidx && f->hidx) API_CHK(ulk_d2h(hidx, f->hidx, (size_t)n * 4, st));
-        if (mask_off) API_CHK(ulk_d2h(mask_off, f->mask_off, (size_t)(n + 1) * 8, st));
-        if (mask && f->mask_words > 0) API_CHK(ulk_d2h(mask, f->mask, (size_t)f->mask_words * 4, st));
-        if (overlaps && f->n_overlaps > 0) API_CHK(ulk_d2h(overlaps, f->overlaps, (size_t)f->n_overlaps * 2 * 4, st));
+        if (bbox) API_CHK(copy_out(bbox, f->bbox, (size_t)n * 6 * 4, st, dev));
+        if (centroid) API_CHK(copy_out(centroid, f->centroid, (size_t)n * 3 * 4, st, dev));
+        if (area) API_CHK(copy_out(area, f->area, (size_t)n * 4, st, dev));
+        if (frontier && f->frontier) API_CHK(copy_out(frontier, f->frontier, (size_t)n * 8, st, dev));
+        if (height && f->height) API_CHK(copy_out(height, f->height, (size_t)n * 8, st, dev));
+        if (hier_id && f->hier_id) API_CHK(copy_out(hier_id, f->hier_id, (size_t)n * 4, st, dev));
+        if (parent && f->parent) API_CHK(copy_out(parent, f->parent, (size_t)n * 4, st, dev));
+        if (hidx && f->hidx) API_CHK(copy_out(hidx, f->hidx, (size_t)n * 4, st, dev));
+        if (mask_off) API_CHK(copy_out(mask_off, f->mask_off, (size_t)(n + 1) * 8, st, dev));
+        if (mask && f->mask_words > 0) API_CHK(copy_out(mask, f->mask, (size_t)f->mask_words * 4, st, dev));
+        if (overlaps && f->n_overlaps > 0) API_CHK(copy_out(overlaps, f->overlaps, (size_t)f->n_overlaps * 2 * 4, st, dev));
     }
     if (labels && f->labels)
-        API_CHK(ulk_d2h(labels, f->labels, (size_t)f->shape[0] * f->shape[1] * f->shape[2] * 4, st));
-    return 0;
+        API_CHK(copy_out(labels, f->labels, (size_t)f->shape[0] * f->shape[1] * f->shape[2] * 4, st, dev));
+    return ulk_sync(st);
 }
 
-int ulk_frame_nodes_from_host(int32_t n_nodes, const int32_t shape[3], const int32_t *bbox,
-                              const int32_t *centroid, const int32_t *area, const int64_t *mask_off,
-                              const uint32_t *mask, void *stream, ulk_frame_nodes **out)
+int ulk_frame_nodes_to_host(const ulk_frame_nodes *f, int32_t *bbox, int32_t *centroid, int32_t *area,
+                            double *frontier, double *height, int32_t *hier_id, int32_t *parent,
+                            int32_t *hidx, int64_t *mask_off, uint32_t *mask, int32_t *overlaps,
+                            int32_t *labels, void *stream)
 {
-    if (!shape || !out || n_nodes < 0) ULK_FAIL(-1, "bad argument");
+    return frame_nodes_export(f, bbox, centroid, area, frontier, height, hier_id, parent, hidx, mask_off, mask,
+                              overlaps, labels, stream, 0);
+}
+
+int ulk_frame_nodes_to_device(const ulk_frame_nodes *f, int32_t *bbox, int32_t *centroid, int32_t *area,
+                              int64_t *mask_off, uint32_t *mask, void *stream)
+{
+    return frame_nodes_export(f, bbox, centroid, area, nullptr, nullptr, nullptr, nullptr, nullptr, mask_off, mask,
+                              nullptr, nullptr, stream, 1);
+}
+
+static int frame_nodes_import(int32_t n_nodes, const int32_t shape[3], const int32_t *bbox,
+                              const int32_t *centroid, const int32_t *area, const int64_t *mask_off,
+                              int64_t words, const uint32_t *mask, void *stream, int dev, ulk_frame_nodes **out)
+{
+    if (!shape || !out || n_nodes < 0 || words < 0) ULK_FAIL(-1, "bad argument");
+    if (n_nodes > 0 && (!bbox || !centroid || !area || !mask_off || (words > 0 && !mask))) ULK_FAIL(-1, "null argument");
     ulk_stream_t st = (ulk_stream_t)stream;
     ulk_set_alloc_stream(st);
     ulk_frame_nodes *F = new ulk_frame_nodes();
@@ -95,7 +137,6 @@ int ulk_frame_nodes_from_host(int32_t n_nodes, const int32_t shape[3], const int
     for (int d = 0; d < 3; ++d) F->shape[d] = shape[d];
     if (n_nodes == 0) return 0;
     i64 n = n_nodes;
-    i64 words = mask_off[n];
     F->mask_words = words;
     void *p;
     int rc = 0;
@@ -105,13 +146,29 @@ int ulk_frame_nodes_from_host(int32_t n_nodes, const int32_t shape[3], const int
     rc |= ulk_dev_alloc(&p, (size_t)(n + 1) * 8); F->mask_off = (i64 *)p;
     rc |= ulk_dev_alloc(&p, (size_t)(words > 0 ? words : 1) * 4); F->mask = (u32 *)p;
     if (rc) { ulk_frame_nodes_free_impl(F); *out = nullptr; ULK_FAIL(-3, "device allocation failed"); }
-    API_CHK(ulk_h2d(F->bbox, bbox, (size_t)n * 6 * 4, st));
-    API_CHK(ulk_h2d(F->centroid, centroid, (size_t)n * 3 * 4, st));
-    API_CHK(ulk_h2d(F->area, area, (size_t)n * 4, st));
-    API_CHK(ulk_h2d(F->mask_off, mask_off, (size_t)(n + 1) * 8, st));
-    if (words > 0) API_CHK(ulk_h2d(F->mask, mask, (size_t)words * 4, st));
+    API_CHK(copy_in(F->bbox, bbox, (size_t)n * 6 * 4, st, dev));
+    API_CHK(copy_in(F->centroid, centroid, (size_t)n * 3 * 4, st, dev));
+    API_CHK(copy_in(F->area, area, (size_t)n * 4, st, dev));
+    API_CHK(copy_in(F->mask_off, mask_off, (size_t)(n + 1) * 8, st, dev));
+    if (words > 0) API_CHK(copy_in(F->mask, mask, (size_t)words * 4, st, dev));
     API_CHK(ulk_sync(st));
     return 0;
+}
+
+int ulk_frame_nodes_from_host(int32_t n_nodes, const int32_t shape[3], const int32_t *bbox,
+                              const int32_t *centroid, const int32_t *area, const int64_t *mask_off,
+                              const uint32_t *mask, void *stream, ulk_frame_nodes **out)
+{
+    if (n_nodes > 0 && !mask_off) ULK_FAIL(-1, "null argument");
+    return frame_nodes_import(n_nodes, shape, bbox, centroid, area, mask_off, n_nodes > 0 ? mask_off[n_nodes] : 0,
+                              mask, stream, 0, out);
+}
+
+int ulk_frame_nodes_from_device(int32_t n_nodes, const int32_t shape[3], const int32_t *bbox,
+                                const int32_t *centroid, const int32_t *area, const int64_t *mask_off,
+                                int64_t mask_words, const uint32_t *mask, void *stream, ulk_frame_nodes **out)
+{
+    return frame_nodes_import(n_nodes, shape, bbox, centroid, area, mask_off, mask_words, mask, stream, 1, out);
 }
 
 int ulk_link_frames(const ulk_frame_nodes *src, const ulk_frame_nodes *dst, const double *dst_shift_host,

@@ -2,6 +2,7 @@
 #include "ulk_rt.h"
 #include <cstdarg>
 #include <string>
+#include <utility>
 
 static thread_local std::string g_err;
 long long g_ulk_launches = 0;
@@ -19,6 +20,9 @@ const char *ulk_error_cstr() { return g_err.c_str(); }
 
 #ifdef ULK_EMU
 // ------------------------------------------------------------------ host emulation
+void ulk_prof_enable(int) {}
+void ulk_prof_reset() {}
+int ulk_prof_report(char *buf, i64 cap) { if (buf && cap > 0) buf[0] = 0; return 1; }
 void ulk_set_alloc_stream(ulk_stream_t) {}
 int ulk_dev_alloc(void **p, size_t bytes) { *p = malloc(bytes ? bytes : 1); return *p ? 0 : -3; }
 void ulk_dev_free(void *p) { free(p); }
@@ -57,6 +61,69 @@ int ulk_sort_pairs_u32(const u32 *ki, u32 *ko, const u32 *vi, u32 *vo, i64 n, ul
 
 #else
 // ------------------------------------------------------------------ CUDA
+// per-kernel timing: one event pair per launch, resolved when the report is read
+#include <cxxabi.h>
+#include <map>
+#include <vector>
+bool g_ulk_prof_on = false;
+struct ProfRec { const char *name; cudaEvent_t a, b; };
+static std::vector<ProfRec> g_prof_recs;
+static std::vector<cudaEvent_t> g_prof_free;
+static std::map<std::string, std::pair<long long, double>> g_prof_acc;
+static cudaEvent_t prof_event()
+{
+    if (!g_prof_free.empty()) { cudaEvent_t e = g_prof_free.back(); g_prof_free.pop_back(); return e; }
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    return e;
+}
+static void prof_drain()
+{
+    for (auto &r : g_prof_recs) {
+        cudaEventSynchronize(r.b);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, r.a, r.b);
+        auto &acc = g_prof_acc[r.name];
+        acc.first += 1;
+        acc.second += ms;
+        g_prof_free.push_back(r.a);
+        g_prof_free.push_back(r.b);
+    }
+    g_prof_recs.clear();
+}
+void ulk_prof_begin(const char *name, ulk_stream_t s)
+{
+    ProfRec r{name, prof_event(), prof_event()};
+    cudaEventRecord(r.a, s);
+    g_prof_recs.push_back(r);
+}
+void ulk_prof_end(ulk_stream_t s)
+{
+    cudaEventRecord(g_prof_recs.back().b, s);
+    if (g_prof_recs.size() >= 4096) prof_drain();
+}
+void ulk_prof_enable(int on) { g_ulk_prof_on = on != 0; }
+void ulk_prof_reset() { prof_drain(); g_prof_acc.clear(); }
+int ulk_prof_report(char *buf, i64 cap)
+{
+    prof_drain();
+    std::string out;
+    for (auto &kv : g_prof_acc) {
+        int status = 0;
+        char *dem = abi::__cxa_demangle(kv.first.c_str(), nullptr, nullptr, &status);
+        char line[512];
+        snprintf(line, sizeof(line), "%s\t%lld\t%.6f\n", status == 0 && dem ? dem : kv.first.c_str(), kv.second.first, kv.second.second);
+        free(dem);
+        out += line;
+    }
+    if (buf && cap > 0) { size_t n = out.size() < (size_t)cap - 1 ? out.size() : (size_t)cap - 1; memcpy(buf, out.data(), n); buf[n] = 0; }
+    return (int)out.size() + 1;
+}
+struct ProfScope {
+    ulk_stream_t s; bool on;
+    ProfScope(const char *name, ulk_stream_t st) : s(st), on(g_ulk_prof_on) { if (on) ulk_prof_begin(name, s); }
+    ~ProfScope() { if (on) ulk_prof_end(s); }
+};
 // stream-ordered allocator: frame-scoped buffers come from the default memory pool, whose
 // release threshold is raised so that freed blocks stay cached between frames
 static cudaStream_t g_alloc_stream = 0;
@@ -81,7 +148,12 @@ int ulk_dev_alloc(void **p, size_t bytes)
     return 0;
 }
 void ulk_dev_free(void *p) { if (p) cudaFreeAsync(p, g_alloc_stream); }
-int ulk_memset(void *p, int byte, size_t bytes, ulk_stream_t s) { ULK_CUDA(cudaMemsetAsync(p, byte, bytes, s)); return 0; }
+int ulk_memset(void *p, int byte, size_t bytes, ulk_stream_t s)
+{
+    ProfScope ps("cudaMemsetAsync", s);
+    ULK_CUDA(cudaMemsetAsync(p, byte, bytes, s));
+    return 0;
+}
 int ulk_d2h(void *dst, const void *src, size_t bytes, ulk_stream_t s)
 {
     ULK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s));
@@ -89,7 +161,12 @@ int ulk_d2h(void *dst, const void *src, size_t bytes, ulk_stream_t s)
     return 0;
 }
 int ulk_h2d(void *dst, const void *src, size_t bytes, ulk_stream_t s) { ULK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s)); return 0; }
-int ulk_d2d(void *dst, const void *src, size_t bytes, ulk_stream_t s) { ULK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, s)); return 0; }
+int ulk_d2d(void *dst, const void *src, size_t bytes, ulk_stream_t s)
+{
+    ProfScope ps("cudaMemcpyAsync(d2d)", s);
+    ULK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, s));
+    return 0;
+}
 int ulk_sync(ulk_stream_t s) { ULK_CUDA(cudaStreamSynchronize(s)); return 0; }
 
 // CUB temp storage: one growable scratch buffer per process (calls are stream-ordered
@@ -110,6 +187,7 @@ int ulk_exclusive_scan_i32(const i32 *in, i32 *out, i64 n, ulk_stream_t s)
     size_t need = 0;
     ULK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, need, in, out, (int)n, s));
     if (cub_tmp(need)) return -2;
+    ProfScope ps("cub::DeviceScan::ExclusiveSum", s);
     ULK_CUDA(cub::DeviceScan::ExclusiveSum(g_cub_tmp, need, in, out, (int)n, s));
     ++g_ulk_launches;
     return 0;
@@ -120,6 +198,7 @@ int ulk_exclusive_scan_i64(const i64 *in, i64 *out, i64 n, ulk_stream_t s)
     size_t need = 0;
     ULK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, need, in, out, (int)n, s));
     if (cub_tmp(need)) return -2;
+    ProfScope ps("cub::DeviceScan::ExclusiveSum", s);
     ULK_CUDA(cub::DeviceScan::ExclusiveSum(g_cub_tmp, need, in, out, (int)n, s));
     ++g_ulk_launches;
     return 0;
@@ -130,6 +209,7 @@ int ulk_sort_pairs_u64(const u64 *ki, u64 *ko, const u32 *vi, u32 *vo, i64 n, ul
     size_t need = 0;
     ULK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, need, ki, ko, vi, vo, (int)n, 0, 64, s));
     if (cub_tmp(need)) return -2;
+    ProfScope ps("cub::DeviceRadixSort::SortPairs", s);
     ULK_CUDA(cub::DeviceRadixSort::SortPairs(g_cub_tmp, need, ki, ko, vi, vo, (int)n, 0, 64, s));
     ++g_ulk_launches;
     return 0;
@@ -140,6 +220,7 @@ int ulk_sort_pairs_u32(const u32 *ki, u32 *ko, const u32 *vi, u32 *vo, i64 n, ul
     size_t need = 0;
     ULK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, need, ki, ko, vi, vo, (int)n, 0, 32, s));
     if (cub_tmp(need)) return -2;
+    ProfScope ps("cub::DeviceRadixSort::SortPairs", s);
     ULK_CUDA(cub::DeviceRadixSort::SortPairs(g_cub_tmp, need, ki, ko, vi, vo, (int)n, 0, 32, s));
     ++g_ulk_launches;
     return 0;

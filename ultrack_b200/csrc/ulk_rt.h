@@ -27,6 +27,7 @@ typedef void *ulk_stream_t;
 #else
 #include <cuda_runtime.h>
 #include <cub/cub.cuh>
+#include <typeinfo>
 #define ULK_HD __host__ __device__
 #define ULK_D __device__
 #define ULK_INLINE __forceinline__
@@ -97,14 +98,23 @@ template <class F> __global__ void __launch_bounds__(256) ulk_kernel(i64 n, F f)
     if (i < n) f(i);
 }
 extern long long g_ulk_launches;
+// optional per-kernel timing (CUDA events on the launching stream), see ulk_profile_* in the C ABI
+extern bool g_ulk_prof_on;
+void ulk_prof_begin(const char *name, ulk_stream_t s);
+void ulk_prof_end(ulk_stream_t s);
 template <class F> void ulk_launch(i64 n, ulk_stream_t s, const F &f)
 {
     if (n <= 0) return;
     i64 grid = (n + 255) / 256;
+    if (g_ulk_prof_on) ulk_prof_begin(typeid(F).name(), s);
     ulk_kernel<F><<<(unsigned)grid, 256, 0, s>>>(n, f);
+    if (g_ulk_prof_on) ulk_prof_end(s);
     ++g_ulk_launches;
 }
 #endif
+int ulk_prof_report(char *buf, i64 cap);   // "name\tlaunches\ttotal_ms\n" per kernel; returns bytes needed
+void ulk_prof_enable(int on);
+void ulk_prof_reset();
 
 // ---------------------------------------------------------------- memory
 struct UlkArena;  // growable pool of device buffers, see ulk_rt.cu

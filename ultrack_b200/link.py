@@ -1,0 +1,153 @@
+"""`link()` -- drop-in for ultrack.core.linking.processing.link.
+
+Same signature, config fields and `links` rows as the reference
+(ultrack/core/linking/processing.py:107-338); per frame pair the body of
+`compute_spatial_neighbors` (KD-tree k-NN, mask IoU, top-k) is one call of the CUDA
+library (`ulk_link_frames`) on device-resident node tables.  Frame pairs are sharded by
+source timepoint across the ranks of the default torch.distributed group; the one table a
+rank does not own -- the first frame of the next rank's block -- is received from that
+rank over NCCL (frames.send_frame / recv_frame).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import logging
+import warnings
+from typing import Optional, Sequence, Tuple
+
+import numpy as np
+
+from ultrack_b200 import _lib, database, frames, sharding
+
+LOG = logging.getLogger(__name__)
+
+
+def link_params(config, scale: Optional[Sequence[float]], ndim: int) -> _lib.LinkParams:
+    """LinkingConfig (+ scale) -> ulk_link_params; `scale[-ndim:]` as in processing.py:215-219."""
+    sc = [1.0, 1.0, 1.0]
+    if scale is not None:
+        m = min(ndim, len(scale))
+        if m < ndim:
+            raise ValueError(f"`scale` must cover the {ndim} spatial axes, found {scale}")
+        sc[3 - m:] = [float(v) for v in list(scale)[-m:]]
+    return _lib.LinkParams(float(config.max_distance), float(config.distance_weight), int(config.max_neighbors),
+                           int(scale is not None), (C.c_double * 3)(*sc))
+
+
+def link_frames_device(lib, src: frames.DeviceFrame, dst: frames.DeviceFrame, prm: _lib.LinkParams,
+                       shift: Optional[np.ndarray] = None, stream: int = 0) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+    """One `ulk_link_frames` call -> (weight, source_id, target_id) rows."""
+    out = C.POINTER(_lib.Links)()
+    sh = None
+    if shift is not None:
+        shift = np.array(shift, dtype=np.float64, order="C")
+        if dst.ndim == 2:
+            shift[:, 0] = 0.0      # `target_shift[:, -n_dim:]` (processing.py:212): no z axis in 2-D
+        sh = shift.ctypes.data_as(C.c_void_p)
+    _lib.check(lib, lib.ulk_link_frames(src.handle, dst.handle, sh, C.byref(prm), C.c_void_p(stream), C.byref(out)))
+    try:
+        n = int(out.contents.n_links)
+        s = np.zeros(n, np.int32)
+        t = np.zeros(n, np.int32)
+        w = np.zeros(n, np.float64)
+        p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+        _lib.check(lib, lib.ulk_links_to_host(out, p(s), p(t), p(w), C.c_void_p(stream)))
+    finally:
+        lib.ulk_links_free(out)
+    return w, src.ids[s], dst.ids[t]
+
+
+def _frame(lib, db: str, t: int, shape3, ndim: int) -> Optional[frames.DeviceFrame]:
+    f = frames.STORE.get(db, t)
+    if f is None:
+        f, _ = frames.frame_from_database(lib, db, t, shape3, ndim)
+        if f is not None:
+            frames.STORE.put(db, t, f)
+    return f
+
+
+def _process(time: int, config, db_path: str, scale, lib, shape3, ndim: int,
+             next_frame: Optional[frames.DeviceFrame] = None) -> None:
+    """linking/processing.py:107-169 + 172-291 for the pair (time, time + 1)."""
+    src = _frame(lib, db_path, time, shape3, ndim)
+    dst = next_frame if next_frame is not None else _frame(lib, db_path, time + 1, shape3, ndim)
+    if dst is None or dst.n_nodes == 0:
+        print(f"No nodes found for time {time + 1}")
+        warnings.warn(f"No segments found at target t={time + 1}; skipping linking from t={time}.",
+                      RuntimeWarning, stacklevel=2)
+        return
+    if src is None or src.n_nodes == 0:
+        print(f"No nodes found for time {time}")
+        warnings.warn(f"No segments found at source t={time}; skipping linking to t={time + 1}.",
+                      RuntimeWarning, stacklevel=2)
+        return
+    shift = frames.load_shifts(db_path, time + 1, dst.n_nodes)
+    prm = link_params(config, scale, ndim)
+    weight, source_id, target_id = link_frames_device(lib, src, dst, prm, shift)
+    if len(weight) == 0:
+        LOG.warning(f"No links found for time {time}. Increase `linking_config.max_distance` parameter.")
+        return
+    LOG.info(f"Pushing links from time {time} to {db_path}")
+    database.insert_links(db_path, weight, source_id, target_id)
+
+
+def link(
+    config,
+    images: Sequence = tuple(),
+    scale: Optional[Sequence[float]] = None,
+    batch_index: Optional[int] = None,
+    overwrite: bool = False,
+) -> None:
+    """Links candidate segments (nodes) with their neighbors on the next time.
+
+    Parameters are those of ultrack.link (linking/processing.py:294-318).  The optional colour
+    z-score filter (`images`, processing.py:52-104) is outside the accelerated path and raises.
+    """
+    LOG.info(f"Linking nodes with LinkingConfig:\n{config.linking_config}")
+    if len(images) > 0:
+        raise NotImplementedError("colour-space filtering (`images`) is not implemented by ultrack_b200")
+    lib = _lib.get_lib()
+    rank, world = sharding.dist_info()
+    if world > 1:
+        _lib.check(lib, lib.ulk_set_device(sharding.local_rank()))
+    db_path = config.data_config.database_path
+    max_t = database.maximum_time_from_database(db_path)
+    time_points = sharding.batch_index_range(max_t, config.linking_config.n_workers, batch_index)
+    LOG.info(f"Linking time points {time_points}")
+    if overwrite and (batch_index is None or batch_index == 0) and rank == 0:
+        database.clear_linking_data(db_path)
+    sharding.barrier()
+    shape = config.data_config.metadata.get("shape")
+    if shape is None:
+        raise ValueError(f"`shape` missing from {config.data_config.metadata_path}; run segment() first")
+    ndim = len(shape) - 1
+    shape3 = tuple(shape[1:]) if ndim == 3 else (1,) + tuple(shape[1:])
+
+    mine = sharding.shard(time_points, world, rank)
+    boundary = None
+    if world > 1:
+        boundary = _exchange_boundary(lib, db_path, time_points, world, rank, shape3, ndim)
+    for time in mine:
+        nxt = boundary if (boundary is not None and time == mine[-1]) else None
+        _process(time, config.linking_config, db_path, scale, lib, shape3, ndim, next_frame=nxt)
+    sharding.barrier()
+
+
+def _exchange_boundary(lib, db_path: str, time_points: Sequence[int], world: int, rank: int, shape3, ndim: int):
+    """Every rank with a non-empty block needs the target frame of its last pair; when that
+    frame is the first source frame of a later rank's block that rank sends it.  All ranks walk
+    the same schedule, so sends and receives pair up without a handshake."""
+    n = len(time_points)
+    received = None
+    for r in range(world):
+        lo, hi = sharding.block_bounds(n, world, r)
+        if lo == hi or hi >= n:
+            continue  # empty block, or the last pair's target lies past every source block
+        sender = sharding.owner_of(hi, n, world)
+        if sender == r:
+            continue
+        if rank == sender:
+            frames.send_frame(_frame(lib, db_path, time_points[hi], shape3, ndim), r)
+        elif rank == r:
+            received = frames.recv_frame(lib, sender)
+    return received

@@ -1,0 +1,231 @@
+"""`segment()` -- drop-in for ultrack.core.segmentation.processing.segment.
+
+Same signature, config fields, SQL rows and side file as the reference
+(ultrack/core/segmentation/processing.py:160-340,393-488); per timepoint the body of
+`_process` (threshold, create_hierarchies, Hierarchy.nodes, ids, overlaps) is one call of
+the CUDA library (`ulk_segment_frame`).  Timepoints are sharded across the ranks of the
+default torch.distributed group when one exists (one process per GPU).
+There is no CPU path: the call raises when the CUDA library or a GPU is missing.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import logging
+import os
+import sqlite3
+import warnings
+from typing import Dict, List, Optional
+
+import numpy as np
+
+from ultrack_b200 import _lib, database, frames, sharding
+from ultrack_b200.config import ws_hierarchy_name
+from ultrack_b200.node import dumps_node
+
+LOG = logging.getLogger(__name__)
+
+
+def rename_argument(from_name: str, to_name: str):
+    """ultrack/utils/deprecation.py: keeps `detection=` / `edge=` working."""
+    from functools import wraps
+
+    def _wrapper(func):
+        @wraps(func)
+        def _update_from_dict(*args, **kwargs):
+            if from_name in kwargs:
+                if to_name in kwargs:
+                    raise ValueError(f"Argument {to_name} already defined, please do not mix {from_name} and {to_name} in one call.")
+                warnings.warn(f"Argument {from_name} is deprecated, please use {to_name} instead.",
+                              category=DeprecationWarning, stacklevel=2)
+                kwargs = kwargs.copy()
+                kwargs[to_name] = kwargs.pop(from_name)
+            return func(*args, **kwargs)
+
+        return _update_from_dict
+
+    return _wrapper
+
+
+def check_array_chunk(array) -> None:
+    """ultrack/utils/array.py:85-96."""
+    if hasattr(array, "chunks") and array.chunks is not None:
+        chunk_shape = array.chunks
+        if isinstance(chunk_shape[0], tuple):
+            chunk_shape = chunk_shape[0]
+        if chunk_shape[0] != 1:
+            warnings.warn(f"Array not chunked over time dimension. Found chunk of shape {array.chunks}."
+                          "Performance will be slower.")
+
+
+def _generate_id(index, time: int, max_segments: int):
+    """processing.py:42-59."""
+    return index + (time + 1) * max_segments
+
+
+def seg_params(config, fg_dtype) -> _lib.SegParams:
+    """SegmentationConfig -> ulk_seg_params.  numpy evaluates `foreground > threshold` in the
+    array's own float precision (processing.py:212), so the threshold is rounded to it here."""
+    thr = float(config.threshold)
+    dt = np.dtype(fg_dtype)
+    if np.issubdtype(dt, np.floating):
+        thr = float(dt.type(thr))
+    name = ws_hierarchy_name(config.ws_hierarchy)
+    if name not in _lib.WS_HIERARCHY_CODES:
+        raise NotImplementedError(f"ws_hierarchy={name!r} is not implemented by the CUDA library")
+    return _lib.SegParams(thr, float(config.min_area), float(config.max_area), float(config.min_area_factor),
+                          float(config.min_frontier), _lib.WS_HIERARCHY_CODES[name], 0)
+
+
+def _is_cuda_tensor(a) -> bool:
+    return type(a).__module__.startswith("torch") and getattr(a, "is_cuda", False)
+
+
+def segment_frame_device(lib, fg, ct, prm: _lib.SegParams, keep_labels: bool = False, stream: int = 0):
+    """One `ulk_segment_frame*` call.  `fg` / `ct`: one frame, numpy (host) or torch CUDA tensors."""
+    if tuple(fg.shape) != tuple(ct.shape):
+        raise ValueError(f"`foreground` and `contours` shape must match. Found {fg.shape} and {ct.shape}")
+    if fg.ndim not in (2, 3):
+        raise ValueError(f"frames must be 2-D or 3-D, found shape {fg.shape}")
+    shape3 = tuple(fg.shape) if fg.ndim == 3 else (1,) + tuple(fg.shape)
+    shp = (C.c_int64 * 3)(*shape3)
+    handle = C.POINTER(_lib.FrameNodes)()
+    if _is_cuda_tensor(fg) and _is_cuda_tensor(ct):
+        import torch
+
+        fg, ct = fg.contiguous(), ct.contiguous()
+        np_dt = lambda t: np.dtype(str(t.dtype).replace("torch.", "")) if t.dtype != torch.bool else np.dtype(bool)  # noqa: E731
+        rc = lib.ulk_segment_frame(C.c_void_p(fg.data_ptr()), _lib.dtype_code(np_dt(fg)),
+                                   C.c_void_p(ct.data_ptr()), _lib.dtype_code(np_dt(ct)),
+                                   shp, C.byref(prm), int(keep_labels), C.c_void_p(stream), C.byref(handle))
+    else:
+        fg = np.ascontiguousarray(fg)
+        ct = np.ascontiguousarray(ct)
+        rc = lib.ulk_segment_frame_host(fg.ctypes.data_as(C.c_void_p), _lib.dtype_code(fg.dtype),
+                                        ct.ctypes.data_as(C.c_void_p), _lib.dtype_code(ct.dtype),
+                                        shp, C.byref(prm), int(keep_labels), C.c_void_p(stream), C.byref(handle))
+    _lib.check(lib, rc)
+    return handle
+
+
+def frame_rows(nodes: Dict[str, np.ndarray], time: int, ndim: int, max_segments_per_time: int):
+    """Node table -> (`nodes` rows, `overlaps` rows) exactly as _process emits them
+    (processing.py:235-300)."""
+    n = len(nodes["area"])
+    if n > max_segments_per_time:
+        raise ValueError(f"Number of segments exceeds upper bound of {max_segments_per_time} per time.")
+    index = np.arange(1, n + 1, dtype=np.int64)
+    ids = _generate_id(index, time, max_segments_per_time)
+    parent = nodes["parent"]
+    hier_parent = np.where(parent >= 0, _generate_id(parent.astype(np.int64) + 1, time, max_segments_per_time),
+                           database.NO_PARENT)
+    rows = []
+    lo = 3 - ndim
+    for i in range(n):
+        bb = nodes["bbox"][i].astype(np.int64)
+        bbox = np.concatenate([bb[lo:3], bb[3 + lo:]])
+        cen3 = nodes["centroid"][i]
+        centroid = cen3[lo:].astype(np.int64)
+        mask = _lib.unpack_mask(nodes, i, ndim)
+        blob = dumps_node(int(nodes["hidx"][i]), int(ids[i]), time, int(nodes["area"][i]),
+                          float(nodes["frontier"][i]), float(nodes["height"][i]), bbox, mask, centroid)
+        z = int(cen3[0]) if ndim == 3 else 0
+        rows.append(database.node_row(time, int(ids[i]), int(index[i]), int(nodes["hier_id"][i]), z,
+                                      int(cen3[1]), int(cen3[2]), int(nodes["area"][i]),
+                                      float(nodes["frontier"][i]), float(nodes["height"][i]), blob,
+                                      hier_parent_id=int(hier_parent[i])))
+    ov = nodes["overlaps"].astype(np.int64)
+    overlaps = [(int(a), int(b)) for a, b in zip(_generate_id(ov[:, 0] + 1, time, max_segments_per_time),
+                                                 _generate_id(ov[:, 1] + 1, time, max_segments_per_time))]
+    return ids, rows, overlaps
+
+
+def _process(time: int, foreground, contours, config, db_path: str, max_segments_per_time: int,
+             catch_duplicates_expection: bool, lib) -> None:
+    """processing.py:160-340 for one timepoint."""
+    if config.random_seed == "frame":
+        np.random.seed(time)
+    fg = foreground[time]
+    edge_map = contours[time]
+    if config.max_noise > 0:
+        # the reference draws from numpy's legacy global RNG seeded with the frame number
+        # (processing.py:201-209); replayed on the host so the result stays bit-identical
+        edge_map = np.asarray(edge_map.cpu() if _is_cuda_tensor(edge_map) else edge_map)
+        noise = np.random.uniform(0, config.max_noise, size=edge_map.shape)
+        noise = noise.astype(np.result_type(edge_map.dtype, np.float16))
+        edge_map = edge_map + noise
+        if _is_cuda_tensor(fg):
+            fg = np.asarray(fg.cpu())
+    if not (_is_cuda_tensor(fg) and _is_cuda_tensor(edge_map)):
+        fg, edge_map = np.asarray(fg), np.asarray(edge_map)
+    ndim = fg.ndim
+    prm = seg_params(config, np.dtype(bool) if str(fg.dtype).endswith("bool") else str(fg.dtype).replace("torch.", ""))
+    handle = segment_frame_device(lib, fg, edge_map, prm)
+    LOG.info(f"Computing nodes of time {time}")
+    try:
+        nodes = _lib.nodes_to_host(lib, handle)
+        ids, rows, overlaps = frame_rows(nodes, time, ndim, max_segments_per_time)
+    except Exception:
+        lib.ulk_frame_nodes_free(handle)
+        raise
+    frames.STORE.put(db_path, time, frames.DeviceFrame(lib, handle, ids, ndim))
+    try:
+        database.insert_nodes(db_path, rows, overlaps)
+    except sqlite3.IntegrityError as e:
+        frames.STORE.drop(db_path, time)
+        if catch_duplicates_expection:
+            LOG.warning(f"IntegrityError: {e}\nSkipping batch {time}.\n"
+                        "Cannot guarantee image was entirely processed.\nSEGMENTS MIGHT BE MISSING!")
+            return
+        raise ValueError("Duplicated nodes found. Set `overwrite=True` to overwrite existing data.") from e
+    LOG.info(f"DONE with time {time}.")
+
+
+@rename_argument("detection", "foreground")
+@rename_argument("edge", "contours")
+def segment(
+    foreground,
+    contours,
+    config,
+    max_segments_per_time: int = 1_000_000,
+    batch_index: Optional[int] = None,
+    overwrite: bool = False,
+    insertion_throttle_rate: int = 50,
+    images=None,
+    properties: Optional[List[str]] = None,
+) -> None:
+    """Add candidate segmentation (nodes) from `foreground` and `contours` to database.
+
+    Parameters are those of ultrack.segment (processing.py:393-430).  `insertion_throttle_rate`
+    is accepted and unused: rows are inserted once per frame.  `properties` (skimage
+    regionprops features, processing.py:107-157) are outside the accelerated path and raise.
+    """
+    LOG.info(f"Adding nodes with SegmentationConfig:\n{config.segmentation_config}")
+    if tuple(foreground.shape) != tuple(contours.shape):
+        raise ValueError(f"`foreground` and `contours` shape must match. Found {foreground.shape} and {contours.shape}")
+    if properties is not None:
+        raise NotImplementedError("`properties` (skimage regionprops features) are not computed by ultrack_b200")
+    check_array_chunk(foreground)
+    check_array_chunk(contours)
+
+    lib = _lib.get_lib()
+    rank, world = sharding.dist_info()
+    if world > 1:
+        _lib.check(lib, lib.ulk_set_device(sharding.local_rank()))
+    length = foreground.shape[0]
+    time_points = sharding.batch_index_range(length, config.segmentation_config.n_workers, batch_index)
+    LOG.info(f"Segmenting time points {time_points}")
+    db_path = config.data_config.database_path
+    batch_start_index = int(os.getenv("ULTRACK_BATCH_INDEX_START", "0"))
+    if rank == 0 and (batch_index is None or batch_index == batch_start_index):
+        if overwrite:
+            database.clear_all_data(db_path)
+        database.create_all(db_path)
+        # `properties` is None on this path and toml drops None values (processing.py:460-467)
+        config.data_config.metadata_add({"shape": [int(s) for s in foreground.shape]})
+    if overwrite:
+        frames.STORE.clear(db_path)
+    sharding.barrier()
+    for time in sharding.shard(time_points, world, rank):
+        _process(time, foreground, contours, config.segmentation_config, db_path, max_segments_per_time,
+                 batch_index is not None, lib)
+    sharding.barrier()

@@ -42,28 +42,39 @@ def cell_fields(shape: Tuple[int, ...], t: int = 0, seed: int = 0, radius: float
     ndim = len(shape)
     unit = np.pi if ndim == 2 else 4.0 / 3.0 * np.pi
     pitch = radius * (unit / fill) ** (1.0 / ndim)
-    grids = np.meshgrid(*[np.arange(s, dtype=np.float64) for s in shape], indexing="ij")
-    cell = [np.floor(g / pitch).astype(np.int64) for g in grids]
+    ncell = [int(np.ceil(s / pitch)) + 2 for s in shape]
+    # per-cell centre and radius on the (small) cell lattice, gathered per voxel below
+    cell_idx = np.meshgrid(*[np.arange(-1, n - 1, dtype=np.int64) for n in ncell], indexing="ij")
+    cid_cell = np.zeros(cell_idx[0].shape, dtype=np.int64)
+    for a in range(ndim):
+        cid_cell = cid_cell * ncell[a] + (cell_idx[a] + 1)
+    centre = []
+    for a in range(ndim):
+        jit = (_hash_u01(seed, cid_cell, 17 + a) - 0.5) * 0.5 * pitch
+        mov = (_hash_u01(seed, cid_cell, 101 + a, t) - 0.5) * 2.0 * motion if motion > 0 else 0.0
+        centre.append(((cell_idx[a] + 0.5) * pitch + jit + mov).ravel())
+    u1 = _hash_u01(seed, cid_cell, 7)
+    u2 = _hash_u01(seed, cid_cell, 8)
+    g = np.sqrt(-2.0 * np.log(np.maximum(u1, 1e-12))) * np.cos(2 * np.pi * u2)
+    rad = np.clip(radius * (1.0 + 0.15 * g), 0.6 * radius, 1.4 * radius).ravel()
+
+    axes = [np.arange(s, dtype=np.float64) for s in shape]
+    cell = [np.floor(ax / pitch).astype(np.int64) for ax in axes]
     s1 = np.full(shape, np.inf)
     s2 = np.full(shape, np.inf)
     lab = np.zeros(shape, dtype=np.int64)
-    ncell = [int(np.ceil(s / pitch)) + 2 for s in shape]
     for off in itertools.product((-1, 0, 1), repeat=ndim):
-        c = [cell[a] + off[a] for a in range(ndim)]
         cid = np.zeros(shape, dtype=np.int64)
         for a in range(ndim):
-            cid = cid * ncell[a] + (c[a] + 1)
+            sl = [None] * ndim
+            sl[a] = slice(None)
+            cid = cid * ncell[a] + (cell[a] + off[a] + 1)[tuple(sl)]
         d2 = np.zeros(shape)
         for a in range(ndim):
-            jit = (_hash_u01(seed, cid, 17 + a) - 0.5) * 0.5 * pitch
-            mov = (_hash_u01(seed, cid, 101 + a, t) - 0.5) * 2.0 * motion if motion > 0 else 0.0
-            ctr = (c[a] + 0.5) * pitch + jit + mov
-            d2 += (grids[a] - ctr) ** 2
-        u1 = _hash_u01(seed, cid, 7)
-        u2 = _hash_u01(seed, cid, 8)
-        g = np.sqrt(-2.0 * np.log(np.maximum(u1, 1e-12))) * np.cos(2 * np.pi * u2)
-        r = np.clip(radius * (1.0 + 0.15 * g), 0.6 * radius, 1.4 * radius)
-        s = np.sqrt(d2) / r
+            sl = [None] * ndim
+            sl[a] = slice(None)
+            d2 += (axes[a][tuple(sl)] - centre[a][cid]) ** 2
+        s = np.sqrt(d2) / rad[cid]
         closer = s < s1
         s2 = np.where(closer, s1, np.minimum(s2, s))
         lab = np.where(closer, cid + 1, lab)
