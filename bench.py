@@ -100,6 +100,12 @@ def _cpu_frame(args):
     return out[1][1] + t_link, 0 if links is None else len(links)
 
 
+def _ws_stats(lib):
+    out = (C.c_int64 * 3)()
+    lib.ulk_workspace_stats(out)
+    return [int(v) for v in out]
+
+
 def cpu_sample_shape(shape):
     """Bounded sample of the workload for the CPU arm: a sub-volume of the same synthetic recipe."""
     if shape[0] == 1:
@@ -336,6 +342,7 @@ def main():
                    "parallelism": f"timepoint shards x{world}", "frame_stats": stats},
         "links_per_sec": float(cnt[0]) / (ms_max * 1e-3),
         "gpu_launches": int(launches),
+        "workspace_bytes": dict(zip(("slab", "peak_in_use", "outside_slab"), _ws_stats(lib))),
         "clocks": clk,
         "roofline": roofline,
         "pipeline_roofline": {"algorithmic_bytes_per_step": b_frame + b_link, "achieved": pipe_gbs, "peak": peak_gbs,

@@ -98,6 +98,9 @@ ULK_API int ulk_device_count(void);
 ULK_API int ulk_set_device(int device);
 /* kernels launched by this library on the calling process so far */
 ULK_API int64_t ulk_launch_count(void);
+/* scratch workspace of the calling process, bytes: [0] retained slab capacity, [1] high-water
+ * mark of scratch in use during a call, [2] most bytes ever served outside the slab */
+ULK_API void ulk_workspace_stats(int64_t out[3]);
 
 /* per-kernel timing for bench.py's roofline line: when enabled every launch is bracketed by a
  * CUDA event pair on its own stream.  report: "kernel name\tlaunches\ttotal ms\n" per kernel;

@@ -35,17 +35,19 @@ def seg_params(threshold=0.5, min_area=100, max_area=1_000_000, min_area_factor=
 
 
 def segment_frame(lib, fg: np.ndarray, ct: np.ndarray, keep_labels: bool = True, **kw):
-    """Runs ulk_segment_frame on host arrays through the emulation library; returns the
-    (handle, numpy node table)."""
+    """Segments one frame held in host (numpy) arrays; returns (handle, numpy node table).
+    The emulation library takes host pointers in `ulk_segment_frame`; the CUDA library takes
+    them in `ulk_segment_frame_host` (copies are part of the call)."""
     fg = np.ascontiguousarray(fg)
     ct = np.ascontiguousarray(ct)
     shape = fg.shape if fg.ndim == 3 else (1,) + fg.shape
     shp = (C.c_int64 * 3)(*shape)
     prm = seg_params(fg_dtype=fg.dtype, **kw)
     handle = C.POINTER(_lib.FrameNodes)()
-    rc = lib.ulk_segment_frame(fg.ctypes.data_as(C.c_void_p), _lib.dtype_code(fg.dtype),
-                               ct.ctypes.data_as(C.c_void_p), _lib.dtype_code(ct.dtype),
-                               shp, C.byref(prm), int(keep_labels), None, C.byref(handle))
+    entry = lib.ulk_segment_frame if lib is _EMU else lib.ulk_segment_frame_host
+    rc = entry(fg.ctypes.data_as(C.c_void_p), _lib.dtype_code(fg.dtype),
+               ct.ctypes.data_as(C.c_void_p), _lib.dtype_code(ct.dtype),
+               shp, C.byref(prm), int(keep_labels), None, C.byref(handle))
     _lib.check(lib, rc)
     return handle, _lib.nodes_to_host(lib, handle, with_labels=keep_labels)
 

@@ -71,6 +71,19 @@ def test_region_too_small_raises_like_reference():
         _seg(lib, fg, ct, min_area=4, max_area=100)
 
 
+def test_golden_edge_inputs_segment_like_the_oracle():
+    """The masks / images of the golden edge-weight file (every contour dtype class) as whole
+    frames; several contain more than one too-small region, the first in label order raises."""
+    from pathlib import Path
+    g = np.load(Path(__file__).resolve().parent / "golden" / "edges_cases.npz")
+    lib = emu_lib()
+    for name in ("f32_3d", "f64_3d", "bool_3d", "u8_3d", "f32_2d", "bool_2d"):
+        mask, img = g[name + "_mask"], g[name + "_img"]
+        if mask.shape[0] == 1:
+            mask, img = mask[0], img[0]
+        cases.run_and_compare(lib, _seg, mask, img, mask.ndim, min_area=4, max_area=60)
+
+
 def _nodes_for_link(nodes, ndim, t):
     from ultrack_b200 import _lib
     out = []

@@ -56,7 +56,7 @@ class Links(C.Structure):
 
 
 EXPORTS = [
-    "ulk_last_error", "ulk_device_count", "ulk_set_device", "ulk_launch_count",
+    "ulk_last_error", "ulk_device_count", "ulk_set_device", "ulk_launch_count", "ulk_workspace_stats",
     "ulk_profile_enable", "ulk_profile_reset", "ulk_profile_report", "ulk_segment_frame",
     "ulk_segment_frame_host", "ulk_frame_nodes_free", "ulk_frame_nodes_to_host",
     "ulk_frame_nodes_from_host", "ulk_frame_nodes_to_device", "ulk_frame_nodes_from_device", "ulk_link_frames", "ulk_links_to_host", "ulk_links_free",
@@ -72,6 +72,8 @@ def bind(lib: C.CDLL) -> C.CDLL:
     lib.ulk_device_count.restype = C.c_int
     lib.ulk_set_device.argtypes = [C.c_int]
     lib.ulk_launch_count.restype = i64
+    lib.ulk_workspace_stats.argtypes = [C.POINTER(i64)]
+    lib.ulk_workspace_stats.restype = None
     lib.ulk_profile_enable.argtypes = [C.c_int]
     lib.ulk_profile_enable.restype = None
     lib.ulk_profile_reset.restype = None

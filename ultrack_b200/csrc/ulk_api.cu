@@ -22,6 +22,12 @@ int ulk_device_count(void)
 }
 
 int64_t ulk_launch_count(void) { return (int64_t)g_ulk_launches; }
+void ulk_workspace_stats(int64_t out[3])
+{
+    size_t v[3];
+    ulk_ws_stats(v);
+    for (int i = 0; i < 3; ++i) out[i] = (int64_t)v[i];
+}
 
 void ulk_profile_enable(int on) { ulk_prof_enable(on); }
 void ulk_profile_reset(void) { ulk_prof_reset(); }
@@ -45,6 +51,7 @@ int ulk_segment_frame(const void *foreground, int fg_dtype, const void *contours
     ulk_stream_t st = (ulk_stream_t)stream;
     ulk_set_alloc_stream(st);
     *out = nullptr;
+    ulk_ws_reserve((size_t)(shape[0] * shape[1] * shape[2]) * 96 + (64u << 20), st);
     int rc = ulk_segment_frame_impl(st, foreground, fg_dtype, contours, ct_dtype, shape, params, keep_labels, out);
     if (rc) { ulk_frame_nodes_free_impl(*out); *out = nullptr; ulk_sync(st); }
     return rc;
@@ -58,6 +65,7 @@ int ulk_segment_frame_host(const void *foreground, int fg_dtype, const void *con
     ulk_stream_t st = (ulk_stream_t)stream;
     ulk_set_alloc_stream(st);
     i64 V = shape[0] * shape[1] * shape[2];
+    ulk_ws_reserve((size_t)V * (96 + ulk_dtype_size(fg_dtype) + ulk_dtype_size(ct_dtype)) + (64u << 20), st);
     UlkArena A;
     u8 *dfg = A.get<u8>(V * ulk_dtype_size(fg_dtype));
     u8 *dct = A.get<u8>(V * ulk_dtype_size(ct_dtype));

@@ -93,16 +93,16 @@ struct UlkArena {
     template <class T> T *get(i64 n)
     {
         void *p = nullptr;
-        if (ulk_dev_alloc(&p, (size_t)(n > 0 ? n : 1) * sizeof(T))) { failed = true; return nullptr; }
+        if (ulk_ws_alloc(&p, (size_t)(n > 0 ? n : 1) * sizeof(T))) { failed = true; return nullptr; }
         ptrs.push_back(p);
         return (T *)p;
     }
     void release(void *p)
     {
         for (size_t i = 0; i < ptrs.size(); ++i)
-            if (ptrs[i] == p) { ulk_dev_free(p); ptrs[i] = ptrs.back(); ptrs.pop_back(); return; }
+            if (ptrs[i] == p) { ulk_ws_free(p); ptrs[i] = ptrs.back(); ptrs.pop_back(); return; }
     }
-    ~UlkArena() { for (void *p : ptrs) ulk_dev_free(p); }
+    ~UlkArena() { for (void *p : ptrs) ulk_ws_free(p); }
 };
 
 template <class T> struct K_Fill {

@@ -26,6 +26,10 @@ int ulk_prof_report(char *buf, i64 cap) { if (buf && cap > 0) buf[0] = 0; return
 void ulk_set_alloc_stream(ulk_stream_t) {}
 int ulk_dev_alloc(void **p, size_t bytes) { *p = malloc(bytes ? bytes : 1); return *p ? 0 : -3; }
 void ulk_dev_free(void *p) { free(p); }
+int ulk_ws_reserve(size_t, ulk_stream_t) { return 0; }
+int ulk_ws_alloc(void **p, size_t bytes) { return ulk_dev_alloc(p, bytes); }
+void ulk_ws_free(void *p) { free(p); }
+void ulk_ws_stats(size_t out[3]) { out[0] = out[1] = out[2] = 0; }
 int ulk_memset(void *p, int byte, size_t bytes, ulk_stream_t) { memset(p, byte, bytes); return 0; }
 int ulk_d2h(void *dst, const void *src, size_t bytes, ulk_stream_t) { memcpy(dst, src, bytes); return 0; }
 int ulk_h2d(void *dst, const void *src, size_t bytes, ulk_stream_t) { memcpy(dst, src, bytes); return 0; }
@@ -130,6 +134,8 @@ static cudaStream_t g_alloc_stream = 0;
 static bool g_pool_ready = false;
 void ulk_set_alloc_stream(ulk_stream_t s)
 {
+    // scratch blocks are recycled in host order: work left on another stream must be done first
+    if (s != g_alloc_stream) cudaStreamSynchronize(g_alloc_stream);
     g_alloc_stream = s;
     if (!g_pool_ready) {
         int dev = 0;
@@ -148,6 +154,93 @@ int ulk_dev_alloc(void **p, size_t bytes)
     return 0;
 }
 void ulk_dev_free(void *p) { if (p) cudaFreeAsync(p, g_alloc_stream); }
+
+// ---- workspace slab: best-fit free list over one retained allocation
+static char *g_ws_base = nullptr;
+static size_t g_ws_cap = 0, g_ws_used = 0, g_ws_peak = 0, g_ws_outside = 0, g_ws_outside_now = 0;
+static std::map<size_t, size_t> g_ws_freelist;             // offset -> size
+static std::map<void *, size_t> g_ws_live;                 // slab pointer -> size
+static std::map<void *, size_t> g_ws_live_outside;         // cudaMallocAsync pointer -> size
+static const size_t WS_ALIGN = 512;
+int ulk_ws_reserve(size_t bytes, ulk_stream_t s)
+{
+    (void)s;
+    // grow when the request, or what the previous call had to take from outside the slab, exceeds it
+    size_t want = bytes;
+    if (g_ws_peak > want) want = g_ws_peak + (g_ws_peak >> 4);
+    if (want <= g_ws_cap || !g_ws_live.empty()) return 0;
+    cudaDeviceSynchronize();
+    if (g_ws_base) { cudaFree(g_ws_base); g_ws_base = nullptr; g_ws_cap = 0; }
+    g_ws_freelist.clear();
+    {   // hand cached blocks of the stream-ordered pool back before sizing the slab
+        int dev = 0;
+        cudaMemPool_t pool;
+        cudaGetDevice(&dev);
+        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
+    }
+    size_t free_b = 0, total_b = 0;
+    cudaMemGetInfo(&free_b, &total_b);
+    size_t lim = free_b > (6ull << 30) ? free_b - (6ull << 30) : free_b / 2;   // leave room for results
+    if (want > lim) want = lim;
+    want = (want + WS_ALIGN - 1) / WS_ALIGN * WS_ALIGN;
+    while (want >= (64ull << 20)) {
+        void *p = nullptr;
+        if (cudaMalloc(&p, want) == cudaSuccess) { g_ws_base = (char *)p; g_ws_cap = want; break; }
+        cudaGetLastError();
+        want = want / 4 * 3 / WS_ALIGN * WS_ALIGN;
+    }
+    if (g_ws_cap) g_ws_freelist[0] = g_ws_cap;
+    return 0;
+}
+int ulk_ws_alloc(void **p, size_t bytes)
+{
+    size_t need = ((bytes ? bytes : 1) + WS_ALIGN - 1) / WS_ALIGN * WS_ALIGN;
+    auto best = g_ws_freelist.end();
+    for (auto it = g_ws_freelist.begin(); it != g_ws_freelist.end(); ++it)
+        if (it->second >= need && (best == g_ws_freelist.end() || it->second < best->second)) best = it;
+    g_ws_used += need;
+    if (g_ws_used > g_ws_peak) g_ws_peak = g_ws_used;
+    if (best == g_ws_freelist.end()) {
+        g_ws_used -= need;
+        int rc = ulk_dev_alloc(p, need);
+        if (rc) return rc;
+        g_ws_used += need;
+        g_ws_live_outside[*p] = need;
+        g_ws_outside_now += need;
+        if (g_ws_outside_now > g_ws_outside) g_ws_outside = g_ws_outside_now;
+        return 0;
+    }
+    size_t off = best->first, sz = best->second;
+    g_ws_freelist.erase(best);
+    if (sz > need) g_ws_freelist[off + need] = sz - need;
+    *p = g_ws_base + off;
+    g_ws_live[*p] = need;
+    return 0;
+}
+void ulk_ws_free(void *p)
+{
+    if (!p) return;
+    auto io = g_ws_live_outside.find(p);
+    if (io != g_ws_live_outside.end()) {
+        g_ws_used -= io->second; g_ws_outside_now -= io->second;
+        g_ws_live_outside.erase(io);
+        ulk_dev_free(p);
+        return;
+    }
+    auto il = g_ws_live.find(p);
+    if (il == g_ws_live.end()) return;
+    size_t off = (size_t)((char *)p - g_ws_base), sz = il->second;
+    g_ws_used -= sz;
+    g_ws_live.erase(il);
+    auto nx = g_ws_freelist.lower_bound(off);
+    if (nx != g_ws_freelist.end() && off + sz == nx->first) { sz += nx->second; nx = g_ws_freelist.erase(nx); }
+    if (nx != g_ws_freelist.begin()) {
+        auto pv = std::prev(nx);
+        if (pv->first + pv->second == off) { pv->second += sz; return; }
+    }
+    g_ws_freelist[off] = sz;
+}
+void ulk_ws_stats(size_t out[3]) { out[0] = g_ws_cap; out[1] = g_ws_peak; out[2] = g_ws_outside; }
 int ulk_memset(void *p, int byte, size_t bytes, ulk_stream_t s)
 {
     ProfScope ps("cudaMemsetAsync", s);

@@ -121,6 +121,14 @@ struct UlkArena;  // growable pool of device buffers, see ulk_rt.cu
 void ulk_set_alloc_stream(ulk_stream_t s);
 int ulk_dev_alloc(void **p, size_t bytes);
 void ulk_dev_free(void *p);
+// frame-scoped scratch: carved out of one retained device slab (host-side bookkeeping only, no
+// driver call per buffer); everything that uses it is ordered on the call's stream.
+// ulk_ws_reserve sizes the slab before a call starts (no-op when it is already large enough).
+int ulk_ws_reserve(size_t bytes, ulk_stream_t s);
+int ulk_ws_alloc(void **p, size_t bytes);
+void ulk_ws_free(void *p);
+// bytes: [0] slab capacity, [1] high-water mark of scratch in use, [2] bytes served outside the slab
+void ulk_ws_stats(size_t out[3]);
 int ulk_memset(void *p, int byte, size_t bytes, ulk_stream_t s);
 int ulk_d2h(void *dst, const void *src, size_t bytes, ulk_stream_t s);  // synchronises
 int ulk_h2d(void *dst, const void *src, size_t bytes, ulk_stream_t s);

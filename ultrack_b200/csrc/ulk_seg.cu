@@ -34,7 +34,6 @@ struct K_HierFull {
 struct K_NodeGather {
     const i32 *bs; const i32 *noff; UlkNodeOut O;
     i32 *bbox, *centroid, *area, *hier_id, *parent, *hidx; double *frontier, *height; i64 *mwords;
-    i32 *err;
     ULK_D void operator()(i64 hh) const
     {
         i32 h = (i32)hh;
@@ -69,7 +68,7 @@ struct K_NodeGather {
 // vendored/hierarchy.py:161-162: a region whose bounding box holds fewer than 8 elements
 // raises RuntimeError in the reference; report the first one back to the host.
 struct K_RegionSizeCheck {
-    const i32 *bs; UlkHierScratch S; i32 *err;
+    const i32 *bs; UlkHierScratch S; u64 *err;   // min over failing regions of (region index, size)
     ULK_D void operator()(i64 hh) const
     {
         i32 h = (i32)hh;
@@ -77,7 +76,7 @@ struct K_RegionSizeCheck {
         i32 root = o + 2 * b - 2;
         i64 vol = 1;
         for (int d = 0; d < 3; ++d) vol *= (i64)(S.nbbmax[3 * root + d] - S.nbbmin[3 * root + d] + 1);
-        if (vol < 8) ulk_atomic_max(err, (i32)(8 - vol));
+        if (vol < 8) ulk_atomic_min(err, ((u64)(u32)h << 8) | (u64)vol);   // the reference raises at the first one
     }
 };
 struct K_BasinNodeGlobal {
@@ -520,18 +519,18 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     O.area = A.get<i32>(N2); O.frontier = A.get<double>(N2); O.height = A.get<double>(N2);
     O.bbmin = A.get<i32>(3 * N2); O.bbmax = A.get<i32>(3 * N2); O.csum = A.get<i64>(3 * N2);
     O.parent = A.get<i32>(N2); O.hidx = A.get<i32>(N2); O.basin_node = A.get<i32>(vb.B);
-    i32 *err = A.get<i32>(1);
+    u64 *err = A.get<u64>(1);
     CHKA(A);
-    CHK(ulk_memset(err, 0, sizeof(i32), st));
+    CHK(ulk_memset(err, 0xff, sizeof(u64), st));
     CHK(ulk_memset(O.count + R, 0, sizeof(i32), st));
     UlkHierParams HP;
     HP.kind = prm->ws_hierarchy; HP.min_area = prm->min_area; HP.max_area = prm->max_area;
     HP.min_frontier = prm->min_frontier; HP.fix_shift = fix_shift;
     ulk_launch(R, st, K_HierFull{vb.bs, vb.es, Bv, Ev, S, HP, O});
     ulk_launch(R, st, K_RegionSizeCheck{vb.bs, S, err});
-    i32 h_err = 0;
+    u64 h_err = 0;
     CHK(ulk_read(&h_err, err, 1, st));
-    if (h_err > 0) ULK_FAIL(-10, "Region too small. Size of %d found.", 8 - h_err);
+    if (h_err != ULK_NONE64) ULK_FAIL(-10, "Region too small. Size of %d found.", (int)(h_err & 0xff));
 
     // ---- node table
     i32 *noff = A.get<i32>(R + 1);
@@ -550,7 +549,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     if (!F->bbox || !F->centroid || !F->area || !F->frontier || !F->height || !F->hier_id || !F->parent || !F->hidx || !F->mask_off)
         ULK_FAIL(-3, "device allocation failed");
     ulk_launch(R, st, K_NodeGather{vb.bs, noff, O, F->bbox, F->centroid, F->area, F->hier_id, F->parent, F->hidx,
-                                   F->frontier, F->height, mwords, err});
+                                   F->frontier, F->height, mwords});
     CHK(ulk_memset(mwords + N, 0, sizeof(i64), st));
     CHK(ulk_exclusive_scan_i64(mwords, F->mask_off, (i64)N + 1, st));
     i64 total_words = 0;
