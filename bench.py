@@ -348,7 +348,7 @@ def main():
         "pipeline_roofline": {"algorithmic_bytes_per_step": b_frame + b_link, "achieved": pipe_gbs, "peak": peak_gbs,
                               "unit": "GB/s", "frac": pipe_gbs / peak_gbs,
                               "kernel_time_ms_per_step": kern_ms / args.steps,
-                              "top_kernels_ms_per_step": {k: round(v[1] / args.steps, 3) for k, v in top[:12]}},
+                              "top_kernels_ms_per_step": {k: round(v[1] / args.steps, 3) for k, v in top[:80]}},
     }
     if e2e:
         ke = e2e[0]

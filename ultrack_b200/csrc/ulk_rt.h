@@ -91,6 +91,8 @@ ULK_D ULK_INLINE u32 ulk_funnel_r(u32 lo, u32 hi, u32 s) { return __funnelshift_
 // ---------------------------------------------------------------- launch
 #ifdef ULK_EMU
 template <class F> void ulk_launch(i64 n, ulk_stream_t, const F &f) { for (i64 i = 0; i < n; ++i) f(i); }
+// warp-cooperative kernels: the emulation runs the functor's scalar statement `operator()`
+template <class F> void ulk_launch_warp(i64 n, ulk_stream_t, const F &f) { for (i64 i = 0; i < n; ++i) f(i); }
 #else
 template <class F> __global__ void __launch_bounds__(256) ulk_kernel(i64 n, F f)
 {
@@ -108,6 +110,22 @@ template <class F> void ulk_launch(i64 n, ulk_stream_t s, const F &f)
     i64 grid = (n + 255) / 256;
     if (g_ulk_prof_on) ulk_prof_begin(typeid(F).name(), s);
     ulk_kernel<F><<<(unsigned)grid, 256, 0, s>>>(n, f);
+    if (g_ulk_prof_on) ulk_prof_end(s);
+    ++g_ulk_launches;
+}
+// warp-cooperative kernels: every thread of the grid calls F::warp(i, i < n), so the body may
+// use full-mask warp collectives; lane l of a warp holds element 32*k + l.
+template <class F> __global__ void __launch_bounds__(256) ulk_kernel_warp(i64 n, F f)
+{
+    i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    f.warp(i, i < n);
+}
+template <class F> void ulk_launch_warp(i64 n, ulk_stream_t s, const F &f)
+{
+    if (n <= 0) return;
+    i64 grid = (n + 255) / 256;
+    if (g_ulk_prof_on) ulk_prof_begin(typeid(F).name(), s);
+    ulk_kernel_warp<F><<<(unsigned)grid, 256, 0, s>>>(n, f);
     if (g_ulk_prof_on) ulk_prof_end(s);
     ++g_ulk_launches;
 }

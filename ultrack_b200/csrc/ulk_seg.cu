@@ -220,7 +220,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const Ul
         ulk_fill<i32>(out.bbmax, -0x7fffffff, 3 * (i64)B, st);
         CHK(ulk_memset(out.csum, 0, (size_t)B * 3 * sizeof(i64), st));
     }
-    ulk_launch(V, st, K_BasinAccum{out.bas, lab, mw, pk, flowkey, ct, dm, out.b_size, out.b_top, ncross,
+    ulk_launch_warp(V, st, K_BasinAccum{out.bas, lab, mw, pk, flowkey, ct, dm, out.b_size, out.b_top, ncross,
                                    need_stats ? 1 : 0, out.bbmin, out.bbmax, out.csum});
     u64 h_ncross = 0;
     CHK(ulk_read(&h_ncross, ncross, 1, st));
@@ -311,7 +311,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const Ul
         CHKA(A);
         CHK(ulk_memset(out.b_k3, 0, (size_t)B * sizeof(u32), st));
         ulk_launch(V, st, K_MinKeyInBasin{out.bas, dm, out.b_k3});
-        ulk_launch(V, st, K_K3Init{out.bas, P3});
+        ulk_launch_warp(V, st, K_K3Init{out.bas, out.b_k3, dm.W, P3});
         ulk_launch(V, st, K_K3Union{out.bas, dm, out.b_k3, P3});
         ulk_launch(V, st, K_Flatten{P3});
         int it = 0;
@@ -399,7 +399,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     u32 *cmax = A.get<u32>(1);
     CHKA(A);
     CHK(ulk_memset(cmax, 0, 4, st));
-    ulk_launch(V, st, K_Threshold{fg, fg_dtype, prm->threshold, ctp, ct_dtype, ctf, ctd, P, cmax});
+    ulk_launch_warp(V, st, K_Threshold{fg, fg_dtype, prm->threshold, ctp, ct_dtype, ctf, ctd, P, cmax, dm.W});
     // ---- connected components (4/6-connected), small-object removal
     ulk_launch(V, st, K_CclUnion{P, dm});
     ulk_launch(V, st, K_Flatten{P});
@@ -408,7 +408,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     CHKA(A);
     CHK(ulk_memset(cnt, 0, (size_t)V * sizeof(i32), st));
     CHK(ulk_memset(ctr, 0, 4 * sizeof(i32), st));
-    ulk_launch(V, st, K_CountByRoot{P, cnt});
+    ulk_launch_warp(V, st, K_CountByRoot{P, cnt});
     const i32 max_area_i = prm->max_area > 2147483646.0 ? 2147483646 : (i32)prm->max_area;
     ulk_launch(V, st, K_CcStats{P, cnt, max_area_i, ctr});
     i32 hc[4];

@@ -32,27 +32,59 @@ ULK_D ULK_INLINE void ulk_vunion(i32 *P, i32 a, i32 b)
 
 // ------------------------------------------------------------------ K1: threshold + contour staging
 // processing.py:212 `foreground[time] > threshold`; vendored/hierarchy.py:158-159,350 up-casts.
+// The component forest starts with every x-run of foreground voxels inside a 32-voxel warp
+// segment already hooked to its first voxel, so K_CclUnion only has to join runs.
+#ifndef ULK_EMU
+// first lane of the chain of `linked` lanes that ends at `lane` (bit l of linked: lane l is
+// joined to lane l-1)
+ULK_D ULK_INLINE int ulk_run_start(u32 linked, int lane)
+{
+    u32 stop = ~linked & (0xffffffffu >> (31 - lane));   // lanes <= lane that start a run
+    return 31 - __clz(stop);                               // lane 0 never has its link bit set
+}
+#endif
 struct K_Threshold {
     const void *fg; int fgt; double thr;
     const void *ct; int ctt;
     float *ctf; double *ctd;
-    i32 *P; u32 *cmax;
-    ULK_D void operator()(i64 v) const
+    i32 *P; u32 *cmax; i32 W;
+    ULK_D ULK_INLINE bool stage(i64 v, u32 &bits) const
     {
         double f = ulk_load_as_double(fg, fgt, v);
-        P[v] = f > thr ? (i32)v : -1;
         double c = ulk_load_as_double(ct, ctt, v);
         if (ctf) ctf[v] = (float)c; else ctd[v] = c;
         float a = (float)(c < 0 ? -c : c);
-        if (a == a && a <= 3.0e38f) {
-            u32 bits;
-            memcpy(&bits, &a, 4);
-            if (bits > *cmax) ulk_atomic_max(cmax, bits);
-        }
+        bits = 0;
+        if (a == a && a <= 3.0e38f) memcpy(&bits, &a, 4);
+        return f > thr;
     }
+#ifdef ULK_EMU
+    void operator()(i64 v) const
+    {
+        u32 bits;
+        bool on = stage(v, bits);
+        if (bits > *cmax) *cmax = bits;
+        bool link = on && (v & 31) != 0 && (v % W) != 0 && P[v - 1] >= 0;
+        P[v] = on ? (link ? P[v - 1] : (i32)v) : -1;
+    }
+#else
+    ULK_D void warp(i64 v, bool valid) const
+    {
+        const int lane = threadIdx.x & 31;
+        u32 bits = 0;
+        bool on = valid && stage(v, bits);
+        u32 m = __reduce_max_sync(0xffffffffu, bits);
+        if (lane == 0 && m > *cmax) atomicMax(cmax, m);
+        bool prev = __shfl_up_sync(0xffffffffu, on ? 1 : 0, 1) != 0;
+        u32 linked = __ballot_sync(0xffffffffu, on && prev && lane > 0 && (v % W) != 0);
+        if (valid) P[v] = on ? (i32)v - (lane - ulk_run_start(linked, lane)) : -1;
+    }
+#endif
 };
 
 // ------------------------------------------------------------------ connected components (ndi.label)
+// joins the runs: an x edge only across a warp-segment boundary, a y / z edge only where the
+// edge one voxel to the left does not already join the same two runs
 struct K_CclUnion {
     i32 *P; UlkDims dm;
     ULK_D void operator()(i64 vv) const
@@ -61,10 +93,14 @@ struct K_CclUnion {
         if (P[v] < 0) return;
         i32 z, y, x;
         dm.coords(v, z, y, x);
-        for (int d = 0; d < 3; ++d) {
+        bool left = x > 0 && P[v - 1] >= 0;
+        if (left && (v & 31) == 0) ulk_vunion(P, v, v - 1);
+        for (int d = 1; d < 3; ++d) {
             if (!dm.bwd(d, z, y, x)) continue;
             i32 u = v - dm.stride(d);
-            if (P[u] >= 0) ulk_vunion(P, v, u);
+            if (P[u] < 0) continue;
+            if (left && P[u - 1] >= 0) continue;
+            ulk_vunion(P, v, u);
         }
     }
 };
@@ -74,7 +110,16 @@ struct K_Flatten {
 };
 struct K_CountByRoot {
     const i32 *P; i32 *cnt;
-    ULK_D void operator()(i64 v) const { if (P[v] >= 0) ulk_atomic_add(&cnt[P[v]], 1); }
+#ifdef ULK_EMU
+    void operator()(i64 v) const { if (P[v] >= 0) cnt[P[v]] += 1; }
+#else
+    ULK_D void warp(i64 v, bool valid) const
+    {
+        i32 r = valid ? P[v] : -1;
+        u32 grp = __match_any_sync(0xffffffffu, r);
+        if (r >= 0 && (threadIdx.x & 31) == __ffs(grp) - 1) atomicAdd(&cnt[r], __popc(grp));
+    }
+#endif
 };
 // counts components and components above max_area
 struct K_CcStats {
@@ -291,34 +336,76 @@ struct K_BasinAccum {
     const i32 *bas; const i32 *lab; const u32 *mw, *pk; const u32 *flowkey; UlkCt ct; UlkDims dm;
     i32 *b_size; u64 *b_top; u64 *ncross;
     int want_stats; i32 *bbmin, *bbmax; i64 *csum;
-    ULK_D void operator()(i64 vv) const
+    // this voxel's contribution: largest spanning-tree key it carries, forward crossing edges
+    ULK_D ULK_INLINE void own(i32 v, i32 b, u64 &top, u32 &nc, i32 c[3]) const
+    {
+        top = 0;
+        if (pk[v] != ULK_NONE32) top = ((u64)mw[v] << 32) | pk[v];
+        u32 fk = flowkey[v];
+        if (fk != ULK_NONE32) {
+            i32 a = (i32)(fk / 3u), e = a + dm.stride((int)(fk % 3u));
+            u64 t2 = ((u64)ulk_f2ord(ct.w(a, e)) << 32) | fk;
+            if (t2 > top) top = t2;
+        }
+        dm.coords(v, c[0], c[1], c[2]);
+        i32 l = lab[v];
+        nc = 0;
+        for (int d = 0; d < 3; ++d)
+            if (dm.fwd(d, c[0], c[1], c[2])) { i32 u = v + dm.stride(d); if (lab[u] == l && bas[u] != b) ++nc; }
+    }
+#ifdef ULK_EMU
+    void operator()(i64 vv) const
     {
         i32 v = (i32)vv;
         i32 b = bas[v];
         if (b < 0) return;
-        ulk_atomic_add(&b_size[b], 1);
-        if (pk[v] != ULK_NONE32) ulk_atomic_max(&b_top[b], ((u64)mw[v] << 32) | pk[v]);
-        u32 fk = flowkey[v];
-        if (fk != ULK_NONE32) {
-            i32 a = (i32)(fk / 3u), c = a + dm.stride((int)(fk % 3u));
-            ulk_atomic_max(&b_top[b], ((u64)ulk_f2ord(ct.w(a, c)) << 32) | fk);
-        }
-        i32 z, y, x;
-        dm.coords(v, z, y, x);
-        i32 l = lab[v];
-        u32 nc = 0;
-        for (int d = 0; d < 3; ++d)
-            if (dm.fwd(d, z, y, x)) { i32 u = v + dm.stride(d); if (lab[u] == l && bas[u] != b) ++nc; }
-        if (nc) ulk_atomic_add(ncross, (u64)nc);
-        if (want_stats) {
-            i32 c[3] = {z, y, x};
+        u64 top; u32 nc; i32 c[3];
+        own(v, b, top, nc, c);
+        b_size[b] += 1;
+        if (top > b_top[b]) b_top[b] = top;
+        *ncross += nc;
+        if (want_stats)
             for (int d = 0; d < 3; ++d) {
                 ulk_atomic_min(&bbmin[3 * b + d], c[d]);
                 ulk_atomic_max(&bbmax[3 * b + d], c[d]);
-                ulk_atomic_add(&csum[3 * b + d], (i64)c[d]);
+                csum[3 * b + d] += c[d];
+            }
+    }
+#else
+    // lanes of a warp that sit in the same basin (consecutive x: usually one or two groups)
+    // reduce among themselves; one lane per group issues the atomics
+    ULK_D void warp(i64 vv, bool valid) const
+    {
+        const int lane = threadIdx.x & 31;
+        i32 v = (i32)vv;
+        i32 b = valid ? bas[v] : -1;
+        u64 top = 0; u32 nc = 0; i32 c[3] = {0, 0, 0};
+        if (b >= 0) own(v, b, top, nc, c);
+        u32 nct = __reduce_add_sync(0xffffffffu, nc);
+        if (lane == 0 && nct) atomicAdd((unsigned long long *)ncross, (unsigned long long)nct);
+        u32 grp = __match_any_sync(0xffffffffu, b);
+        if (b < 0) return;
+        const bool lead = lane == __ffs(grp) - 1;
+        u32 thi = __reduce_max_sync(grp, (u32)(top >> 32));
+        u32 tlo = __reduce_max_sync(grp, (u32)(top >> 32) == thi ? (u32)top : 0u);
+        if (lead) {
+            atomicAdd(&b_size[b], __popc(grp));
+            u64 t = ((u64)thi << 32) | tlo;
+            if (t) atomicMax((unsigned long long *)&b_top[b], (unsigned long long)t);
+        }
+        if (want_stats) {
+            for (int d = 0; d < 3; ++d) {
+                i32 lo = __reduce_min_sync(grp, c[d]), hi = __reduce_max_sync(grp, c[d]);
+                u32 sm = __reduce_add_sync(grp, (u32)c[d]);
+                if (lead) {
+                    atomicMin(&bbmin[3 * b + d], lo);
+                    atomicMax(&bbmax[3 * b + d], hi);
+                    atomicAdd((unsigned long long *)&csum[3 * b + d], (unsigned long long)sm);
+                }
             }
         }
     }
+#endif
 };
 
 // ------------------------------------------------------------------ join keys (area hierarchy)
@@ -494,9 +581,29 @@ struct K_MinKeyInBasin {
         if (k != ULK_NONE32 && k > K0[b]) ulk_atomic_max(&K0[b], k);
     }
 };
+// edges of a basin whose raster key is <= K0[basin]; runs of x edges inside a warp segment are
+// hooked to their first voxel at initialisation (same scheme as the component labelling)
 struct K_K3Init {
-    const i32 *bas; i32 *P;
-    ULK_D void operator()(i64 v) const { P[v] = bas[v] < 0 ? -1 : (i32)v; }
+    const i32 *bas; const u32 *K0; i32 W; i32 *P;
+    ULK_D ULK_INLINE bool xlink(i64 v, i32 b) const
+    {
+        return b >= 0 && (v % W) != 0 && bas[v - 1] == b && 3u * (u32)(v - 1) <= K0[b];
+    }
+#ifdef ULK_EMU
+    void operator()(i64 v) const
+    {
+        i32 b = bas[v];
+        P[v] = b < 0 ? -1 : ((v & 31) != 0 && xlink(v, b) ? P[v - 1] : (i32)v);
+    }
+#else
+    ULK_D void warp(i64 v, bool valid) const
+    {
+        const int lane = threadIdx.x & 31;
+        i32 b = valid ? bas[v] : -1;
+        u32 linked = __ballot_sync(0xffffffffu, lane > 0 && xlink(v, b));
+        if (valid) P[v] = b < 0 ? -1 : (i32)v - (lane - ulk_run_start(linked, lane));
+    }
+#endif
 };
 struct K_K3Union {
     const i32 *bas; UlkDims dm; const u32 *K0; i32 *P;
@@ -508,10 +615,15 @@ struct K_K3Union {
         i32 z, y, x;
         dm.coords(v, z, y, x);
         u32 kmax = K0[b];
-        for (int d = 0; d < 3; ++d) {
+        bool left = x > 0 && bas[v - 1] == b && 3u * (u32)(v - 1) <= kmax;
+        if (left && (v & 31) == 0) ulk_vunion(P, v, v - 1);
+        for (int d = 1; d < 3; ++d) {
             if (!dm.bwd(d, z, y, x)) continue;
             i32 u = v - dm.stride(d);
-            if (bas[u] == b && 3u * (u32)u + d <= kmax) ulk_vunion(P, v, u);
+            if (bas[u] != b || 3u * (u32)u + d > kmax) continue;
+            // (u-1,u), (u-1,v-1) carry smaller keys than (u,v): with (v-1,v) they already join u and v
+            if (left && bas[u - 1] == b) continue;
+            ulk_vunion(P, v, u);
         }
     }
 };
