@@ -62,6 +62,20 @@ static int emu_sort(const K *ki, K *ko, const u32 *vi, u32 *vo, i64 n)
 }
 int ulk_sort_pairs_u64(const u64 *ki, u64 *ko, const u32 *vi, u32 *vo, i64 n, ulk_stream_t) { return emu_sort(ki, ko, vi, vo, n); }
 int ulk_sort_pairs_u32(const u32 *ki, u32 *ko, const u32 *vi, u32 *vo, i64 n, ulk_stream_t) { return emu_sort(ki, ko, vi, vo, n); }
+int ulk_sort_keys_u32(const u32 *ki, u32 *ko, i64 n, ulk_stream_t)
+{
+    std::vector<u32> k(ki, ki + n);
+    std::sort(k.begin(), k.end());
+    for (i64 i = 0; i < n; ++i) ko[i] = k[i];
+    return 0;
+}
+int ulk_sort_keys_u64(const u64 *ki, u64 *ko, i64 n, ulk_stream_t)
+{
+    std::vector<u64> k(ki, ki + n);
+    std::sort(k.begin(), k.end());
+    for (i64 i = 0; i < n; ++i) ko[i] = k[i];
+    return 0;
+}
 
 #else
 // ------------------------------------------------------------------ CUDA
@@ -315,6 +329,28 @@ int ulk_sort_pairs_u32(const u32 *ki, u32 *ko, const u32 *vi, u32 *vo, i64 n, ul
     if (cub_tmp(need)) return -2;
     ProfScope ps("cub::DeviceRadixSort::SortPairs", s);
     ULK_CUDA(cub::DeviceRadixSort::SortPairs(g_cub_tmp, need, ki, ko, vi, vo, (int)n, 0, 32, s));
+    ++g_ulk_launches;
+    return 0;
+}
+int ulk_sort_keys_u32(const u32 *ki, u32 *ko, i64 n, ulk_stream_t s)
+{
+    if (n <= 0) return 0;
+    size_t need = 0;
+    ULK_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, need, ki, ko, (int)n, 0, 32, s));
+    if (cub_tmp(need)) return -2;
+    ProfScope ps("cub::DeviceRadixSort::SortKeys", s);
+    ULK_CUDA(cub::DeviceRadixSort::SortKeys(g_cub_tmp, need, ki, ko, (int)n, 0, 32, s));
+    ++g_ulk_launches;
+    return 0;
+}
+int ulk_sort_keys_u64(const u64 *ki, u64 *ko, i64 n, ulk_stream_t s)
+{
+    if (n <= 0) return 0;
+    size_t need = 0;
+    ULK_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, need, ki, ko, (int)n, 0, 64, s));
+    if (cub_tmp(need)) return -2;
+    ProfScope ps("cub::DeviceRadixSort::SortKeys", s);
+    ULK_CUDA(cub::DeviceRadixSort::SortKeys(g_cub_tmp, need, ki, ko, (int)n, 0, 64, s));
     ++g_ulk_launches;
     return 0;
 }

@@ -162,6 +162,8 @@ int ulk_sort_pairs_u64(const u64 *keys_in, u64 *keys_out, const u32 *vals_in, u3
                        i64 n, ulk_stream_t s);
 int ulk_sort_pairs_u32(const u32 *keys_in, u32 *keys_out, const u32 *vals_in, u32 *vals_out,
                        i64 n, ulk_stream_t s);
+int ulk_sort_keys_u32(const u32 *keys_in, u32 *keys_out, i64 n, ulk_stream_t s);
+int ulk_sort_keys_u64(const u64 *keys_in, u64 *keys_out, i64 n, ulk_stream_t s);
 
 // ---------------------------------------------------------------- numerics
 // order-preserving map float32 -> uint32 (handles negatives)

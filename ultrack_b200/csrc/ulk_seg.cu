@@ -123,10 +123,6 @@ struct K_OverlapWrite {
         for (i32 a = parent[n]; a >= 0; a = parent[a]) { ov[2 * k] = (i32)n; ov[2 * k + 1] = a; ++k; }
     }
 };
-struct K_LabelSmallOnly {
-    const i32 *P; const i32 *ccpre; i32 *lab2;
-    ULK_D void operator()(i64 v) const { i32 r = P[v]; lab2[v] = r < 0 ? 0 : ccpre[r] + 1; }
-};
 struct K_Iota { u32 *p; ULK_D void operator()(i64 i) const { p[i] = (u32)i; } };
 struct K_Valid { const u32 *c; i32 *f; ULK_D void operator()(i64 i) const { f[i] = c[i] != ULK_NONE32; } };
 
@@ -149,27 +145,33 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const Ul
     u32 *mw = A.get<u32>(V), *pk = A.get<u32>(V);
     i32 *bp = A.get<i32>(V);
     u8 *state = A.get<u8>(V + 4);
-    u32 *Lr = A.get<u32>(V), *best = A.get<u32>(V), *flowkey = A.get<u32>(V);
+    u32 *Lr = A.get<u32>(V), *best = A.get<u32>(V);
     u8 *fmark = A.get<u8>(V + 8);
     i32 *cand = A.get<i32>(V), *cand2 = A.get<i32>(V);
-    i32 *groots = A.get<i32>(V), *groots2 = A.get<i32>(V), *tgt = A.get<i32>(V);
-    i32 *ctr = A.get<i32>(8);
+    i32 *groots = A.get<i32>(V);
+    i32 *ctr = A.get<i32>(8);        // [0] candidates [1] growing roots [2] scratch flag [4] basins [5] flow edges
     CHKA(A);
     CHK(ulk_memset(fmark, 0, (size_t)V + 8, st));
     CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
     ulk_launch(V, st, K_MinEdge{lab, ct, dm, mw, pk});
-    ulk_launch(V, st, K_Hook1{lab, mw, pk, dm, bp, state, Lr, best, flowkey});
-    ulk_launch(V, st, K_Compress{bp});
-    ulk_launch(V, st, K_CandInit{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1});
+    ulk_launch(V, st, K_Hook1{lab, mw, pk, dm, bp, state, Lr, best, ctr + 4});
+    ulk_launch_warp(V, st, K_CompressCand{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1});
     i32 hc[8];
     CHK(ulk_read(hc, ctr, 8, st));
     i32 ncand = hc[0], ng = hc[1];
+    // every growing root hooks at most once: that bounds the flow-edge list
+    const i32 flow_cap = ng;
+    i32 *groots2 = A.get<i32>(ng), *tgt = A.get<i32>(ng);
+    i32 *flow_root = A.get<i32>(flow_cap);
+    u32 *flow_key = A.get<u32>(flow_cap);
+    CHKA(A);
     int rounds = 0;
     while (ng > 0) {
-        CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
+        CHK(ulk_memset(ctr, 0, 2 * sizeof(i32), st));
         ulk_launch(ncand, st, K_FindFlow{cand, lab, bp, mw, Lr, state, ct, dm, best, cand2, ctr + 0});
         ulk_launch(ng, st, K_Decide1{groots, bp, best, dm, tgt});
-        ulk_launch(ng, st, K_Decide2{groots, tgt, bp, state, best, flowkey, fmark, groots2, ctr + 1});
+        ulk_launch(ng, st, K_Decide2{groots, tgt, bp, state, best, fmark, groots2, ctr + 1,
+                                     flow_root, flow_key, ctr + 5, ctr + 4});
         CHK(ulk_read(hc, ctr, 8, st));
         ncand = hc[0]; ng = hc[1];
         i32 *t = cand; cand = cand2; cand2 = t;
@@ -177,70 +179,64 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const Ul
         if (++rounds > 100000) ULK_FAIL(-4, "flow rounds did not converge");
     }
     if (stats) stats->flow_rounds += rounds;
-    ulk_launch(V, st, K_Compress{bp});
+    const i32 B = hc[4], nflow = hc[5];
+    out.B = B;
     A.release(cand); A.release(cand2); A.release(groots); A.release(groots2); A.release(tgt);
 
-    // ---- basin ids, grouped by region label
-    i32 *flag = A.get<i32>(V + 1), *pre = A.get<i32>(V + 1);
-    CHKA(A);
-    ulk_launch(V, st, K_FlagRoots{bp, flag});
-    CHK(ulk_memset(flag + V, 0, sizeof(i32), st));
-    CHK(ulk_exclusive_scan_i32(flag, pre, V + 1, st));
-    i32 B = 0;
-    CHK(ulk_read(&B, pre + V, 1, st));
-    out.B = B;
-    i32 *b_root = A.get<i32>(B);
-    u32 *b_labkey = A.get<u32>(B), *b_labsorted = A.get<u32>(B), *iota = A.get<u32>(B), *sorted_pre = A.get<u32>(B);
-    i32 *gid_of_pre = A.get<i32>(B);
+    // ---- basin ids, grouped by region label: sort of the (label, root voxel) keys
+    u64 *rootkeys = A.get<u64>(B), *rootsorted = A.get<u64>(B);
     out.g_root = A.get<i32>(B); out.g_lab = A.get<i32>(B); out.g_L = A.get<u32>(B);
     out.bs = A.get<i32>(R + 1);
     i32 *lab_hist = A.get<i32>(R + 1);
-    CHKA(A);
-    CHK(ulk_memset(lab_hist, 0, (size_t)(R + 1) * sizeof(i32), st));
-    ulk_launch(V, st, K_BasinRootInfo{bp, lab, Lr, pre, b_root, b_labkey});
-    ulk_launch(B, st, K_Iota{iota});
-    CHK(ulk_sort_pairs_u32(b_labkey, b_labsorted, iota, sorted_pre, B, st));
-    ulk_launch(B, st, K_BasinRegroup{sorted_pre, b_root, lab, Lr, gid_of_pre, out.g_root, out.g_lab, out.g_L, lab_hist});
-    CHK(ulk_exclusive_scan_i32(lab_hist, out.bs, R + 1, st));
     out.bas = A.get<i32>(V);
     CHKA(A);
-    ulk_launch(V, st, K_AssignBasin{bp, pre, gid_of_pre, out.bas});
-    A.release(flag); A.release(pre);
+    CHK(ulk_memset(ctr, 0, sizeof(i32), st));
+    CHK(ulk_memset(lab_hist, 0, (size_t)(R + 1) * sizeof(i32), st));
+    ulk_launch(V, st, K_CompressRoots{bp, lab, rootkeys, ctr + 0});
+    CHK(ulk_sort_keys_u64(rootkeys, rootsorted, B, st));
+    u32 *gid_at_root = best;         // free after the flow rounds
+    ulk_launch(B, st, K_BasinRegroup{rootsorted, Lr, gid_at_root, out.g_root, out.g_lab, out.g_L, lab_hist});
+    CHK(ulk_exclusive_scan_i32(lab_hist, out.bs, R + 1, st));
+    ulk_launch(V, st, K_AssignBasin{bp, gid_at_root, out.bas});
+    A.release(rootkeys); A.release(rootsorted);
 
-    // ---- per-basin accumulators
+    // ---- per-basin accumulators, join keys (area attribute), bottleneck lower bound: one pass
     out.b_size = A.get<i32>(B); out.b_top = A.get<u64>(B);
     u64 *ncross = A.get<u64>(1);
     if (need_stats) { out.bbmin = A.get<i32>(3 * (i64)B); out.bbmax = A.get<i32>(3 * (i64)B); out.csum = A.get<i64>(3 * (i64)B); }
+    i32 *hp = nullptr;
+    out.mw = mw;
+    if (need_join) { out.jk = A.get<u32>(V); hp = A.get<i32>(V); }
+    if (need_k3) out.b_k3 = A.get<u32>(B);
     CHKA(A);
     CHK(ulk_memset(out.b_size, 0, (size_t)B * sizeof(i32), st));
     CHK(ulk_memset(out.b_top, 0, (size_t)B * sizeof(u64), st));
     CHK(ulk_memset(ncross, 0, sizeof(u64), st));
+    CHK(ulk_memset(ctr, 0, 4 * sizeof(i32), st));
+    if (need_k3) CHK(ulk_memset(out.b_k3, 0, (size_t)B * sizeof(u32), st));
     if (need_stats) {
         ulk_fill<i32>(out.bbmin, 0x7fffffff, 3 * (i64)B, st);
         ulk_fill<i32>(out.bbmax, -0x7fffffff, 3 * (i64)B, st);
         CHK(ulk_memset(out.csum, 0, (size_t)B * 3 * sizeof(i64), st));
     }
-    ulk_launch_warp(V, st, K_BasinAccum{out.bas, lab, mw, pk, flowkey, ct, dm, out.b_size, out.b_top, ncross,
-                                   need_stats ? 1 : 0, out.bbmin, out.bbmax, out.csum});
+    ulk_launch_warp(V, st, K_BasinAccum{out.bas, lab, mw, pk, dm, out.b_size, out.b_top, ncross,
+                                        need_stats ? 1 : 0, out.bbmin, out.bbmax, out.csum,
+                                        need_join ? 1 : 0, out.g_L, out.jk, hp, ctr + 0,
+                                        need_k3 ? 1 : 0, out.b_k3});
+    ulk_launch(nflow, st, K_FlowTop{flow_root, flow_key, out.bas, ct, dm, out.b_top});
+    A.release(flow_root); A.release(flow_key);
     u64 h_ncross = 0;
     CHK(ulk_read(&h_ncross, ncross, 1, st));
-
-    // ---- join keys for the area attribute
-    out.mw = mw;
     if (need_join) {
-        out.jk = A.get<u32>(V);
-        i32 *hp = A.get<i32>(V);
-        CHKA(A);
-        CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
-        ulk_launch(V, st, K_JoinKey{out.bas, mw, pk, out.g_L, dm, out.jk, hp, ctr + 0});
-        CHK(ulk_read(hc, ctr, 8, st));
+        // plateau voxels above their basin level: minimax relaxation along spanning-tree edges
+        CHK(ulk_read(hc, ctr, 4, st));
         i32 nhp = hc[0];
         if (stats) stats->plateau_voxels += nhp;
         int it = 0;
         while (nhp > 0) {
             CHK(ulk_memset(ctr + 2, 0, sizeof(i32), st));
             ulk_launch(nhp, st, K_PlateauRelax{hp, lab, mw, pk, fmark, ct, dm, out.jk, ctr + 2});
-            CHK(ulk_read(hc, ctr, 8, st));
+            CHK(ulk_read(hc, ctr, 4, st));
             if (!hc[2]) break;
             if (++it > 1000000) ULK_FAIL(-4, "plateau relaxation did not converge");
         }
@@ -305,32 +301,26 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const Ul
 
     // ---- raster-key bottleneck per basin
     if (need_k3) {
-        out.b_k3 = A.get<u32>(B);
         i32 *P3 = bp;          // basin forest no longer needed
         i32 *nroot = A.get<i32>(B);
         CHKA(A);
-        CHK(ulk_memset(out.b_k3, 0, (size_t)B * sizeof(u32), st));
-        ulk_launch(V, st, K_MinKeyInBasin{out.bas, dm, out.b_k3});
         ulk_launch_warp(V, st, K_K3Init{out.bas, out.b_k3, dm.W, P3});
         ulk_launch(V, st, K_K3Union{out.bas, dm, out.b_k3, P3});
-        ulk_launch(V, st, K_Flatten{P3});
-        int it = 0;
-        for (;;) {
+        for (int it = 0;; ++it) {
             CHK(ulk_memset(nroot, 0, (size_t)B * sizeof(i32), st));
-            CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
-            ulk_launch(V, st, K_K3CountRoots{out.bas, P3, nroot, ctr + 0});
-            CHK(ulk_read(hc, ctr, 8, st));
+            CHK(ulk_memset(ctr, 0, sizeof(i32), st));
+            ulk_launch(V, st, K_K3FlattenCount{out.bas, P3, nroot, ctr + 0});
+            CHK(ulk_read(hc, ctr, 1, st));
             if (hc[0] == 0) break;
             if (stats) stats->k3_rounds += 1;
-            ulk_fill<u32>(best, ULK_NONE32, V, st);
+            if (it == 0) ulk_fill<u32>(best, ULK_NONE32, V, st);     // K_K3Hook resets what it used
             ulk_launch(V, st, K_K3FindBest{out.bas, dm, nroot, P3, best});
             ulk_launch(V, st, K_K3Hook{out.bas, dm, P3, best, out.b_k3});
-            ulk_launch(V, st, K_Flatten{P3});
-            if (++it > 100000) ULK_FAIL(-4, "bottleneck rounds did not converge");
+            if (it > 100000) ULK_FAIL(-4, "bottleneck rounds did not converge");
         }
         A.release(nroot);
     }
-    A.release(pk); A.release(state); A.release(Lr); A.release(best); A.release(flowkey); A.release(fmark);
+    A.release(pk); A.release(state); A.release(Lr); A.release(best); A.release(fmark);
     A.release(bp);
     if (stats) { stats->n_basins += B; stats->n_rag_edges += Eg; }
     return 0;
@@ -390,46 +380,34 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     F->shape[0] = dm.D; F->shape[1] = dm.H; F->shape[2] = dm.W;
     *result = F;
 
-    // ---- K1 threshold, contour staging
+    // ---- K1 threshold; contours are staged only when their dtype is not already float32
     UlkCt ct;
     ct.f = nullptr; ct.d = nullptr;
     float *ctf = nullptr; double *ctd = nullptr;
-    if (ulk_ct_is_f32(ct_dtype)) { ctf = A.get<float>(V); ct.f = ctf; } else { ctd = A.get<double>(V); ct.d = ctd; }
+    if (ct_dtype == ULK_F32) ct.f = (const float *)ctp;
+    else if (ulk_ct_is_f32(ct_dtype)) { ctf = A.get<float>(V); ct.f = ctf; }
+    else { ctd = A.get<double>(V); ct.d = ctd; }
     i32 *P = A.get<i32>(V);
     u32 *cmax = A.get<u32>(1);
     CHKA(A);
     CHK(ulk_memset(cmax, 0, 4, st));
     ulk_launch_warp(V, st, K_Threshold{fg, fg_dtype, prm->threshold, ctp, ct_dtype, ctf, ctd, P, cmax, dm.W});
-    // ---- connected components (4/6-connected), small-object removal
+    // ---- connected components (4/6-connected): union of runs, flatten + sizes + root list
     ulk_launch(V, st, K_CclUnion{P, dm});
-    ulk_launch(V, st, K_Flatten{P});
-    i32 *cnt = A.get<i32>(V);
+    i32 *cnt = A.get<i32>(V);            // sizes at the roots, later the component code at the roots
+    i32 *lab2 = A.get<i32>(V);           // region labels; until they are written: the root list
     i32 *ctr = A.get<i32>(4);
     CHKA(A);
     CHK(ulk_memset(cnt, 0, (size_t)V * sizeof(i32), st));
     CHK(ulk_memset(ctr, 0, 4 * sizeof(i32), st));
-    ulk_launch_warp(V, st, K_CountByRoot{P, cnt});
-    const i32 max_area_i = prm->max_area > 2147483646.0 ? 2147483646 : (i32)prm->max_area;
-    ulk_launch(V, st, K_CcStats{P, cnt, max_area_i, ctr});
+    u32 *roots0 = (u32 *)lab2;
+    ulk_launch_warp(V, st, K_FlattenCount{P, cnt, (i32 *)roots0, ctr});
     i32 hc[4];
     u32 h_cmax = 0;
     CHK(ulk_read(hc, ctr, 4, st));
     CHK(ulk_read(&h_cmax, cmax, 1, st));
-    i32 n_cc = hc[0], n_big = hc[1];
-    if (n_cc > 1) {
-        i32 max_size = (i32)(prm->min_area / prm->min_area_factor) - 1;
-        if (max_size >= 1) {
-            u8 *drop = A.get<u8>(V);
-            CHKA(A);
-            ulk_launch(V, st, K_RemoveSmall{P, cnt, max_size, drop});
-            ulk_launch(V, st, K_ApplyDrop{P, drop});
-            A.release(drop);
-            CHK(ulk_memset(ctr, 0, 4 * sizeof(i32), st));
-            ulk_launch(V, st, K_CcStats{P, cnt, max_area_i, ctr});
-            CHK(ulk_read(hc, ctr, 4, st));
-            n_cc = hc[0]; n_big = hc[1];
-        }
-    }
+    const i32 n_roots = hc[0];
+    const i32 max_area_i = prm->max_area > 2147483646.0 ? 2147483646 : (i32)prm->max_area;
     float cmaxf;
     memcpy(&cmaxf, &h_cmax, 4);
     int e2 = 0;
@@ -437,26 +415,39 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     const int fix_shift = 62 - e2;
     const double fixscale = ldexp(1.0, fix_shift);
     F->fix_shift = fix_shift;
+    if (n_roots == 0) { F->n_nodes = 0; F->stats = stats_local; return 0; }
+    // ---- per-component decisions on the (sorted) root list: small-object removal
+    //      (hierarchy.py:64-73), components above max_area, consecutive numbering
+    u32 *roots = A.get<u32>(n_roots);
+    i32 *keep = A.get<i32>(n_roots + 1), *keeppre = A.get<i32>(n_roots + 1);
+    i32 *big = A.get<i32>(n_roots + 1), *bigpre = A.get<i32>(n_roots + 1);
+    i32 *rsize = A.get<i32>(n_roots), *cc_big = A.get<i32>(n_roots);
+    CHKA(A);
+    CHK(ulk_sort_keys_u32(roots0, roots, n_roots, st));
+    i32 max_size = (i32)(prm->min_area / prm->min_area_factor) - 1;
+    int do_remove = n_roots > 1 && max_size >= 1;
+    ulk_launch(n_roots, st, K_RootFlags{roots, cnt, max_size, do_remove, max_area_i, keep, big, rsize});
+    CHK(ulk_memset(keep + n_roots, 0, sizeof(i32), st));
+    CHK(ulk_memset(big + n_roots, 0, sizeof(i32), st));
+    CHK(ulk_exclusive_scan_i32(keep, keeppre, (i64)n_roots + 1, st));
+    CHK(ulk_exclusive_scan_i32(big, bigpre, (i64)n_roots + 1, st));
+    i32 n_cc = 0, n_big = 0;
+    CHK(ulk_read(&n_cc, keeppre + n_roots, 1, st));
+    CHK(ulk_read(&n_big, bigpre + n_roots, 1, st));
     if (n_cc == 0) { F->n_nodes = 0; F->stats = stats_local; return 0; }
+    i32 *code = cnt;
+    ulk_launch(n_roots, st, K_RootCode{roots, keep, keeppre, big, bigpre, code, cc_big});
+    A.release(roots); A.release(keep); A.release(keeppre); A.release(big); A.release(bigpre); A.release(rsize);
 
     // ---- region labels: components, oversegmented where area > max_area
-    i32 *flag = A.get<i32>(V + 1), *ccpre = A.get<i32>(V + 1);
-    i32 *lab2 = A.get<i32>(V);
-    CHKA(A);
-    ulk_launch(V, st, K_FlagRoots{P, flag});
-    CHK(ulk_memset(flag + V, 0, sizeof(i32), st));
-    CHK(ulk_exclusive_scan_i32(flag, ccpre, V + 1, st));
     i32 R = n_cc;
     if (n_big == 0) {
-        ulk_launch(V, st, K_LabelSmallOnly{P, ccpre, lab2});
+        ulk_launch(V, st, K_LabelCc{P, code, cc_big, 0, lab2});
     } else {
         UlkArena AA;
-        i32 *bigpre = AA.get<i32>(V + 1), *labA = AA.get<i32>(V);
+        i32 *labA = AA.get<i32>(V);
         CHKA(AA);
-        ulk_launch(V, st, K_FlagBigRoots{P, cnt, max_area_i, flag});
-        CHK(ulk_memset(flag + V, 0, sizeof(i32), st));
-        CHK(ulk_exclusive_scan_i32(flag, bigpre, V + 1, st));
-        ulk_launch(V, st, K_LabelBigCc{P, cnt, bigpre, max_area_i, labA});
+        ulk_launch(V, st, K_LabelCc{P, code, cc_big, 1, labA});
         VoxelStage va;
         CHK(voxel_stage(st, AA, dm, ct, labA, n_big, true, false, false, fixscale, va, &stats_local));
         UlkHierScratch S;
@@ -475,8 +466,8 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         u32 *c0 = AA.get<u32>(nrec), *c1 = AA.get<u32>(nrec);
         i32 *label_of_rec = AA.get<i32>(nrec);
         CHKA(AA);
-        ulk_launch(V, st, K_SmallCcRecords{P, cnt, ccpre, max_area_i, rec_cc, rec_w, rec_k});
-        ulk_launch(va.B, st, K_RegionRecords{region_of, rkey_w, rkey_k, va.g_root, P, ccpre, n_cc, rec_cc, rec_w, rec_k});
+        ulk_launch(n_cc, st, K_SmallCcRecords{cc_big, rec_cc, rec_w, rec_k});
+        ulk_launch(va.B, st, K_RegionRecords{region_of, rkey_w, rkey_k, va.g_root, P, code, n_cc, rec_cc, rec_w, rec_k});
         ulk_launch(nrec, st, K_Iota{perm0});
         CHK(ulk_sort_pairs_u64(rec_k, k1, perm0, perm1, nrec, st));           // by tie key
         ulk_launch(nrec, st, K_Gather<u64>{rec_w, perm1, k0});
@@ -484,7 +475,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         ulk_launch(nrec, st, K_Gather<u32>{rec_cc, perm0, c0});
         CHK(ulk_sort_pairs_u32(c0, c1, perm0, perm1, nrec, st));              // then by component
         ulk_launch(nrec, st, K_RankToLabel{perm1, c1, label_of_rec});
-        ulk_launch(V, st, K_WriteLabels{P, cnt, ccpre, max_area_i, n_cc, va.bas, region_of, label_of_rec, lab2});
+        ulk_launch(V, st, K_WriteLabels{P, code, cc_big, n_cc, va.bas, region_of, label_of_rec, lab2});
         // number of valid records = regions
         i32 *nvalid = AA.get<i32>(nrec + 1), *nvpre = AA.get<i32>(nrec + 1);
         CHKA(AA);
@@ -494,7 +485,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         CHK(ulk_read(&R, nvpre + nrec, 1, st));
         CHK(ulk_sync(st));
     }
-    A.release(flag); A.release(ccpre); A.release(cnt); A.release(P);
+    A.release(cc_big); A.release(cnt); A.release(P);
     if (keep_labels) {
         F->labels = keep_alloc<i32>(V);
         if (!F->labels) return -3;

@@ -52,7 +52,7 @@ struct K_Threshold {
     {
         double f = ulk_load_as_double(fg, fgt, v);
         double c = ulk_load_as_double(ct, ctt, v);
-        if (ctf) ctf[v] = (float)c; else ctd[v] = c;
+        if (ctf) ctf[v] = (float)c; else if (ctd) ctd[v] = c;
         float a = (float)(c < 0 ? -c : c);
         bits = 0;
         if (a == a && a <= 3.0e38f) memcpy(&bits, &a, 4);
@@ -108,41 +108,69 @@ struct K_Flatten {
     i32 *P;
     ULK_D void operator()(i64 v) const { if (P[v] >= 0) P[v] = ulk_vfind(P, (i32)v); }
 };
-struct K_CountByRoot {
-    const i32 *P; i32 *cnt;
+// flatten, component sizes (one atomic per group of lanes with the same root) and root list
+struct K_FlattenCount {
+    i32 *P; i32 *cnt; i32 *roots; i32 *nroots;
 #ifdef ULK_EMU
-    void operator()(i64 v) const { if (P[v] >= 0) cnt[P[v]] += 1; }
+    void operator()(i64 v) const
+    {
+        if (P[v] < 0) return;
+        i32 r = ulk_vfind(P, (i32)v);
+        P[v] = r;
+        cnt[r] += 1;
+        if (r == (i32)v) roots[(*nroots)++] = r;
+    }
 #else
     ULK_D void warp(i64 v, bool valid) const
     {
-        i32 r = valid ? P[v] : -1;
+        i32 r = -1;
+        if (valid && P[v] >= 0) { r = ulk_vfind(P, (i32)v); P[v] = r; }
         u32 grp = __match_any_sync(0xffffffffu, r);
-        if (r >= 0 && (threadIdx.x & 31) == __ffs(grp) - 1) atomicAdd(&cnt[r], __popc(grp));
+        if (r < 0) return;
+        if ((threadIdx.x & 31) == __ffs(grp) - 1) atomicAdd(&cnt[r], __popc(grp));
+        if (r == (i32)v) roots[atomicAdd(nroots, 1)] = r;
     }
 #endif
 };
-// counts components and components above max_area
-struct K_CcStats {
-    const i32 *P; const i32 *cnt; i32 max_area; i32 *out;   // out[0]=n_cc out[1]=n_big out[2]=n_fg
-    ULK_D void operator()(i64 v) const
+// per component, over the root list in raster order: morphology.remove_small_objects drops
+// components with count <= max_size (only when there is more than one component,
+// hierarchy.py:64-73); `big` marks kept components above max_area
+struct K_RootFlags {
+    const u32 *roots; const i32 *cnt; i32 max_size; int do_remove; i32 max_area;
+    i32 *keep; i32 *big; i32 *size;
+    ULK_D void operator()(i64 i) const
     {
-        if (P[v] != (i32)v) return;
-        ulk_atomic_add(&out[0], 1);
-        if (cnt[v] > max_area) ulk_atomic_add(&out[1], 1);
+        i32 s = cnt[roots[i]];
+        size[i] = s;
+        i32 k = !(do_remove && s <= max_size);
+        keep[i] = k;
+        big[i] = k && s > max_area;
     }
 };
-// morphology.remove_small_objects(labels, max_size=m): drop components with count <= m
-struct K_RemoveSmall {
-    i32 *P; const i32 *cnt; i32 max_size; u8 *drop;
+// code[root] = 1-based index among the kept components (0: dropped); cc_big[index] = index
+// among the components above max_area or -1
+struct K_RootCode {
+    const u32 *roots; const i32 *keep, *keeppre, *big, *bigpre; i32 *code; i32 *cc_big;
+    ULK_D void operator()(i64 i) const
+    {
+        u32 r = roots[i];
+        if (!keep[i]) { code[r] = 0; return; }
+        i32 c = keeppre[i];
+        code[r] = c + 1;
+        cc_big[c] = big[i] ? bigpre[i] : -1;
+    }
+};
+// mode 0: every kept component gets its index as label; mode 1: only the components above
+// max_area, numbered among themselves (input of the oversegmentation pass)
+struct K_LabelCc {
+    const i32 *P; const i32 *code; const i32 *cc_big; int mode; i32 *lab;
     ULK_D void operator()(i64 v) const
     {
         i32 r = P[v];
-        drop[v] = (r >= 0 && cnt[r] <= max_size) ? 1 : 0;
+        i32 c = r < 0 ? 0 : code[r];
+        if (mode == 0) lab[v] = c;
+        else lab[v] = (c > 0 && cc_big[c - 1] >= 0) ? cc_big[c - 1] + 1 : 0;
     }
-};
-struct K_ApplyDrop {
-    i32 *P; const u8 *drop;
-    ULK_D void operator()(i64 v) const { if (drop[v]) P[v] = -1; }
 };
 struct K_FlagRoots {
     const i32 *P; i32 *flag;
@@ -195,18 +223,20 @@ ULK_HD ULK_INLINE i32 ulk_edge_other(u32 key, i32 v, const UlkDims &dm)
 // smaller voxel as root.  state: 0 growing, 1 minimum (basin seed)
 struct K_Hook1 {
     const i32 *lab; const u32 *mw, *pk; UlkDims dm;
-    i32 *bp; u8 *state; u32 *Lr; u32 *best; u32 *flowkey;
+    i32 *bp; u8 *state; u32 *Lr; u32 *best; i32 *nbasins;
     ULK_D void operator()(i64 vv) const
     {
         i32 v = (i32)vv;
-        best[v] = ULK_NONE32;
-        flowkey[v] = ULK_NONE32;
         state[v] = 0;
         if (lab[v] <= 0) { bp[v] = -1; return; }
         u32 k = pk[v];
-        if (k == ULK_NONE32) { bp[v] = v; state[v] = 1; Lr[v] = ULK_NONE32; return; }
+        if (k == ULK_NONE32) {
+            bp[v] = v; state[v] = 1; Lr[v] = ULK_NONE32; best[v] = ULK_NONE32;
+            ulk_atomic_add(nbasins, 1);
+            return;
+        }
         i32 u = ulk_edge_other(k, v, dm);
-        if (pk[u] == k && v < u) { bp[v] = v; Lr[v] = mw[v]; }
+        if (pk[u] == k && v < u) { bp[v] = v; Lr[v] = mw[v]; best[v] = ULK_NONE32; }
         else bp[v] = u;
     }
 };
@@ -214,18 +244,50 @@ struct K_Compress {
     i32 *bp;
     ULK_D void operator()(i64 v) const { if (bp[v] >= 0) bp[v] = ulk_vfind(bp, (i32)v); }
 };
-// candidates of the flow rounds: voxels whose steepest weight equals their supervertex level
-struct K_CandInit {
-    const i32 *bp; const u32 *mw; const u32 *Lr; const u8 *state;
+#ifndef ULK_EMU
+// appends `value` of every lane with `flag` to a list: one atomic per warp
+ULK_D ULK_INLINE void ulk_warp_append(bool flag, i32 value, i32 *list, i32 *counter)
+{
+    u32 m = __ballot_sync(0xffffffffu, flag);
+    if (!m) return;
+    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+    i32 base = 0;
+    if (lane == leader) base = atomicAdd(counter, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (flag) list[base + __popc(m & ((1u << lane) - 1u))] = value;
+}
+#endif
+// path compression of the hook forest, fused with the lists of the flow rounds: growing
+// roots, and candidates = voxels whose steepest weight equals their supervertex level
+struct K_CompressCand {
+    i32 *bp; const u32 *mw; const u32 *Lr; const u8 *state;
     i32 *cand; i32 *ncand; i32 *groots; i32 *ngroots;
-    ULK_D void operator()(i64 vv) const
+#ifdef ULK_EMU
+    void operator()(i64 vv) const
     {
         i32 v = (i32)vv;
-        i32 r = bp[v];
-        if (r < 0) return;
-        if (r == v && state[v] == 0) groots[ulk_atomic_add(ngroots, 1)] = v;
-        if (state[r] == 0 && mw[v] == Lr[r]) cand[ulk_atomic_add(ncand, 1)] = v;
+        if (bp[v] < 0) return;
+        i32 r = ulk_vfind(bp, v);
+        bp[v] = r;
+        if (r == v && state[v] == 0) groots[(*ngroots)++] = v;
+        if (state[r] == 0 && mw[v] == Lr[r]) cand[(*ncand)++] = v;
     }
+#else
+    ULK_D void warp(i64 vv, bool valid) const
+    {
+        i32 v = (i32)vv;
+        bool is_groot = false, is_cand = false;
+        if (valid && bp[v] >= 0) {
+            i32 r = ulk_vfind(bp, v);
+            bp[v] = r;
+            bool growing = state[r] == 0;
+            is_groot = r == v && growing;
+            is_cand = growing && mw[v] == Lr[r];
+        }
+        ulk_warp_append(is_groot, v, groots, ngroots);
+        ulk_warp_append(is_cand, v, cand, ncand);
+    }
+#endif
 };
 // a growing supervertex looks for its minimum-key outgoing edge at its own level
 struct K_FindFlow {
@@ -282,76 +344,109 @@ struct K_Decide1 {
 };
 struct K_Decide2 {
     const i32 *groots; const i32 *tgt;
-    i32 *bp; u8 *state; u32 *best; u32 *flowkey; u8 *fmark;
+    i32 *bp; u8 *state; u32 *best; u8 *fmark;
     i32 *groots2; i32 *ngroots2;
+    i32 *flow_root; u32 *flow_key; i32 *nflow; i32 *nbasins;
     ULK_D void operator()(i64 i) const
     {
         i32 r = groots[i];
         i32 t = tgt[i];
         u32 k = best[r];
         best[r] = ULK_NONE32;
-        if (t == -1) { state[r] = 1; return; }
+        if (t == -1) { state[r] = 1; ulk_atomic_add(nbasins, 1); return; }
         if (t == -2) { groots2[ulk_atomic_add(ngroots2, 1)] = r; return; }
         bp[r] = t;
-        flowkey[r] = k;
+        i32 j = ulk_atomic_add(nflow, 1);
+        flow_root[j] = r; flow_key[j] = k;
         u32 a = k / 3u, d = k % 3u;
         ulk_atomic_or((u32 *)(fmark + (a & ~3u)), (1u << d) << (8u * (a & 3u)));
     }
 };
 
 // ------------------------------------------------------------------ basins
-struct K_BasinRootInfo {     // per basin root: label and level
-    const i32 *bp; const i32 *lab; const u32 *Lr; const i32 *pre;   // pre: exclusive scan of root flags
-    i32 *b_root; u32 *b_labkey;
+// second path compression; every basin root appends (region label, root voxel): sorting
+// these keys numbers the basins grouped by region, in raster order of their roots
+struct K_CompressRoots {
+    i32 *bp; const i32 *lab; u64 *rootkeys; i32 *nroots;
     ULK_D void operator()(i64 vv) const
     {
         i32 v = (i32)vv;
-        if (bp[v] != v) return;
-        i32 i = pre[v];
-        b_root[i] = v;
-        b_labkey[i] = (u32)lab[v];
+        if (bp[v] < 0) return;
+        i32 r = ulk_vfind(bp, v);
+        bp[v] = r;
+        if (r == v) rootkeys[ulk_atomic_add(nroots, 1)] = ((u64)(u32)lab[v] << 32) | (u32)v;
     }
 };
-struct K_BasinRegroup {      // sorted position -> global basin id
-    const u32 *sorted_pre; const i32 *b_root; const i32 *lab; const u32 *Lr;
-    i32 *gid_of_pre; i32 *g_root; i32 *g_lab; u32 *g_L; i32 *lab_hist;
+struct K_BasinRegroup {      // sorted position = global basin id
+    const u64 *sorted; const u32 *Lr;
+    u32 *gid_at_root; i32 *g_root; i32 *g_lab; u32 *g_L; i32 *lab_hist;
     ULK_D void operator()(i64 g) const
     {
-        i32 p = (i32)sorted_pre[g];
-        gid_of_pre[p] = (i32)g;
-        i32 v = b_root[p];
+        u64 key = sorted[g];
+        i32 v = (i32)(u32)key, l = (i32)(key >> 32);
+        gid_at_root[v] = (u32)g;
         g_root[g] = v;
-        g_lab[g] = lab[v];
+        g_lab[g] = l;
         g_L[g] = Lr[v];
-        ulk_atomic_add(&lab_hist[lab[v] - 1], 1);
+        ulk_atomic_add(&lab_hist[l - 1], 1);
     }
 };
 struct K_AssignBasin {
-    const i32 *bp; const i32 *pre; const i32 *gid_of_pre;
+    const i32 *bp; const u32 *gid_at_root;
     i32 *bas;
-    ULK_D void operator()(i64 v) const { i32 r = bp[v]; bas[v] = r < 0 ? -1 : gid_of_pre[pre[r]]; }
+    ULK_D void operator()(i64 v) const { i32 r = bp[v]; bas[v] = r < 0 ? -1 : (i32)gid_at_root[r]; }
 };
-// per-basin size, spanning-tree top key, crossing-edge count, optional statistics
+// flow edges are spanning-tree edges of the basin of their supervertex
+struct K_FlowTop {
+    const i32 *flow_root; const u32 *flow_key; const i32 *bas; UlkCt ct; UlkDims dm; u64 *b_top;
+    ULK_D void operator()(i64 j) const
+    {
+        u32 fk = flow_key[j];
+        i32 a = (i32)(fk / 3u), e = a + dm.stride((int)(fk % 3u));
+        ulk_atomic_max(&b_top[bas[flow_root[j]]], ((u64)ulk_f2ord(ct.w(a, e)) << 32) | fk);
+    }
+};
+// One pass over the voxels once basin ids exist:
+//  * per-basin size, largest spanning-tree key, bbox / coordinate sums, and the number of
+//    voxel edges between different basins of a region (sizes the adjacency hash table);
+//  * join keys for the area attribute: J(v) = (mw[v], jk[v]) is the Kruskal position at which
+//    voxel v joins a component that holds a regional minimum; core voxels (mw == basin level)
+//    belong to the minimum, plateau voxels above it go to the relaxation list `hp`;
+//  * K0[basin] = max over its voxels of their smallest in-basin edge key, the lower bound of
+//    the basin's raster-key bottleneck (see K_K3*).
 struct K_BasinAccum {
-    const i32 *bas; const i32 *lab; const u32 *mw, *pk; const u32 *flowkey; UlkCt ct; UlkDims dm;
+    const i32 *bas; const i32 *lab; const u32 *mw, *pk; UlkDims dm;
     i32 *b_size; u64 *b_top; u64 *ncross;
     int want_stats; i32 *bbmin, *bbmax; i64 *csum;
-    // this voxel's contribution: largest spanning-tree key it carries, forward crossing edges
-    ULK_D ULK_INLINE void own(i32 v, i32 b, u64 &top, u32 &nc, i32 c[3]) const
+    int want_join; const u32 *b_L; u32 *jk; i32 *hp; i32 *nhp;
+    int want_k0; u32 *K0;
+    struct Own { u64 top; u32 nc; u32 kmin; i32 c[3]; bool plateau; };
+    ULK_D ULK_INLINE void own(i32 v, i32 b, Own &o) const
     {
-        top = 0;
-        if (pk[v] != ULK_NONE32) top = ((u64)mw[v] << 32) | pk[v];
-        u32 fk = flowkey[v];
-        if (fk != ULK_NONE32) {
-            i32 a = (i32)(fk / 3u), e = a + dm.stride((int)(fk % 3u));
-            u64 t2 = ((u64)ulk_f2ord(ct.w(a, e)) << 32) | fk;
-            if (t2 > top) top = t2;
+        const u32 m = mw[v], k = pk[v];
+        o.top = k != ULK_NONE32 ? ((u64)m << 32) | k : 0;
+        dm.coords(v, o.c[0], o.c[1], o.c[2]);
+        const i32 l = lab[v];
+        o.nc = 0;
+        o.kmin = ULK_NONE32;
+        for (int d = 0; d < 3; ++d) {
+            const i32 st = dm.stride(d);
+            if (dm.fwd(d, o.c[0], o.c[1], o.c[2])) {
+                i32 bu = bas[v + st];
+                if (bu == b) { u32 kk = 3u * (u32)v + d; if (kk < o.kmin) o.kmin = kk; }
+                else if (lab[v + st] == l) ++o.nc;
+            }
+            if (want_k0 && dm.bwd(d, o.c[0], o.c[1], o.c[2]) && bas[v - st] == b) {
+                u32 kk = 3u * (u32)(v - st) + d;
+                if (kk < o.kmin) o.kmin = kk;
+            }
         }
-        dm.coords(v, c[0], c[1], c[2]);
-        i32 l = lab[v];
-        nc = 0;
-        for (int d = 0; d < 3; ++d)
-            if (dm.fwd(d, c[0], c[1], c[2])) { i32 u = v + dm.stride(d); if (lab[u] == l && bas[u] != b) ++nc; }
+        o.plateau = false;
+        if (want_join) {
+            if (m == b_L[b] || k == ULK_NONE32) jk[v] = ULK_JK_CORE;
+            else if (mw[ulk_edge_other(k, v, dm)] < m) jk[v] = k;
+            else { jk[v] = ULK_NONE32; o.plateau = true; }
+        }
     }
 #ifdef ULK_EMU
     void operator()(i64 vv) const
@@ -359,16 +454,18 @@ struct K_BasinAccum {
         i32 v = (i32)vv;
         i32 b = bas[v];
         if (b < 0) return;
-        u64 top; u32 nc; i32 c[3];
-        own(v, b, top, nc, c);
+        Own o;
+        own(v, b, o);
         b_size[b] += 1;
-        if (top > b_top[b]) b_top[b] = top;
-        *ncross += nc;
+        if (o.top > b_top[b]) b_top[b] = o.top;
+        *ncross += o.nc;
+        if (o.plateau) hp[(*nhp)++] = v;
+        if (want_k0 && o.kmin != ULK_NONE32 && o.kmin > K0[b]) K0[b] = o.kmin;
         if (want_stats)
             for (int d = 0; d < 3; ++d) {
-                ulk_atomic_min(&bbmin[3 * b + d], c[d]);
-                ulk_atomic_max(&bbmax[3 * b + d], c[d]);
-                csum[3 * b + d] += c[d];
+                ulk_atomic_min(&bbmin[3 * b + d], o.c[d]);
+                ulk_atomic_max(&bbmax[3 * b + d], o.c[d]);
+                csum[3 * b + d] += o.c[d];
             }
     }
 #else
@@ -379,24 +476,30 @@ struct K_BasinAccum {
         const int lane = threadIdx.x & 31;
         i32 v = (i32)vv;
         i32 b = valid ? bas[v] : -1;
-        u64 top = 0; u32 nc = 0; i32 c[3] = {0, 0, 0};
-        if (b >= 0) own(v, b, top, nc, c);
-        u32 nct = __reduce_add_sync(0xffffffffu, nc);
+        Own o;
+        o.top = 0; o.nc = 0; o.kmin = ULK_NONE32; o.c[0] = o.c[1] = o.c[2] = 0; o.plateau = false;
+        if (b >= 0) own(v, b, o);
+        u32 nct = __reduce_add_sync(0xffffffffu, o.nc);
         if (lane == 0 && nct) atomicAdd((unsigned long long *)ncross, (unsigned long long)nct);
+        if (want_join) ulk_warp_append(o.plateau, v, hp, nhp);
         u32 grp = __match_any_sync(0xffffffffu, b);
         if (b < 0) return;
         const bool lead = lane == __ffs(grp) - 1;
-        u32 thi = __reduce_max_sync(grp, (u32)(top >> 32));
-        u32 tlo = __reduce_max_sync(grp, (u32)(top >> 32) == thi ? (u32)top : 0u);
+        u32 thi = __reduce_max_sync(grp, (u32)(o.top >> 32));
+        u32 tlo = __reduce_max_sync(grp, (u32)(o.top >> 32) == thi ? (u32)o.top : 0u);
         if (lead) {
             atomicAdd(&b_size[b], __popc(grp));
             u64 t = ((u64)thi << 32) | tlo;
             if (t) atomicMax((unsigned long long *)&b_top[b], (unsigned long long)t);
         }
+        if (want_k0) {
+            u32 km = __reduce_max_sync(grp, o.kmin == ULK_NONE32 ? 0u : o.kmin);
+            if (lead && km > K0[b]) atomicMax(&K0[b], km);
+        }
         if (want_stats) {
             for (int d = 0; d < 3; ++d) {
-                i32 lo = __reduce_min_sync(grp, c[d]), hi = __reduce_max_sync(grp, c[d]);
-                u32 sm = __reduce_add_sync(grp, (u32)c[d]);
+                i32 lo = __reduce_min_sync(grp, o.c[d]), hi = __reduce_max_sync(grp, o.c[d]);
+                u32 sm = __reduce_add_sync(grp, (u32)o.c[d]);
                 if (lead) {
                     atomicMin(&bbmin[3 * b + d], lo);
                     atomicMax(&bbmax[3 * b + d], hi);
@@ -409,22 +512,6 @@ struct K_BasinAccum {
 };
 
 // ------------------------------------------------------------------ join keys (area hierarchy)
-// J(v) = (mw[v], jk[v]): the Kruskal position at which voxel v joins a component that
-// holds a regional minimum.  Core voxels (mw == basin level) belong to the minimum.
-struct K_JoinKey {
-    const i32 *bas; const u32 *mw, *pk; const u32 *b_L; UlkDims dm;
-    u32 *jk; i32 *hp; i32 *nhp;
-    ULK_D void operator()(i64 vv) const
-    {
-        i32 v = (i32)vv;
-        i32 b = bas[v];
-        if (b < 0) { jk[v] = ULK_JK_CORE; return; }
-        if (mw[v] == b_L[b] || pk[v] == ULK_NONE32) { jk[v] = ULK_JK_CORE; return; }
-        i32 u = ulk_edge_other(pk[v], v, dm);
-        if (mw[u] < mw[v]) jk[v] = pk[v];
-        else { jk[v] = ULK_NONE32; hp[ulk_atomic_add(nhp, 1)] = v; }
-    }
-};
 // plateau voxels above the basin level: minimax relaxation along spanning-tree edges
 struct K_PlateauRelax {
     const i32 *hp; const i32 *lab; const u32 *mw, *pk; const u8 *fmark; UlkCt ct; UlkDims dm;
@@ -564,23 +651,6 @@ struct K_Hist {
 // alone and the basin's altitude-0 node is created by the LAST edge it accepts: the
 // bottleneck of the raster-key MST.  K0 = max over voxels of their smallest in-basin edge
 // key is a lower bound that is tight whenever edges <= K0 already connect the basin.
-struct K_MinKeyInBasin {
-    const i32 *bas; UlkDims dm; u32 *K0;
-    ULK_D void operator()(i64 vv) const
-    {
-        i32 v = (i32)vv;
-        i32 b = bas[v];
-        if (b < 0) return;
-        i32 z, y, x;
-        dm.coords(v, z, y, x);
-        u32 k = ULK_NONE32;
-        for (int d = 0; d < 3; ++d) {
-            if (dm.bwd(d, z, y, x)) { i32 u = v - dm.stride(d); if (bas[u] == b) { u32 kk = 3u * (u32)u + d; if (kk < k) k = kk; } }
-            if (dm.fwd(d, z, y, x)) { i32 u = v + dm.stride(d); if (bas[u] == b) { u32 kk = 3u * (u32)v + d; if (kk < k) k = kk; } }
-        }
-        if (k != ULK_NONE32 && k > K0[b]) ulk_atomic_max(&K0[b], k);
-    }
-};
 // edges of a basin whose raster key is <= K0[basin]; runs of x edges inside a warp segment are
 // hooked to their first voxel at initialisation (same scheme as the component labelling)
 struct K_K3Init {
@@ -627,11 +697,14 @@ struct K_K3Union {
         }
     }
 };
-struct K_K3CountRoots {
-    const i32 *bas; const i32 *P; i32 *nroot; i32 *nmulti;
+struct K_K3FlattenCount {
+    const i32 *bas; i32 *P; i32 *nroot; i32 *nmulti;
     ULK_D void operator()(i64 v) const
     {
-        if (bas[v] < 0 || P[v] != (i32)v) return;
+        if (P[v] < 0) return;
+        i32 r = ulk_vfind(P, (i32)v);
+        P[v] = r;
+        if (r != (i32)v) return;
         i32 old = ulk_atomic_add(&nroot[bas[v]], 1);
         if (old == 1) ulk_atomic_add(nmulti, 1);
     }
@@ -672,26 +745,21 @@ struct K_K3Hook {
 
 // ------------------------------------------------------------------ label writing (pass A -> pass B)
 struct K_SmallCcRecords {   // one region record per component that is not oversegmented
-    const i32 *P; const i32 *cnt; const i32 *ccpre; i32 max_area;
-    u32 *rec_cc; u64 *rec_w; u64 *rec_k;
-    ULK_D void operator()(i64 vv) const
+    const i32 *cc_big; u32 *rec_cc; u64 *rec_w; u64 *rec_k;
+    ULK_D void operator()(i64 c) const
     {
-        i32 v = (i32)vv;
-        if (P[v] != v) return;
-        i32 c = ccpre[v];
-        bool big = cnt[v] > max_area;
-        rec_cc[c] = big ? ULK_NONE32 : (u32)c;
+        rec_cc[c] = cc_big[c] >= 0 ? ULK_NONE32 : (u32)c;
         rec_w[c] = 0; rec_k[c] = 0;
     }
 };
 struct K_RegionRecords {    // one record per cut region of an oversegmented component
-    const i32 *region_of; const u64 *rkey_w, *rkey_k; const i32 *g_root; const i32 *P; const i32 *ccpre; i32 ncc;
+    const i32 *region_of; const u64 *rkey_w, *rkey_k; const i32 *g_root; const i32 *P; const i32 *code; i32 ncc;
     u32 *rec_cc; u64 *rec_w; u64 *rec_k;
     ULK_D void operator()(i64 g) const
     {
         i32 i = ncc + (i32)g;
         if (region_of[g] != (i32)g) { rec_cc[i] = ULK_NONE32; rec_w[i] = 0; rec_k[i] = 0; return; }
-        rec_cc[i] = (u32)ccpre[P[g_root[g]]];
+        rec_cc[i] = (u32)(code[P[g_root[g]]] - 1);
         rec_w[i] = rkey_w[g]; rec_k[i] = rkey_k[g];
     }
 };
@@ -703,26 +771,15 @@ struct K_RankToLabel {
     }
 };
 struct K_WriteLabels {
-    const i32 *P; const i32 *cnt; const i32 *ccpre; i32 max_area; i32 ncc;
+    const i32 *P; const i32 *code; const i32 *cc_big; i32 ncc;
     const i32 *basA; const i32 *region_of; const i32 *label_of_rec;
     i32 *lab2;
     ULK_D void operator()(i64 v) const
     {
         i32 r = P[v];
-        if (r < 0) { lab2[v] = 0; return; }
-        if (cnt[r] > max_area) lab2[v] = label_of_rec[ncc + region_of[basA[v]]];
-        else lab2[v] = label_of_rec[ccpre[r]];
+        i32 c = r < 0 ? 0 : code[r];
+        if (c == 0) { lab2[v] = 0; return; }
+        if (cc_big[c - 1] >= 0) lab2[v] = label_of_rec[ncc + region_of[basA[v]]];
+        else lab2[v] = label_of_rec[c - 1];
     }
-};
-struct K_LabelBigCc {       // pass A works only on the oversize components
-    const i32 *P; const i32 *cnt; const i32 *bigpre; i32 max_area; i32 *labA;
-    ULK_D void operator()(i64 v) const
-    {
-        i32 r = P[v];
-        labA[v] = (r >= 0 && cnt[r] > max_area) ? bigpre[r] + 1 : 0;
-    }
-};
-struct K_FlagBigRoots {
-    const i32 *P; const i32 *cnt; i32 max_area; i32 *flag;
-    ULK_D void operator()(i64 v) const { flag[v] = (P[v] == (i32)v && cnt[v] > max_area) ? 1 : 0; }
 };
