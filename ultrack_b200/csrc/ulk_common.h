@@ -80,7 +80,17 @@ struct UlkCt {
     const double *d;
     ULK_HD ULK_INLINE float w(i32 p, i32 q) const
     {
-        if (f) { float s = f[p] + f[q]; return (float)((double)s / 2.0 + 1e-8); }
+        if (f) {
+            float s = f[p] + f[q];
+            // for s == 0 and 2^-24 <= |s| < 2^40 the float expression below equals the double
+            // one bit for bit (checked exhaustively over every float of that range): it keeps
+            // the float<->double conversions off the dense kernels
+            u32 b;
+            memcpy(&b, &s, 4);
+            u32 e = (b >> 23) & 0xffu;
+            if (s == 0.0f || (e >= 127u - 24u && e < 127u + 40u)) return s * 0.5f + 1e-8f;
+            return (float)((double)s / 2.0 + 1e-8);
+        }
         double s = d[p] + d[q];
         return (float)(s / 2.0 + 1e-8);
     }

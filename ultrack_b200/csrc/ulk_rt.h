@@ -93,6 +93,13 @@ ULK_D ULK_INLINE u32 ulk_funnel_r(u32 lo, u32 hi, u32 s) { return __funnelshift_
 template <class F> void ulk_launch(i64 n, ulk_stream_t, const F &f) { for (i64 i = 0; i < n; ++i) f(i); }
 // warp-cooperative kernels: the emulation runs the functor's scalar statement `operator()`
 template <class F> void ulk_launch_warp(i64 n, ulk_stream_t, const F &f) { for (i64 i = 0; i < n; ++i) f(i); }
+// voxel kernels that need coordinates: f(v, z, y, x) for every voxel of a [D,H,W] frame
+template <class F> void ulk_launch_vox(i32 D, i32 H, i32 W, ulk_stream_t, const F &f)
+{
+    i64 v = 0;
+    for (i32 z = 0; z < D; ++z) for (i32 y = 0; y < H; ++y) for (i32 x = 0; x < W; ++x) f(v++, z, y, x);
+}
+template <class F> void ulk_launch_vox_warp(i32 D, i32 H, i32 W, ulk_stream_t s, const F &f) { ulk_launch_vox(D, H, W, s, f); }
 #else
 template <class F> __global__ void __launch_bounds__(256) ulk_kernel(i64 n, F f)
 {
@@ -126,6 +133,38 @@ template <class F> void ulk_launch_warp(i64 n, ulk_stream_t s, const F &f)
     i64 grid = (n + 255) / 256;
     if (g_ulk_prof_on) ulk_prof_begin(typeid(F).name(), s);
     ulk_kernel_warp<F><<<(unsigned)grid, 256, 0, s>>>(n, f);
+    if (g_ulk_prof_on) ulk_prof_end(s);
+    ++g_ulk_launches;
+}
+// voxel kernels that need coordinates: 3-D grid (x blocks, y, z), no index division; lane l of a
+// warp holds x = 32*k + l of one row.  The _warp form calls F::warp(v, z, y, x, valid) from
+// every thread (valid = x < W) so the body may use full-mask warp collectives.
+#define ULK_VOX_BX 128
+template <class F> __global__ void __launch_bounds__(ULK_VOX_BX) ulk_kernel_vox(i32 H, i32 W, F f)
+{
+    i32 x = blockIdx.x * ULK_VOX_BX + threadIdx.x, y = blockIdx.y, z = blockIdx.z;
+    if (x < W) f(((i64)z * H + y) * W + x, z, y, x);
+}
+template <class F> __global__ void __launch_bounds__(ULK_VOX_BX) ulk_kernel_vox_warp(i32 H, i32 W, F f)
+{
+    i32 x = blockIdx.x * ULK_VOX_BX + threadIdx.x, y = blockIdx.y, z = blockIdx.z;
+    f.warp(((i64)z * H + y) * W + x, z, y, x, x < W);
+}
+template <class F> void ulk_launch_vox(i32 D, i32 H, i32 W, ulk_stream_t s, const F &f)
+{
+    if (D <= 0 || H <= 0 || W <= 0) return;
+    dim3 grid((unsigned)((W + ULK_VOX_BX - 1) / ULK_VOX_BX), (unsigned)H, (unsigned)D);
+    if (g_ulk_prof_on) ulk_prof_begin(typeid(F).name(), s);
+    ulk_kernel_vox<F><<<grid, ULK_VOX_BX, 0, s>>>(H, W, f);
+    if (g_ulk_prof_on) ulk_prof_end(s);
+    ++g_ulk_launches;
+}
+template <class F> void ulk_launch_vox_warp(i32 D, i32 H, i32 W, ulk_stream_t s, const F &f)
+{
+    if (D <= 0 || H <= 0 || W <= 0) return;
+    dim3 grid((unsigned)((W + ULK_VOX_BX - 1) / ULK_VOX_BX), (unsigned)H, (unsigned)D);
+    if (g_ulk_prof_on) ulk_prof_begin(typeid(F).name(), s);
+    ulk_kernel_vox_warp<F><<<grid, ULK_VOX_BX, 0, s>>>(H, W, f);
     if (g_ulk_prof_on) ulk_prof_end(s);
     ++g_ulk_launches;
 }

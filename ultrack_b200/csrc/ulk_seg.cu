@@ -90,13 +90,11 @@ struct K_BasinNodeGlobal {
 struct K_MaskPaint {
     const i32 *bas; const i32 *bnode; const i32 *parent; const i32 *bbox; const i64 *moff; UlkDims dm;
     u32 *mask;
-    ULK_D void operator()(i64 vv) const
+    ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
     {
         i32 v = (i32)vv;
         i32 b = bas[v];
         if (b < 0) return;
-        i32 z, y, x;
-        dm.coords(v, z, y, x);
         for (i32 n = bnode[b]; n >= 0; n = parent[n]) {
             const i32 *bb = bbox + 6 * n;
             i64 bh = bb[4] - bb[1], wpr = (bb[5] - bb[2] + 31) / 32;
@@ -153,7 +151,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const Ul
     CHKA(A);
     CHK(ulk_memset(fmark, 0, (size_t)V + 8, st));
     CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
-    ulk_launch(V, st, K_MinEdge{lab, ct, dm, mw, pk});
+    ulk_launch_vox(dm.D, dm.H, dm.W, st, K_MinEdge{lab, ct, dm, mw, pk});
     ulk_launch(V, st, K_Hook1{lab, mw, pk, dm, bp, state, Lr, best, ctr + 4});
     ulk_launch_warp(V, st, K_CompressCand{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1});
     i32 hc[8];
@@ -219,7 +217,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const Ul
         ulk_fill<i32>(out.bbmax, -0x7fffffff, 3 * (i64)B, st);
         CHK(ulk_memset(out.csum, 0, (size_t)B * 3 * sizeof(i64), st));
     }
-    ulk_launch_warp(V, st, K_BasinAccum{out.bas, lab, mw, pk, dm, out.b_size, out.b_top, ncross,
+    ulk_launch_vox_warp(dm.D, dm.H, dm.W, st, K_BasinAccum{out.bas, lab, mw, pk, dm, out.b_size, out.b_top, ncross,
                                         need_stats ? 1 : 0, out.bbmin, out.bbmax, out.csum,
                                         need_join ? 1 : 0, out.g_L, out.jk, hp, ctr + 0,
                                         need_k3 ? 1 : 0, out.b_k3});
@@ -257,7 +255,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const Ul
     CHK(ulk_memset(T.cnt, 0, cap * 4, st));
     CHK(ulk_memset(T.shi, 0, cap * 8, st));
     CHK(ulk_memset(T.slo, 0, cap * 8, st));
-    ulk_launch(V, st, K_RagInsert{out.bas, lab, ct, dm, T, fixscale});
+    ulk_launch_vox(dm.D, dm.H, dm.W, st, K_RagInsert{out.bas, lab, ct, dm, T, fixscale});
     i32 *eflag = A.get<i32>((i64)cap + 1), *epre = A.get<i32>((i64)cap + 1);
     CHKA(A);
     ulk_launch((i64)cap, st, K_RagFlag{T.key, eflag});
@@ -304,8 +302,8 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const Ul
         i32 *P3 = bp;          // basin forest no longer needed
         i32 *nroot = A.get<i32>(B);
         CHKA(A);
-        ulk_launch_warp(V, st, K_K3Init{out.bas, out.b_k3, dm.W, P3});
-        ulk_launch(V, st, K_K3Union{out.bas, dm, out.b_k3, P3});
+        ulk_launch_vox_warp(dm.D, dm.H, dm.W, st, K_K3Init{out.bas, out.b_k3, P3});
+        ulk_launch_vox(dm.D, dm.H, dm.W, st, K_K3Union{out.bas, dm, out.b_k3, P3});
         for (int it = 0;; ++it) {
             CHK(ulk_memset(nroot, 0, (size_t)B * sizeof(i32), st));
             CHK(ulk_memset(ctr, 0, sizeof(i32), st));
@@ -314,7 +312,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const Ul
             if (hc[0] == 0) break;
             if (stats) stats->k3_rounds += 1;
             if (it == 0) ulk_fill<u32>(best, ULK_NONE32, V, st);     // K_K3Hook resets what it used
-            ulk_launch(V, st, K_K3FindBest{out.bas, dm, nroot, P3, best});
+            ulk_launch_vox(dm.D, dm.H, dm.W, st, K_K3FindBest{out.bas, dm, nroot, P3, best});
             ulk_launch(V, st, K_K3Hook{out.bas, dm, P3, best, out.b_k3});
             if (it > 100000) ULK_FAIL(-4, "bottleneck rounds did not converge");
         }
@@ -368,6 +366,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     dm.D = (i32)shape[0]; dm.H = (i32)shape[1]; dm.W = (i32)shape[2];
     dm.V = (i64)dm.D * dm.H * dm.W;
     if (dm.V <= 0) ULK_FAIL(-1, "empty frame");
+    if (dm.D > 65535 || dm.H > 65535) ULK_FAIL(-1, "frame too large: depth and height are limited to 65535");
     if (dm.V > 1431655000ll) ULK_FAIL(-1, "frame too large: %lld voxels (edge keys are 32-bit)", (long long)dm.V);
     if (prm->ws_hierarchy != 0 && prm->ws_hierarchy != 1)
         ULK_FAIL(-1, "ws_hierarchy=%d is not supported (0 area, 1 dynamics)", prm->ws_hierarchy);
@@ -391,9 +390,9 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     u32 *cmax = A.get<u32>(1);
     CHKA(A);
     CHK(ulk_memset(cmax, 0, 4, st));
-    ulk_launch_warp(V, st, K_Threshold{fg, fg_dtype, prm->threshold, ctp, ct_dtype, ctf, ctd, P, cmax, dm.W});
+    ulk_launch_vox_warp(dm.D, dm.H, dm.W, st, K_Threshold{fg, fg_dtype, prm->threshold, ctp, ct_dtype, ctf, ctd, P, cmax});
     // ---- connected components (4/6-connected): union of runs, flatten + sizes + root list
-    ulk_launch(V, st, K_CclUnion{P, dm});
+    ulk_launch_vox(dm.D, dm.H, dm.W, st, K_CclUnion{P, dm});
     i32 *cnt = A.get<i32>(V);            // sizes at the roots, later the component code at the roots
     i32 *lab2 = A.get<i32>(V);           // region labels; until they are written: the root list
     i32 *ctr = A.get<i32>(4);
@@ -550,7 +549,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     if (!F->mask) ULK_FAIL(-3, "device allocation failed");
     CHK(ulk_memset(F->mask, 0, (size_t)total_words * 4, st));
     ulk_launch(vb.B, st, K_BasinNodeGlobal{vb.g_lab, noff, O.basin_node, bnode});
-    ulk_launch(V, st, K_MaskPaint{vb.bas, bnode, F->parent, F->bbox, F->mask_off, dm, F->mask});
+    ulk_launch_vox(dm.D, dm.H, dm.W, st, K_MaskPaint{vb.bas, bnode, F->parent, F->bbox, F->mask_off, dm, F->mask});
     // ---- overlaps: (node, emitted proper ancestor) pairs, processing.py:289-296
     i32 *depth = A.get<i32>(N + 1), *ooff = A.get<i32>(N + 1);
     CHKA(A);

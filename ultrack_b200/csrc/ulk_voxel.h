@@ -47,36 +47,41 @@ struct K_Threshold {
     const void *fg; int fgt; double thr;
     const void *ct; int ctt;
     float *ctf; double *ctd;
-    i32 *P; u32 *cmax; i32 W;
+    i32 *P; u32 *cmax;
     ULK_D ULK_INLINE bool stage(i64 v, u32 &bits) const
     {
         double f = ulk_load_as_double(fg, fgt, v);
+        bits = 0;
+        if (ctt == ULK_F32) {       // read in place, never staged
+            float a = fabsf(((const float *)ct)[v]);
+            if (a <= 3.0e38f) memcpy(&bits, &a, 4);
+            return f > thr;
+        }
         double c = ulk_load_as_double(ct, ctt, v);
         if (ctf) ctf[v] = (float)c; else if (ctd) ctd[v] = c;
         float a = (float)(c < 0 ? -c : c);
-        bits = 0;
         if (a == a && a <= 3.0e38f) memcpy(&bits, &a, 4);
         return f > thr;
     }
 #ifdef ULK_EMU
-    void operator()(i64 v) const
+    void operator()(i64 v, i32, i32, i32 x) const
     {
         u32 bits;
         bool on = stage(v, bits);
         if (bits > *cmax) *cmax = bits;
-        bool link = on && (v & 31) != 0 && (v % W) != 0 && P[v - 1] >= 0;
+        bool link = on && (x & 31) != 0 && P[v - 1] >= 0;
         P[v] = on ? (link ? P[v - 1] : (i32)v) : -1;
     }
 #else
-    ULK_D void warp(i64 v, bool valid) const
+    ULK_D void warp(i64 v, i32, i32, i32, bool valid) const
     {
-        const int lane = threadIdx.x & 31;
+        const int lane = threadIdx.x & 31;     // == x & 31
         u32 bits = 0;
         bool on = valid && stage(v, bits);
         u32 m = __reduce_max_sync(0xffffffffu, bits);
         if (lane == 0 && m > *cmax) atomicMax(cmax, m);
         bool prev = __shfl_up_sync(0xffffffffu, on ? 1 : 0, 1) != 0;
-        u32 linked = __ballot_sync(0xffffffffu, on && prev && lane > 0 && (v % W) != 0);
+        u32 linked = __ballot_sync(0xffffffffu, on && prev && lane > 0);
         if (valid) P[v] = on ? (i32)v - (lane - ulk_run_start(linked, lane)) : -1;
     }
 #endif
@@ -87,14 +92,12 @@ struct K_Threshold {
 // edge one voxel to the left does not already join the same two runs
 struct K_CclUnion {
     i32 *P; UlkDims dm;
-    ULK_D void operator()(i64 vv) const
+    ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
     {
         i32 v = (i32)vv;
         if (P[v] < 0) return;
-        i32 z, y, x;
-        dm.coords(v, z, y, x);
         bool left = x > 0 && P[v - 1] >= 0;
-        if (left && (v & 31) == 0) ulk_vunion(P, v, v - 1);
+        if (left && (x & 31) == 0) ulk_vunion(P, v, v - 1);
         for (int d = 1; d < 3; ++d) {
             if (!dm.bwd(d, z, y, x)) continue;
             i32 u = v - dm.stride(d);
@@ -184,13 +187,11 @@ struct K_FlagRoots {
 struct K_MinEdge {
     const i32 *lab; UlkCt ct; UlkDims dm;
     u32 *mw, *pk;
-    ULK_D void operator()(i64 vv) const
+    ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
     {
         i32 v = (i32)vv;
         i32 l = lab[v];
-        if (l <= 0) { mw[v] = ULK_NONE32; pk[v] = ULK_NONE32; return; }
-        i32 z, y, x;
-        dm.coords(v, z, y, x);
+        if (l <= 0) return;          // mw / pk are only ever read where lab > 0
         u64 best = ULK_NONE64;
         for (int d = 0; d < 3; ++d) {
             i32 st = dm.stride(d);
@@ -421,11 +422,11 @@ struct K_BasinAccum {
     int want_join; const u32 *b_L; u32 *jk; i32 *hp; i32 *nhp;
     int want_k0; u32 *K0;
     struct Own { u64 top; u32 nc; u32 kmin; i32 c[3]; bool plateau; };
-    ULK_D ULK_INLINE void own(i32 v, i32 b, Own &o) const
+    ULK_D ULK_INLINE void own(i32 v, i32 z, i32 y, i32 x, i32 b, Own &o) const
     {
         const u32 m = mw[v], k = pk[v];
         o.top = k != ULK_NONE32 ? ((u64)m << 32) | k : 0;
-        dm.coords(v, o.c[0], o.c[1], o.c[2]);
+        o.c[0] = z; o.c[1] = y; o.c[2] = x;
         const i32 l = lab[v];
         o.nc = 0;
         o.kmin = ULK_NONE32;
@@ -449,13 +450,13 @@ struct K_BasinAccum {
         }
     }
 #ifdef ULK_EMU
-    void operator()(i64 vv) const
+    void operator()(i64 vv, i32 z, i32 y, i32 x) const
     {
         i32 v = (i32)vv;
         i32 b = bas[v];
         if (b < 0) return;
         Own o;
-        own(v, b, o);
+        own(v, z, y, x, b, o);
         b_size[b] += 1;
         if (o.top > b_top[b]) b_top[b] = o.top;
         *ncross += o.nc;
@@ -471,14 +472,14 @@ struct K_BasinAccum {
 #else
     // lanes of a warp that sit in the same basin (consecutive x: usually one or two groups)
     // reduce among themselves; one lane per group issues the atomics
-    ULK_D void warp(i64 vv, bool valid) const
+    ULK_D void warp(i64 vv, i32 z, i32 y, i32 x, bool valid) const
     {
         const int lane = threadIdx.x & 31;
         i32 v = (i32)vv;
         i32 b = valid ? bas[v] : -1;
         Own o;
         o.top = 0; o.nc = 0; o.kmin = ULK_NONE32; o.c[0] = o.c[1] = o.c[2] = 0; o.plateau = false;
-        if (b >= 0) own(v, b, o);
+        if (b >= 0) own(v, z, y, x, b, o);
         u32 nct = __reduce_add_sync(0xffffffffu, o.nc);
         if (lane == 0 && nct) atomicAdd((unsigned long long *)ncross, (unsigned long long)nct);
         if (want_join) ulk_warp_append(o.plateau, v, hp, nhp);
@@ -586,14 +587,12 @@ ULK_HD ULK_INLINE u64 ulk_hash64(u64 x)
 }
 struct K_RagInsert {
     const i32 *bas; const i32 *lab; UlkCt ct; UlkDims dm; UlkRagTable T; double fixscale;
-    ULK_D void operator()(i64 vv) const
+    ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
     {
         i32 v = (i32)vv;
         i32 b = bas[v];
         if (b < 0) return;
         i32 l = lab[v];
-        i32 z, y, x;
-        dm.coords(v, z, y, x);
         for (int d = 0; d < 3; ++d) {
             if (!dm.fwd(d, z, y, x)) continue;
             i32 u = v + dm.stride(d);
@@ -654,39 +653,37 @@ struct K_Hist {
 // edges of a basin whose raster key is <= K0[basin]; runs of x edges inside a warp segment are
 // hooked to their first voxel at initialisation (same scheme as the component labelling)
 struct K_K3Init {
-    const i32 *bas; const u32 *K0; i32 W; i32 *P;
-    ULK_D ULK_INLINE bool xlink(i64 v, i32 b) const
+    const i32 *bas; const u32 *K0; i32 *P;
+    ULK_D ULK_INLINE bool xlink(i64 v, i32 x, i32 b) const
     {
-        return b >= 0 && (v % W) != 0 && bas[v - 1] == b && 3u * (u32)(v - 1) <= K0[b];
+        return b >= 0 && x > 0 && bas[v - 1] == b && 3u * (u32)(v - 1) <= K0[b];
     }
 #ifdef ULK_EMU
-    void operator()(i64 v) const
+    void operator()(i64 v, i32, i32, i32 x) const
     {
         i32 b = bas[v];
-        P[v] = b < 0 ? -1 : ((v & 31) != 0 && xlink(v, b) ? P[v - 1] : (i32)v);
+        P[v] = b < 0 ? -1 : ((x & 31) != 0 && xlink(v, x, b) ? P[v - 1] : (i32)v);
     }
 #else
-    ULK_D void warp(i64 v, bool valid) const
+    ULK_D void warp(i64 v, i32, i32, i32 x, bool valid) const
     {
-        const int lane = threadIdx.x & 31;
+        const int lane = threadIdx.x & 31;     // == x & 31
         i32 b = valid ? bas[v] : -1;
-        u32 linked = __ballot_sync(0xffffffffu, lane > 0 && xlink(v, b));
+        u32 linked = __ballot_sync(0xffffffffu, lane > 0 && xlink(v, x, b));
         if (valid) P[v] = b < 0 ? -1 : (i32)v - (lane - ulk_run_start(linked, lane));
     }
 #endif
 };
 struct K_K3Union {
     const i32 *bas; UlkDims dm; const u32 *K0; i32 *P;
-    ULK_D void operator()(i64 vv) const
+    ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
     {
         i32 v = (i32)vv;
         i32 b = bas[v];
         if (b < 0) return;
-        i32 z, y, x;
-        dm.coords(v, z, y, x);
         u32 kmax = K0[b];
         bool left = x > 0 && bas[v - 1] == b && 3u * (u32)(v - 1) <= kmax;
-        if (left && (v & 31) == 0) ulk_vunion(P, v, v - 1);
+        if (left && (x & 31) == 0) ulk_vunion(P, v, v - 1);
         for (int d = 1; d < 3; ++d) {
             if (!dm.bwd(d, z, y, x)) continue;
             i32 u = v - dm.stride(d);
@@ -711,14 +708,12 @@ struct K_K3FlattenCount {
 };
 struct K_K3FindBest {     // Boruvka step on the basins that are still split
     const i32 *bas; UlkDims dm; const i32 *nroot; const i32 *P; u32 *best;
-    ULK_D void operator()(i64 vv) const
+    ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
     {
         i32 v = (i32)vv;
         i32 b = bas[v];
         if (b < 0 || nroot[b] <= 1) return;
         i32 r = ulk_vfind(P, v);
-        i32 z, y, x;
-        dm.coords(v, z, y, x);
         u32 k = ULK_NONE32;
         for (int d = 0; d < 3; ++d) {
             i32 st = dm.stride(d);
