@@ -64,8 +64,7 @@ int ulk_labels_to_contours_impl(ulk_stream_t st, const int32_t *labels, int32_t 
                                 uint8_t *foreground, float *contours)
 {
     UlkDims dm;
-    dm.D = (i32)shape[0]; dm.H = (i32)shape[1]; dm.W = (i32)shape[2];
-    dm.V = (i64)dm.D * dm.H * dm.W;
+    dm.init(shape[0], shape[1], shape[2]);
     ulk_launch(dm.V, st, K_LabelsToContours{labels, n_sets, dm, foreground, contours});
     return ulk_sync(st);
 }
@@ -144,8 +143,7 @@ int ulk_synth_frame_impl(ulk_stream_t st, const int64_t shape[3], int32_t t, uin
                          double fill, double motion, double noise, float *fg, float *ct)
 {
     K_SynthFrame k;
-    k.dm.D = (i32)shape[0]; k.dm.H = (i32)shape[1]; k.dm.W = (i32)shape[2];
-    k.dm.V = (i64)k.dm.D * k.dm.H * k.dm.W;
+    k.dm.init(shape[0], shape[1], shape[2]);
     k.ndim = k.dm.D == 1 ? 2 : 3;
     double unit = k.ndim == 2 ? 3.141592653589793 : 4.0 / 3.0 * 3.141592653589793;
     k.pitch = radius * pow(unit / fill, 1.0 / k.ndim);

@@ -56,41 +56,71 @@ inline int ulk_dtype_size(int dt)
 // contour dtypes whose pairwise sum numba evaluates in float32 (exactly or by its typing rules)
 inline bool ulk_ct_is_f32(int dt) { return dt == ULK_U8 || dt == ULK_I8 || dt == ULK_U16 || dt == ULK_I16 || dt == ULK_F16 || dt == ULK_F32; }
 
+// division of a u32 by a run-time constant without the divide unit (Granlund-Montgomery,
+// branch-free form): q = (t + ((v - t) >> s1)) >> s2 with t = hi32(M * v)
+struct UlkFastDiv {
+    u32 M, s1, s2;
+    void init(u32 d)
+    {
+        u32 l = 0;
+        while (((u64)1 << l) < d) ++l;
+        M = (u32)((((u64)1 << 32) * (((u64)1 << l) - d)) / d + 1);
+        s1 = l < 1 ? l : 1;
+        s2 = l > 1 ? l - 1 : 0;
+    }
+    ULK_HD ULK_INLINE u32 div(u32 v) const
+    {
+#if defined(__CUDA_ARCH__)
+        u32 t = __umulhi(M, v);
+#else
+        u32 t = (u32)(((u64)M * v) >> 32);
+#endif
+        return (t + ((v - t) >> s1)) >> s2;
+    }
+};
 struct UlkDims {
     i32 D, H, W;
     i64 V;
+    UlkFastDiv fW, fH;
+    void init(i64 d, i64 h, i64 w)
+    {
+        D = (i32)d; H = (i32)h; W = (i32)w;
+        V = d * h * w;
+        fW.init((u32)(W > 0 ? W : 1)); fH.init((u32)(H > 0 ? H : 1));
+    }
     ULK_HD ULK_INLINE i32 stride(int d) const { return d == 0 ? 1 : (d == 1 ? W : W * H); }
     ULK_HD ULK_INLINE void coords(i32 v, i32 &z, i32 &y, i32 &x) const
     {
-        x = v % W;
-        i32 t = v / W;
-        y = t % H;
-        z = t / H;
+        u32 t = fW.div((u32)v);
+        x = (i32)((u32)v - t * (u32)W);
+        u32 q = fH.div(t);
+        y = (i32)(t - q * (u32)H);
+        z = (i32)q;
     }
     // can voxel with coords c step forward / backward along direction d (0=x,1=y,2=z)
     ULK_HD ULK_INLINE bool fwd(int d, i32 z, i32 y, i32 x) const { return d == 0 ? x + 1 < W : (d == 1 ? y + 1 < H : z + 1 < D); }
     ULK_HD ULK_INLINE bool bwd(int d, i32 z, i32 y, i32 x) const { return d == 0 ? x > 0 : (d == 1 ? y > 0 : z > 0); }
 };
 
-// contour values as the graph builder sees them (vendored/graph.py:32, SURVEY a-5):
-// the pairwise sum is evaluated in float32 for every dtype that promotes to it and in
-// float64 otherwise, then `/ 2.0 + 1e-8` in double, rounded to float32.
+// weight of an edge from the float32 sum of its endpoints' contours: for s == 0 and
+// 2^-24 <= |s| < 2^40 the float expression equals the double one bit for bit (checked
+// exhaustively over every float of that range), which keeps float<->double conversions off the
+// dense kernels
+ULK_HD ULK_INLINE bool ulk_wsum_fast(float s)
+{
+    u32 b;
+    memcpy(&b, &s, 4);
+    u32 e = (b >> 23) & 0xffu;
+    return s == 0.0f || (e - 103u) < 64u;
+}
+ULK_HD ULK_INLINE float ulk_wsum_slow(float s) { return (float)((double)s / 2.0 + 1e-8); }
+ULK_HD ULK_INLINE float ulk_wsum(float s) { return ulk_wsum_fast(s) ? s * 0.5f + 1e-8f : ulk_wsum_slow(s); }
 struct UlkCt {
     const float *f;
     const double *d;
     ULK_HD ULK_INLINE float w(i32 p, i32 q) const
     {
-        if (f) {
-            float s = f[p] + f[q];
-            // for s == 0 and 2^-24 <= |s| < 2^40 the float expression below equals the double
-            // one bit for bit (checked exhaustively over every float of that range): it keeps
-            // the float<->double conversions off the dense kernels
-            u32 b;
-            memcpy(&b, &s, 4);
-            u32 e = (b >> 23) & 0xffu;
-            if (s == 0.0f || (e >= 127u - 24u && e < 127u + 40u)) return s * 0.5f + 1e-8f;
-            return (float)((double)s / 2.0 + 1e-8);
-        }
+        if (f) return ulk_wsum(f[p] + f[q]);
         double s = d[p] + d[q];
         return (float)(s / 2.0 + 1e-8);
     }

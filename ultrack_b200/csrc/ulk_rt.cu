@@ -62,6 +62,13 @@ static int emu_sort(const K *ki, K *ko, const u32 *vi, u32 *vo, i64 n)
 }
 int ulk_sort_pairs_u64(const u64 *ki, u64 *ko, const u32 *vi, u32 *vo, i64 n, ulk_stream_t) { return emu_sort(ki, ko, vi, vo, n); }
 int ulk_sort_pairs_u32(const u32 *ki, u32 *ko, const u32 *vi, u32 *vo, i64 n, ulk_stream_t) { return emu_sort(ki, ko, vi, vo, n); }
+int ulk_select_nonneg_i32(const i32 *in, i64 n, i32 *out, i32 *count, ulk_stream_t)
+{
+    i32 c = 0;
+    for (i64 i = 0; i < n; ++i) if (in[i] >= 0) out[c++] = (i32)i;
+    *count = c;
+    return 0;
+}
 int ulk_sort_keys_u32(const u32 *ki, u32 *ko, i64 n, ulk_stream_t)
 {
     std::vector<u32> k(ki, ki + n);
@@ -351,6 +358,23 @@ int ulk_sort_keys_u64(const u64 *ki, u64 *ko, i64 n, ulk_stream_t s)
     if (cub_tmp(need)) return -2;
     ProfScope ps("cub::DeviceRadixSort::SortKeys", s);
     ULK_CUDA(cub::DeviceRadixSort::SortKeys(g_cub_tmp, need, ki, ko, (int)n, 0, 64, s));
+    ++g_ulk_launches;
+    return 0;
+}
+struct UlkNonNegAt {
+    const i32 *p;
+    __device__ bool operator()(const i32 &i) const { return p[i] >= 0; }
+};
+int ulk_select_nonneg_i32(const i32 *in, i64 n, i32 *out, i32 *count_dev, ulk_stream_t s)
+{
+    if (n <= 0) return 0;
+    cub::CountingInputIterator<i32> it(0);
+    UlkNonNegAt pred{in};
+    size_t need = 0;
+    ULK_CUDA(cub::DeviceSelect::If(nullptr, need, it, out, count_dev, (int)n, pred, s));
+    if (cub_tmp(need)) return -2;
+    ProfScope ps("cub::DeviceSelect::If", s);
+    ULK_CUDA(cub::DeviceSelect::If(g_cub_tmp, need, it, out, count_dev, (int)n, pred, s));
     ++g_ulk_launches;
     return 0;
 }

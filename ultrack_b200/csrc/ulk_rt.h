@@ -100,6 +100,12 @@ template <class F> void ulk_launch_vox(i32 D, i32 H, i32 W, ulk_stream_t, const 
     for (i32 z = 0; z < D; ++z) for (i32 y = 0; y < H; ++y) for (i32 x = 0; x < W; ++x) f(v++, z, y, x);
 }
 template <class F> void ulk_launch_vox_warp(i32 D, i32 H, i32 W, ulk_stream_t s, const F &f) { ulk_launch_vox(D, H, W, s, f); }
+// list kernels: f(v, z, y, x) for every voxel index of a list (the foreground voxels of a frame)
+template <class F, class DM> void ulk_launch_list(const i32 *list, i64 n, const DM &dm, ulk_stream_t, const F &f)
+{
+    for (i64 i = 0; i < n; ++i) { i32 z, y, x; dm.coords(list[i], z, y, x); f((i64)list[i], z, y, x); }
+}
+template <class F, class DM> void ulk_launch_list_warp(const i32 *list, i64 n, const DM &dm, ulk_stream_t s, const F &f) { ulk_launch_list(list, n, dm, s, f); }
 #else
 template <class F> __global__ void __launch_bounds__(256) ulk_kernel(i64 n, F f)
 {
@@ -168,6 +174,41 @@ template <class F> void ulk_launch_vox_warp(i32 D, i32 H, i32 W, ulk_stream_t s,
     if (g_ulk_prof_on) ulk_prof_end(s);
     ++g_ulk_launches;
 }
+// list kernels: one thread per entry of a voxel list (the foreground voxels of a frame, in
+// raster order): every lane does useful work, and consecutive entries are mostly consecutive
+// voxels of a row, so accesses stay coalesced.  Coordinates come from UlkDims::coords (multiply-
+// shift division).  The _warp form calls F::warp(v, z, y, x, valid) from every thread.
+template <class F, class DM> __global__ void __launch_bounds__(256) ulk_kernel_list(const i32 *list, i64 n, DM dm, F f)
+{
+    i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    i32 v = list[i], z, y, x;
+    dm.coords(v, z, y, x);
+    f((i64)v, z, y, x);
+}
+template <class F, class DM> __global__ void __launch_bounds__(256) ulk_kernel_list_warp(const i32 *list, i64 n, DM dm, F f)
+{
+    i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    i32 v = 0, z = 0, y = 0, x = 0;
+    if (i < n) { v = list[i]; dm.coords(v, z, y, x); }
+    f.warp((i64)v, z, y, x, i < n);
+}
+template <class F, class DM> void ulk_launch_list(const i32 *list, i64 n, const DM &dm, ulk_stream_t s, const F &f)
+{
+    if (n <= 0) return;
+    if (g_ulk_prof_on) ulk_prof_begin(typeid(F).name(), s);
+    ulk_kernel_list<F, DM><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(list, n, dm, f);
+    if (g_ulk_prof_on) ulk_prof_end(s);
+    ++g_ulk_launches;
+}
+template <class F, class DM> void ulk_launch_list_warp(const i32 *list, i64 n, const DM &dm, ulk_stream_t s, const F &f)
+{
+    if (n <= 0) return;
+    if (g_ulk_prof_on) ulk_prof_begin(typeid(F).name(), s);
+    ulk_kernel_list_warp<F, DM><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(list, n, dm, f);
+    if (g_ulk_prof_on) ulk_prof_end(s);
+    ++g_ulk_launches;
+}
 #endif
 int ulk_prof_report(char *buf, i64 cap);   // "name\tlaunches\ttotal_ms\n" per kernel; returns bytes needed
 void ulk_prof_enable(int on);
@@ -202,6 +243,8 @@ int ulk_sort_pairs_u64(const u64 *keys_in, u64 *keys_out, const u32 *vals_in, u3
 int ulk_sort_pairs_u32(const u32 *keys_in, u32 *keys_out, const u32 *vals_in, u32 *vals_out,
                        i64 n, ulk_stream_t s);
 int ulk_sort_keys_u32(const u32 *keys_in, u32 *keys_out, i64 n, ulk_stream_t s);
+// indices i (ascending) with in[i] >= 0 -> out; *count_dev receives how many
+int ulk_select_nonneg_i32(const i32 *in, i64 n, i32 *out, i32 *count_dev, ulk_stream_t s);
 int ulk_sort_keys_u64(const u64 *keys_in, u64 *keys_out, i64 n, ulk_stream_t s);
 
 // ---------------------------------------------------------------- numerics

@@ -135,7 +135,7 @@ struct VoxelStage {
     u32 *mw = nullptr, *jk = nullptr;
 };
 
-static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const UlkCt &ct, const i32 *lab,
+static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i32 *fgl, i64 nfg, const UlkCt &ct, const i32 *lab,
                        i32 R, bool need_join, bool need_k3, bool need_stats, double fixscale,
                        VoxelStage &out, ulk_seg_stats *stats)
 {
@@ -151,9 +151,9 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const Ul
     CHKA(A);
     CHK(ulk_memset(fmark, 0, (size_t)V + 8, st));
     CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
-    ulk_launch_vox(dm.D, dm.H, dm.W, st, K_MinEdge{lab, ct, dm, mw, pk});
-    ulk_launch(V, st, K_Hook1{lab, mw, pk, dm, bp, state, Lr, best, ctr + 4});
-    ulk_launch_warp(V, st, K_CompressCand{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1});
+    ulk_launch_list(fgl, nfg, dm, st, K_MinEdge{lab, ct, dm, mw, pk});
+    ulk_launch_list(fgl, nfg, dm, st, K_Hook1{lab, mw, pk, dm, bp, state, Lr, best, ctr + 4});
+    ulk_launch_list_warp(fgl, nfg, dm, st, K_CompressCand{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1});
     i32 hc[8];
     CHK(ulk_read(hc, ctr, 8, st));
     i32 ncand = hc[0], ng = hc[1];
@@ -190,12 +190,13 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const Ul
     CHKA(A);
     CHK(ulk_memset(ctr, 0, sizeof(i32), st));
     CHK(ulk_memset(lab_hist, 0, (size_t)(R + 1) * sizeof(i32), st));
-    ulk_launch(V, st, K_CompressRoots{bp, lab, rootkeys, ctr + 0});
+    ulk_launch_list(fgl, nfg, dm, st, K_CompressRoots{bp, lab, rootkeys, ctr + 0});
     CHK(ulk_sort_keys_u64(rootkeys, rootsorted, B, st));
     u32 *gid_at_root = best;         // free after the flow rounds
     ulk_launch(B, st, K_BasinRegroup{rootsorted, Lr, gid_at_root, out.g_root, out.g_lab, out.g_L, lab_hist});
     CHK(ulk_exclusive_scan_i32(lab_hist, out.bs, R + 1, st));
-    ulk_launch(V, st, K_AssignBasin{bp, gid_at_root, out.bas});
+    CHK(ulk_memset(out.bas, 0xff, (size_t)V * sizeof(i32), st));
+    ulk_launch_list(fgl, nfg, dm, st, K_AssignBasin{bp, gid_at_root, out.bas});
     A.release(rootkeys); A.release(rootsorted);
 
     // ---- per-basin accumulators, join keys (area attribute), bottleneck lower bound: one pass
@@ -217,7 +218,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const Ul
         ulk_fill<i32>(out.bbmax, -0x7fffffff, 3 * (i64)B, st);
         CHK(ulk_memset(out.csum, 0, (size_t)B * 3 * sizeof(i64), st));
     }
-    ulk_launch_vox_warp(dm.D, dm.H, dm.W, st, K_BasinAccum{out.bas, lab, mw, pk, dm, out.b_size, out.b_top, ncross,
+    ulk_launch_list_warp(fgl, nfg, dm, st, K_BasinAccum{out.bas, lab, mw, pk, dm, out.b_size, out.b_top, ncross,
                                         need_stats ? 1 : 0, out.bbmin, out.bbmax, out.csum,
                                         need_join ? 1 : 0, out.g_L, out.jk, hp, ctr + 0,
                                         need_k3 ? 1 : 0, out.b_k3});
@@ -255,7 +256,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const Ul
     CHK(ulk_memset(T.cnt, 0, cap * 4, st));
     CHK(ulk_memset(T.shi, 0, cap * 8, st));
     CHK(ulk_memset(T.slo, 0, cap * 8, st));
-    ulk_launch_vox(dm.D, dm.H, dm.W, st, K_RagInsert{out.bas, lab, ct, dm, T, fixscale});
+    ulk_launch_list(fgl, nfg, dm, st, K_RagInsert{out.bas, lab, ct, dm, T, fixscale});
     i32 *eflag = A.get<i32>((i64)cap + 1), *epre = A.get<i32>((i64)cap + 1);
     CHKA(A);
     ulk_launch((i64)cap, st, K_RagFlag{T.key, eflag});
@@ -302,18 +303,18 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const Ul
         i32 *P3 = bp;          // basin forest no longer needed
         i32 *nroot = A.get<i32>(B);
         CHKA(A);
-        ulk_launch_vox_warp(dm.D, dm.H, dm.W, st, K_K3Init{out.bas, out.b_k3, P3});
-        ulk_launch_vox(dm.D, dm.H, dm.W, st, K_K3Union{out.bas, dm, out.b_k3, P3});
+        ulk_launch_list_warp(fgl, nfg, dm, st, K_K3Init{out.bas, out.b_k3, P3});
+        ulk_launch_list_warp(fgl, nfg, dm, st, K_K3Union{out.bas, dm, out.b_k3, P3});
         for (int it = 0;; ++it) {
             CHK(ulk_memset(nroot, 0, (size_t)B * sizeof(i32), st));
             CHK(ulk_memset(ctr, 0, sizeof(i32), st));
-            ulk_launch(V, st, K_K3FlattenCount{out.bas, P3, nroot, ctr + 0});
+            ulk_launch_list(fgl, nfg, dm, st, K_K3FlattenCount{out.bas, P3, nroot, ctr + 0});
             CHK(ulk_read(hc, ctr, 1, st));
             if (hc[0] == 0) break;
             if (stats) stats->k3_rounds += 1;
-            if (it == 0) ulk_fill<u32>(best, ULK_NONE32, V, st);     // K_K3Hook resets what it used
-            ulk_launch_vox(dm.D, dm.H, dm.W, st, K_K3FindBest{out.bas, dm, nroot, P3, best});
-            ulk_launch(V, st, K_K3Hook{out.bas, dm, P3, best, out.b_k3});
+            if (it == 0) ulk_launch_list(fgl, nfg, dm, st, K_FillAt<u32>{best, ULK_NONE32});     // K_K3Hook resets what it used
+            ulk_launch_list(fgl, nfg, dm, st, K_K3FindBest{out.bas, dm, nroot, P3, best});
+            ulk_launch_list(fgl, nfg, dm, st, K_K3Hook{out.bas, dm, P3, best, out.b_k3});
             if (it > 100000) ULK_FAIL(-4, "bottleneck rounds did not converge");
         }
         A.release(nroot);
@@ -363,8 +364,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
                            ulk_frame_nodes **result)
 {
     UlkDims dm;
-    dm.D = (i32)shape[0]; dm.H = (i32)shape[1]; dm.W = (i32)shape[2];
-    dm.V = (i64)dm.D * dm.H * dm.W;
+    dm.init(shape[0], shape[1], shape[2]);
     if (dm.V <= 0) ULK_FAIL(-1, "empty frame");
     if (dm.D > 65535 || dm.H > 65535) ULK_FAIL(-1, "frame too large: depth and height are limited to 65535");
     if (dm.V > 1431655000ll) ULK_FAIL(-1, "frame too large: %lld voxels (edge keys are 32-bit)", (long long)dm.V);
@@ -392,7 +392,14 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     CHK(ulk_memset(cmax, 0, 4, st));
     ulk_launch_vox_warp(dm.D, dm.H, dm.W, st, K_Threshold{fg, fg_dtype, prm->threshold, ctp, ct_dtype, ctf, ctd, P, cmax});
     // ---- connected components (4/6-connected): union of runs, flatten + sizes + root list
-    ulk_launch_vox(dm.D, dm.H, dm.W, st, K_CclUnion{P, dm});
+    // ---- the foreground voxel list (raster order): every later voxel kernel runs on it
+    i32 *fgl = A.get<i32>(V);
+    i32 *nfg_dev = A.get<i32>(1);
+    CHKA(A);
+    CHK(ulk_select_nonneg_i32(P, V, fgl, nfg_dev, st));
+    i32 nfg = 0;
+    CHK(ulk_read(&nfg, nfg_dev, 1, st));
+    ulk_launch_list(fgl, nfg, dm, st, K_CclUnion{P, dm});
     i32 *cnt = A.get<i32>(V);            // sizes at the roots, later the component code at the roots
     i32 *lab2 = A.get<i32>(V);           // region labels; until they are written: the root list
     i32 *ctr = A.get<i32>(4);
@@ -400,7 +407,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     CHK(ulk_memset(cnt, 0, (size_t)V * sizeof(i32), st));
     CHK(ulk_memset(ctr, 0, 4 * sizeof(i32), st));
     u32 *roots0 = (u32 *)lab2;
-    ulk_launch_warp(V, st, K_FlattenCount{P, cnt, (i32 *)roots0, ctr});
+    ulk_launch_list_warp(fgl, nfg, dm, st, K_FlattenCount{P, cnt, (i32 *)roots0, ctr});
     i32 hc[4];
     u32 h_cmax = 0;
     CHK(ulk_read(hc, ctr, 4, st));
@@ -441,20 +448,22 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     // ---- region labels: components, oversegmented where area > max_area
     i32 R = n_cc;
     if (n_big == 0) {
-        ulk_launch(V, st, K_LabelCc{P, code, cc_big, 0, lab2});
+        CHK(ulk_memset(lab2, 0, (size_t)V * sizeof(i32), st));
+        ulk_launch_list(fgl, nfg, dm, st, K_LabelCc{P, code, cc_big, 0, lab2});
     } else {
         UlkArena AA;
         i32 *labA = AA.get<i32>(V);
         CHKA(AA);
-        ulk_launch(V, st, K_LabelCc{P, code, cc_big, 1, labA});
+        CHK(ulk_memset(labA, 0, (size_t)V * sizeof(i32), st));
+        ulk_launch_list(fgl, nfg, dm, st, K_LabelCc{P, code, cc_big, 1, labA});
         VoxelStage va;
-        CHK(voxel_stage(st, AA, dm, ct, labA, n_big, true, false, false, fixscale, va, &stats_local));
+        CHK(voxel_stage(st, AA, dm, fgl, nfg, ct, labA, n_big, true, false, false, fixscale, va, &stats_local));
         UlkHierScratch S;
         CHK(alloc_scratch(AA, va.B, va.Eg, S));
         UlkBasins Bv{va.b_size, va.g_L, va.b_top, nullptr, nullptr, nullptr, nullptr};
         UlkEdges Ev{va.ea, va.eb, va.wk, va.k3, va.cnt, va.shi, va.slo};
         ulk_launch(n_big, st, K_HierStage1{va.bs, va.es, Bv, Ev, S});
-        ulk_launch(V, st, K_Attach{va.bas, va.mw, va.jk, va.g_lab, va.bs, S.Ipar, S.Iwk, S.attach});
+        ulk_launch_list(fgl, nfg, dm, st, K_Attach{va.bas, va.mw, va.jk, va.g_lab, va.bs, S.Ipar, S.Iwk, S.attach});
         i32 *region_of = AA.get<i32>(va.B);
         u64 *rkey_w = AA.get<u64>(va.B), *rkey_k = AA.get<u64>(va.B);
         CHKA(AA);
@@ -474,7 +483,8 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         ulk_launch(nrec, st, K_Gather<u32>{rec_cc, perm0, c0});
         CHK(ulk_sort_pairs_u32(c0, c1, perm0, perm1, nrec, st));              // then by component
         ulk_launch(nrec, st, K_RankToLabel{perm1, c1, label_of_rec});
-        ulk_launch(V, st, K_WriteLabels{P, code, cc_big, n_cc, va.bas, region_of, label_of_rec, lab2});
+        CHK(ulk_memset(lab2, 0, (size_t)V * sizeof(i32), st));
+        ulk_launch_list(fgl, nfg, dm, st, K_WriteLabels{P, code, cc_big, n_cc, va.bas, region_of, label_of_rec, lab2});
         // number of valid records = regions
         i32 *nvalid = AA.get<i32>(nrec + 1), *nvpre = AA.get<i32>(nrec + 1);
         CHKA(AA);
@@ -495,14 +505,14 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     // ---- pass B: the configured hierarchy on every region
     const bool area_mode = prm->ws_hierarchy == 0;
     VoxelStage vb;
-    CHK(voxel_stage(st, A, dm, ct, lab2, R, area_mode, true, true, fixscale, vb, &stats_local));
+    CHK(voxel_stage(st, A, dm, fgl, nfg, ct, lab2, R, area_mode, true, true, fixscale, vb, &stats_local));
     UlkHierScratch S;
     CHK(alloc_scratch(A, vb.B, vb.Eg, S));
     UlkBasins Bv{vb.b_size, vb.g_L, vb.b_top, vb.b_k3, vb.bbmin, vb.bbmax, vb.csum};
     UlkEdges Ev{vb.ea, vb.eb, vb.wk, vb.k3, vb.cnt, vb.shi, vb.slo};
     ulk_launch(R, st, K_HierStage1{vb.bs, vb.es, Bv, Ev, S});
     if (area_mode)
-        ulk_launch(V, st, K_Attach{vb.bas, vb.mw, vb.jk, vb.g_lab, vb.bs, S.Ipar, S.Iwk, S.attach});
+        ulk_launch_list(fgl, nfg, dm, st, K_Attach{vb.bas, vb.mw, vb.jk, vb.g_lab, vb.bs, S.Ipar, S.Iwk, S.attach});
     i64 N2 = 2 * (i64)vb.B + 2;
     UlkNodeOut O;
     O.count = A.get<i32>(R + 1); O.nsurv = A.get<i32>(R + 1); O.rsize = A.get<i32>(R + 1);
@@ -549,7 +559,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     if (!F->mask) ULK_FAIL(-3, "device allocation failed");
     CHK(ulk_memset(F->mask, 0, (size_t)total_words * 4, st));
     ulk_launch(vb.B, st, K_BasinNodeGlobal{vb.g_lab, noff, O.basin_node, bnode});
-    ulk_launch_vox(dm.D, dm.H, dm.W, st, K_MaskPaint{vb.bas, bnode, F->parent, F->bbox, F->mask_off, dm, F->mask});
+    ulk_launch_list(fgl, nfg, dm, st, K_MaskPaint{vb.bas, bnode, F->parent, F->bbox, F->mask_off, dm, F->mask});
     // ---- overlaps: (node, emitted proper ancestor) pairs, processing.py:289-296
     i32 *depth = A.get<i32>(N + 1), *ooff = A.get<i32>(N + 1);
     CHKA(A);

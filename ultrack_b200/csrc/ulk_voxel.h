@@ -115,7 +115,7 @@ struct K_Flatten {
 struct K_FlattenCount {
     i32 *P; i32 *cnt; i32 *roots; i32 *nroots;
 #ifdef ULK_EMU
-    void operator()(i64 v) const
+    void operator()(i64 v, i32, i32, i32) const
     {
         if (P[v] < 0) return;
         i32 r = ulk_vfind(P, (i32)v);
@@ -124,7 +124,7 @@ struct K_FlattenCount {
         if (r == (i32)v) roots[(*nroots)++] = r;
     }
 #else
-    ULK_D void warp(i64 v, bool valid) const
+    ULK_D void warp(i64 v, i32, i32, i32, bool valid) const
     {
         i32 r = -1;
         if (valid && P[v] >= 0) { r = ulk_vfind(P, (i32)v); P[v] = r; }
@@ -167,7 +167,7 @@ struct K_RootCode {
 // max_area, numbered among themselves (input of the oversegmentation pass)
 struct K_LabelCc {
     const i32 *P; const i32 *code; const i32 *cc_big; int mode; i32 *lab;
-    ULK_D void operator()(i64 v) const
+    ULK_D void operator()(i64 v, i32, i32, i32) const
     {
         i32 r = P[v];
         i32 c = r < 0 ? 0 : code[r];
@@ -184,34 +184,29 @@ struct K_FlagRoots {
 // For every active voxel the minimum incident edge by (weight, edge key); edge key =
 // 3*source + direction reproduces the enumeration order of edges_from_mask
 // (vendored/graph.py:41-57), i.e. higra's stable tie-break.
+// Candidates are visited in increasing edge-key order (-z, -y, -x, +x, +y, +z), so a strict
+// comparison of the weights alone yields the minimum of (weight, key).
 struct K_MinEdge {
     const i32 *lab; UlkCt ct; UlkDims dm;
     u32 *mw, *pk;
     ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
     {
-        i32 v = (i32)vv;
-        i32 l = lab[v];
+        const i32 v = (i32)vv;
+        const i32 l = lab[v];
         if (l <= 0) return;          // mw / pk are only ever read where lab > 0
-        u64 best = ULK_NONE64;
-        for (int d = 0; d < 3; ++d) {
-            i32 st = dm.stride(d);
-            if (dm.bwd(d, z, y, x)) {
-                i32 u = v - st;
-                if (lab[u] == l) {
-                    u64 k = ((u64)ulk_f2ord(ct.w(u, v)) << 32) | (u32)(3u * (u32)u + d);
-                    if (k < best) best = k;
-                }
-            }
-            if (dm.fwd(d, z, y, x)) {
-                i32 u = v + st;
-                if (lab[u] == l) {
-                    u64 k = ((u64)ulk_f2ord(ct.w(v, u)) << 32) | (u32)(3u * (u32)v + d);
-                    if (k < best) best = k;
-                }
-            }
-        }
-        mw[v] = (u32)(best >> 32);
-        pk[v] = (u32)best;
+        const i32 sy = dm.W, sz = dm.W * dm.H;
+        const i32 u0 = v - sz, u1 = v - sy, u2 = v - 1, u3 = v + 1, u4 = v + sy, u5 = v + sz;
+        const bool s0 = z > 0 && lab[u0] == l, s1 = y > 0 && lab[u1] == l, s2 = x > 0 && lab[u2] == l;
+        const bool s3 = x + 1 < dm.W && lab[u3] == l, s4 = y + 1 < dm.H && lab[u4] == l, s5 = z + 1 < dm.D && lab[u5] == l;
+        u32 bw = ULK_NONE32, bk = ULK_NONE32, w;
+        if (s0) { w = ulk_f2ord(ct.w(u0, v)); if (w < bw) { bw = w; bk = 3u * (u32)u0 + 2u; } }
+        if (s1) { w = ulk_f2ord(ct.w(u1, v)); if (w < bw) { bw = w; bk = 3u * (u32)u1 + 1u; } }
+        if (s2) { w = ulk_f2ord(ct.w(u2, v)); if (w < bw) { bw = w; bk = 3u * (u32)u2; } }
+        if (s3) { w = ulk_f2ord(ct.w(v, u3)); if (w < bw) { bw = w; bk = 3u * (u32)v; } }
+        if (s4) { w = ulk_f2ord(ct.w(v, u4)); if (w < bw) { bw = w; bk = 3u * (u32)v + 1u; } }
+        if (s5) { w = ulk_f2ord(ct.w(v, u5)); if (w < bw) { bw = w; bk = 3u * (u32)v + 2u; } }
+        mw[v] = bw;
+        pk[v] = bk;
     }
 };
 ULK_HD ULK_INLINE i32 ulk_edge_other(u32 key, i32 v, const UlkDims &dm)
@@ -225,7 +220,7 @@ ULK_HD ULK_INLINE i32 ulk_edge_other(u32 key, i32 v, const UlkDims &dm)
 struct K_Hook1 {
     const i32 *lab; const u32 *mw, *pk; UlkDims dm;
     i32 *bp; u8 *state; u32 *Lr; u32 *best; i32 *nbasins;
-    ULK_D void operator()(i64 vv) const
+    ULK_D void operator()(i64 vv, i32, i32, i32) const
     {
         i32 v = (i32)vv;
         state[v] = 0;
@@ -264,7 +259,7 @@ struct K_CompressCand {
     i32 *bp; const u32 *mw; const u32 *Lr; const u8 *state;
     i32 *cand; i32 *ncand; i32 *groots; i32 *ngroots;
 #ifdef ULK_EMU
-    void operator()(i64 vv) const
+    void operator()(i64 vv, i32, i32, i32) const
     {
         i32 v = (i32)vv;
         if (bp[v] < 0) return;
@@ -274,7 +269,7 @@ struct K_CompressCand {
         if (state[r] == 0 && mw[v] == Lr[r]) cand[(*ncand)++] = v;
     }
 #else
-    ULK_D void warp(i64 vv, bool valid) const
+    ULK_D void warp(i64 vv, i32, i32, i32, bool valid) const
     {
         i32 v = (i32)vv;
         bool is_groot = false, is_cand = false;
@@ -369,7 +364,7 @@ struct K_Decide2 {
 // these keys numbers the basins grouped by region, in raster order of their roots
 struct K_CompressRoots {
     i32 *bp; const i32 *lab; u64 *rootkeys; i32 *nroots;
-    ULK_D void operator()(i64 vv) const
+    ULK_D void operator()(i64 vv, i32, i32, i32) const
     {
         i32 v = (i32)vv;
         if (bp[v] < 0) return;
@@ -392,10 +387,10 @@ struct K_BasinRegroup {      // sorted position = global basin id
         ulk_atomic_add(&lab_hist[l - 1], 1);
     }
 };
-struct K_AssignBasin {
+struct K_AssignBasin {     // background stays at the memset value -1
     const i32 *bp; const u32 *gid_at_root;
     i32 *bas;
-    ULK_D void operator()(i64 v) const { i32 r = bp[v]; bas[v] = r < 0 ? -1 : (i32)gid_at_root[r]; }
+    ULK_D void operator()(i64 v, i32, i32, i32) const { i32 r = bp[v]; bas[v] = r < 0 ? -1 : (i32)gid_at_root[r]; }
 };
 // flow edges are spanning-tree edges of the basin of their supervertex
 struct K_FlowTop {
@@ -551,7 +546,7 @@ struct K_PlateauRelax {
 struct K_Attach {
     const i32 *bas; const u32 *mw, *jk; const i32 *b_lab; const i32 *bs;
     const i32 *Ipar; const u64 *Iwk; i32 *attach;
-    ULK_D void operator()(i64 v) const
+    ULK_D void operator()(i64 v, i32, i32, i32) const
     {
         i32 b = bas[v];
         if (b < 0) return;
@@ -650,8 +645,9 @@ struct K_Hist {
 // alone and the basin's altitude-0 node is created by the LAST edge it accepts: the
 // bottleneck of the raster-key MST.  K0 = max over voxels of their smallest in-basin edge
 // key is a lower bound that is tight whenever edges <= K0 already connect the basin.
-// edges of a basin whose raster key is <= K0[basin]; runs of x edges inside a warp segment are
-// hooked to their first voxel at initialisation (same scheme as the component labelling)
+// edges of a basin whose raster key is <= K0[basin].  Runs of x edges between voxels that are
+// neighbours in the (raster-ordered) voxel list and sit in one warp are hooked to their first
+// voxel at initialisation; K_K3Union joins the runs (same scheme as the component labelling).
 struct K_K3Init {
     const i32 *bas; const u32 *K0; i32 *P;
     ULK_D ULK_INLINE bool xlink(i64 v, i32 x, i32 b) const
@@ -667,23 +663,24 @@ struct K_K3Init {
 #else
     ULK_D void warp(i64 v, i32, i32, i32 x, bool valid) const
     {
-        const int lane = threadIdx.x & 31;     // == x & 31
+        const int lane = threadIdx.x & 31;
         i32 b = valid ? bas[v] : -1;
-        u32 linked = __ballot_sync(0xffffffffu, lane > 0 && xlink(v, x, b));
+        i32 vprev = __shfl_up_sync(0xffffffffu, (i32)v, 1);
+        u32 linked = __ballot_sync(0xffffffffu, lane > 0 && vprev == (i32)v - 1 && xlink(v, x, b));
         if (valid) P[v] = b < 0 ? -1 : (i32)v - (lane - ulk_run_start(linked, lane));
     }
 #endif
 };
 struct K_K3Union {
     const i32 *bas; UlkDims dm; const u32 *K0; i32 *P;
-    ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
+    // `boundary`: the x edge to v-1 was not joined at initialisation
+    ULK_D ULK_INLINE void join(i32 v, i32 z, i32 y, i32 x, bool boundary) const
     {
-        i32 v = (i32)vv;
         i32 b = bas[v];
         if (b < 0) return;
         u32 kmax = K0[b];
         bool left = x > 0 && bas[v - 1] == b && 3u * (u32)(v - 1) <= kmax;
-        if (left && (x & 31) == 0) ulk_vunion(P, v, v - 1);
+        if (left && boundary) ulk_vunion(P, v, v - 1);
         for (int d = 1; d < 3; ++d) {
             if (!dm.bwd(d, z, y, x)) continue;
             i32 u = v - dm.stride(d);
@@ -693,10 +690,19 @@ struct K_K3Union {
             ulk_vunion(P, v, u);
         }
     }
+#ifdef ULK_EMU
+    void operator()(i64 v, i32 z, i32 y, i32 x) const { join((i32)v, z, y, x, (x & 31) == 0); }
+#else
+    ULK_D void warp(i64 v, i32 z, i32 y, i32 x, bool valid) const
+    {
+        i32 vprev = __shfl_up_sync(0xffffffffu, (i32)v, 1);
+        if (valid) join((i32)v, z, y, x, (threadIdx.x & 31) == 0 || vprev != (i32)v - 1);
+    }
+#endif
 };
 struct K_K3FlattenCount {
     const i32 *bas; i32 *P; i32 *nroot; i32 *nmulti;
-    ULK_D void operator()(i64 v) const
+    ULK_D void operator()(i64 v, i32, i32, i32) const
     {
         if (P[v] < 0) return;
         i32 r = ulk_vfind(P, (i32)v);
@@ -725,7 +731,7 @@ struct K_K3FindBest {     // Boruvka step on the basins that are still split
 };
 struct K_K3Hook {
     const i32 *bas; UlkDims dm; i32 *P; u32 *best; u32 *K0;
-    ULK_D void operator()(i64 vv) const
+    ULK_D void operator()(i64 vv, i32, i32, i32) const
     {
         i32 v = (i32)vv;
         if (bas[v] < 0) return;
@@ -769,7 +775,7 @@ struct K_WriteLabels {
     const i32 *P; const i32 *code; const i32 *cc_big; i32 ncc;
     const i32 *basA; const i32 *region_of; const i32 *label_of_rec;
     i32 *lab2;
-    ULK_D void operator()(i64 v) const
+    ULK_D void operator()(i64 v, i32, i32, i32) const
     {
         i32 r = P[v];
         i32 c = r < 0 ? 0 : code[r];
@@ -777,4 +783,8 @@ struct K_WriteLabels {
         if (cc_big[c - 1] >= 0) lab2[v] = label_of_rec[ncc + region_of[basA[v]]];
         else lab2[v] = label_of_rec[c - 1];
     }
+};
+template <class T> struct K_FillAt {
+    T *p; T val;
+    ULK_D void operator()(i64 v, i32, i32, i32) const { p[v] = val; }
 };
