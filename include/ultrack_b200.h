@@ -118,6 +118,17 @@ ULK_API int ulk_segment_frame(const void *foreground, int fg_dtype, const void *
 ULK_API int ulk_segment_frame_host(const void *foreground, int fg_dtype, const void *contours, int ct_dtype,
                            const int64_t shape[3], const ulk_seg_params *params, int keep_labels,
                            void *stream, ulk_frame_nodes **out);
+/* pipelined ingest (processing.py:204,212 read `foreground[t]` / `contours[t]` per frame):
+ * ulk_upload_begin starts the host->device copy of a frame on the library's own copy stream and
+ * returns at once (asynchronous only for pinned host memory); ulk_segment_frame_uploaded waits
+ * for it on `stream`, segments the frame and releases the upload.  Begin frame t+1 before
+ * segmenting frame t and the copy is hidden behind the kernels.  At most two uploads in flight. */
+typedef struct ulk_frame_upload ulk_frame_upload;
+ULK_API int ulk_upload_begin(const void *foreground_host, int fg_dtype, const void *contours_host, int ct_dtype,
+                     const int64_t shape[3], ulk_frame_upload **out);
+ULK_API int ulk_segment_frame_uploaded(ulk_frame_upload *upload, const ulk_seg_params *params, int keep_labels,
+                               void *stream, ulk_frame_nodes **out);
+ULK_API void ulk_upload_free(ulk_frame_upload *upload);
 ULK_API void ulk_frame_nodes_free(ulk_frame_nodes *nodes);
 /* copies the device arrays into caller-provided host buffers (any may be NULL) */
 ULK_API int ulk_frame_nodes_to_host(const ulk_frame_nodes *nodes, int32_t *bbox, int32_t *centroid, int32_t *area,

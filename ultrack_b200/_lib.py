@@ -61,6 +61,7 @@ EXPORTS = [
     "ulk_segment_frame_host", "ulk_frame_nodes_free", "ulk_frame_nodes_to_host",
     "ulk_frame_nodes_from_host", "ulk_frame_nodes_to_device", "ulk_frame_nodes_from_device", "ulk_link_frames", "ulk_links_to_host", "ulk_links_free",
     "ulk_labels_to_contours", "ulk_synth_frame",
+    "ulk_upload_begin", "ulk_segment_frame_uploaded", "ulk_upload_free",
 ]
 
 
@@ -83,6 +84,10 @@ def bind(lib: C.CDLL) -> C.CDLL:
     lib.ulk_segment_frame_host.argtypes = seg_args
     lib.ulk_frame_nodes_free.argtypes = [PF]
     lib.ulk_frame_nodes_free.restype = None
+    lib.ulk_upload_begin.argtypes = [vp, C.c_int, vp, C.c_int, C.POINTER(i64), C.POINTER(vp)]
+    lib.ulk_segment_frame_uploaded.argtypes = [vp, C.POINTER(SegParams), C.c_int, vp, C.POINTER(PF)]
+    lib.ulk_upload_free.argtypes = [vp]
+    lib.ulk_upload_free.restype = None
     lib.ulk_frame_nodes_to_host.argtypes = [PF] + [vp] * 12 + [vp]
     lib.ulk_frame_nodes_from_host.argtypes = [i32, C.POINTER(i32), vp, vp, vp, vp, vp, vp, C.POINTER(PF)]
     lib.ulk_frame_nodes_to_device.argtypes = [PF, vp, vp, vp, vp, vp, vp]

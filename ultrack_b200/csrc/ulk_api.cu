@@ -75,6 +75,95 @@ int ulk_segment_frame_host(const void *foreground, int fg_dtype, const void *con
     return ulk_segment_frame(dfg, fg_dtype, dct, ct_dtype, shape, params, keep_labels, stream, out);
 }
 
+// ---- pipelined ingest: the copy of frame t+1 runs on the library's copy stream while frame t
+// is being segmented on the caller's stream.  Staging buffers are cached (two frames deep).
+struct ulk_frame_upload {
+    void *dfg, *dct;
+    size_t bfg, bct;
+    int fg_dtype, ct_dtype;
+    int64_t shape[3];
+#ifndef ULK_EMU
+    cudaEvent_t done;
+#endif
+};
+#ifndef ULK_EMU
+static cudaStream_t g_copy_stream = nullptr;
+struct StageBuf { void *p; size_t cap; bool busy; };
+static StageBuf g_stage[4] = {{nullptr, 0, false}, {nullptr, 0, false}, {nullptr, 0, false}, {nullptr, 0, false}};
+static void *stage_get(size_t bytes)
+{
+    for (auto &b : g_stage) if (!b.busy && b.p && b.cap >= bytes) { b.busy = true; return b.p; }
+    for (auto &b : g_stage) if (!b.busy) {
+        if (b.p) { cudaFree(b.p); b.p = nullptr; b.cap = 0; }
+        if (cudaMalloc(&b.p, bytes) != cudaSuccess) { cudaGetLastError(); b.p = nullptr; return nullptr; }
+        b.cap = bytes; b.busy = true;
+        return b.p;
+    }
+    return nullptr;
+}
+static void stage_put(void *p) { for (auto &b : g_stage) if (b.p == p) b.busy = false; }
+#endif
+
+int ulk_upload_begin(const void *foreground, int fg_dtype, const void *contours, int ct_dtype,
+                     const int64_t shape[3], ulk_frame_upload **out)
+{
+    if (!foreground || !contours || !shape || !out) ULK_FAIL(-1, "null argument");
+    *out = nullptr;
+    i64 V = shape[0] * shape[1] * shape[2];
+    if (V <= 0) ULK_FAIL(-1, "empty frame");
+    ulk_frame_upload *u = new ulk_frame_upload();
+    memset(u, 0, sizeof(*u));
+    u->fg_dtype = fg_dtype; u->ct_dtype = ct_dtype;
+    for (int d = 0; d < 3; ++d) u->shape[d] = shape[d];
+    u->bfg = (size_t)V * ulk_dtype_size(fg_dtype);
+    u->bct = (size_t)V * ulk_dtype_size(ct_dtype);
+#ifdef ULK_EMU
+    u->dfg = malloc(u->bfg); u->dct = malloc(u->bct);
+    memcpy(u->dfg, foreground, u->bfg); memcpy(u->dct, contours, u->bct);
+#else
+    if (!g_copy_stream) ULK_CUDA(cudaStreamCreateWithFlags(&g_copy_stream, cudaStreamNonBlocking));
+    u->dfg = stage_get(u->bfg);
+    u->dct = u->dfg ? stage_get(u->bct) : nullptr;
+    if (!u->dfg || !u->dct) {
+        if (u->dfg) stage_put(u->dfg);
+        delete u;
+        ULK_FAIL(-3, "device allocation failed (upload staging)");
+    }
+    ULK_CUDA(cudaEventCreateWithFlags(&u->done, cudaEventDisableTiming));
+    ULK_CUDA(cudaMemcpyAsync(u->dfg, foreground, u->bfg, cudaMemcpyHostToDevice, g_copy_stream));
+    ULK_CUDA(cudaMemcpyAsync(u->dct, contours, u->bct, cudaMemcpyHostToDevice, g_copy_stream));
+    ULK_CUDA(cudaEventRecord(u->done, g_copy_stream));
+#endif
+    *out = u;
+    return 0;
+}
+
+void ulk_upload_free(ulk_frame_upload *u)
+{
+    if (!u) return;
+#ifdef ULK_EMU
+    free(u->dfg); free(u->dct);
+#else
+    cudaEventSynchronize(u->done);       // the staging buffers go back only when the copy is over
+    cudaEventDestroy(u->done);
+    stage_put(u->dfg); stage_put(u->dct);
+#endif
+    delete u;
+}
+
+int ulk_segment_frame_uploaded(ulk_frame_upload *u, const ulk_seg_params *params, int keep_labels,
+                               void *stream, ulk_frame_nodes **out)
+{
+    if (!u || !params || !out) ULK_FAIL(-1, "null argument");
+#ifndef ULK_EMU
+    ULK_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, u->done, 0));
+#endif
+    // ulk_segment_frame returns after the stream has drained: the staging can be reused then
+    int rc = ulk_segment_frame(u->dfg, u->fg_dtype, u->dct, u->ct_dtype, u->shape, params, keep_labels, stream, out);
+    ulk_upload_free(u);
+    return rc;
+}
+
 void ulk_frame_nodes_free(ulk_frame_nodes *nodes) { ulk_frame_nodes_free_impl(nodes); }
 
 // copies between a node table and caller buffers; `dev` selects device-resident caller

@@ -88,6 +88,7 @@ int ulk_sort_keys_u64(const u64 *ki, u64 *ko, i64 n, ulk_stream_t)
 // ------------------------------------------------------------------ CUDA
 // per-kernel timing: one event pair per launch, resolved when the report is read
 #include <cxxabi.h>
+#include <thrust/iterator/counting_iterator.h>
 #include <map>
 #include <vector>
 bool g_ulk_prof_on = false;
@@ -368,7 +369,7 @@ struct UlkNonNegAt {
 int ulk_select_nonneg_i32(const i32 *in, i64 n, i32 *out, i32 *count_dev, ulk_stream_t s)
 {
     if (n <= 0) return 0;
-    cub::CountingInputIterator<i32> it(0);
+    thrust::counting_iterator<i32> it(0);
     UlkNonNegAt pred{in};
     size_t need = 0;
     ULK_CUDA(cub::DeviceSelect::If(nullptr, need, it, out, count_dev, (int)n, pred, s));

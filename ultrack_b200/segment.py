@@ -107,6 +107,58 @@ def segment_frame_device(lib, fg, ct, prm: _lib.SegParams, keep_labels: bool = F
     return handle
 
 
+class FrameUpload:
+    """Host->device copy of one frame in flight on the library's copy stream (`ulk_upload_begin`).
+
+    `segment()` begins the upload of frame t+1 before it segments frame t, so the PCIe copy is
+    hidden behind the kernels (the copy is asynchronous for pinned host memory only; pageable
+    numpy memory still works, the copy then happens inside `begin`)."""
+
+    def __init__(self, lib, fg, ct):
+        if tuple(fg.shape) != tuple(ct.shape):
+            raise ValueError(f"`foreground` and `contours` shape must match. Found {fg.shape} and {ct.shape}")
+        if fg.ndim not in (2, 3):
+            raise ValueError(f"frames must be 2-D or 3-D, found shape {fg.shape}")
+        self.lib = lib
+        self.keep = (fg, ct)          # the host buffers must outlive the copy
+        shape3 = tuple(fg.shape) if fg.ndim == 3 else (1,) + tuple(fg.shape)
+        self.handle = C.c_void_p()
+        _lib.check(lib, lib.ulk_upload_begin(
+            C.c_void_p(_host_ptr(fg)), _lib.dtype_code(_np_dtype(fg)), C.c_void_p(_host_ptr(ct)),
+            _lib.dtype_code(_np_dtype(ct)), (C.c_int64 * 3)(*shape3), C.byref(self.handle)))
+
+    def segment(self, prm: _lib.SegParams, keep_labels: bool = False, stream: int = 0):
+        """`ulk_segment_frame_uploaded`: waits for the copy on `stream`, segments, releases the upload."""
+        out = C.POINTER(_lib.FrameNodes)()
+        handle, self.handle = self.handle, None
+        rc = self.lib.ulk_segment_frame_uploaded(handle, C.byref(prm), int(keep_labels), C.c_void_p(stream), C.byref(out))
+        self.keep = None
+        _lib.check(self.lib, rc)
+        return out
+
+    def __del__(self):  # noqa: D105
+        if getattr(self, "handle", None):
+            self.lib.ulk_upload_free(self.handle)
+            self.handle = None
+
+
+def _np_dtype(a) -> np.dtype:
+    if type(a).__module__.startswith("torch"):
+        name = str(a.dtype).replace("torch.", "")
+        return np.dtype(bool) if name == "bool" else np.dtype(name)
+    return a.dtype
+
+
+def _host_ptr(a) -> int:
+    if type(a).__module__.startswith("torch"):
+        if not a.is_contiguous():
+            raise ValueError("host frames must be contiguous")
+        return a.data_ptr()
+    if not a.flags["C_CONTIGUOUS"]:
+        raise ValueError("host frames must be C-contiguous")
+    return a.ctypes.data
+
+
 def frame_rows(nodes: Dict[str, np.ndarray], time: int, ndim: int, max_segments_per_time: int):
     """Node table -> (`nodes` rows, `overlaps` rows) exactly as _process emits them
     (processing.py:235-300)."""
@@ -139,9 +191,9 @@ def frame_rows(nodes: Dict[str, np.ndarray], time: int, ndim: int, max_segments_
     return ids, rows, overlaps
 
 
-def _process(time: int, foreground, contours, config, db_path: str, max_segments_per_time: int,
-             catch_duplicates_expection: bool, lib) -> None:
-    """processing.py:160-340 for one timepoint."""
+def _stage(time: int, foreground, contours, config, lib):
+    """Reads frame `time` (processing.py:201-212) and starts moving it to the GPU.  Returns a
+    callable that segments it and the frame's ndim."""
     if config.random_seed == "frame":
         np.random.seed(time)
     fg = foreground[time]
@@ -155,11 +207,21 @@ def _process(time: int, foreground, contours, config, db_path: str, max_segments
         edge_map = edge_map + noise
         if _is_cuda_tensor(fg):
             fg = np.asarray(fg.cpu())
-    if not (_is_cuda_tensor(fg) and _is_cuda_tensor(edge_map)):
-        fg, edge_map = np.asarray(fg), np.asarray(edge_map)
-    ndim = fg.ndim
+    on_device = _is_cuda_tensor(fg) and _is_cuda_tensor(edge_map)
+    if not on_device:
+        fg, edge_map = np.ascontiguousarray(fg), np.ascontiguousarray(edge_map)
     prm = seg_params(config, np.dtype(bool) if str(fg.dtype).endswith("bool") else str(fg.dtype).replace("torch.", ""))
-    handle = segment_frame_device(lib, fg, edge_map, prm)
+    if on_device:
+        return (lambda: segment_frame_device(lib, fg, edge_map, prm)), fg.ndim
+    up = FrameUpload(lib, fg, edge_map)
+    return (lambda: up.segment(prm)), fg.ndim
+
+
+def _process(time: int, staged, db_path: str, max_segments_per_time: int,
+             catch_duplicates_expection: bool, lib) -> None:
+    """processing.py:160-340 for one timepoint (`staged` comes from `_stage`)."""
+    run, ndim = staged
+    handle = run()
     LOG.info(f"Computing nodes of time {time}")
     try:
         nodes = _lib.nodes_to_host(lib, handle)
@@ -225,7 +287,11 @@ def segment(
     if overwrite:
         frames.STORE.clear(db_path)
     sharding.barrier()
-    for time in sharding.shard(time_points, world, rank):
-        _process(time, foreground, contours, config.segmentation_config, db_path, max_segments_per_time,
-                 batch_index is not None, lib)
+    # the host->device copy of the next frame overlaps the kernels of the current one
+    mine = list(sharding.shard(time_points, world, rank))
+    staged = _stage(mine[0], foreground, contours, config.segmentation_config, lib) if mine else None
+    for k, time in enumerate(mine):
+        nxt = _stage(mine[k + 1], foreground, contours, config.segmentation_config, lib) if k + 1 < len(mine) else None
+        _process(time, staged, db_path, max_segments_per_time, batch_index is not None, lib)
+        staged = nxt
     sharding.barrier()
