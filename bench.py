@@ -349,15 +349,22 @@ def main():
     value = V * args.steps * world / (ms_max * 1e-3)
     kern_ms = sum(v[1] for v in prof.values())
     top = sorted(prof.items(), key=lambda kv: -kv[1][1])
-    dom_name, (dom_cnt, dom_ms) = top[0]
-    dom_bytes = bytes_model.kernel_bytes(dom_name, V)
+    # the dominant kernel = the one with the largest share of the timed region that is one of
+    # this library's voxel kernels (it has an entry in the byte model)
+    dom_name, (dom_cnt, dom_ms) = next(((k, v) for k, v in top if bytes_model.kernel_bytes(k, V, n_fg)), top[0])
+    dom_bytes = bytes_model.kernel_bytes(dom_name, V, n_fg)
     dom_avg_ms = dom_ms / dom_cnt
+    traffic = None
+    tf = ROOT / "profiles" / "ncu_traffic.json"     # dram bytes per launch from `ncu --set full` captures
+    if tf.exists():
+        traffic = json.loads(tf.read_text()).get(name, {}).get(dom_name.split("<")[0])
     roofline = {
         "bound": "hbm", "kernel": dom_name, "launches": dom_cnt, "avg_ms": dom_avg_ms,
         "share_of_kernel_time": dom_ms / kern_ms if kern_ms else None,
         "achieved": (dom_bytes / (dom_avg_ms * 1e-3) / 1e9) if dom_bytes else None, "peak": peak_gbs, "unit": "GB/s",
         "frac": (dom_bytes / (dom_avg_ms * 1e-3) / 1e9 / peak_gbs) if dom_bytes else None,
-        "algorithmic_bytes_per_launch": dom_bytes, "traffic": None, "peak_source": peak_src,
+        "algorithmic_bytes_per_launch": dom_bytes, "traffic": traffic, "peak_source": peak_src,
+        "n_foreground": n_fg,
     }
     b_frame = bytes_model.frame_bytes(V, 4, 4, n_fg, stats["n_nodes"], stats["mask_words"], stats["n_overlaps"])
     b_link = bytes_model.link_bytes(tot_links // max(args.steps, 1), tot_pairs // max(args.steps, 1),

@@ -8,44 +8,39 @@ Linking, per frame pair:  20 bytes per emitted link + per evaluated pair 2*36 by
 bbox/centroid records + the mask words of both bbox-overlap windows (bounded above by the two
 masks themselves; the model charges min(mask_i, mask_j) words twice).
 
-Per kernel: every array the kernel must read or write once per voxel (its own voxel's
-element; neighbour elements belong to other threads and are counted once there).  Values are
-bytes per voxel of the frame for float32 inputs; kernels that run on lists (basins, RAG edges,
-candidates) are not voxel-bound and carry no entry.
+Per kernel: every array element the kernel must read or write once for its own voxel
+(neighbour elements belong to other threads and are counted once there).  Dense kernels run
+over all V voxels of the frame; list kernels run over the n_fg foreground voxels only and also
+read their 4-byte list entry.  Kernels that run on small lists (basins, RAG edges, candidates,
+roots) are not voxel-bound and carry no entry.
 """
 from __future__ import annotations
 
 from typing import Dict, Optional
 
-# kernel name (as reported by ulk_profile_report) -> bytes per frame voxel per launch
-KERNEL_BYTES_PER_VOXEL: Dict[str, float] = {
-    "K_Threshold": 4 + 4 + 4 + 4,        # fg, ct in; staged ct, parent out
-    "K_CclUnion": 4 + 4,                 # parent in / out
-    "K_Flatten": 4 + 4,
-    "K_Compress": 4 + 4,
-    "K_CountByRoot": 4,
-    "K_CcStats": 4,
-    "K_RemoveSmall": 4 + 1,
-    "K_ApplyDrop": 1 + 4,
-    "K_FlagRoots": 4 + 4,
-    "K_FlagBigRoots": 4 + 4,
-    "K_LabelBigCc": 4 + 4,
-    "K_LabelSmallOnly": 4 + 4,
-    "K_WriteLabels": 4 + 4 + 4,
-    "K_MinEdge": 4 + 4 + 4 + 4,          # label, ct in; min weight, min key out
-    "K_Hook1": 4 + 4 + 4 + 4 + 1 + 4 + 4 + 4,
-    "K_CandInit": 4 + 4 + 1,
-    "K_BasinRootInfo": 4,
+# kernel name (as reported by ulk_profile_report) -> bytes per frame voxel per launch (float32 inputs)
+DENSE_BYTES_PER_VOXEL: Dict[str, float] = {
+    "K_Threshold": 4 + 4 + 4,            # fg, ct in; component forest out (float32 contours are not staged)
+    "cub::DeviceSelect::If": 4 + 0.3 * 4,   # forest in, list entry out for the foreground fraction
+}
+# kernel name -> bytes per FOREGROUND voxel per launch (including the 4-byte list entry)
+LIST_BYTES_PER_FG_VOXEL: Dict[str, float] = {
+    "K_CclUnion": 4 + 4 + 4,             # list, forest in / out
+    "K_FlattenCount": 4 + 4 + 4,
+    "K_LabelCc": 4 + 4 + 4,
+    "K_WriteLabels": 4 + 4 + 4 + 4,      # list, forest, basin, label out
+    "K_MinEdge": 4 + 4 + 4 + 4 + 4,      # list, label, contour in; min weight, min key out
+    "K_Hook1": 4 + 4 + 4 + 4 + 4 + 1,    # list, label, weight, key in; forest, state out
+    "K_CompressCand": 4 + 4 + 4 + 4,     # list, forest in/out, weight
+    "K_CompressRoots": 4 + 4 + 4,
     "K_AssignBasin": 4 + 4 + 4,
-    "K_BasinAccum": 4 + 4 + 4 + 4 + 4 + 4,
-    "K_JoinKey": 4 + 4 + 4 + 4,
-    "K_Attach": 4 + 4 + 4,
-    "K_RagInsert": 4 + 4 + 4,
-    "K_MinKeyInBasin": 4,
-    "K_K3Init": 4 + 4,
-    "K_K3Union": 4 + 4,
-    "K_K3CountRoots": 4 + 4,
-    "K_MaskPaint": 4,
+    "K_BasinAccum": 4 + 4 + 4 + 4 + 4 + 4,   # list, basin, label, weight, key in; join key out
+    "K_RagInsert": 4 + 4 + 4 + 4,        # list, basin, label, contour
+    "K_Attach": 4 + 4 + 4 + 4,           # list, basin, weight, join key
+    "K_K3Init": 4 + 4 + 4,
+    "K_K3Union": 4 + 4 + 4 + 4,
+    "K_K3FlattenCount": 4 + 4 + 4 + 4,
+    "K_MaskPaint": 4 + 4 + 0.125,        # list, basin in; one mask bit out (per emitted ancestor)
 }
 
 
@@ -59,7 +54,12 @@ def link_bytes(n_links: int, n_pairs: int, mean_mask_words: float) -> int:
     return int(20 * n_links + n_pairs * (2 * 36 + 2 * 4 * mean_mask_words))
 
 
-def kernel_bytes(name: str, voxels: int) -> Optional[float]:
+def kernel_bytes(name: str, voxels: int, n_foreground: int) -> Optional[float]:
+    """Algorithmic bytes of one launch of kernel `name` on a frame of `voxels` voxels of which
+    `n_foreground` are foreground."""
     base = name.split("<")[0]
-    bpv = KERNEL_BYTES_PER_VOXEL.get(base)
-    return None if bpv is None else bpv * voxels
+    if base in DENSE_BYTES_PER_VOXEL:
+        return DENSE_BYTES_PER_VOXEL[base] * voxels
+    if base in LIST_BYTES_PER_FG_VOXEL:
+        return LIST_BYTES_PER_FG_VOXEL[base] * n_foreground
+    return None
