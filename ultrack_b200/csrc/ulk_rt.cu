@@ -69,6 +69,13 @@ int ulk_select_nonneg_i32(const i32 *in, i64 n, i32 *out, i32 *count, ulk_stream
     *count = c;
     return 0;
 }
+int ulk_select_list_pos_i32(const i32 *list, i64 n, const i32 *lab, i32 *out, i32 *count, ulk_stream_t)
+{
+    i32 c = 0;
+    for (i64 i = 0; i < n; ++i) if (lab[list[i]] > 0) out[c++] = list[i];
+    *count = c;
+    return 0;
+}
 int ulk_sort_keys_u32(const u32 *ki, u32 *ko, i64 n, ulk_stream_t)
 {
     std::vector<u32> k(ki, ki + n);
@@ -89,6 +96,7 @@ int ulk_sort_keys_u64(const u64 *ki, u64 *ko, i64 n, ulk_stream_t)
 // per-kernel timing: one event pair per launch, resolved when the report is read
 #include <cxxabi.h>
 #include <thrust/iterator/counting_iterator.h>
+#include <thrust/iterator/transform_iterator.h>
 #include <map>
 #include <vector>
 bool g_ulk_prof_on = false;
@@ -376,6 +384,44 @@ int ulk_select_nonneg_i32(const i32 *in, i64 n, i32 *out, i32 *count_dev, ulk_st
     if (cub_tmp(need)) return -2;
     ProfScope ps("cub::DeviceSelect::If", s);
     ULK_CUDA(cub::DeviceSelect::If(g_cub_tmp, need, it, out, count_dev, (int)n, pred, s));
+    ++g_ulk_launches;
+    return 0;
+}
+struct UlkPopc {
+    __host__ __device__ i32 operator()(const u32 &w) const
+    {
+#ifdef __CUDA_ARCH__
+        return __popc(w);
+#else
+        return __builtin_popcount(w);
+#endif
+    }
+};
+int ulk_exclusive_scan_popc_u32(const u32 *words, i32 *out, i64 n, ulk_stream_t s)
+{
+    if (n <= 0) return 0;
+    auto it = thrust::make_transform_iterator(words, UlkPopc());
+    size_t need = 0;
+    ULK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, need, it, out, (int)n, s));
+    if (cub_tmp(need)) return -2;
+    ProfScope ps("cub::DeviceScan::ExclusiveSum", s);
+    ULK_CUDA(cub::DeviceScan::ExclusiveSum(g_cub_tmp, need, it, out, (int)n, s));
+    ++g_ulk_launches;
+    return 0;
+}
+struct UlkPosAt {
+    const i32 *p;
+    __device__ bool operator()(const i32 &v) const { return p[v] > 0; }
+};
+int ulk_select_list_pos_i32(const i32 *list, i64 n, const i32 *lab, i32 *out, i32 *count_dev, ulk_stream_t s)
+{
+    if (n <= 0) return ulk_memset(count_dev, 0, sizeof(i32), s);
+    UlkPosAt pred{lab};
+    size_t need = 0;
+    ULK_CUDA(cub::DeviceSelect::If(nullptr, need, list, out, count_dev, (int)n, pred, s));
+    if (cub_tmp(need)) return -2;
+    ProfScope ps("cub::DeviceSelect::If", s);
+    ULK_CUDA(cub::DeviceSelect::If(g_cub_tmp, need, list, out, count_dev, (int)n, pred, s));
     ++g_ulk_launches;
     return 0;
 }

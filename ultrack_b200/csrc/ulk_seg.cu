@@ -124,6 +124,106 @@ struct K_OverlapWrite {
 struct K_Iota { u32 *p; ULK_D void operator()(i64 i) const { p[i] = (u32)i; } };
 struct K_Valid { const u32 *c; i32 *f; ULK_D void operator()(i64 i) const { f[i] = c[i] != ULK_NONE32; } };
 
+// ------------------------------------------------------------------ threshold + foreground list
+// K_Threshold streams the two input volumes once: a warp takes U consecutive 32-voxel row
+// segments, issues all its loads first, then writes the component forest (runs hooked to
+// their first voxel) and one foreground bit word per segment.  The raster-ordered foreground
+// list comes from those words (prefix sum of their population counts + one expansion pass),
+// not from a second pass over the voxels.
+#ifndef ULK_EMU
+template <int U, bool F32> __global__ void __launch_bounds__(256)
+ulk_threshold_kernel(K_Threshold k, i32 W, u32 S, u32 ntask, u32 *words)
+{
+    const int lane = threadIdx.x & 31;
+    const u32 t0 = (u32)((((i64)blockIdx.x * 256 + threadIdx.x) >> 5) * U);
+    if (t0 >= ntask) return;                  // the whole warp leaves together
+    u32 r = t0 / S, sg = t0 - r * S;
+    i64 v[U]; bool valid[U]; float f[U], c[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        i32 x = (i32)sg * 32 + lane;
+        valid[u] = t0 + u < ntask && x < W;
+        v[u] = (i64)r * W + x;
+        if (F32 && valid[u]) { f[u] = ((const float *)k.fg)[v[u]]; c[u] = ((const float *)k.ct)[v[u]]; }
+        if (++sg == S) { sg = 0; ++r; }
+    }
+    u32 mx = 0;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        bool on = false;
+        u32 bits = 0;
+        if (valid[u]) {
+            if (F32) {
+                on = (double)f[u] > k.thr;
+                float a = fabsf(c[u]);
+                if (a <= 3.0e38f) bits = __float_as_uint(a);
+            } else on = k.stage(v[u], bits);
+        }
+        mx = bits > mx ? bits : mx;
+        bool prev = __shfl_up_sync(0xffffffffu, on ? 1 : 0, 1) != 0;
+        u32 linked = __ballot_sync(0xffffffffu, on && prev && lane > 0);
+        u32 fgm = __ballot_sync(0xffffffffu, on);
+        if (valid[u]) k.P[v[u]] = on ? (i32)v[u] - (lane - ulk_run_start(linked, lane)) : -1;
+        if (lane == 0 && t0 + u < ntask) words[t0 + u] = fgm;
+    }
+    u32 m = __reduce_max_sync(0xffffffffu, mx);
+    if (lane == 0 && m > *k.cmax) atomicMax(k.cmax, m);
+}
+__global__ void __launch_bounds__(256)
+ulk_expand_kernel(const u32 *words, const i32 *off, u32 ntask, i32 W, u32 S, UlkFastDiv fS, i32 *list, i32 *count)
+{
+    const int lane = threadIdx.x & 31;
+    const u32 t = blockIdx.x * 256u + threadIdx.x;
+    u32 w = 0; i32 o = 0, base = 0;
+    if (t < ntask) {
+        w = words[t]; o = off[t];
+        u32 r = fS.div(t);
+        base = (i32)(r * (u32)W + (t - r * S) * 32u);
+    }
+    if (t == ntask - 1) *count = o + __popc(w);
+    u32 m = __ballot_sync(0xffffffffu, w != 0);
+    while (m) {
+        int j = __ffs(m) - 1;
+        m &= m - 1;
+        u32 wj = __shfl_sync(0xffffffffu, w, j);
+        i32 oj = __shfl_sync(0xffffffffu, o, j), bj = __shfl_sync(0xffffffffu, base, j);
+        if ((wj >> lane) & 1u) list[oj + __popc(wj & ((1u << lane) - 1u))] = bj + lane;
+    }
+}
+#endif
+// P (component forest, -1 on the background), *cmax, the foreground list and its length
+static int threshold_and_list(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const K_Threshold &k, i32 *fgl, i32 *nfg_dev)
+{
+#ifdef ULK_EMU
+    ulk_launch_vox_warp(dm.D, dm.H, dm.W, st, k);
+    return ulk_select_nonneg_i32(k.P, dm.V, fgl, nfg_dev, st);
+#else
+    const u32 S = (u32)((dm.W + 31) / 32);
+    const i64 nt = (i64)dm.D * dm.H * S;
+    const u32 ntask = (u32)nt;
+    u32 *words = A.get<u32>(nt);
+    i32 *off = A.get<i32>(nt);
+    CHKA(A);
+    const int U = 4;
+    const i64 warps = (nt + U - 1) / U;
+    const unsigned grid = (unsigned)((warps + 7) / 8);
+    if (g_ulk_prof_on) ulk_prof_begin(typeid(K_Threshold).name(), st);
+    if (k.fgt == ULK_F32 && k.ctt == ULK_F32) ulk_threshold_kernel<U, true><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
+    else ulk_threshold_kernel<U, false><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
+    if (g_ulk_prof_on) ulk_prof_end(st);
+    ++g_ulk_launches;
+    CHK(ulk_exclusive_scan_popc_u32(words, off, nt, st));
+    UlkFastDiv fS;
+    fS.init(S);
+    if (g_ulk_prof_on) ulk_prof_begin("K_ExpandForeground", st);
+    ulk_expand_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(words, off, ntask, dm.W, S, fS, fgl, nfg_dev);
+    if (g_ulk_prof_on) ulk_prof_end(st);
+    ++g_ulk_launches;
+    A.release(words); A.release(off);
+    return 0;
+#endif
+}
+
 // ------------------------------------------------------------------ voxel stage
 struct VoxelStage {
     i32 *bas = nullptr; i32 B = 0; i32 Eg = 0;
@@ -390,13 +490,12 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     u32 *cmax = A.get<u32>(1);
     CHKA(A);
     CHK(ulk_memset(cmax, 0, 4, st));
-    ulk_launch_vox_warp(dm.D, dm.H, dm.W, st, K_Threshold{fg, fg_dtype, prm->threshold, ctp, ct_dtype, ctf, ctd, P, cmax});
-    // ---- connected components (4/6-connected): union of runs, flatten + sizes + root list
     // ---- the foreground voxel list (raster order): every later voxel kernel runs on it
     i32 *fgl = A.get<i32>(V);
     i32 *nfg_dev = A.get<i32>(1);
     CHKA(A);
-    CHK(ulk_select_nonneg_i32(P, V, fgl, nfg_dev, st));
+    CHK(threshold_and_list(st, A, dm, K_Threshold{fg, fg_dtype, prm->threshold, ctp, ct_dtype, ctf, ctd, P, cmax}, fgl, nfg_dev));
+    // ---- connected components (4/6-connected): union of runs, flatten + sizes + root list
     i32 nfg = 0;
     CHK(ulk_read(&nfg, nfg_dev, 1, st));
     ulk_launch_list(fgl, nfg, dm, st, K_CclUnion{P, dm});
@@ -456,14 +555,22 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         CHKA(AA);
         CHK(ulk_memset(labA, 0, (size_t)V * sizeof(i32), st));
         ulk_launch_list(fgl, nfg, dm, st, K_LabelCc{P, code, cc_big, 1, labA});
+        // pass A only ever touches the voxels of the components above max_area: its kernels run
+        // on that sub-list (raster order kept), not on the whole foreground
+        i32 *fglA = AA.get<i32>(nfg);
+        i32 *nfgA_dev = AA.get<i32>(1);
+        CHKA(AA);
+        CHK(ulk_select_list_pos_i32(fgl, nfg, labA, fglA, nfgA_dev, st));
+        i32 nfgA = 0;
+        CHK(ulk_read(&nfgA, nfgA_dev, 1, st));
         VoxelStage va;
-        CHK(voxel_stage(st, AA, dm, fgl, nfg, ct, labA, n_big, true, false, false, fixscale, va, &stats_local));
+        CHK(voxel_stage(st, AA, dm, fglA, nfgA, ct, labA, n_big, true, false, false, fixscale, va, &stats_local));
         UlkHierScratch S;
         CHK(alloc_scratch(AA, va.B, va.Eg, S));
         UlkBasins Bv{va.b_size, va.g_L, va.b_top, nullptr, nullptr, nullptr, nullptr};
         UlkEdges Ev{va.ea, va.eb, va.wk, va.k3, va.cnt, va.shi, va.slo};
         ulk_launch(n_big, st, K_HierStage1{va.bs, va.es, Bv, Ev, S});
-        ulk_launch_list(fgl, nfg, dm, st, K_Attach{va.bas, va.mw, va.jk, va.g_lab, va.bs, S.Ipar, S.Iwk, S.attach});
+        ulk_launch_list(fglA, nfgA, dm, st, K_Attach{va.bas, va.mw, va.jk, va.g_lab, va.bs, S.Ipar, S.Iwk, S.attach});
         i32 *region_of = AA.get<i32>(va.B);
         u64 *rkey_w = AA.get<u64>(va.B), *rkey_k = AA.get<u64>(va.B);
         CHKA(AA);
