@@ -49,8 +49,37 @@ class ClockSampler:
 
     def __init__(self, index: int):
         self.index, self.rows, self.proc = index, [], None
+        self.nvml = None
+
+    def _nvml_loop(self, pynvml, h):
+        R = {"hw_slowdown": pynvml.nvmlClocksEventReasonHwSlowdown,
+             "hw_thermal_slowdown": pynvml.nvmlClocksEventReasonHwThermalSlowdown,
+             "sw_thermal_slowdown": pynvml.nvmlClocksEventReasonSwThermalSlowdown,
+             "sw_power_cap": pynvml.nvmlClocksEventReasonSwPowerCap}
+        mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+        while not self._stop.is_set():
+            sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+            bits = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+            self.rows.append([str(sm), str(mx)] + ["Active" if bits & R[n] else "Not Active" for n in
+                                                   ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")])
+            self._stop.wait(0.05)
 
     def start(self):
+        # in-process NVML (two light queries per sample); a spawned `nvidia-smi -lms` re-initialises
+        # the driver query path every 100 ms and was seen to stall kernel launches for > 100 ms
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[self.index]) if vis and vis.split(",")[self.index].isdigit() else self.index
+            h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+            self._stop = threading.Event()
+            self.nvml = threading.Thread(target=self._nvml_loop, args=(pynvml, h), daemon=True)
+            self.nvml.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index),
@@ -64,10 +93,14 @@ class ClockSampler:
             self.rows.append([c.strip() for c in line.split(",")])
 
     def stop(self):
-        if self.proc is None:
+        if self.nvml is not None:
+            self._stop.set()
+            self.nvml.join(1.0)
+        elif self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
+        else:
+            time.sleep(0.15)
+            self.proc.terminate()
         sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
         mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
@@ -144,7 +177,7 @@ def run_cpu_arm(shape, radius, steps: int, warmup: int, max_workers: int = 0):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=4)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default=os.environ.get("ULK_BENCH_WORKLOAD", "auto"))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
@@ -263,13 +296,17 @@ def main():
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         tot_links = tot_pairs = 0
+        step_ev = []
         for i in range(args.steps):
             prev, nl, npairs, _ = step(i, prev)
             tot_links += nl
             tot_pairs += npairs
+            step_ev.append(torch.cuda.Event(enable_timing=True))
+            step_ev[-1].record(stream)
         e1.record(stream)
         barrier()
         ms = e0.elapsed_time(e1)
+        ms_steps = [round(a.elapsed_time(b), 3) for a, b in zip([e0] + step_ev[:-1], step_ev)]
         clk = clocks.stop()
         lib.ulk_profile_enable(0)
         launches = lib.ulk_launch_count() - launches0
@@ -372,7 +409,8 @@ def main():
     pipe_gbs = (b_frame + b_link) * args.steps / (ms * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": "voxels/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "ms_steps_rank0": ms_steps,
+        "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": desc, "frame_shape": list(shape), "segmentation": SEG, "linking": LINK,
                    "synthetic": dict(SYNTH, radius=radius), "l2": "inputs larger than L2 (no flush needed)",

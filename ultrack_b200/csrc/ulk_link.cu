@@ -56,6 +56,28 @@ struct K_SrcBounds {
             ulk_atomic_max(&mx[d], ulk_d2ord(p[d]));
         }
     }
+#ifndef ULK_EMU
+    ULK_D void warp(i64 i, bool valid) const     // one pair of atomics per axis and warp
+    {
+        u64 lo[3] = {ULK_NONE64, ULK_NONE64, ULK_NONE64}, hi[3] = {0, 0, 0};
+        if (valid) {
+            double p[3];
+            src_pos(cen + 3 * i, g, p);
+            for (int d = 0; d < 3; ++d) lo[d] = hi[d] = ulk_d2ord(p[d]);
+        }
+        for (int d = 0; d < 3; ++d) {
+            for (int o = 16; o > 0; o >>= 1) {
+                u64 a = __shfl_xor_sync(0xffffffffu, lo[d], o), b = __shfl_xor_sync(0xffffffffu, hi[d], o);
+                lo[d] = a < lo[d] ? a : lo[d];
+                hi[d] = b > hi[d] ? b : hi[d];
+            }
+            if ((threadIdx.x & 31) == 0 && lo[d] != ULK_NONE64) {
+                if (lo[d] < mn[d]) ulk_atomic_min(&mn[d], lo[d]);
+                if (hi[d] > mx[d]) ulk_atomic_max(&mx[d], hi[d]);
+            }
+        }
+    }
+#endif
 };
 struct K_SrcCell {
     const i32 *cen; LinkGeom g; u32 *cell; u32 *idx; i32 *hist;
@@ -127,7 +149,61 @@ struct K_PairIoU {
     const i32 *sbb, *sarea; const i64 *soff; const u32 *smask;
     const i32 *dbb, *darea; const i64 *doff; const u32 *dmask;
     const double *shift; i32 k; const i32 *cidx; const double *cd2; const i32 *ccount;
-    double dw; double *cw; double *cdist;
+    double dw; double *cw; double *cdist; i64 slots;
+#ifndef ULK_EMU
+    // one warp per candidate pair: lanes take the (z, y) rows of the bbox overlap window
+    ULK_D void warp(i64 ii, bool) const
+    {
+        const int lane = threadIdx.x & 31;
+        const i64 i = ii >> 5;
+        if (i >= slots) return;
+        i64 t = i / k;
+        i32 slot = (i32)(i % k);
+        if (slot >= ccount[t]) return;
+        i32 s = cidx[i];
+        i32 b1[6], b2[6];
+        for (int d = 0; d < 6; ++d) { b1[d] = dbb[6 * t + d]; b2[d] = sbb[6 * s + d]; }
+        if (shift)
+            for (int d = 0; d < 3; ++d) { i32 r = (i32)rint(shift[3 * t + d]); b1[d] += r; b1[d + 3] += r; }
+        i32 lo[3], hi[3];
+        bool hit = true;
+        for (int d = 0; d < 3; ++d) {
+            lo[d] = b1[d] > b2[d] ? b1[d] : b2[d];
+            hi[d] = b1[d + 3] < b2[d + 3] ? b1[d + 3] : b2[d + 3];
+            if (lo[d] >= hi[d]) hit = false;
+        }
+        u32 cnt = 0;
+        if (hit) {
+            i64 h1 = b1[4] - b1[1], w1 = (b1[5] - b1[2] + 31) / 32;
+            i64 h2 = b2[4] - b2[1], w2 = (b2[5] - b2[2] + 31) / 32;
+            const u32 *m1 = dmask + doff[t], *m2 = smask + soff[s];
+            const i32 nx = hi[2] - lo[2], ny = hi[1] - lo[1];
+            const i32 rows = (hi[0] - lo[0]) * ny;      // a window of one node: far below 2^31
+            for (i32 r = lane; r < rows; r += 32) {
+                i32 z = lo[0] + r / ny, y = lo[1] + r % ny;
+                const u32 *r1 = m1 + ((i64)(z - b1[0]) * h1 + (y - b1[1])) * w1;
+                const u32 *r2 = m2 + ((i64)(z - b2[0]) * h2 + (y - b2[1])) * w2;
+                for (i32 x = 0; x < nx; x += 32) {
+                    u32 a = mask_bits32(r1, w1, (i64)(lo[2] - b1[2]) + x);
+                    u32 b = mask_bits32(r2, w2, (i64)(lo[2] - b2[2]) + x);
+                    u32 m = a & b;
+                    i32 rem = nx - x;
+                    if (rem < 32) m &= (1u << rem) - 1u;
+                    cnt += ulk_popc(m);
+                }
+            }
+        }
+        // per-lane counts stay below 2^32 for any window that fits a frame of < 2^31 voxels
+        i64 inter = (i64)__reduce_add_sync(0xffffffffu, cnt);
+        if (lane != 0) return;
+        double dist = sqrt(cd2[i]);
+        cdist[i] = dist;
+        double iou = 0.0;
+        if (inter > 0) iou = (double)inter / (double)((i64)darea[t] + (i64)sarea[s] - inter);
+        double pen = dw * dist;
+        cw[i] = iou - pen;
+    }
+#endif
     ULK_D void operator()(i64 i) const
     {
         i64 t = i / k;
@@ -234,7 +310,7 @@ int ulk_link_frames_impl(ulk_stream_t st, const ulk_frame_nodes *src, const ulk_
     CHK(ulk_memset(bounds + 3, 0, 3 * 8, st));
     for (int d = 0; d < 3; ++d) { g.mn[d] = 0; g.nc[d] = 1; }
     g.cs = 1;
-    ulk_launch(Ns, st, K_SrcBounds{src->centroid, g, bounds, bounds + 3});
+    ulk_launch_warp(Ns, st, K_SrcBounds{src->centroid, g, bounds, bounds + 3});
     u64 hb[6];
     CHK(ulk_read(hb, bounds, 6, st));
     double mx[3];
@@ -271,9 +347,13 @@ int ulk_link_frames_impl(ulk_stream_t st, const ulk_frame_nodes *src, const ulk_
     i64 *nout64 = A.get<i64>(Nd + 1), *ooff = A.get<i64>(Nd + 1);
     CHKA(A);
     ulk_launch(Nd, st, K_KnnSelect{src->centroid, dst->centroid, shift, g, sidx, cstart, k, cidx, cd2, ccount});
-    ulk_launch(slots, st, K_PairIoU{src->bbox, src->area, src->mask_off, src->mask, dst->bbox, dst->area,
-                                    dst->mask_off, dst->mask, shift, k, cidx, cd2, ccount,
-                                    prm->distance_weight, cw, cdist});
+    K_PairIoU piou{src->bbox, src->area, src->mask_off, src->mask, dst->bbox, dst->area,
+                   dst->mask_off, dst->mask, shift, k, cidx, cd2, ccount, prm->distance_weight, cw, cdist, slots};
+#ifdef ULK_EMU
+    ulk_launch(slots, st, piou);
+#else
+    ulk_launch_warp(slots * 32, st, piou);
+#endif
     ulk_launch(Nd, st, K_LinkTopK{k, prm->max_neighbors, ccount, cidx, cw, cdist, nout});
     CHK(ulk_memset(nout + Nd, 0, sizeof(i32), st));
     ulk_launch(Nd + 1, st, K_I32ToI64{nout, nout64});

@@ -103,6 +103,26 @@ struct K_MaskPaint {
             ulk_atomic_or(&mask[word], 1u << (rx & 31));
         }
     }
+#ifndef ULK_EMU
+    // lanes of one basin climb the same ancestor chain in lockstep; those that fall into the
+    // same mask word (consecutive x of one row) merge their bits and issue one atomic
+    ULK_D void warp(i64 vv, i32 z, i32 y, i32 x, bool valid) const
+    {
+        const int lane = threadIdx.x & 31;
+        i32 b = valid ? bas[(i32)vv] : -1;
+        u32 grp = __match_any_sync(0xffffffffu, b);
+        if (b < 0) return;
+        for (i32 n = bnode[b]; n >= 0; n = parent[n]) {
+            const i32 *bb = bbox + 6 * n;
+            i64 bh = bb[4] - bb[1], wpr = (bb[5] - bb[2] + 31) / 32;
+            i32 rx = x - bb[2];
+            i64 word = moff[n] + ((i64)(z - bb[0]) * bh + (y - bb[1])) * wpr + (rx >> 5);
+            u32 sub = __match_any_sync(grp, (unsigned long long)word);
+            u32 bits = __reduce_or_sync(sub, 1u << (rx & 31));
+            if (lane == __ffs(sub) - 1) atomicOr(&mask[word], bits);
+        }
+    }
+#endif
 };
 struct K_AncestorCount {
     const i32 *parent; i32 *depth;
@@ -204,12 +224,19 @@ static int threshold_and_list(ulk_stream_t st, UlkArena &A, const UlkDims &dm, c
     u32 *words = A.get<u32>(nt);
     i32 *off = A.get<i32>(nt);
     CHKA(A);
-    const int U = 4;
+    static const int U = getenv("ULK_THR_U") ? atoi(getenv("ULK_THR_U")) : 4;
     const i64 warps = (nt + U - 1) / U;
     const unsigned grid = (unsigned)((warps + 7) / 8);
     if (g_ulk_prof_on) ulk_prof_begin(typeid(K_Threshold).name(), st);
-    if (k.fgt == ULK_F32 && k.ctt == ULK_F32) ulk_threshold_kernel<U, true><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
-    else ulk_threshold_kernel<U, false><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
+    if (k.fgt == ULK_F32 && k.ctt == ULK_F32) {
+        if (U == 8) ulk_threshold_kernel<8, true><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
+        else if (U == 2) ulk_threshold_kernel<2, true><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
+        else ulk_threshold_kernel<4, true><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
+    } else {
+        if (U == 8) ulk_threshold_kernel<8, false><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
+        else if (U == 2) ulk_threshold_kernel<2, false><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
+        else ulk_threshold_kernel<4, false><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
+    }
     if (g_ulk_prof_on) ulk_prof_end(st);
     ++g_ulk_launches;
     CHK(ulk_exclusive_scan_popc_u32(words, off, nt, st));
@@ -498,14 +525,13 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     // ---- connected components (4/6-connected): union of runs, flatten + sizes + root list
     i32 nfg = 0;
     CHK(ulk_read(&nfg, nfg_dev, 1, st));
-    ulk_launch_list(fgl, nfg, dm, st, K_CclUnion{P, dm});
     i32 *cnt = A.get<i32>(V);            // sizes at the roots, later the component code at the roots
-    i32 *lab2 = A.get<i32>(V);           // region labels; until they are written: the root list
+    i32 *lab2 = P;                       // region labels are written in place over the component forest (-1 stays on the background)
     i32 *ctr = A.get<i32>(4);
+    u32 *roots0 = A.get<u32>(nfg);
     CHKA(A);
-    CHK(ulk_memset(cnt, 0, (size_t)V * sizeof(i32), st));
+    ulk_launch_list(fgl, nfg, dm, st, K_CclUnion{P, dm, cnt});
     CHK(ulk_memset(ctr, 0, 4 * sizeof(i32), st));
-    u32 *roots0 = (u32 *)lab2;
     ulk_launch_list_warp(fgl, nfg, dm, st, K_FlattenCount{P, cnt, (i32 *)roots0, ctr});
     i32 hc[4];
     u32 h_cmax = 0;
@@ -529,6 +555,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     i32 *rsize = A.get<i32>(n_roots), *cc_big = A.get<i32>(n_roots);
     CHKA(A);
     CHK(ulk_sort_keys_u32(roots0, roots, n_roots, st));
+    A.release(roots0);
     i32 max_size = (i32)(prm->min_area / prm->min_area_factor) - 1;
     int do_remove = n_roots > 1 && max_size >= 1;
     ulk_launch(n_roots, st, K_RootFlags{roots, cnt, max_size, do_remove, max_area_i, keep, big, rsize});
@@ -547,7 +574,6 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     // ---- region labels: components, oversegmented where area > max_area
     i32 R = n_cc;
     if (n_big == 0) {
-        CHK(ulk_memset(lab2, 0, (size_t)V * sizeof(i32), st));
         ulk_launch_list(fgl, nfg, dm, st, K_LabelCc{P, code, cc_big, 0, lab2});
     } else {
         UlkArena AA;
@@ -590,7 +616,6 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         ulk_launch(nrec, st, K_Gather<u32>{rec_cc, perm0, c0});
         CHK(ulk_sort_pairs_u32(c0, c1, perm0, perm1, nrec, st));              // then by component
         ulk_launch(nrec, st, K_RankToLabel{perm1, c1, label_of_rec});
-        CHK(ulk_memset(lab2, 0, (size_t)V * sizeof(i32), st));
         ulk_launch_list(fgl, nfg, dm, st, K_WriteLabels{P, code, cc_big, n_cc, va.bas, region_of, label_of_rec, lab2});
         // number of valid records = regions
         i32 *nvalid = AA.get<i32>(nrec + 1), *nvpre = AA.get<i32>(nrec + 1);
@@ -601,11 +626,11 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         CHK(ulk_read(&R, nvpre + nrec, 1, st));
         CHK(ulk_sync(st));
     }
-    A.release(cc_big); A.release(cnt); A.release(P);
+    A.release(cc_big); A.release(cnt);
     if (keep_labels) {
         F->labels = keep_alloc<i32>(V);
         if (!F->labels) return -3;
-        CHK(ulk_d2d(F->labels, lab2, (size_t)V * sizeof(i32), st));
+        ulk_launch(V, st, K_CopyLabels{lab2, F->labels});
     }
     F->n_hier = R;
 
@@ -666,7 +691,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     if (!F->mask) ULK_FAIL(-3, "device allocation failed");
     CHK(ulk_memset(F->mask, 0, (size_t)total_words * 4, st));
     ulk_launch(vb.B, st, K_BasinNodeGlobal{vb.g_lab, noff, O.basin_node, bnode});
-    ulk_launch_list(fgl, nfg, dm, st, K_MaskPaint{vb.bas, bnode, F->parent, F->bbox, F->mask_off, dm, F->mask});
+    ulk_launch_list_warp(fgl, nfg, dm, st, K_MaskPaint{vb.bas, bnode, F->parent, F->bbox, F->mask_off, dm, F->mask});
     // ---- overlaps: (node, emitted proper ancestor) pairs, processing.py:289-296
     i32 *depth = A.get<i32>(N + 1), *ooff = A.get<i32>(N + 1);
     CHKA(A);

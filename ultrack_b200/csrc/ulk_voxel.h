@@ -17,11 +17,24 @@ ULK_D ULK_INLINE i32 ulk_vfind(const i32 *P, i32 x)
     while (p != x) { x = p; p = P[x]; }
     return x;
 }
+// find with path halving: every store replaces a parent by one of its ancestors (parents only
+// ever decrease), so plain stores are safe next to the atomicMin hooks of ulk_vunion
+ULK_D ULK_INLINE i32 ulk_vfind_halve(i32 *P, i32 x)
+{
+    for (;;) {
+        i32 p = P[x];
+        if (p == x) return x;
+        i32 g = P[p];
+        if (g == p) return p;
+        P[x] = g;
+        x = g;
+    }
+}
 ULK_D ULK_INLINE void ulk_vunion(i32 *P, i32 a, i32 b)
 {
     for (;;) {
-        a = ulk_vfind(P, a);
-        b = ulk_vfind(P, b);
+        a = ulk_vfind_halve(P, a);
+        b = ulk_vfind_halve(P, b);
         if (a == b) return;
         if (a < b) { i32 t = a; a = b; b = t; }
         i32 old = ulk_atomic_min(&P[a], b);   // hook the larger root under the smaller
@@ -91,11 +104,13 @@ struct K_Threshold {
 // joins the runs: an x edge only across a warp-segment boundary, a y / z edge only where the
 // edge one voxel to the left does not already join the same two runs
 struct K_CclUnion {
-    i32 *P; UlkDims dm;
+    i32 *P; UlkDims dm; i32 *cnt;
     ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
     {
         i32 v = (i32)vv;
-        if (P[v] < 0) return;
+        i32 p0 = P[v];
+        if (p0 < 0) return;
+        if (p0 == v) cnt[v] = 0;      // a final root is never hooked: its size counter starts at 0
         bool left = x > 0 && P[v - 1] >= 0;
         if (left && (x & 31) == 0) ulk_vunion(P, v, v - 1);
         for (int d = 1; d < 3; ++d) {
@@ -783,6 +798,10 @@ struct K_WriteLabels {
         if (cc_big[c - 1] >= 0) lab2[v] = label_of_rec[ncc + region_of[basA[v]]];
         else lab2[v] = label_of_rec[c - 1];
     }
+};
+struct K_CopyLabels {       // region labels as the caller sees them: 0 on the background
+    const i32 *lab; i32 *out;
+    ULK_D void operator()(i64 v) const { i32 l = lab[v]; out[v] = l > 0 ? l : 0; }
 };
 template <class T> struct K_FillAt {
     T *p; T val;
