@@ -65,6 +65,8 @@ class ClockSampler:
             self._stop.wait(0.05)
 
     def start(self):
+        if os.environ.get("ULK_BENCH_NO_CLOCKS"):      # diagnosis only: no sampling at all
+            return
         # in-process NVML (two light queries per sample); a spawned `nvidia-smi -lms` re-initialises
         # the driver query path every 100 ms and was seen to stall kernel launches for > 100 ms
         try:
@@ -284,11 +286,13 @@ def main():
 
     with torch.cuda.stream(stream):
         prev = seg(1)
+        # per-kernel events are on during the warm-up too, so the timed steps take exactly the
+        # same host path (event pool already created); the reset drops the warm-up's records
+        lib.ulk_profile_enable(1)
         for i in range(args.warmup):
             prev, *_ = step(i, prev)
         # ---- timed region: K steps, device-resident inputs, per-kernel events on
         lib.ulk_profile_reset()
-        lib.ulk_profile_enable(1)
         launches0 = lib.ulk_launch_count()
         clocks = ClockSampler(local_rank)
         clocks.start()

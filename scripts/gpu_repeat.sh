@@ -1,6 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-for i in 1 2 3 4; do
+for i in ${REPS:-1 2 3 4}; do
   timeout 600 python bench.py --workload c5 --no-cpu-baseline --no-e2e --steps ${1:-4} > gpurun_out/rep_$i.json 2> gpurun_out/rep_$i.err
   python - gpurun_out/rep_$i.json <<'PY'
 import json,sys

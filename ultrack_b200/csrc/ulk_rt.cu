@@ -136,7 +136,17 @@ void ulk_prof_end(ulk_stream_t s)
     cudaEventRecord(g_prof_recs.back().b, s);
     if (g_prof_recs.size() >= 4096) prof_drain();
 }
-void ulk_prof_enable(int on) { g_ulk_prof_on = on != 0; }
+void ulk_prof_enable(int on)
+{
+    g_ulk_prof_on = on != 0;
+    // the event pool is created here, not launch by launch inside a timed region
+    if (g_ulk_prof_on)
+        while (g_prof_free.size() < 2 * 4096 + 64) {
+            cudaEvent_t e;
+            if (cudaEventCreate(&e) != cudaSuccess) break;
+            g_prof_free.push_back(e);
+        }
+}
 void ulk_prof_reset() { prof_drain(); g_prof_acc.clear(); }
 int ulk_prof_report(char *buf, i64 cap)
 {
@@ -220,6 +230,16 @@ int ulk_ws_reserve(size_t bytes, ulk_stream_t s)
         want = want / 4 * 3 / WS_ALIGN * WS_ALIGN;
     }
     if (g_ws_cap) g_ws_freelist[0] = g_ws_cap;
+    // prime the stream-ordered pool the results come from (node tables, masks, links of the two
+    // or three frames alive at a time): one block allocated and handed back stays cached (the
+    // release threshold is unlimited), so steady-state calls never grow the pool
+    {
+        size_t prime = bytes / 64;
+        if (prime < (256ull << 20)) prime = 256ull << 20;
+        void *p = nullptr;
+        if (cudaMallocAsync(&p, prime, g_alloc_stream) == cudaSuccess) cudaFreeAsync(p, g_alloc_stream);
+        else cudaGetLastError();
+    }
     return 0;
 }
 int ulk_ws_alloc(void **p, size_t bytes)
@@ -277,8 +297,24 @@ int ulk_memset(void *p, int byte, size_t bytes, ulk_stream_t s)
     ULK_CUDA(cudaMemsetAsync(p, byte, bytes, s));
     return 0;
 }
+// small counter read-backs go through one pinned staging page (a pageable destination makes
+// the driver stage and pin on every call)
+static void *g_pinned_page = nullptr;
+static const size_t kPinnedPage = 4096;
 int ulk_d2h(void *dst, const void *src, size_t bytes, ulk_stream_t s)
 {
+    if (bytes <= kPinnedPage) {
+        if (!g_pinned_page && cudaHostAlloc(&g_pinned_page, kPinnedPage, cudaHostAllocDefault) != cudaSuccess) {
+            g_pinned_page = nullptr;
+            cudaGetLastError();
+        }
+        if (g_pinned_page) {
+            ULK_CUDA(cudaMemcpyAsync(g_pinned_page, src, bytes, cudaMemcpyDeviceToHost, s));
+            ULK_CUDA(cudaStreamSynchronize(s));
+            memcpy(dst, g_pinned_page, bytes);
+            return 0;
+        }
+    }
     ULK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s));
     ULK_CUDA(cudaStreamSynchronize(s));
     return 0;

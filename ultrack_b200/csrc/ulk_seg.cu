@@ -552,7 +552,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     u32 *roots = A.get<u32>(n_roots);
     i32 *keep = A.get<i32>(n_roots + 1), *keeppre = A.get<i32>(n_roots + 1);
     i32 *big = A.get<i32>(n_roots + 1), *bigpre = A.get<i32>(n_roots + 1);
-    i32 *rsize = A.get<i32>(n_roots), *cc_big = A.get<i32>(n_roots);
+    i32 *rsize = A.get<i32>(n_roots), *cc_big = A.get<i32>(n_roots), *big_cc = A.get<i32>(n_roots);
     CHKA(A);
     CHK(ulk_sort_keys_u32(roots0, roots, n_roots, st));
     A.release(roots0);
@@ -568,19 +568,19 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     CHK(ulk_read(&n_big, bigpre + n_roots, 1, st));
     if (n_cc == 0) { F->n_nodes = 0; F->stats = stats_local; return 0; }
     i32 *code = cnt;
-    ulk_launch(n_roots, st, K_RootCode{roots, keep, keeppre, big, bigpre, code, cc_big});
+    ulk_launch(n_roots, st, K_RootCode{roots, keep, keeppre, big, bigpre, code, cc_big, big_cc});
     A.release(roots); A.release(keep); A.release(keeppre); A.release(big); A.release(bigpre); A.release(rsize);
 
     // ---- region labels: components, oversegmented where area > max_area
     i32 R = n_cc;
     if (n_big == 0) {
-        ulk_launch_list(fgl, nfg, dm, st, K_LabelCc{P, code, cc_big, 0, lab2});
+        ulk_launch_list(fgl, nfg, dm, st, K_LabelCc{code, cc_big, 0, lab2});
     } else {
         UlkArena AA;
-        i32 *labA = AA.get<i32>(V);
-        CHKA(AA);
-        CHK(ulk_memset(labA, 0, (size_t)V * sizeof(i32), st));
-        ulk_launch_list(fgl, nfg, dm, st, K_LabelCc{P, code, cc_big, 1, labA});
+        // the labels of the oversegmentation pass live in place too: > 0 on the components above
+        // max_area, negative everywhere else
+        i32 *labA = lab2;
+        ulk_launch_list(fgl, nfg, dm, st, K_LabelCc{code, cc_big, 1, labA});
         // pass A only ever touches the voxels of the components above max_area: its kernels run
         // on that sub-list (raster order kept), not on the whole foreground
         i32 *fglA = AA.get<i32>(nfg);
@@ -608,7 +608,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         i32 *label_of_rec = AA.get<i32>(nrec);
         CHKA(AA);
         ulk_launch(n_cc, st, K_SmallCcRecords{cc_big, rec_cc, rec_w, rec_k});
-        ulk_launch(va.B, st, K_RegionRecords{region_of, rkey_w, rkey_k, va.g_root, P, code, n_cc, rec_cc, rec_w, rec_k});
+        ulk_launch(va.B, st, K_RegionRecords{region_of, rkey_w, rkey_k, va.g_lab, big_cc, n_cc, rec_cc, rec_w, rec_k});
         ulk_launch(nrec, st, K_Iota{perm0});
         CHK(ulk_sort_pairs_u64(rec_k, k1, perm0, perm1, nrec, st));           // by tie key
         ulk_launch(nrec, st, K_Gather<u64>{rec_w, perm1, k0});
@@ -616,7 +616,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         ulk_launch(nrec, st, K_Gather<u32>{rec_cc, perm0, c0});
         CHK(ulk_sort_pairs_u32(c0, c1, perm0, perm1, nrec, st));              // then by component
         ulk_launch(nrec, st, K_RankToLabel{perm1, c1, label_of_rec});
-        ulk_launch_list(fgl, nfg, dm, st, K_WriteLabels{P, code, cc_big, n_cc, va.bas, region_of, label_of_rec, lab2});
+        ulk_launch_list(fgl, nfg, dm, st, K_WriteLabels{n_cc, va.bas, region_of, label_of_rec, lab2});
         // number of valid records = regions
         i32 *nvalid = AA.get<i32>(nrec + 1), *nvpre = AA.get<i32>(nrec + 1);
         CHKA(AA);
@@ -626,7 +626,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         CHK(ulk_read(&R, nvpre + nrec, 1, st));
         CHK(ulk_sync(st));
     }
-    A.release(cc_big); A.release(cnt);
+    A.release(cc_big); A.release(big_cc); A.release(cnt);
     if (keep_labels) {
         F->labels = keep_alloc<i32>(V);
         if (!F->labels) return -3;

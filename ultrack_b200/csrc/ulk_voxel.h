@@ -166,9 +166,9 @@ struct K_RootFlags {
     }
 };
 // code[root] = 1-based index among the kept components (0: dropped); cc_big[index] = index
-// among the components above max_area or -1
+// among the components above max_area or -1; big_cc = the inverse of cc_big
 struct K_RootCode {
-    const u32 *roots; const i32 *keep, *keeppre, *big, *bigpre; i32 *code; i32 *cc_big;
+    const u32 *roots; const i32 *keep, *keeppre, *big, *bigpre; i32 *code; i32 *cc_big; i32 *big_cc;
     ULK_D void operator()(i64 i) const
     {
         u32 r = roots[i];
@@ -176,18 +176,22 @@ struct K_RootCode {
         i32 c = keeppre[i];
         code[r] = c + 1;
         cc_big[c] = big[i] ? bigpre[i] : -1;
+        if (big[i]) big_cc[bigpre[i]] = c;
     }
 };
-// mode 0: every kept component gets its index as label; mode 1: only the components above
-// max_area, numbered among themselves (input of the oversegmentation pass)
+// Component labels, written in place over the flattened component forest (the background keeps
+// its -1).  mode 0 (no component above max_area): the 1-based component index, 0 if dropped.
+// mode 1: components above max_area get their 1-based index among themselves (the region labels
+// of the oversegmentation pass), the other kept components -(index + 2), dropped ones -1.
 struct K_LabelCc {
-    const i32 *P; const i32 *code; const i32 *cc_big; int mode; i32 *lab;
+    const i32 *code; const i32 *cc_big; int mode; i32 *lab;
     ULK_D void operator()(i64 v, i32, i32, i32) const
     {
-        i32 r = P[v];
-        i32 c = r < 0 ? 0 : code[r];
-        if (mode == 0) lab[v] = c;
-        else lab[v] = (c > 0 && cc_big[c - 1] >= 0) ? cc_big[c - 1] + 1 : 0;
+        i32 c = code[lab[v]];
+        if (mode == 0) { lab[v] = c; return; }
+        if (c == 0) { lab[v] = -1; return; }
+        i32 g = cc_big[c - 1];
+        lab[v] = g >= 0 ? g + 1 : -(c - 1) - 2;
     }
 };
 struct K_FlagRoots {
@@ -480,8 +484,10 @@ struct K_BasinAccum {
             }
     }
 #else
-    // lanes of a warp that sit in the same basin (consecutive x: usually one or two groups)
-    // reduce among themselves; one lane per group issues the atomics
+    // lanes of a warp that sit in the same basin AND the same row form a group (usually one or
+    // two per warp): z and y are uniform in it and x grows with the lane, so the bounding box and
+    // the coordinate sums need no reduction; one lane per group issues the atomics, and only
+    // those that can still change the accumulator (a stale cached value only costs an atomic)
     ULK_D void warp(i64 vv, i32 z, i32 y, i32 x, bool valid) const
     {
         const int lane = threadIdx.x & 31;
@@ -493,29 +499,38 @@ struct K_BasinAccum {
         u32 nct = __reduce_add_sync(0xffffffffu, o.nc);
         if (lane == 0 && nct) atomicAdd((unsigned long long *)ncross, (unsigned long long)nct);
         if (want_join) ulk_warp_append(o.plateau, v, hp, nhp);
-        u32 grp = __match_any_sync(0xffffffffu, b);
+        u32 grp = __match_any_sync(0xffffffffu, b < 0 ? ULK_NONE64 : (((u64)(u32)b << 32) | (u32)(v - x)));
         if (b < 0) return;
-        const bool lead = lane == __ffs(grp) - 1;
+        const int first = __ffs(grp) - 1;
+        const bool lead = lane == first;
+        const i32 n = __popc(grp);
         u32 thi = __reduce_max_sync(grp, (u32)(o.top >> 32));
         u32 tlo = __reduce_max_sync(grp, (u32)(o.top >> 32) == thi ? (u32)o.top : 0u);
         if (lead) {
-            atomicAdd(&b_size[b], __popc(grp));
+            atomicAdd(&b_size[b], n);
             u64 t = ((u64)thi << 32) | tlo;
-            if (t) atomicMax((unsigned long long *)&b_top[b], (unsigned long long)t);
+            if (t > b_top[b]) atomicMax((unsigned long long *)&b_top[b], (unsigned long long)t);
         }
         if (want_k0) {
             u32 km = __reduce_max_sync(grp, o.kmin == ULK_NONE32 ? 0u : o.kmin);
             if (lead && km > K0[b]) atomicMax(&K0[b], km);
         }
         if (want_stats) {
-            for (int d = 0; d < 3; ++d) {
-                i32 lo = __reduce_min_sync(grp, o.c[d]), hi = __reduce_max_sync(grp, o.c[d]);
-                u32 sm = __reduce_add_sync(grp, (u32)o.c[d]);
-                if (lead) {
-                    atomicMin(&bbmin[3 * b + d], lo);
-                    atomicMax(&bbmax[3 * b + d], hi);
-                    atomicAdd((unsigned long long *)&csum[3 * b + d], (unsigned long long)sm);
-                }
+            const i32 x1 = __shfl_sync(grp, x, 31 - __clz(grp));       // x of the group's last lane
+            u32 sx = (x1 - x + 1 == n) ? (u32)(((i64)(x + x1) * n) >> 1) : 0u;   // meaningful in the first lane
+            if (__shfl_sync(grp, x1 - x + 1 != n ? 1 : 0, first)) sx = __reduce_add_sync(grp, (u32)x);
+            if (lead) {
+                i32 *lo = bbmin + 3 * b, *hi = bbmax + 3 * b;
+                i64 *cs = csum + 3 * b;
+                if (z < lo[0]) atomicMin(&lo[0], z);
+                if (z > hi[0]) atomicMax(&hi[0], z);
+                if (y < lo[1]) atomicMin(&lo[1], y);
+                if (y > hi[1]) atomicMax(&hi[1], y);
+                if (x < lo[2]) atomicMin(&lo[2], x);
+                if (x1 > hi[2]) atomicMax(&hi[2], x1);
+                atomicAdd((unsigned long long *)&cs[0], (unsigned long long)((i64)z * n));
+                atomicAdd((unsigned long long *)&cs[1], (unsigned long long)((i64)y * n));
+                atomicAdd((unsigned long long *)&cs[2], (unsigned long long)sx);
             }
         }
     }
@@ -573,10 +588,15 @@ struct K_Attach {
         i32 o = 2 * s;
         i32 node = b - s;
         i32 start = node;
-        for (;;) {
-            i32 p = Ipar[o + node];
-            if (p == node || !(Iwk[o + p] < J)) break;
+        // the parent's merge key and the grandparent index are loaded together: one memory
+        // round trip per level of the climb
+        i32 p = Ipar[o + node];
+        while (p != node) {
+            u64 w = Iwk[o + p];
+            i32 pp = Ipar[o + p];
+            if (!(w < J)) break;
             node = p;
+            p = pp;
         }
         if (node != start) {
             ulk_atomic_add(&attach[o + start], -1);
@@ -769,13 +789,13 @@ struct K_SmallCcRecords {   // one region record per component that is not overs
     }
 };
 struct K_RegionRecords {    // one record per cut region of an oversegmented component
-    const i32 *region_of; const u64 *rkey_w, *rkey_k; const i32 *g_root; const i32 *P; const i32 *code; i32 ncc;
+    const i32 *region_of; const u64 *rkey_w, *rkey_k; const i32 *g_lab; const i32 *big_cc; i32 ncc;
     u32 *rec_cc; u64 *rec_w; u64 *rec_k;
     ULK_D void operator()(i64 g) const
     {
         i32 i = ncc + (i32)g;
         if (region_of[g] != (i32)g) { rec_cc[i] = ULK_NONE32; rec_w[i] = 0; rec_k[i] = 0; return; }
-        rec_cc[i] = (u32)(code[P[g_root[g]]] - 1);
+        rec_cc[i] = (u32)big_cc[g_lab[g] - 1];
         rec_w[i] = rkey_w[g]; rec_k[i] = rkey_k[g];
     }
 };
@@ -786,17 +806,16 @@ struct K_RankToLabel {
         label_of_rec[perm[i]] = rec_cc_sorted[i] == ULK_NONE32 ? 0 : (i32)i + 1;
     }
 };
+// final region labels over the mode-1 component labels, in place
 struct K_WriteLabels {
-    const i32 *P; const i32 *code; const i32 *cc_big; i32 ncc;
-    const i32 *basA; const i32 *region_of; const i32 *label_of_rec;
-    i32 *lab2;
+    i32 ncc; const i32 *basA; const i32 *region_of; const i32 *label_of_rec;
+    i32 *lab;
     ULK_D void operator()(i64 v, i32, i32, i32) const
     {
-        i32 r = P[v];
-        i32 c = r < 0 ? 0 : code[r];
-        if (c == 0) { lab2[v] = 0; return; }
-        if (cc_big[c - 1] >= 0) lab2[v] = label_of_rec[ncc + region_of[basA[v]]];
-        else lab2[v] = label_of_rec[c - 1];
+        i32 l = lab[v];
+        if (l > 0) lab[v] = label_of_rec[ncc + region_of[basA[v]]];
+        else if (l <= -2) lab[v] = label_of_rec[-l - 2];
+        else lab[v] = 0;
     }
 };
 struct K_CopyLabels {       // region labels as the caller sees them: 0 on the background
