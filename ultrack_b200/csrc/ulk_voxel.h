@@ -107,19 +107,19 @@ struct K_CclUnion {
     i32 *P; UlkDims dm; i32 *cnt;
     ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
     {
-        i32 v = (i32)vv;
-        i32 p0 = P[v];
+        const i32 v = (i32)vv;
+        // every neighbour is loaded up front (clamped to v at the frame border) so the loads
+        // overlap; only the sign is used, and the sign of an entry never changes
+        const bool hx = x > 0, hy = y > 0, hz = z > 0;
+        const i32 uy = hy ? v - dm.W : v, uz = hz ? v - dm.W * dm.H : v;
+        const i32 p0 = P[v];
+        const i32 pl = P[hx ? v - 1 : v], py = P[uy], pyl = P[hx ? uy - 1 : uy], pz = P[uz], pzl = P[hx ? uz - 1 : uz];
         if (p0 < 0) return;
         if (p0 == v) cnt[v] = 0;      // a final root is never hooked: its size counter starts at 0
-        bool left = x > 0 && P[v - 1] >= 0;
+        const bool left = hx && pl >= 0;
         if (left && (x & 31) == 0) ulk_vunion(P, v, v - 1);
-        for (int d = 1; d < 3; ++d) {
-            if (!dm.bwd(d, z, y, x)) continue;
-            i32 u = v - dm.stride(d);
-            if (P[u] < 0) continue;
-            if (left && P[u - 1] >= 0) continue;
-            ulk_vunion(P, v, u);
-        }
+        if (hy && py >= 0 && !(left && pyl >= 0)) ulk_vunion(P, v, uy);
+        if (hz && pz >= 0 && !(left && pzl >= 0)) ulk_vunion(P, v, uz);
     }
 };
 struct K_Flatten {
@@ -211,19 +211,34 @@ struct K_MinEdge {
     ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
     {
         const i32 v = (i32)vv;
-        const i32 l = lab[v];
-        if (l <= 0) return;          // mw / pk are only ever read where lab > 0
         const i32 sy = dm.W, sz = dm.W * dm.H;
-        const i32 u0 = v - sz, u1 = v - sy, u2 = v - 1, u3 = v + 1, u4 = v + sy, u5 = v + sz;
-        const bool s0 = z > 0 && lab[u0] == l, s1 = y > 0 && lab[u1] == l, s2 = x > 0 && lab[u2] == l;
-        const bool s3 = x + 1 < dm.W && lab[u3] == l, s4 = y + 1 < dm.H && lab[u4] == l, s5 = z + 1 < dm.D && lab[u5] == l;
+        // neighbour indices clamped to v at the frame border: all loads are issued together
+        const bool h0 = z > 0, h1 = y > 0, h2 = x > 0, h3 = x + 1 < dm.W, h4 = y + 1 < dm.H, h5 = z + 1 < dm.D;
+        const i32 u0 = h0 ? v - sz : v, u1 = h1 ? v - sy : v, u2 = h2 ? v - 1 : v;
+        const i32 u3 = h3 ? v + 1 : v, u4 = h4 ? v + sy : v, u5 = h5 ? v + sz : v;
+        const i32 l = lab[v];
+        const i32 l0 = lab[u0], l1 = lab[u1], l2 = lab[u2], l3 = lab[u3], l4 = lab[u4], l5 = lab[u5];
+        if (l <= 0) return;          // mw / pk are only ever read where lab > 0
+        const bool s0 = h0 && l0 == l, s1 = h1 && l1 == l, s2 = h2 && l2 == l;
+        const bool s3 = h3 && l3 == l, s4 = h4 && l4 == l, s5 = h5 && l5 == l;
         u32 bw = ULK_NONE32, bk = ULK_NONE32, w;
-        if (s0) { w = ulk_f2ord(ct.w(u0, v)); if (w < bw) { bw = w; bk = 3u * (u32)u0 + 2u; } }
-        if (s1) { w = ulk_f2ord(ct.w(u1, v)); if (w < bw) { bw = w; bk = 3u * (u32)u1 + 1u; } }
-        if (s2) { w = ulk_f2ord(ct.w(u2, v)); if (w < bw) { bw = w; bk = 3u * (u32)u2; } }
-        if (s3) { w = ulk_f2ord(ct.w(v, u3)); if (w < bw) { bw = w; bk = 3u * (u32)v; } }
-        if (s4) { w = ulk_f2ord(ct.w(v, u4)); if (w < bw) { bw = w; bk = 3u * (u32)v + 1u; } }
-        if (s5) { w = ulk_f2ord(ct.w(v, u5)); if (w < bw) { bw = w; bk = 3u * (u32)v + 2u; } }
+        if (ct.f) {
+            const float c = ct.f[v];
+            const float c0 = ct.f[u0], c1 = ct.f[u1], c2 = ct.f[u2], c3 = ct.f[u3], c4 = ct.f[u4], c5 = ct.f[u5];
+            if (s0) { w = ulk_f2ord(ulk_wsum(c0 + c)); if (w < bw) { bw = w; bk = 3u * (u32)u0 + 2u; } }
+            if (s1) { w = ulk_f2ord(ulk_wsum(c1 + c)); if (w < bw) { bw = w; bk = 3u * (u32)u1 + 1u; } }
+            if (s2) { w = ulk_f2ord(ulk_wsum(c2 + c)); if (w < bw) { bw = w; bk = 3u * (u32)u2; } }
+            if (s3) { w = ulk_f2ord(ulk_wsum(c + c3)); if (w < bw) { bw = w; bk = 3u * (u32)v; } }
+            if (s4) { w = ulk_f2ord(ulk_wsum(c + c4)); if (w < bw) { bw = w; bk = 3u * (u32)v + 1u; } }
+            if (s5) { w = ulk_f2ord(ulk_wsum(c + c5)); if (w < bw) { bw = w; bk = 3u * (u32)v + 2u; } }
+        } else {
+            if (s0) { w = ulk_f2ord(ct.w(u0, v)); if (w < bw) { bw = w; bk = 3u * (u32)u0 + 2u; } }
+            if (s1) { w = ulk_f2ord(ct.w(u1, v)); if (w < bw) { bw = w; bk = 3u * (u32)u1 + 1u; } }
+            if (s2) { w = ulk_f2ord(ct.w(u2, v)); if (w < bw) { bw = w; bk = 3u * (u32)u2; } }
+            if (s3) { w = ulk_f2ord(ct.w(v, u3)); if (w < bw) { bw = w; bk = 3u * (u32)v; } }
+            if (s4) { w = ulk_f2ord(ct.w(v, u4)); if (w < bw) { bw = w; bk = 3u * (u32)v + 1u; } }
+            if (s5) { w = ulk_f2ord(ct.w(v, u5)); if (w < bw) { bw = w; bk = 3u * (u32)v + 2u; } }
+        }
         mw[v] = bw;
         pk[v] = bk;
     }
@@ -438,24 +453,24 @@ struct K_BasinAccum {
     struct Own { u64 top; u32 nc; u32 kmin; i32 c[3]; bool plateau; };
     ULK_D ULK_INLINE void own(i32 v, i32 z, i32 y, i32 x, i32 b, Own &o) const
     {
+        // neighbour basins first, all loads in flight together (indices clamped at the border)
+        const i32 sy = dm.W, sz = dm.W * dm.H;
+        const bool f0 = x + 1 < dm.W, f1 = y + 1 < dm.H, f2 = z + 1 < dm.D;
+        const i32 a0 = bas[f0 ? v + 1 : v], a1 = bas[f1 ? v + sy : v], a2 = bas[f2 ? v + sz : v];
+        i32 c0 = -1, c1 = -1, c2 = -1;
+        if (want_k0) { c0 = bas[x > 0 ? v - 1 : v]; c1 = bas[y > 0 ? v - sy : v]; c2 = bas[z > 0 ? v - sz : v]; }
         const u32 m = mw[v], k = pk[v];
+        const i32 l = lab[v];
         o.top = k != ULK_NONE32 ? ((u64)m << 32) | k : 0;
         o.c[0] = z; o.c[1] = y; o.c[2] = x;
-        const i32 l = lab[v];
         o.nc = 0;
         o.kmin = ULK_NONE32;
-        for (int d = 0; d < 3; ++d) {
-            const i32 st = dm.stride(d);
-            if (dm.fwd(d, o.c[0], o.c[1], o.c[2])) {
-                i32 bu = bas[v + st];
-                if (bu == b) { u32 kk = 3u * (u32)v + d; if (kk < o.kmin) o.kmin = kk; }
-                else if (lab[v + st] == l) ++o.nc;
-            }
-            if (want_k0 && dm.bwd(d, o.c[0], o.c[1], o.c[2]) && bas[v - st] == b) {
-                u32 kk = 3u * (u32)(v - st) + d;
-                if (kk < o.kmin) o.kmin = kk;
-            }
-        }
+        if (f0) { if (a0 == b) { u32 kk = 3u * (u32)v; if (kk < o.kmin) o.kmin = kk; } else if (lab[v + 1] == l) ++o.nc; }
+        if (want_k0 && x > 0 && c0 == b) { u32 kk = 3u * (u32)(v - 1); if (kk < o.kmin) o.kmin = kk; }
+        if (f1) { if (a1 == b) { u32 kk = 3u * (u32)v + 1u; if (kk < o.kmin) o.kmin = kk; } else if (lab[v + sy] == l) ++o.nc; }
+        if (want_k0 && y > 0 && c1 == b) { u32 kk = 3u * (u32)(v - sy) + 1u; if (kk < o.kmin) o.kmin = kk; }
+        if (f2) { if (a2 == b) { u32 kk = 3u * (u32)v + 2u; if (kk < o.kmin) o.kmin = kk; } else if (lab[v + sz] == l) ++o.nc; }
+        if (want_k0 && z > 0 && c2 == b) { u32 kk = 3u * (u32)(v - sz) + 2u; if (kk < o.kmin) o.kmin = kk; }
         o.plateau = false;
         if (want_join) {
             if (m == b_L[b] || k == ULK_NONE32) jk[v] = ULK_JK_CORE;
@@ -619,18 +634,18 @@ struct K_RagInsert {
     const i32 *bas; const i32 *lab; UlkCt ct; UlkDims dm; UlkRagTable T; double fixscale;
     ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
     {
-        i32 v = (i32)vv;
-        i32 b = bas[v];
+        const i32 v = (i32)vv;
+        const bool f[3] = {x + 1 < dm.W, y + 1 < dm.H, z + 1 < dm.D};
+        const i32 u[3] = {f[0] ? v + 1 : v, f[1] ? v + dm.W : v, f[2] ? v + dm.W * dm.H : v};
+        const i32 b = bas[v], l = lab[v];
+        const i32 cb[3] = {bas[u[0]], bas[u[1]], bas[u[2]]};
+        const i32 cl[3] = {lab[u[0]], lab[u[1]], lab[u[2]]};
         if (b < 0) return;
-        i32 l = lab[v];
         for (int d = 0; d < 3; ++d) {
-            if (!dm.fwd(d, z, y, x)) continue;
-            i32 u = v + dm.stride(d);
-            if (lab[u] != l) continue;
-            i32 c = bas[u];
-            if (c == b) continue;
+            if (!f[d] || cl[d] != l || cb[d] == b) continue;
+            const i32 c = cb[d];
             u64 key = b < c ? ((u64)(u32)b << 32) | (u32)c : ((u64)(u32)c << 32) | (u32)b;
-            float w = ct.w(v, u);
+            float w = ct.w(v, u[d]);
             u32 ek = 3u * (u32)v + d;
             u64 h = ulk_hash64(key) & T.mask;
             for (;;) {
@@ -711,19 +726,17 @@ struct K_K3Union {
     // `boundary`: the x edge to v-1 was not joined at initialisation
     ULK_D ULK_INLINE void join(i32 v, i32 z, i32 y, i32 x, bool boundary) const
     {
-        i32 b = bas[v];
+        const bool hx = x > 0, hy = y > 0, hz = z > 0;
+        const i32 uy = hy ? v - dm.W : v, uz = hz ? v - dm.W * dm.H : v;
+        const i32 b = bas[v];
+        const i32 bl = bas[hx ? v - 1 : v], by = bas[uy], byl = bas[hx ? uy - 1 : uy], bz = bas[uz], bzl = bas[hx ? uz - 1 : uz];
         if (b < 0) return;
-        u32 kmax = K0[b];
-        bool left = x > 0 && bas[v - 1] == b && 3u * (u32)(v - 1) <= kmax;
+        const u32 kmax = K0[b];
+        const bool left = hx && bl == b && 3u * (u32)(v - 1) <= kmax;
         if (left && boundary) ulk_vunion(P, v, v - 1);
-        for (int d = 1; d < 3; ++d) {
-            if (!dm.bwd(d, z, y, x)) continue;
-            i32 u = v - dm.stride(d);
-            if (bas[u] != b || 3u * (u32)u + d > kmax) continue;
-            // (u-1,u), (u-1,v-1) carry smaller keys than (u,v): with (v-1,v) they already join u and v
-            if (left && bas[u - 1] == b) continue;
-            ulk_vunion(P, v, u);
-        }
+        // (u-1,u), (u-1,v-1) carry smaller keys than (u,v): with (v-1,v) they already join u and v
+        if (hy && by == b && 3u * (u32)uy + 1u <= kmax && !(left && byl == b)) ulk_vunion(P, v, uy);
+        if (hz && bz == b && 3u * (u32)uz + 2u <= kmax && !(left && bzl == b)) ulk_vunion(P, v, uz);
     }
 #ifdef ULK_EMU
     void operator()(i64 v, i32 z, i32 y, i32 x) const { join((i32)v, z, y, x, (x & 31) == 0); }
