@@ -106,6 +106,16 @@ template <class F, class DM> void ulk_launch_list(const i32 *list, i64 n, const 
     for (i64 i = 0; i < n; ++i) { i32 z, y, x; dm.coords(list[i], z, y, x); f((i64)list[i], z, y, x); }
 }
 template <class F, class DM> void ulk_launch_list_warp(const i32 *list, i64 n, const DM &dm, ulk_stream_t s, const F &f) { ulk_launch_list(list, n, dm, s, f); }
+// phased list kernels: S1 load1(v,z,y,x,ok) -> S2 load2(S1,ok) -> run(S2,ok)
+template <int U, class F, class DM> void ulk_launch_list_ph(const i32 *list, i64 n, const DM &dm, ulk_stream_t, const F &f)
+{
+    for (i64 i = 0; i < n; ++i) { i32 z, y, x; dm.coords(list[i], z, y, x); f.run(f.load2(f.load1(list[i], z, y, x, true), true), true); }
+}
+// pointer-chasing list kernels (no coordinates): the emulation runs the scalar statement
+template <class F> void ulk_launch_list_multi(const i32 *list, i64 n, ulk_stream_t, const F &f)
+{
+    for (i64 i = 0; i < n; ++i) f((i64)list[i], 0, 0, 0);
+}
 #else
 template <class F> __global__ void __launch_bounds__(256) ulk_kernel(i64 n, F f)
 {
@@ -206,6 +216,63 @@ template <class F, class DM> void ulk_launch_list_warp(const i32 *list, i64 n, c
     if (n <= 0) return;
     if (g_ulk_prof_on) ulk_prof_begin(typeid(F).name(), s);
     ulk_kernel_list_warp<F, DM><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(list, n, dm, f);
+    if (g_ulk_prof_on) ulk_prof_end(s);
+    ++g_ulk_launches;
+}
+// pointer-chasing list kernels: a thread takes ULK_MULTI entries (256 apart, so every load of
+// the list stays coalesced) and calls F::multi(v[], valid[]) from every thread of the block; the
+// body walks its ULK_MULTI chains in lockstep so that many loads are in flight per thread
+#define ULK_MULTI 4
+template <class F> __global__ void __launch_bounds__(256) ulk_kernel_list_multi(const i32 *list, i64 n, F f)
+{
+    const i64 base = (i64)blockIdx.x * (256 * ULK_MULTI) + threadIdx.x;
+    i32 v[ULK_MULTI];
+    bool ok[ULK_MULTI];
+#pragma unroll
+    for (int u = 0; u < ULK_MULTI; ++u) {
+        const i64 i = base + u * 256;
+        ok[u] = i < n;
+        v[u] = ok[u] ? list[i] : -1;
+    }
+    f.multi(v, ok);
+}
+// phased list kernels: a thread takes U entries (256 apart: lane l of a warp still holds list
+// entry 32*k + l, so warp collectives see neighbours of the raster-ordered list) and runs the
+// functor's phases entry-interleaved -- S1 load1(v,z,y,x,ok), S2 load2(S1,ok), run(S2,ok) -- so
+// that the U independent loads of every dependency level are in flight together.  Every thread
+// calls every phase (ok = false past the end of the list): phases may use full-mask collectives.
+template <int U, class F, class DM> __global__ void __launch_bounds__(256) ulk_kernel_list_ph(const i32 *list, i64 n, DM dm, F f)
+{
+    const i64 base = (i64)blockIdx.x * (256 * U) + threadIdx.x;
+    typename F::S1 a[U];
+    typename F::S2 b[U];
+    bool ok[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        const i64 i = base + u * 256;
+        ok[u] = i < n;
+        i32 v = 0, z = 0, y = 0, x = 0;
+        if (ok[u]) { v = list[i]; dm.coords(v, z, y, x); }
+        a[u] = f.load1(v, z, y, x, ok[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) b[u] = f.load2(a[u], ok[u]);
+#pragma unroll
+    for (int u = 0; u < U; ++u) f.run(b[u], ok[u]);
+}
+template <int U, class F, class DM> void ulk_launch_list_ph(const i32 *list, i64 n, const DM &dm, ulk_stream_t s, const F &f)
+{
+    if (n <= 0) return;
+    if (g_ulk_prof_on) ulk_prof_begin(typeid(F).name(), s);
+    ulk_kernel_list_ph<U, F, DM><<<(unsigned)((n + 256 * U - 1) / (256 * U)), 256, 0, s>>>(list, n, dm, f);
+    if (g_ulk_prof_on) ulk_prof_end(s);
+    ++g_ulk_launches;
+}
+template <class F> void ulk_launch_list_multi(const i32 *list, i64 n, ulk_stream_t s, const F &f)
+{
+    if (n <= 0) return;
+    if (g_ulk_prof_on) ulk_prof_begin(typeid(F).name(), s);
+    ulk_kernel_list_multi<F><<<(unsigned)((n + 256 * ULK_MULTI - 1) / (256 * ULK_MULTI)), 256, 0, s>>>(list, n, f);
     if (g_ulk_prof_on) ulk_prof_end(s);
     ++g_ulk_launches;
 }

@@ -87,42 +87,65 @@ struct K_BasinNodeGlobal {
         bnode[b] = s < 0 ? -1 : noff[g_lab[b] - 1] + s;
     }
 };
-struct K_MaskPaint {
-    const i32 *bas; const i32 *bnode; const i32 *parent; const i32 *bbox; const i64 *moff; UlkDims dm;
-    u32 *mask;
-    ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
+// one 32-byte record per node for the painter: bbox origin, row geometry, mask offset, parent
+struct UlkPaintInfo { i32 z0, y0, x0, bh; i32 wpr, parent; i64 moff; };
+struct K_PaintInfo {
+    const i32 *parent; const i32 *bbox; const i64 *moff; UlkPaintInfo *info;
+    ULK_D void operator()(i64 n) const
     {
-        i32 v = (i32)vv;
-        i32 b = bas[v];
-        if (b < 0) return;
-        for (i32 n = bnode[b]; n >= 0; n = parent[n]) {
-            const i32 *bb = bbox + 6 * n;
-            i64 bh = bb[4] - bb[1], wpr = (bb[5] - bb[2] + 31) / 32;
-            i32 rx = x - bb[2];
-            i64 word = moff[n] + ((i64)(z - bb[0]) * bh + (y - bb[1])) * wpr + (rx >> 5);
-            ulk_atomic_or(&mask[word], 1u << (rx & 31));
-        }
+        const i32 *bb = bbox + 6 * n;
+        UlkPaintInfo r;
+        r.z0 = bb[0]; r.y0 = bb[1]; r.x0 = bb[2]; r.bh = bb[4] - bb[1];
+        r.wpr = (bb[5] - bb[2] + 31) / 32; r.parent = parent[n]; r.moff = moff[n];
+        info[n] = r;
     }
-#ifndef ULK_EMU
+};
+struct K_MaskPaint {
+    const i32 *bas; const i32 *bnode; const UlkPaintInfo *info; UlkDims dm;
+    u32 *mask;
+    ULK_D ULK_INLINE UlkPaintInfo load(i32 n) const
+    {
+#ifdef ULK_EMU
+        return info[n];
+#else
+        const int4 a = ((const int4 *)info)[2 * n], c = ((const int4 *)info)[2 * n + 1];
+        UlkPaintInfo r;
+        r.z0 = a.x; r.y0 = a.y; r.x0 = a.z; r.bh = a.w; r.wpr = c.x; r.parent = c.y;
+        r.moff = (i64)(((u64)(u32)c.w << 32) | (u32)c.z);
+        return r;
+#endif
+    }
+    struct S1 { i32 z, y, x, b; };
+    struct S2 { i32 z, y, x, b, n; };
+    ULK_D ULK_INLINE S1 load1(i32 v, i32 z, i32 y, i32 x, bool ok) const { S1 s; s.z = z; s.y = y; s.x = x; s.b = ok ? bas[v] : -1; return s; }
+    ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const { S2 s; s.z = a.z; s.y = a.y; s.x = a.x; s.b = a.b; s.n = a.b >= 0 ? bnode[a.b] : -1; return s; }
     // lanes of one basin climb the same ancestor chain in lockstep; those that fall into the
     // same mask word (consecutive x of one row) merge their bits and issue one atomic
-    ULK_D void warp(i64 vv, i32 z, i32 y, i32 x, bool valid) const
+    ULK_D ULK_INLINE void run(const S2 &s, bool) const
     {
+#ifdef ULK_EMU
+        for (i32 n = s.n; n >= 0;) {
+            const UlkPaintInfo r = load(n);
+            i32 rx = s.x - r.x0;
+            i64 word = r.moff + ((i64)(s.z - r.z0) * r.bh + (s.y - r.y0)) * r.wpr + (rx >> 5);
+            ulk_atomic_or(&mask[word], 1u << (rx & 31));
+            n = r.parent;
+        }
+#else
         const int lane = threadIdx.x & 31;
-        i32 b = valid ? bas[(i32)vv] : -1;
-        u32 grp = __match_any_sync(0xffffffffu, b);
-        if (b < 0) return;
-        for (i32 n = bnode[b]; n >= 0; n = parent[n]) {
-            const i32 *bb = bbox + 6 * n;
-            i64 bh = bb[4] - bb[1], wpr = (bb[5] - bb[2] + 31) / 32;
-            i32 rx = x - bb[2];
-            i64 word = moff[n] + ((i64)(z - bb[0]) * bh + (y - bb[1])) * wpr + (rx >> 5);
+        u32 grp = __match_any_sync(0xffffffffu, s.b);
+        if (s.b < 0) return;
+        for (i32 n = s.n; n >= 0;) {
+            const UlkPaintInfo r = load(n);
+            i32 rx = s.x - r.x0;
+            i64 word = r.moff + ((i64)(s.z - r.z0) * r.bh + (s.y - r.y0)) * r.wpr + (rx >> 5);
             u32 sub = __match_any_sync(grp, (unsigned long long)word);
             u32 bits = __reduce_or_sync(sub, 1u << (rx & 31));
             if (lane == __ffs(sub) - 1) atomicOr(&mask[word], bits);
+            n = r.parent;
         }
-    }
 #endif
+    }
 };
 struct K_AncestorCount {
     const i32 *parent; i32 *depth;
@@ -278,9 +301,9 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     CHKA(A);
     CHK(ulk_memset(fmark, 0, (size_t)V + 8, st));
     CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
-    ulk_launch_list(fgl, nfg, dm, st, K_MinEdge{lab, ct, dm, mw, pk});
-    ulk_launch_list(fgl, nfg, dm, st, K_Hook1{lab, mw, pk, dm, bp, state, Lr, best, ctr + 4});
-    ulk_launch_list_warp(fgl, nfg, dm, st, K_CompressCand{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1});
+    ulk_launch_list_ph<2>(fgl, nfg, dm, st, K_MinEdge{lab, ct, dm, mw, pk});
+    ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_Hook1{lab, mw, pk, dm, bp, state, Lr, best, ctr + 4});
+    ulk_launch_list_multi(fgl, nfg, st, K_CompressCand{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1});
     i32 hc[8];
     CHK(ulk_read(hc, ctr, 8, st));
     i32 ncand = hc[0], ng = hc[1];
@@ -317,13 +340,13 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     CHKA(A);
     CHK(ulk_memset(ctr, 0, sizeof(i32), st));
     CHK(ulk_memset(lab_hist, 0, (size_t)(R + 1) * sizeof(i32), st));
-    ulk_launch_list(fgl, nfg, dm, st, K_CompressRoots{bp, lab, rootkeys, ctr + 0});
+    ulk_launch_list_multi(fgl, nfg, st, K_CompressRoots{bp, lab, rootkeys, ctr + 0});
     CHK(ulk_sort_keys_u64(rootkeys, rootsorted, B, st));
     u32 *gid_at_root = best;         // free after the flow rounds
     ulk_launch(B, st, K_BasinRegroup{rootsorted, Lr, gid_at_root, out.g_root, out.g_lab, out.g_L, lab_hist});
     CHK(ulk_exclusive_scan_i32(lab_hist, out.bs, R + 1, st));
     CHK(ulk_memset(out.bas, 0xff, (size_t)V * sizeof(i32), st));
-    ulk_launch_list(fgl, nfg, dm, st, K_AssignBasin{bp, gid_at_root, out.bas});
+    ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_AssignBasin{bp, gid_at_root, out.bas});
     A.release(rootkeys); A.release(rootsorted);
 
     // ---- per-basin accumulators, join keys (area attribute), bottleneck lower bound: one pass
@@ -345,7 +368,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
         ulk_fill<i32>(out.bbmax, -0x7fffffff, 3 * (i64)B, st);
         CHK(ulk_memset(out.csum, 0, (size_t)B * 3 * sizeof(i64), st));
     }
-    ulk_launch_list_warp(fgl, nfg, dm, st, K_BasinAccum{out.bas, lab, mw, pk, dm, out.b_size, out.b_top, ncross,
+    ulk_launch_list_ph<2>(fgl, nfg, dm, st, K_BasinAccum{out.bas, lab, mw, pk, dm, out.b_size, out.b_top, ncross,
                                         need_stats ? 1 : 0, out.bbmin, out.bbmax, out.csum,
                                         need_join ? 1 : 0, out.g_L, out.jk, hp, ctr + 0,
                                         need_k3 ? 1 : 0, out.b_k3});
@@ -383,7 +406,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     CHK(ulk_memset(T.cnt, 0, cap * 4, st));
     CHK(ulk_memset(T.shi, 0, cap * 8, st));
     CHK(ulk_memset(T.slo, 0, cap * 8, st));
-    ulk_launch_list(fgl, nfg, dm, st, K_RagInsert{out.bas, lab, ct, dm, T, fixscale});
+    ulk_launch_list_ph<2>(fgl, nfg, dm, st, K_RagInsert{out.bas, lab, ct, dm, T, fixscale});
     i32 *eflag = A.get<i32>((i64)cap + 1), *epre = A.get<i32>((i64)cap + 1);
     CHKA(A);
     ulk_launch((i64)cap, st, K_RagFlag{T.key, eflag});
@@ -430,12 +453,12 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
         i32 *P3 = bp;          // basin forest no longer needed
         i32 *nroot = A.get<i32>(B);
         CHKA(A);
-        ulk_launch_list_warp(fgl, nfg, dm, st, K_K3Init{out.bas, out.b_k3, P3});
-        ulk_launch_list_warp(fgl, nfg, dm, st, K_K3Union{out.bas, dm, out.b_k3, P3});
+        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_K3Init{out.bas, out.b_k3, P3});
+        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_K3Union{out.bas, dm, out.b_k3, P3});
         for (int it = 0;; ++it) {
             CHK(ulk_memset(nroot, 0, (size_t)B * sizeof(i32), st));
             CHK(ulk_memset(ctr, 0, sizeof(i32), st));
-            ulk_launch_list(fgl, nfg, dm, st, K_K3FlattenCount{out.bas, P3, nroot, ctr + 0});
+            ulk_launch_list_multi(fgl, nfg, st, K_K3FlattenCount{out.bas, P3, nroot, ctr + 0});
             CHK(ulk_read(hc, ctr, 1, st));
             if (hc[0] == 0) break;
             if (stats) stats->k3_rounds += 1;
@@ -530,9 +553,9 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     i32 *ctr = A.get<i32>(4);
     u32 *roots0 = A.get<u32>(nfg);
     CHKA(A);
-    ulk_launch_list(fgl, nfg, dm, st, K_CclUnion{P, dm, cnt});
+    ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_CclUnion{P, dm, cnt});
     CHK(ulk_memset(ctr, 0, 4 * sizeof(i32), st));
-    ulk_launch_list_warp(fgl, nfg, dm, st, K_FlattenCount{P, cnt, (i32 *)roots0, ctr});
+    ulk_launch_list_multi(fgl, nfg, st, K_FlattenCount{P, cnt, (i32 *)roots0, ctr});
     i32 hc[4];
     u32 h_cmax = 0;
     CHK(ulk_read(hc, ctr, 4, st));
@@ -574,13 +597,13 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     // ---- region labels: components, oversegmented where area > max_area
     i32 R = n_cc;
     if (n_big == 0) {
-        ulk_launch_list(fgl, nfg, dm, st, K_LabelCc{code, cc_big, 0, lab2});
+        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_LabelCc{code, cc_big, 0, lab2});
     } else {
         UlkArena AA;
         // the labels of the oversegmentation pass live in place too: > 0 on the components above
         // max_area, negative everywhere else
         i32 *labA = lab2;
-        ulk_launch_list(fgl, nfg, dm, st, K_LabelCc{code, cc_big, 1, labA});
+        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_LabelCc{code, cc_big, 1, labA});
         // pass A only ever touches the voxels of the components above max_area: its kernels run
         // on that sub-list (raster order kept), not on the whole foreground
         i32 *fglA = AA.get<i32>(nfg);
@@ -596,7 +619,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         UlkBasins Bv{va.b_size, va.g_L, va.b_top, nullptr, nullptr, nullptr, nullptr};
         UlkEdges Ev{va.ea, va.eb, va.wk, va.k3, va.cnt, va.shi, va.slo};
         ulk_launch(n_big, st, K_HierStage1{va.bs, va.es, Bv, Ev, S});
-        ulk_launch_list(fglA, nfgA, dm, st, K_Attach{va.bas, va.mw, va.jk, va.g_lab, va.bs, S.Ipar, S.Iwk, S.attach});
+        ulk_launch_list_ph<4>(fglA, nfgA, dm, st, K_Attach{va.bas, va.mw, va.jk, va.g_lab, va.bs, S.Ipar, S.Iwk, S.attach});
         i32 *region_of = AA.get<i32>(va.B);
         u64 *rkey_w = AA.get<u64>(va.B), *rkey_k = AA.get<u64>(va.B);
         CHKA(AA);
@@ -616,7 +639,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         ulk_launch(nrec, st, K_Gather<u32>{rec_cc, perm0, c0});
         CHK(ulk_sort_pairs_u32(c0, c1, perm0, perm1, nrec, st));              // then by component
         ulk_launch(nrec, st, K_RankToLabel{perm1, c1, label_of_rec});
-        ulk_launch_list(fgl, nfg, dm, st, K_WriteLabels{n_cc, va.bas, region_of, label_of_rec, lab2});
+        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_WriteLabels{n_cc, va.bas, region_of, label_of_rec, lab2});
         // number of valid records = regions
         i32 *nvalid = AA.get<i32>(nrec + 1), *nvpre = AA.get<i32>(nrec + 1);
         CHKA(AA);
@@ -644,7 +667,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     UlkEdges Ev{vb.ea, vb.eb, vb.wk, vb.k3, vb.cnt, vb.shi, vb.slo};
     ulk_launch(R, st, K_HierStage1{vb.bs, vb.es, Bv, Ev, S});
     if (area_mode)
-        ulk_launch_list(fgl, nfg, dm, st, K_Attach{vb.bas, vb.mw, vb.jk, vb.g_lab, vb.bs, S.Ipar, S.Iwk, S.attach});
+        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_Attach{vb.bas, vb.mw, vb.jk, vb.g_lab, vb.bs, S.Ipar, S.Iwk, S.attach});
     i64 N2 = 2 * (i64)vb.B + 2;
     UlkNodeOut O;
     O.count = A.get<i32>(R + 1); O.nsurv = A.get<i32>(R + 1); O.rsize = A.get<i32>(R + 1);
@@ -691,7 +714,10 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     if (!F->mask) ULK_FAIL(-3, "device allocation failed");
     CHK(ulk_memset(F->mask, 0, (size_t)total_words * 4, st));
     ulk_launch(vb.B, st, K_BasinNodeGlobal{vb.g_lab, noff, O.basin_node, bnode});
-    ulk_launch_list_warp(fgl, nfg, dm, st, K_MaskPaint{vb.bas, bnode, F->parent, F->bbox, F->mask_off, dm, F->mask});
+    UlkPaintInfo *pinfo = A.get<UlkPaintInfo>(N);
+    CHKA(A);
+    ulk_launch(N, st, K_PaintInfo{F->parent, F->bbox, F->mask_off, pinfo});
+    ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_MaskPaint{vb.bas, bnode, pinfo, dm, F->mask});
     // ---- overlaps: (node, emitted proper ancestor) pairs, processing.py:289-296
     i32 *depth = A.get<i32>(N + 1), *ooff = A.get<i32>(N + 1);
     CHKA(A);

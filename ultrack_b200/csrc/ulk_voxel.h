@@ -43,6 +43,24 @@ ULK_D ULK_INLINE void ulk_vunion(i32 *P, i32 a, i32 b)
     }
 }
 
+#ifndef ULK_EMU
+// roots of ULK_MULTI chains walked in lockstep (x < 0: no chain); every round issues one load
+// per unfinished chain, all independent
+ULK_D ULK_INLINE void ulk_vfind_multi(const i32 *P, i32 (&x)[ULK_MULTI])
+{
+    bool more;
+    do {
+        more = false;
+        i32 p[ULK_MULTI];
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u) p[u] = x[u] >= 0 ? P[x[u]] : -1;
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u)
+            if (p[u] != x[u]) { x[u] = p[u]; more = true; }
+    } while (more);
+}
+#endif
+
 // ------------------------------------------------------------------ K1: threshold + contour staging
 // processing.py:212 `foreground[time] > threshold`; vendored/hierarchy.py:158-159,350 up-casts.
 // The component forest starts with every x-run of foreground voxels inside a 32-voxel warp
@@ -105,21 +123,32 @@ struct K_Threshold {
 // edge one voxel to the left does not already join the same two runs
 struct K_CclUnion {
     i32 *P; UlkDims dm; i32 *cnt;
-    ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
+    // every neighbour is loaded up front (clamped to v at the frame border) so the loads
+    // overlap; only the sign is used, and the sign of an entry never changes
+    struct S1 { i32 v, p0, pl, py, pyl, pz, pzl; u32 h; };
+    typedef S1 S2;
+    ULK_D ULK_INLINE S1 load1(i32 v, i32 z, i32 y, i32 x, bool ok) const
     {
-        const i32 v = (i32)vv;
-        // every neighbour is loaded up front (clamped to v at the frame border) so the loads
-        // overlap; only the sign is used, and the sign of an entry never changes
+        S1 s;
+        s.v = v; s.p0 = -1; s.h = 0;
+        if (!ok) return s;
         const bool hx = x > 0, hy = y > 0, hz = z > 0;
         const i32 uy = hy ? v - dm.W : v, uz = hz ? v - dm.W * dm.H : v;
-        const i32 p0 = P[v];
-        const i32 pl = P[hx ? v - 1 : v], py = P[uy], pyl = P[hx ? uy - 1 : uy], pz = P[uz], pzl = P[hx ? uz - 1 : uz];
-        if (p0 < 0) return;
-        if (p0 == v) cnt[v] = 0;      // a final root is never hooked: its size counter starts at 0
-        const bool left = hx && pl >= 0;
-        if (left && (x & 31) == 0) ulk_vunion(P, v, v - 1);
-        if (hy && py >= 0 && !(left && pyl >= 0)) ulk_vunion(P, v, uy);
-        if (hz && pz >= 0 && !(left && pzl >= 0)) ulk_vunion(P, v, uz);
+        s.h = (hx ? 1u : 0u) | (hy ? 2u : 0u) | (hz ? 4u : 0u) | ((x & 31) == 0 ? 8u : 0u);
+        s.p0 = P[v];
+        s.pl = P[hx ? v - 1 : v]; s.py = P[uy]; s.pyl = P[hx ? uy - 1 : uy]; s.pz = P[uz]; s.pzl = P[hx ? uz - 1 : uz];
+        return s;
+    }
+    ULK_D ULK_INLINE S2 load2(const S1 &s, bool) const { return s; }
+    ULK_D ULK_INLINE void run(const S2 &s, bool) const
+    {
+        const i32 v = s.v;
+        if (s.p0 < 0) return;
+        if (s.p0 == v) cnt[v] = 0;      // a final root is never hooked: its size counter starts at 0
+        const bool left = (s.h & 1u) && s.pl >= 0;
+        if (left && (s.h & 8u)) ulk_vunion(P, v, v - 1);
+        if ((s.h & 2u) && s.py >= 0 && !(left && s.pyl >= 0)) ulk_vunion(P, v, v - dm.W);
+        if ((s.h & 4u) && s.pz >= 0 && !(left && s.pzl >= 0)) ulk_vunion(P, v, v - dm.W * dm.H);
     }
 };
 struct K_Flatten {
@@ -147,6 +176,21 @@ struct K_FlattenCount {
         if (r < 0) return;
         if ((threadIdx.x & 31) == __ffs(grp) - 1) atomicAdd(&cnt[r], __popc(grp));
         if (r == (i32)v) roots[atomicAdd(nroots, 1)] = r;
+    }
+    ULK_D void multi(const i32 (&v)[ULK_MULTI], const bool (&ok)[ULK_MULTI]) const
+    {
+        i32 r[ULK_MULTI];
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u) r[u] = ok[u] ? P[v[u]] : -1;     // foreground only: P >= 0
+        ulk_vfind_multi(P, r);
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u) {
+            if (r[u] >= 0) P[v[u]] = r[u];
+            u32 grp = __match_any_sync(0xffffffffu, r[u]);
+            if (r[u] < 0) continue;
+            if ((threadIdx.x & 31) == __ffs(grp) - 1) atomicAdd(&cnt[r[u]], __popc(grp));
+            if (r[u] == v[u]) roots[atomicAdd(nroots, 1)] = r[u];
+        }
     }
 #endif
 };
@@ -185,13 +229,18 @@ struct K_RootCode {
 // of the oversegmentation pass), the other kept components -(index + 2), dropped ones -1.
 struct K_LabelCc {
     const i32 *code; const i32 *cc_big; int mode; i32 *lab;
-    ULK_D void operator()(i64 v, i32, i32, i32) const
+    struct S1 { i32 v, r; };
+    struct S2 { i32 v, c; };
+    ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32, bool ok) const { S1 s; s.v = v; s.r = ok ? lab[v] : -1; return s; }
+    ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const { S2 s; s.v = a.v; s.c = a.r >= 0 ? code[a.r] : -1; return s; }
+    ULK_D ULK_INLINE void run(const S2 &s, bool) const
     {
-        i32 c = code[lab[v]];
-        if (mode == 0) { lab[v] = c; return; }
-        if (c == 0) { lab[v] = -1; return; }
+        const i32 c = s.c;
+        if (c < 0) return;
+        if (mode == 0) { lab[s.v] = c; return; }
+        if (c == 0) { lab[s.v] = -1; return; }
         i32 g = cc_big[c - 1];
-        lab[v] = g >= 0 ? g + 1 : -(c - 1) - 2;
+        lab[s.v] = g >= 0 ? g + 1 : -(c - 1) - 2;
     }
 };
 struct K_FlagRoots {
@@ -208,36 +257,54 @@ struct K_FlagRoots {
 struct K_MinEdge {
     const i32 *lab; UlkCt ct; UlkDims dm;
     u32 *mw, *pk;
-    ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
+    // neighbour indices clamped to v at the frame border: all loads are issued together
+    struct S1 { i32 v, l; u32 h; i32 ln[6]; float c, cn[6]; };
+    typedef S1 S2;
+    ULK_D ULK_INLINE i32 nb(i32 v, int i, u32 h) const
     {
-        const i32 v = (i32)vv;
         const i32 sy = dm.W, sz = dm.W * dm.H;
-        // neighbour indices clamped to v at the frame border: all loads are issued together
-        const bool h0 = z > 0, h1 = y > 0, h2 = x > 0, h3 = x + 1 < dm.W, h4 = y + 1 < dm.H, h5 = z + 1 < dm.D;
-        const i32 u0 = h0 ? v - sz : v, u1 = h1 ? v - sy : v, u2 = h2 ? v - 1 : v;
-        const i32 u3 = h3 ? v + 1 : v, u4 = h4 ? v + sy : v, u5 = h5 ? v + sz : v;
-        const i32 l = lab[v];
-        const i32 l0 = lab[u0], l1 = lab[u1], l2 = lab[u2], l3 = lab[u3], l4 = lab[u4], l5 = lab[u5];
-        if (l <= 0) return;          // mw / pk are only ever read where lab > 0
-        const bool s0 = h0 && l0 == l, s1 = h1 && l1 == l, s2 = h2 && l2 == l;
-        const bool s3 = h3 && l3 == l, s4 = h4 && l4 == l, s5 = h5 && l5 == l;
-        u32 bw = ULK_NONE32, bk = ULK_NONE32, w;
+        const i32 off = i == 0 ? -sz : i == 1 ? -sy : i == 2 ? -1 : i == 3 ? 1 : i == 4 ? sy : sz;
+        return ((h >> i) & 1u) ? v + off : v;
+    }
+    ULK_D ULK_INLINE S1 load1(i32 v, i32 z, i32 y, i32 x, bool ok) const
+    {
+        S1 s;
+        s.v = v; s.l = 0; s.h = 0;
+        if (!ok) return s;
+        s.h = (z > 0 ? 1u : 0u) | (y > 0 ? 2u : 0u) | (x > 0 ? 4u : 0u) | (x + 1 < dm.W ? 8u : 0u) | (y + 1 < dm.H ? 16u : 0u) | (z + 1 < dm.D ? 32u : 0u);
+        s.l = lab[v];
+#ifdef ULK_EMU
+        for (int i = 0; i < 6; ++i) s.ln[i] = lab[nb(v, i, s.h)];
+        if (ct.f) { s.c = ct.f[v]; for (int i = 0; i < 6; ++i) s.cn[i] = ct.f[nb(v, i, s.h)]; }
+#else
+#pragma unroll
+        for (int i = 0; i < 6; ++i) s.ln[i] = lab[nb(v, i, s.h)];
         if (ct.f) {
-            const float c = ct.f[v];
-            const float c0 = ct.f[u0], c1 = ct.f[u1], c2 = ct.f[u2], c3 = ct.f[u3], c4 = ct.f[u4], c5 = ct.f[u5];
-            if (s0) { w = ulk_f2ord(ulk_wsum(c0 + c)); if (w < bw) { bw = w; bk = 3u * (u32)u0 + 2u; } }
-            if (s1) { w = ulk_f2ord(ulk_wsum(c1 + c)); if (w < bw) { bw = w; bk = 3u * (u32)u1 + 1u; } }
-            if (s2) { w = ulk_f2ord(ulk_wsum(c2 + c)); if (w < bw) { bw = w; bk = 3u * (u32)u2; } }
-            if (s3) { w = ulk_f2ord(ulk_wsum(c + c3)); if (w < bw) { bw = w; bk = 3u * (u32)v; } }
-            if (s4) { w = ulk_f2ord(ulk_wsum(c + c4)); if (w < bw) { bw = w; bk = 3u * (u32)v + 1u; } }
-            if (s5) { w = ulk_f2ord(ulk_wsum(c + c5)); if (w < bw) { bw = w; bk = 3u * (u32)v + 2u; } }
-        } else {
-            if (s0) { w = ulk_f2ord(ct.w(u0, v)); if (w < bw) { bw = w; bk = 3u * (u32)u0 + 2u; } }
-            if (s1) { w = ulk_f2ord(ct.w(u1, v)); if (w < bw) { bw = w; bk = 3u * (u32)u1 + 1u; } }
-            if (s2) { w = ulk_f2ord(ct.w(u2, v)); if (w < bw) { bw = w; bk = 3u * (u32)u2; } }
-            if (s3) { w = ulk_f2ord(ct.w(v, u3)); if (w < bw) { bw = w; bk = 3u * (u32)v; } }
-            if (s4) { w = ulk_f2ord(ct.w(v, u4)); if (w < bw) { bw = w; bk = 3u * (u32)v + 1u; } }
-            if (s5) { w = ulk_f2ord(ct.w(v, u5)); if (w < bw) { bw = w; bk = 3u * (u32)v + 2u; } }
+            s.c = ct.f[v];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) s.cn[i] = ct.f[nb(v, i, s.h)];
+        }
+#endif
+        return s;
+    }
+    ULK_D ULK_INLINE S2 load2(const S1 &s, bool) const { return s; }
+    ULK_D ULK_INLINE void run(const S2 &s, bool) const
+    {
+        const i32 v = s.v, l = s.l;
+        if (l <= 0) return;          // mw / pk are only ever read where lab > 0
+        u32 bw = ULK_NONE32, bk = ULK_NONE32;
+#ifndef ULK_EMU
+#pragma unroll
+#endif
+        for (int i = 0; i < 6; ++i) {
+            if (!((s.h >> i) & 1u) || s.ln[i] != l) continue;
+            const i32 u = nb(v, i, s.h);
+            // candidates in increasing edge-key order: the first strictly smaller weight wins
+            const i32 a = i < 3 ? u : v, b = i < 3 ? v : u;
+            const float wf = ct.f ? (i < 3 ? ulk_wsum(s.cn[i] + s.c) : ulk_wsum(s.c + s.cn[i])) : ct.w(a, b);
+            const u32 w = ulk_f2ord(wf);
+            const u32 d = i == 0 || i == 5 ? 2u : (i == 1 || i == 4 ? 1u : 0u);
+            if (w < bw) { bw = w; bk = 3u * (u32)a + d; }
         }
         mw[v] = bw;
         pk[v] = bk;
@@ -254,20 +321,35 @@ ULK_HD ULK_INLINE i32 ulk_edge_other(u32 key, i32 v, const UlkDims &dm)
 struct K_Hook1 {
     const i32 *lab; const u32 *mw, *pk; UlkDims dm;
     i32 *bp; u8 *state; u32 *Lr; u32 *best; i32 *nbasins;
-    ULK_D void operator()(i64 vv, i32, i32, i32) const
+    struct S1 { i32 v, l; u32 k, m; };
+    struct S2 { i32 v, l, u; u32 k, m, ku; };
+    ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32, bool ok) const
     {
-        i32 v = (i32)vv;
+        S1 s;
+        s.v = v; s.l = 0; s.k = ULK_NONE32; s.m = 0;
+        if (ok) { s.l = lab[v]; s.k = pk[v]; s.m = mw[v]; }   // pk / mw hold stale values where lab <= 0: never used
+        return s;
+    }
+    ULK_D ULK_INLINE S2 load2(const S1 &a, bool ok) const
+    {
+        S2 s;
+        s.v = a.v; s.l = a.l; s.k = a.k; s.m = a.m; s.u = a.v; s.ku = ULK_NONE32;
+        if (ok && a.l > 0 && a.k != ULK_NONE32) { s.u = ulk_edge_other(a.k, a.v, dm); s.ku = pk[s.u]; }
+        return s;
+    }
+    ULK_D ULK_INLINE void run(const S2 &s, bool ok) const
+    {
+        if (!ok) return;
+        const i32 v = s.v;
         state[v] = 0;
-        if (lab[v] <= 0) { bp[v] = -1; return; }
-        u32 k = pk[v];
-        if (k == ULK_NONE32) {
+        if (s.l <= 0) { bp[v] = -1; return; }
+        if (s.k == ULK_NONE32) {
             bp[v] = v; state[v] = 1; Lr[v] = ULK_NONE32; best[v] = ULK_NONE32;
             ulk_atomic_add(nbasins, 1);
             return;
         }
-        i32 u = ulk_edge_other(k, v, dm);
-        if (pk[u] == k && v < u) { bp[v] = v; Lr[v] = mw[v]; best[v] = ULK_NONE32; }
-        else bp[v] = u;
+        if (s.ku == s.k && v < s.u) { bp[v] = v; Lr[v] = s.m; best[v] = ULK_NONE32; }
+        else bp[v] = s.u;
     }
 };
 struct K_Compress {
@@ -316,6 +398,23 @@ struct K_CompressCand {
         }
         ulk_warp_append(is_groot, v, groots, ngroots);
         ulk_warp_append(is_cand, v, cand, ncand);
+    }
+    ULK_D void multi(const i32 (&v)[ULK_MULTI], const bool (&ok)[ULK_MULTI]) const
+    {
+        i32 r[ULK_MULTI];
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u) r[u] = ok[u] ? bp[v[u]] : -1;    // -1 where the voxel is not in a region
+        ulk_vfind_multi(bp, r);
+        u8 st[ULK_MULTI]; u32 m[ULK_MULTI], L[ULK_MULTI];
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u)
+            if (r[u] >= 0) { bp[v[u]] = r[u]; st[u] = state[r[u]]; m[u] = mw[v[u]]; L[u] = Lr[r[u]]; }
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u) {
+            const bool growing = r[u] >= 0 && st[u] == 0;
+            ulk_warp_append(growing && r[u] == v[u], v[u], groots, ngroots);
+            ulk_warp_append(growing && m[u] == L[u], v[u], cand, ncand);
+        }
     }
 #endif
 };
@@ -406,6 +505,21 @@ struct K_CompressRoots {
         bp[v] = r;
         if (r == v) rootkeys[ulk_atomic_add(nroots, 1)] = ((u64)(u32)lab[v] << 32) | (u32)v;
     }
+#ifndef ULK_EMU
+    ULK_D void multi(const i32 (&v)[ULK_MULTI], const bool (&ok)[ULK_MULTI]) const
+    {
+        i32 r[ULK_MULTI];
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u) r[u] = ok[u] ? bp[v[u]] : -1;
+        ulk_vfind_multi(bp, r);
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u) {
+            if (r[u] < 0) continue;
+            bp[v[u]] = r[u];
+            if (r[u] == v[u]) rootkeys[ulk_atomic_add(nroots, 1)] = ((u64)(u32)lab[v[u]] << 32) | (u32)v[u];
+        }
+    }
+#endif
 };
 struct K_BasinRegroup {      // sorted position = global basin id
     const u64 *sorted; const u32 *Lr;
@@ -424,7 +538,11 @@ struct K_BasinRegroup {      // sorted position = global basin id
 struct K_AssignBasin {     // background stays at the memset value -1
     const i32 *bp; const u32 *gid_at_root;
     i32 *bas;
-    ULK_D void operator()(i64 v, i32, i32, i32) const { i32 r = bp[v]; bas[v] = r < 0 ? -1 : (i32)gid_at_root[r]; }
+    struct S1 { i32 v, r; };
+    struct S2 { i32 v, g; };
+    ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32, bool ok) const { S1 s; s.v = ok ? v : -1; s.r = ok ? bp[v] : -1; return s; }
+    ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const { S2 s; s.v = a.v; s.g = a.r < 0 ? -1 : (i32)gid_at_root[a.r]; return s; }
+    ULK_D ULK_INLINE void run(const S2 &s, bool) const { if (s.v >= 0) bas[s.v] = s.g; }
 };
 // flow edges are spanning-tree edges of the basin of their supervertex
 struct K_FlowTop {
@@ -450,70 +568,94 @@ struct K_BasinAccum {
     int want_stats; i32 *bbmin, *bbmax; i64 *csum;
     int want_join; const u32 *b_L; u32 *jk; i32 *hp; i32 *nhp;
     int want_k0; u32 *K0;
-    struct Own { u64 top; u32 nc; u32 kmin; i32 c[3]; bool plateau; };
-    ULK_D ULK_INLINE void own(i32 v, i32 z, i32 y, i32 x, i32 b, Own &o) const
+    // phase 1: the voxel's own entries and its neighbours' basins (indices clamped at the border)
+    struct S1 { i32 v, z, y, x, b, l; u32 m, k; i32 a[3], c[3]; };
+    // phase 2: what depends on them -- the basin level, the weight across the steepest edge, the
+    // labels of forward neighbours in another basin
+    struct S2 { i32 v, z, y, x, b; u64 top; u32 nc, kmin, jkv; bool plateau; };
+    ULK_D ULK_INLINE S1 load1(i32 v, i32 z, i32 y, i32 x, bool ok) const
     {
-        // neighbour basins first, all loads in flight together (indices clamped at the border)
+        S1 s;
+        s.v = v; s.z = z; s.y = y; s.x = x; s.b = -1;
+        if (!ok) return s;
         const i32 sy = dm.W, sz = dm.W * dm.H;
-        const bool f0 = x + 1 < dm.W, f1 = y + 1 < dm.H, f2 = z + 1 < dm.D;
-        const i32 a0 = bas[f0 ? v + 1 : v], a1 = bas[f1 ? v + sy : v], a2 = bas[f2 ? v + sz : v];
-        i32 c0 = -1, c1 = -1, c2 = -1;
-        if (want_k0) { c0 = bas[x > 0 ? v - 1 : v]; c1 = bas[y > 0 ? v - sy : v]; c2 = bas[z > 0 ? v - sz : v]; }
-        const u32 m = mw[v], k = pk[v];
-        const i32 l = lab[v];
-        o.top = k != ULK_NONE32 ? ((u64)m << 32) | k : 0;
-        o.c[0] = z; o.c[1] = y; o.c[2] = x;
-        o.nc = 0;
-        o.kmin = ULK_NONE32;
-        if (f0) { if (a0 == b) { u32 kk = 3u * (u32)v; if (kk < o.kmin) o.kmin = kk; } else if (lab[v + 1] == l) ++o.nc; }
-        if (want_k0 && x > 0 && c0 == b) { u32 kk = 3u * (u32)(v - 1); if (kk < o.kmin) o.kmin = kk; }
-        if (f1) { if (a1 == b) { u32 kk = 3u * (u32)v + 1u; if (kk < o.kmin) o.kmin = kk; } else if (lab[v + sy] == l) ++o.nc; }
-        if (want_k0 && y > 0 && c1 == b) { u32 kk = 3u * (u32)(v - sy) + 1u; if (kk < o.kmin) o.kmin = kk; }
-        if (f2) { if (a2 == b) { u32 kk = 3u * (u32)v + 2u; if (kk < o.kmin) o.kmin = kk; } else if (lab[v + sz] == l) ++o.nc; }
-        if (want_k0 && z > 0 && c2 == b) { u32 kk = 3u * (u32)(v - sz) + 2u; if (kk < o.kmin) o.kmin = kk; }
-        o.plateau = false;
-        if (want_join) {
-            if (m == b_L[b] || k == ULK_NONE32) jk[v] = ULK_JK_CORE;
-            else if (mw[ulk_edge_other(k, v, dm)] < m) jk[v] = k;
-            else { jk[v] = ULK_NONE32; o.plateau = true; }
+        s.b = bas[v];
+        s.a[0] = bas[x + 1 < dm.W ? v + 1 : v]; s.a[1] = bas[y + 1 < dm.H ? v + sy : v]; s.a[2] = bas[z + 1 < dm.D ? v + sz : v];
+        s.c[0] = s.c[1] = s.c[2] = -1;
+        if (want_k0) { s.c[0] = bas[x > 0 ? v - 1 : v]; s.c[1] = bas[y > 0 ? v - sy : v]; s.c[2] = bas[z > 0 ? v - sz : v]; }
+        s.m = mw[v]; s.k = pk[v]; s.l = lab[v];
+        return s;
+    }
+    ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const
+    {
+        S2 o;
+        o.v = a.v; o.z = a.z; o.y = a.y; o.x = a.x; o.b = a.b;
+        o.top = 0; o.nc = 0; o.kmin = ULK_NONE32; o.jkv = ULK_JK_CORE; o.plateau = false;
+        const i32 b = a.b, v = a.v;
+        if (b < 0) return o;
+        const i32 sy = dm.W, sz = dm.W * dm.H;
+        const bool f0 = a.x + 1 < dm.W, f1 = a.y + 1 < dm.H, f2 = a.z + 1 < dm.D;
+        // issue the dependent loads first
+        const bool q0 = f0 && a.a[0] != b, q1 = f1 && a.a[1] != b, q2 = f2 && a.a[2] != b;
+        const i32 l0 = q0 ? lab[v + 1] : 0, l1 = q1 ? lab[v + sy] : 0, l2 = q2 ? lab[v + sz] : 0;
+        u32 bl = 0, mo = 0;
+        const bool has_edge = a.k != ULK_NONE32;
+        if (want_join) { bl = b_L[b]; if (has_edge) mo = mw[ulk_edge_other(a.k, v, dm)]; }
+        o.top = has_edge ? ((u64)a.m << 32) | a.k : 0;
+        if (q0 && l0 == a.l) ++o.nc;
+        if (q1 && l1 == a.l) ++o.nc;
+        if (q2 && l2 == a.l) ++o.nc;
+        u32 kk;
+        if (f0 && a.a[0] == b) { kk = 3u * (u32)v; if (kk < o.kmin) o.kmin = kk; }
+        if (f1 && a.a[1] == b) { kk = 3u * (u32)v + 1u; if (kk < o.kmin) o.kmin = kk; }
+        if (f2 && a.a[2] == b) { kk = 3u * (u32)v + 2u; if (kk < o.kmin) o.kmin = kk; }
+        if (want_k0) {
+            if (a.x > 0 && a.c[0] == b) { kk = 3u * (u32)(v - 1); if (kk < o.kmin) o.kmin = kk; }
+            if (a.y > 0 && a.c[1] == b) { kk = 3u * (u32)(v - sy) + 1u; if (kk < o.kmin) o.kmin = kk; }
+            if (a.z > 0 && a.c[2] == b) { kk = 3u * (u32)(v - sz) + 2u; if (kk < o.kmin) o.kmin = kk; }
         }
+        if (want_join) {
+            if (a.m == bl || !has_edge) o.jkv = ULK_JK_CORE;
+            else if (mo < a.m) o.jkv = a.k;
+            else { o.jkv = ULK_NONE32; o.plateau = true; }
+        }
+        return o;
     }
 #ifdef ULK_EMU
-    void operator()(i64 vv, i32 z, i32 y, i32 x) const
+    void run(const S2 &o, bool) const
     {
-        i32 v = (i32)vv;
-        i32 b = bas[v];
+        const i32 b = o.b;
         if (b < 0) return;
-        Own o;
-        own(v, z, y, x, b, o);
+        if (want_join) jk[o.v] = o.jkv;
         b_size[b] += 1;
         if (o.top > b_top[b]) b_top[b] = o.top;
         *ncross += o.nc;
-        if (o.plateau) hp[(*nhp)++] = v;
+        if (o.plateau) hp[(*nhp)++] = o.v;
         if (want_k0 && o.kmin != ULK_NONE32 && o.kmin > K0[b]) K0[b] = o.kmin;
-        if (want_stats)
+        if (want_stats) {
+            const i32 c[3] = {o.z, o.y, o.x};
             for (int d = 0; d < 3; ++d) {
-                ulk_atomic_min(&bbmin[3 * b + d], o.c[d]);
-                ulk_atomic_max(&bbmax[3 * b + d], o.c[d]);
-                csum[3 * b + d] += o.c[d];
+                ulk_atomic_min(&bbmin[3 * b + d], c[d]);
+                ulk_atomic_max(&bbmax[3 * b + d], c[d]);
+                csum[3 * b + d] += c[d];
             }
+        }
     }
 #else
     // lanes of a warp that sit in the same basin AND the same row form a group (usually one or
     // two per warp): z and y are uniform in it and x grows with the lane, so the bounding box and
     // the coordinate sums need no reduction; one lane per group issues the atomics, and only
     // those that can still change the accumulator (a stale cached value only costs an atomic)
-    ULK_D void warp(i64 vv, i32 z, i32 y, i32 x, bool valid) const
+    ULK_D ULK_INLINE void run(const S2 &o, bool) const
     {
         const int lane = threadIdx.x & 31;
-        i32 v = (i32)vv;
-        i32 b = valid ? bas[v] : -1;
-        Own o;
-        o.top = 0; o.nc = 0; o.kmin = ULK_NONE32; o.c[0] = o.c[1] = o.c[2] = 0; o.plateau = false;
-        if (b >= 0) own(v, z, y, x, b, o);
+        const i32 b = o.b, v = o.v, x = o.x;
         u32 nct = __reduce_add_sync(0xffffffffu, o.nc);
         if (lane == 0 && nct) atomicAdd((unsigned long long *)ncross, (unsigned long long)nct);
-        if (want_join) ulk_warp_append(o.plateau, v, hp, nhp);
+        if (want_join) {
+            if (b >= 0) jk[v] = o.jkv;
+            ulk_warp_append(o.plateau, v, hp, nhp);
+        }
         u32 grp = __match_any_sync(0xffffffffu, b < 0 ? ULK_NONE64 : (((u64)(u32)b << 32) | (u32)(v - x)));
         if (b < 0) return;
         const int first = __ffs(grp) - 1;
@@ -531,6 +673,7 @@ struct K_BasinAccum {
             if (lead && km > K0[b]) atomicMax(&K0[b], km);
         }
         if (want_stats) {
+            const i32 z = o.z, y = o.y;
             const i32 x1 = __shfl_sync(grp, x, 31 - __clz(grp));       // x of the group's last lane
             u32 sx = (x1 - x + 1 == n) ? (u32)(((i64)(x + x1) * n) >> 1) : 0u;   // meaningful in the first lane
             if (__shfl_sync(grp, x1 - x + 1 != n ? 1 : 0, first)) sx = __reduce_add_sync(grp, (u32)x);
@@ -591,25 +734,38 @@ struct K_PlateauRelax {
 struct K_Attach {
     const i32 *bas; const u32 *mw, *jk; const i32 *b_lab; const i32 *bs;
     const i32 *Ipar; const u64 *Iwk; i32 *attach;
-    ULK_D void operator()(i64 v, i32, i32, i32) const
+    struct S1 { i32 b; u32 j, m; };
+    struct S2 { i32 o, node, p; u64 J; };
+    ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32, bool ok) const
     {
-        i32 b = bas[v];
-        if (b < 0) return;
-        u32 j = jk[v];
-        if (j == ULK_JK_CORE) return;
-        u64 J = ((u64)mw[v] << 32) | j;
-        i32 h = b_lab[b] - 1;
-        i32 s = bs[h];
-        i32 o = 2 * s;
-        i32 node = b - s;
-        i32 start = node;
+        S1 s;
+        s.b = -1; s.j = ULK_JK_CORE; s.m = 0;
+        if (ok) { s.b = bas[v]; s.j = jk[v]; s.m = mw[v]; }
+        return s;
+    }
+    ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const
+    {
+        S2 s;
+        s.o = 0; s.node = -1; s.p = -1; s.J = 0;
+        if (a.b < 0 || a.j == ULK_JK_CORE) return s;
+        s.J = ((u64)a.m << 32) | a.j;
+        const i32 st = bs[b_lab[a.b] - 1];
+        s.o = 2 * st;
+        s.node = a.b - st;
+        s.p = Ipar[s.o + s.node];
+        return s;
+    }
+    ULK_D ULK_INLINE void run(const S2 &s, bool) const
+    {
+        if (s.node < 0) return;
+        const i32 o = s.o, start = s.node;
+        i32 node = start, p = s.p;
         // the parent's merge key and the grandparent index are loaded together: one memory
         // round trip per level of the climb
-        i32 p = Ipar[o + node];
         while (p != node) {
             u64 w = Iwk[o + p];
             i32 pp = Ipar[o + p];
-            if (!(w < J)) break;
+            if (!(w < s.J)) break;
             node = p;
             p = pp;
         }
@@ -632,20 +788,31 @@ ULK_HD ULK_INLINE u64 ulk_hash64(u64 x)
 }
 struct K_RagInsert {
     const i32 *bas; const i32 *lab; UlkCt ct; UlkDims dm; UlkRagTable T; double fixscale;
-    ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
+    struct S1 { i32 v, b, l; u32 f; i32 cb[3], cl[3]; };
+    typedef S1 S2;
+    ULK_D ULK_INLINE S1 load1(i32 v, i32 z, i32 y, i32 x, bool ok) const
     {
-        const i32 v = (i32)vv;
-        const bool f[3] = {x + 1 < dm.W, y + 1 < dm.H, z + 1 < dm.D};
-        const i32 u[3] = {f[0] ? v + 1 : v, f[1] ? v + dm.W : v, f[2] ? v + dm.W * dm.H : v};
-        const i32 b = bas[v], l = lab[v];
-        const i32 cb[3] = {bas[u[0]], bas[u[1]], bas[u[2]]};
-        const i32 cl[3] = {lab[u[0]], lab[u[1]], lab[u[2]]};
+        S1 s;
+        s.v = v; s.b = -1; s.l = 0; s.f = 0;
+        if (!ok) return s;
+        s.f = (x + 1 < dm.W ? 1u : 0u) | (y + 1 < dm.H ? 2u : 0u) | (z + 1 < dm.D ? 4u : 0u);
+        const i32 u0 = (s.f & 1u) ? v + 1 : v, u1 = (s.f & 2u) ? v + dm.W : v, u2 = (s.f & 4u) ? v + dm.W * dm.H : v;
+        s.b = bas[v]; s.l = lab[v];
+        s.cb[0] = bas[u0]; s.cb[1] = bas[u1]; s.cb[2] = bas[u2];
+        s.cl[0] = lab[u0]; s.cl[1] = lab[u1]; s.cl[2] = lab[u2];
+        return s;
+    }
+    ULK_D ULK_INLINE S2 load2(const S1 &s, bool) const { return s; }
+    ULK_D ULK_INLINE void run(const S2 &s, bool) const
+    {
+        const i32 v = s.v, b = s.b, l = s.l;
         if (b < 0) return;
         for (int d = 0; d < 3; ++d) {
-            if (!f[d] || cl[d] != l || cb[d] == b) continue;
-            const i32 c = cb[d];
+            if (!((s.f >> d) & 1u) || s.cl[d] != l || s.cb[d] == b) continue;
+            const i32 c = s.cb[d];
+            const i32 u = v + dm.stride(d);
             u64 key = b < c ? ((u64)(u32)b << 32) | (u32)c : ((u64)(u32)c << 32) | (u32)b;
-            float w = ct.w(v, u[d]);
+            float w = ct.w(v, u);
             u32 ek = 3u * (u32)v + d;
             u64 h = ulk_hash64(key) & T.mask;
             for (;;) {
@@ -700,53 +867,82 @@ struct K_Hist {
 // voxel at initialisation; K_K3Union joins the runs (same scheme as the component labelling).
 struct K_K3Init {
     const i32 *bas; const u32 *K0; i32 *P;
-    ULK_D ULK_INLINE bool xlink(i64 v, i32 x, i32 b) const
+    struct S1 { i32 v, b, bl; bool ok, cons; };     // cons: the previous lane holds voxel v-1 of the same row
+    struct S2 { i32 v, b; bool ok, link; };
+    ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32 x, bool ok) const
     {
-        return b >= 0 && x > 0 && bas[v - 1] == b && 3u * (u32)(v - 1) <= K0[b];
-    }
+        S1 s;
+        s.v = v; s.ok = ok; s.b = -1; s.bl = -1;
 #ifdef ULK_EMU
-    void operator()(i64 v, i32, i32, i32 x) const
-    {
-        i32 b = bas[v];
-        P[v] = b < 0 ? -1 : ((x & 31) != 0 && xlink(v, x, b) ? P[v - 1] : (i32)v);
-    }
+        s.cons = x > 0 && (x & 31) != 0;
 #else
-    ULK_D void warp(i64 v, i32, i32, i32 x, bool valid) const
-    {
-        const int lane = threadIdx.x & 31;
-        i32 b = valid ? bas[v] : -1;
-        i32 vprev = __shfl_up_sync(0xffffffffu, (i32)v, 1);
-        u32 linked = __ballot_sync(0xffffffffu, lane > 0 && vprev == (i32)v - 1 && xlink(v, x, b));
-        if (valid) P[v] = b < 0 ? -1 : (i32)v - (lane - ulk_run_start(linked, lane));
-    }
+        i32 vprev = __shfl_up_sync(0xffffffffu, v, 1);
+        s.cons = (threadIdx.x & 31) > 0 && x > 0 && vprev == v - 1;
 #endif
+        if (ok) { s.b = bas[v]; s.bl = bas[x > 0 ? v - 1 : v]; }
+        return s;
+    }
+    ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const
+    {
+        S2 s;
+        s.v = a.v; s.b = a.b; s.ok = a.ok;
+        s.link = a.ok && a.cons && a.b >= 0 && a.bl == a.b && 3u * (u32)(a.v - 1) <= K0[a.b];
+        return s;
+    }
+    ULK_D ULK_INLINE void run(const S2 &s, bool) const
+    {
+#ifdef ULK_EMU
+        P[s.v] = s.b < 0 ? -1 : (s.link ? P[s.v - 1] : s.v);
+#else
+        const int lane = threadIdx.x & 31;
+        u32 linked = __ballot_sync(0xffffffffu, s.link);
+        if (s.ok) P[s.v] = s.b < 0 ? -1 : s.v - (lane - ulk_run_start(linked, lane));
+#endif
+    }
 };
 struct K_K3Union {
     const i32 *bas; UlkDims dm; const u32 *K0; i32 *P;
-    // `boundary`: the x edge to v-1 was not joined at initialisation
-    ULK_D ULK_INLINE void join(i32 v, i32 z, i32 y, i32 x, bool boundary) const
+    struct S1 { i32 v, b, bl, by, byl, bz, bzl; u32 h; };     // h: x>0, y>0, z>0, run boundary
+    struct S2 { i32 v; u32 todo; };                             // todo: unions with -x, -y, -z
+    ULK_D ULK_INLINE S1 load1(i32 v, i32 z, i32 y, i32 x, bool ok) const
     {
+        S1 s;
+        s.v = v; s.b = -1; s.h = 0;
+#ifdef ULK_EMU
+        const bool boundary = (x & 31) == 0;
+#else
+        i32 vprev = __shfl_up_sync(0xffffffffu, v, 1);
+        const bool boundary = (threadIdx.x & 31) == 0 || vprev != v - 1;
+#endif
+        if (!ok) return s;
         const bool hx = x > 0, hy = y > 0, hz = z > 0;
         const i32 uy = hy ? v - dm.W : v, uz = hz ? v - dm.W * dm.H : v;
-        const i32 b = bas[v];
-        const i32 bl = bas[hx ? v - 1 : v], by = bas[uy], byl = bas[hx ? uy - 1 : uy], bz = bas[uz], bzl = bas[hx ? uz - 1 : uz];
-        if (b < 0) return;
-        const u32 kmax = K0[b];
-        const bool left = hx && bl == b && 3u * (u32)(v - 1) <= kmax;
-        if (left && boundary) ulk_vunion(P, v, v - 1);
-        // (u-1,u), (u-1,v-1) carry smaller keys than (u,v): with (v-1,v) they already join u and v
-        if (hy && by == b && 3u * (u32)uy + 1u <= kmax && !(left && byl == b)) ulk_vunion(P, v, uy);
-        if (hz && bz == b && 3u * (u32)uz + 2u <= kmax && !(left && bzl == b)) ulk_vunion(P, v, uz);
+        s.h = (hx ? 1u : 0u) | (hy ? 2u : 0u) | (hz ? 4u : 0u) | (boundary ? 8u : 0u);
+        s.b = bas[v];
+        s.bl = bas[hx ? v - 1 : v]; s.by = bas[uy]; s.byl = bas[hx ? uy - 1 : uy]; s.bz = bas[uz]; s.bzl = bas[hx ? uz - 1 : uz];
+        return s;
     }
-#ifdef ULK_EMU
-    void operator()(i64 v, i32 z, i32 y, i32 x) const { join((i32)v, z, y, x, (x & 31) == 0); }
-#else
-    ULK_D void warp(i64 v, i32 z, i32 y, i32 x, bool valid) const
+    ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const
     {
-        i32 vprev = __shfl_up_sync(0xffffffffu, (i32)v, 1);
-        if (valid) join((i32)v, z, y, x, (threadIdx.x & 31) == 0 || vprev != (i32)v - 1);
+        S2 s;
+        s.v = a.v; s.todo = 0;
+        const i32 b = a.b, v = a.v;
+        if (b < 0) return s;
+        const u32 kmax = K0[b];
+        const i32 uy = v - dm.W, uz = v - dm.W * dm.H;
+        const bool left = (a.h & 1u) && a.bl == b && 3u * (u32)(v - 1) <= kmax;
+        if (left && (a.h & 8u)) s.todo |= 1u;
+        // (u-1,u), (u-1,v-1) carry smaller keys than (u,v): with (v-1,v) they already join u and v
+        if ((a.h & 2u) && a.by == b && 3u * (u32)uy + 1u <= kmax && !(left && a.byl == b)) s.todo |= 2u;
+        if ((a.h & 4u) && a.bz == b && 3u * (u32)uz + 2u <= kmax && !(left && a.bzl == b)) s.todo |= 4u;
+        return s;
     }
-#endif
+    ULK_D ULK_INLINE void run(const S2 &s, bool) const
+    {
+        if (s.todo & 1u) ulk_vunion(P, s.v, s.v - 1);
+        if (s.todo & 2u) ulk_vunion(P, s.v, s.v - dm.W);
+        if (s.todo & 4u) ulk_vunion(P, s.v, s.v - dm.W * dm.H);
+    }
 };
 struct K_K3FlattenCount {
     const i32 *bas; i32 *P; i32 *nroot; i32 *nmulti;
@@ -759,6 +955,23 @@ struct K_K3FlattenCount {
         i32 old = ulk_atomic_add(&nroot[bas[v]], 1);
         if (old == 1) ulk_atomic_add(nmulti, 1);
     }
+#ifndef ULK_EMU
+    ULK_D void multi(const i32 (&v)[ULK_MULTI], const bool (&ok)[ULK_MULTI]) const
+    {
+        i32 r[ULK_MULTI];
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u) r[u] = ok[u] ? P[v[u]] : -1;
+        ulk_vfind_multi(P, r);
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u) {
+            if (r[u] < 0) continue;
+            P[v[u]] = r[u];
+            if (r[u] != v[u]) continue;
+            i32 old = ulk_atomic_add(&nroot[bas[v[u]]], 1);
+            if (old == 1) ulk_atomic_add(nmulti, 1);
+        }
+    }
+#endif
 };
 struct K_K3FindBest {     // Boruvka step on the basins that are still split
     const i32 *bas; UlkDims dm; const i32 *nroot; const i32 *P; u32 *best;
@@ -823,12 +1036,29 @@ struct K_RankToLabel {
 struct K_WriteLabels {
     i32 ncc; const i32 *basA; const i32 *region_of; const i32 *label_of_rec;
     i32 *lab;
-    ULK_D void operator()(i64 v, i32, i32, i32) const
+    struct S1 { i32 v, l, ba; };
+    struct S2 { i32 v, rec; };       // rec: index into label_of_rec, -1: label 0, -2: nothing to write
+    ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32, bool ok) const
     {
-        i32 l = lab[v];
-        if (l > 0) lab[v] = label_of_rec[ncc + region_of[basA[v]]];
-        else if (l <= -2) lab[v] = label_of_rec[-l - 2];
-        else lab[v] = 0;
+        S1 s;
+        s.v = v; s.l = 0; s.ba = 0;
+        if (ok) { s.l = lab[v]; if (s.l > 0) s.ba = basA[v]; }
+        return s;
+    }
+    ULK_D ULK_INLINE S2 load2(const S1 &a, bool ok) const
+    {
+        S2 s;
+        s.v = a.v;
+        if (!ok) s.rec = -2;
+        else if (a.l > 0) s.rec = ncc + region_of[a.ba];
+        else if (a.l <= -2) s.rec = -a.l - 2;
+        else s.rec = -1;
+        return s;
+    }
+    ULK_D ULK_INLINE void run(const S2 &s, bool) const
+    {
+        if (s.rec == -2) return;
+        lab[s.v] = s.rec >= 0 ? label_of_rec[s.rec] : 0;
     }
 };
 struct K_CopyLabels {       // region labels as the caller sees them: 0 on the background
