@@ -111,6 +111,7 @@ template <int U, class F, class DM> void ulk_launch_list_ph(const i32 *list, i64
 {
     for (i64 i = 0; i < n; ++i) { i32 z, y, x; dm.coords(list[i], z, y, x); f.run(f.load2(f.load1(list[i], z, y, x, true), true), true); }
 }
+template <int U, class F, class DM> void ulk_launch_list_phx(const char *, const i32 *list, i64 n, const DM &dm, ulk_stream_t s, const F &f) { ulk_launch_list_ph<U>(list, n, dm, s, f); }
 // pointer-chasing list kernels (no coordinates): the emulation runs the scalar statement
 template <class F> void ulk_launch_list_multi(const i32 *list, i64 n, ulk_stream_t, const F &f)
 {
@@ -267,6 +268,17 @@ template <int U, class F, class DM> void ulk_launch_list_ph(const i32 *list, i64
     ulk_kernel_list_ph<U, F, DM><<<(unsigned)((n + 256 * U - 1) / (256 * U)), 256, 0, s>>>(list, n, dm, f);
     if (g_ulk_prof_on) ulk_prof_end(s);
     ++g_ulk_launches;
+}
+// tuning aid: entries per thread from the environment (ULK_U_<tag> = 1, 2 or 4), else the default
+template <int UDEF, class F, class DM> void ulk_launch_list_phx(const char *tag, const i32 *list, i64 n, const DM &dm, ulk_stream_t s, const F &f)
+{
+    char name[64];
+    snprintf(name, sizeof(name), "ULK_U_%s", tag);
+    const char *e = getenv(name);
+    int U = e ? atoi(e) : UDEF;
+    if (U == 1) ulk_launch_list_ph<1>(list, n, dm, s, f);
+    else if (U == 2) ulk_launch_list_ph<2>(list, n, dm, s, f);
+    else ulk_launch_list_ph<4>(list, n, dm, s, f);
 }
 template <class F> void ulk_launch_list_multi(const i32 *list, i64 n, ulk_stream_t s, const F &f)
 {

@@ -133,13 +133,16 @@ struct K_MaskPaint {
         }
 #else
         const int lane = threadIdx.x & 31;
-        u32 grp = __match_any_sync(0xffffffffu, s.b);
+        const i32 bprev = __shfl_up_sync(0xffffffffu, s.b, 1);
+        const u32 grp = ulk_run_mask(__ballot_sync(0xffffffffu, lane == 0 || bprev != s.b), lane);
         if (s.b < 0) return;
+        const bool first = lane == __ffs(grp) - 1;
         for (i32 n = s.n; n >= 0;) {
             const UlkPaintInfo r = load(n);
             i32 rx = s.x - r.x0;
             i64 word = r.moff + ((i64)(s.z - r.z0) * r.bh + (s.y - r.y0)) * r.wpr + (rx >> 5);
-            u32 sub = __match_any_sync(grp, (unsigned long long)word);
+            const i64 wprev = __shfl_up_sync(grp, word, 1);
+            const u32 sub = ulk_run_mask(__ballot_sync(grp, first || wprev != word) | ~grp, lane) & grp;
             u32 bits = __reduce_or_sync(sub, 1u << (rx & 31));
             if (lane == __ffs(sub) - 1) atomicOr(&mask[word], bits);
             n = r.parent;
@@ -301,8 +304,8 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     CHKA(A);
     CHK(ulk_memset(fmark, 0, (size_t)V + 8, st));
     CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
-    ulk_launch_list_ph<2>(fgl, nfg, dm, st, K_MinEdge{lab, ct, dm, mw, pk});
-    ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_Hook1{lab, mw, pk, dm, bp, state, Lr, best, ctr + 4});
+    ulk_launch_list_phx<1>("MinEdge", fgl, nfg, dm, st, K_MinEdge{lab, ct, dm, mw, pk});
+    ulk_launch_list_phx<4>("Hook1", fgl, nfg, dm, st, K_Hook1{lab, mw, pk, dm, bp, state, Lr, best, ctr + 4});
     ulk_launch_list_multi(fgl, nfg, st, K_CompressCand{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1});
     i32 hc[8];
     CHK(ulk_read(hc, ctr, 8, st));
@@ -368,7 +371,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
         ulk_fill<i32>(out.bbmax, -0x7fffffff, 3 * (i64)B, st);
         CHK(ulk_memset(out.csum, 0, (size_t)B * 3 * sizeof(i64), st));
     }
-    ulk_launch_list_ph<2>(fgl, nfg, dm, st, K_BasinAccum{out.bas, lab, mw, pk, dm, out.b_size, out.b_top, ncross,
+    ulk_launch_list_phx<2>("BasinAccum", fgl, nfg, dm, st, K_BasinAccum{out.bas, lab, mw, pk, dm, out.b_size, out.b_top, ncross,
                                         need_stats ? 1 : 0, out.bbmin, out.bbmax, out.csum,
                                         need_join ? 1 : 0, out.g_L, out.jk, hp, ctr + 0,
                                         need_k3 ? 1 : 0, out.b_k3});
@@ -406,7 +409,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     CHK(ulk_memset(T.cnt, 0, cap * 4, st));
     CHK(ulk_memset(T.shi, 0, cap * 8, st));
     CHK(ulk_memset(T.slo, 0, cap * 8, st));
-    ulk_launch_list_ph<2>(fgl, nfg, dm, st, K_RagInsert{out.bas, lab, ct, dm, T, fixscale});
+    ulk_launch_list_phx<1>("RagInsert", fgl, nfg, dm, st, K_RagInsert{out.bas, lab, ct, dm, T, fixscale});
     i32 *eflag = A.get<i32>((i64)cap + 1), *epre = A.get<i32>((i64)cap + 1);
     CHKA(A);
     ulk_launch((i64)cap, st, K_RagFlag{T.key, eflag});
@@ -454,7 +457,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
         i32 *nroot = A.get<i32>(B);
         CHKA(A);
         ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_K3Init{out.bas, out.b_k3, P3});
-        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_K3Union{out.bas, dm, out.b_k3, P3});
+        ulk_launch_list_phx<4>("K3Union", fgl, nfg, dm, st, K_K3Union{out.bas, dm, out.b_k3, P3});
         for (int it = 0;; ++it) {
             CHK(ulk_memset(nroot, 0, (size_t)B * sizeof(i32), st));
             CHK(ulk_memset(ctr, 0, sizeof(i32), st));
@@ -553,7 +556,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     i32 *ctr = A.get<i32>(4);
     u32 *roots0 = A.get<u32>(nfg);
     CHKA(A);
-    ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_CclUnion{P, dm, cnt});
+    ulk_launch_list_phx<2>("CclUnion", fgl, nfg, dm, st, K_CclUnion{P, dm, cnt});
     CHK(ulk_memset(ctr, 0, 4 * sizeof(i32), st));
     ulk_launch_list_multi(fgl, nfg, st, K_FlattenCount{P, cnt, (i32 *)roots0, ctr});
     i32 hc[4];
@@ -717,7 +720,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     UlkPaintInfo *pinfo = A.get<UlkPaintInfo>(N);
     CHKA(A);
     ulk_launch(N, st, K_PaintInfo{F->parent, F->bbox, F->mask_off, pinfo});
-    ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_MaskPaint{vb.bas, bnode, pinfo, dm, F->mask});
+    ulk_launch_list_phx<2>("MaskPaint", fgl, nfg, dm, st, K_MaskPaint{vb.bas, bnode, pinfo, dm, F->mask});
     // ---- overlaps: (node, emitted proper ancestor) pairs, processing.py:289-296
     i32 *depth = A.get<i32>(N + 1), *ooff = A.get<i32>(N + 1);
     CHKA(A);

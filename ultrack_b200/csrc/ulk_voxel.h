@@ -44,6 +44,18 @@ ULK_D ULK_INLINE void ulk_vunion(i32 *P, i32 a, i32 b)
 }
 
 #ifndef ULK_EMU
+// lanes hold consecutive entries of a raster-ordered list, so lanes that share a key are almost
+// always neighbours: `heads` has a bit for every lane whose key differs from the lane below it;
+// returns the lane mask of the caller's run (runs need not be maximal groups -- a key that
+// comes back later in the warp simply forms a second run)
+ULK_D ULK_INLINE u32 ulk_run_mask(u32 heads, int lane)
+{
+    const u32 upto = 0xffffffffu >> (31 - lane);
+    const int start = 31 - __clz((heads | 1u) & upto);
+    const u32 above = heads & ~upto;
+    const int end = above ? __ffs(above) - 2 : 31;
+    return (0xffffffffu >> (31 - end)) & (0xffffffffu << start);
+}
 // roots of ULK_MULTI chains walked in lockstep (x < 0: no chain); every round issues one load
 // per unfinished chain, all independent
 ULK_D ULK_INLINE void ulk_vfind_multi(const i32 *P, i32 (&x)[ULK_MULTI])
@@ -186,7 +198,9 @@ struct K_FlattenCount {
 #pragma unroll
         for (int u = 0; u < ULK_MULTI; ++u) {
             if (r[u] >= 0) P[v[u]] = r[u];
-            u32 grp = __match_any_sync(0xffffffffu, r[u]);
+            const int lane = threadIdx.x & 31;
+            const i32 rp_ = __shfl_up_sync(0xffffffffu, r[u], 1);
+            const u32 grp = ulk_run_mask(__ballot_sync(0xffffffffu, lane == 0 || rp_ != r[u]), lane);
             if (r[u] < 0) continue;
             if ((threadIdx.x & 31) == __ffs(grp) - 1) atomicAdd(&cnt[r[u]], __popc(grp));
             if (r[u] == v[u]) roots[atomicAdd(nroots, 1)] = r[u];
@@ -656,7 +670,9 @@ struct K_BasinAccum {
             if (b >= 0) jk[v] = o.jkv;
             ulk_warp_append(o.plateau, v, hp, nhp);
         }
-        u32 grp = __match_any_sync(0xffffffffu, b < 0 ? ULK_NONE64 : (((u64)(u32)b << 32) | (u32)(v - x)));
+        const i32 row = v - x;
+        const i32 bp_ = __shfl_up_sync(0xffffffffu, b, 1), rp_ = __shfl_up_sync(0xffffffffu, row, 1);
+        const u32 grp = ulk_run_mask(__ballot_sync(0xffffffffu, lane == 0 || bp_ != b || rp_ != row), lane);
         if (b < 0) return;
         const int first = __ffs(grp) - 1;
         const bool lead = lane == first;
