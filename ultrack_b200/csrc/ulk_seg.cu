@@ -215,6 +215,57 @@ ulk_threshold_kernel(K_Threshold k, i32 W, u32 S, u32 ntask, u32 *words)
     u32 m = __reduce_max_sync(0xffffffffu, mx);
     if (lane == 0 && m > *k.cmax) atomicMax(k.cmax, m);
 }
+// float32 + float32 inputs, W % 4 == 0, 16-byte aligned volumes: a lane loads four consecutive
+// voxels of each volume with one 128-bit load, a warp covers four 32-voxel row segments; the
+// foreground word of a segment is the OR of its eight lanes' nibbles, and the run starts of a
+// lane's voxels follow from that word alone (linked = word & word << 1)
+template <int U> __global__ void __launch_bounds__(256)
+ulk_threshold_kernel_v4(K_Threshold k, i32 W, u32 S, u32 T, u32 ntask4, u32 *words)
+{
+    const int lane = threadIdx.x & 31;
+    const u32 t0 = (u32)((((i64)blockIdx.x * 256 + threadIdx.x) >> 5) * U);
+    if (t0 >= ntask4) return;                 // the whole warp leaves together
+    u32 r = t0 / T, q = t0 - r * T;           // row, 128-voxel chunk of the row
+    float4 f[U], c[U]; i64 v[U]; bool valid[U]; u32 wbase[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        const i32 x = (i32)q * 128 + lane * 4;
+        valid[u] = t0 + u < ntask4 && x < W;
+        v[u] = (i64)r * W + x;
+        wbase[u] = r * S + q * 4u;
+        if (valid[u]) { f[u] = *(const float4 *)((const float *)k.fg + v[u]); c[u] = *(const float4 *)((const float *)k.ct + v[u]); }
+        if (++q == T) { q = 0; ++r; }
+    }
+    u32 mx = 0;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        u32 nib = 0;
+        if (valid[u]) {
+            nib = ((double)f[u].x > k.thr ? 1u : 0u) | ((double)f[u].y > k.thr ? 2u : 0u) | ((double)f[u].z > k.thr ? 4u : 0u) | ((double)f[u].w > k.thr ? 8u : 0u);
+            const float a0 = fabsf(c[u].x), a1 = fabsf(c[u].y), a2 = fabsf(c[u].z), a3 = fabsf(c[u].w);
+            u32 b;
+            b = a0 <= 3.0e38f ? __float_as_uint(a0) : 0u; mx = b > mx ? b : mx;
+            b = a1 <= 3.0e38f ? __float_as_uint(a1) : 0u; mx = b > mx ? b : mx;
+            b = a2 <= 3.0e38f ? __float_as_uint(a2) : 0u; mx = b > mx ? b : mx;
+            b = a3 <= 3.0e38f ? __float_as_uint(a3) : 0u; mx = b > mx ? b : mx;
+        }
+        const int sub = lane >> 3, pos = (lane & 7) * 4;
+        const u32 word = __reduce_or_sync(0xffu << (sub * 8), nib << pos);
+        const u32 linked = word & (word << 1);
+        if (valid[u]) {
+            int4 o;
+            const i32 vb = (i32)v[u] - pos;        // first voxel of this 32-voxel segment
+            o.x = (nib & 1u) ? vb + ulk_run_start(linked, pos) : -1;
+            o.y = (nib & 2u) ? vb + ulk_run_start(linked, pos + 1) : -1;
+            o.z = (nib & 4u) ? vb + ulk_run_start(linked, pos + 2) : -1;
+            o.w = (nib & 8u) ? vb + ulk_run_start(linked, pos + 3) : -1;
+            *(int4 *)(k.P + v[u]) = o;
+            if ((lane & 7) == 0) words[wbase[u] + sub] = word;
+        }
+    }
+    u32 m = __reduce_max_sync(0xffffffffu, mx);
+    if (lane == 0 && m > *k.cmax) atomicMax(k.cmax, m);
+}
 __global__ void __launch_bounds__(256)
 ulk_expand_kernel(const u32 *words, const i32 *off, u32 ntask, i32 W, u32 S, UlkFastDiv fS, i32 *list, i32 *count)
 {
@@ -254,7 +305,15 @@ static int threshold_and_list(ulk_stream_t st, UlkArena &A, const UlkDims &dm, c
     const i64 warps = (nt + U - 1) / U;
     const unsigned grid = (unsigned)((warps + 7) / 8);
     if (g_ulk_prof_on) ulk_prof_begin(typeid(K_Threshold).name(), st);
-    if (k.fgt == ULK_F32 && k.ctt == ULK_F32) {
+    const bool vec4 = k.fgt == ULK_F32 && k.ctt == ULK_F32 && dm.W % 4 == 0 && !getenv("ULK_THR_SCALAR") &&
+                      (((uintptr_t)k.fg | (uintptr_t)k.ct | (uintptr_t)k.P) & 15u) == 0;
+    if (vec4) {
+        const u32 T = (u32)((dm.W + 127) / 128);
+        const i64 nt4 = (i64)dm.D * dm.H * T;
+        const int U4 = 2;
+        const i64 warps4 = (nt4 + U4 - 1) / U4;
+        ulk_threshold_kernel_v4<U4><<<(unsigned)((warps4 + 7) / 8), 256, 0, st>>>(k, dm.W, S, T, (u32)nt4, words);
+    } else if (k.fgt == ULK_F32 && k.ctt == ULK_F32) {
         if (U == 8) ulk_threshold_kernel<8, true><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
         else if (U == 2) ulk_threshold_kernel<2, true><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
         else ulk_threshold_kernel<4, true><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);

@@ -677,35 +677,46 @@ struct K_BasinAccum {
         const int first = __ffs(grp) - 1;
         const bool lead = lane == first;
         const i32 n = __popc(grp);
+        // the leader reads the accumulators it may have to update before the reductions start,
+        // so those loads overlap them
+        u64 cur_top = 0; u32 cur_k0 = 0;
+        i32 clo[3] = {0, 0, 0}, chi[3] = {0, 0, 0};
+        if (lead) {
+            cur_top = b_top[b];
+            if (want_k0) cur_k0 = K0[b];
+            if (want_stats) {
+                clo[0] = bbmin[3 * b]; clo[1] = bbmin[3 * b + 1]; clo[2] = bbmin[3 * b + 2];
+                chi[0] = bbmax[3 * b]; chi[1] = bbmax[3 * b + 1]; chi[2] = bbmax[3 * b + 2];
+            }
+        }
         u32 thi = __reduce_max_sync(grp, (u32)(o.top >> 32));
         u32 tlo = __reduce_max_sync(grp, (u32)(o.top >> 32) == thi ? (u32)o.top : 0u);
-        if (lead) {
-            atomicAdd(&b_size[b], n);
-            u64 t = ((u64)thi << 32) | tlo;
-            if (t > b_top[b]) atomicMax((unsigned long long *)&b_top[b], (unsigned long long)t);
+        u32 km = 0;
+        if (want_k0) km = __reduce_max_sync(grp, o.kmin == ULK_NONE32 ? 0u : o.kmin);
+        i32 x1 = x; u32 sx = 0;
+        if (want_stats) {
+            x1 = __shfl_sync(grp, x, 31 - __clz(grp));                 // x of the run's last lane
+            sx = (x1 - x + 1 == n) ? (u32)(((i64)(x + x1) * n) >> 1) : 0u;   // meaningful in the first lane
+            if (__shfl_sync(grp, x1 - x + 1 != n ? 1 : 0, first)) sx = __reduce_add_sync(grp, (u32)x);
         }
-        if (want_k0) {
-            u32 km = __reduce_max_sync(grp, o.kmin == ULK_NONE32 ? 0u : o.kmin);
-            if (lead && km > K0[b]) atomicMax(&K0[b], km);
-        }
+        if (!lead) return;
+        atomicAdd(&b_size[b], n);
+        const u64 t = ((u64)thi << 32) | tlo;
+        if (t > cur_top) atomicMax((unsigned long long *)&b_top[b], (unsigned long long)t);
+        if (want_k0 && km > cur_k0) atomicMax(&K0[b], km);
         if (want_stats) {
             const i32 z = o.z, y = o.y;
-            const i32 x1 = __shfl_sync(grp, x, 31 - __clz(grp));       // x of the group's last lane
-            u32 sx = (x1 - x + 1 == n) ? (u32)(((i64)(x + x1) * n) >> 1) : 0u;   // meaningful in the first lane
-            if (__shfl_sync(grp, x1 - x + 1 != n ? 1 : 0, first)) sx = __reduce_add_sync(grp, (u32)x);
-            if (lead) {
-                i32 *lo = bbmin + 3 * b, *hi = bbmax + 3 * b;
-                i64 *cs = csum + 3 * b;
-                if (z < lo[0]) atomicMin(&lo[0], z);
-                if (z > hi[0]) atomicMax(&hi[0], z);
-                if (y < lo[1]) atomicMin(&lo[1], y);
-                if (y > hi[1]) atomicMax(&hi[1], y);
-                if (x < lo[2]) atomicMin(&lo[2], x);
-                if (x1 > hi[2]) atomicMax(&hi[2], x1);
-                atomicAdd((unsigned long long *)&cs[0], (unsigned long long)((i64)z * n));
-                atomicAdd((unsigned long long *)&cs[1], (unsigned long long)((i64)y * n));
-                atomicAdd((unsigned long long *)&cs[2], (unsigned long long)sx);
-            }
+            i32 *lo = bbmin + 3 * b, *hi = bbmax + 3 * b;
+            i64 *cs = csum + 3 * b;
+            if (z < clo[0]) atomicMin(&lo[0], z);
+            if (z > chi[0]) atomicMax(&hi[0], z);
+            if (y < clo[1]) atomicMin(&lo[1], y);
+            if (y > chi[1]) atomicMax(&hi[1], y);
+            if (x < clo[2]) atomicMin(&lo[2], x);
+            if (x1 > chi[2]) atomicMax(&hi[2], x1);
+            atomicAdd((unsigned long long *)&cs[0], (unsigned long long)((i64)z * n));
+            atomicAdd((unsigned long long *)&cs[1], (unsigned long long)((i64)y * n));
+            atomicAdd((unsigned long long *)&cs[2], (unsigned long long)sx);
         }
     }
 #endif
