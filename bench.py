@@ -318,7 +318,9 @@ def main():
         f = prev.contents
         stats = dict(n_nodes=int(f.n_nodes), n_overlaps=int(f.n_overlaps), mask_words=int(f.mask_words),
                      n_hier=int(f.n_hier), n_basins=int(f.stats.n_basins), n_rag_edges=int(f.stats.n_rag_edges))
-        n_fg = int((frames_in[(args.steps - 1) % 2][0] > SEG["threshold"]).sum().item())
+        n_fg = int(f.stats.n_foreground)
+        n_fg_a = int(f.stats.pass_a_voxels)
+        stats["n_foreground"], stats["pass_a_voxels"] = n_fg, n_fg_a
 
         # ---- e2e: the same steps from pinned HOST buffers through the ingest API segment() uses
         # (ulk_upload_begin of frame i+1 before ulk_segment_frame_uploaded of frame i), node
@@ -392,8 +394,8 @@ def main():
     top = sorted(prof.items(), key=lambda kv: -kv[1][1])
     # the dominant kernel = the one with the largest share of the timed region that is one of
     # this library's voxel kernels (it has an entry in the byte model)
-    dom_name, (dom_cnt, dom_ms) = next(((k, v) for k, v in top if bytes_model.kernel_bytes(k, V, n_fg)), top[0])
-    dom_bytes = bytes_model.kernel_bytes(dom_name, V, n_fg)
+    dom_name, (dom_cnt, dom_ms) = next(((k, v) for k, v in top if bytes_model.kernel_bytes(k, V, n_fg, n_fg_a)), top[0])
+    dom_bytes = bytes_model.kernel_bytes(dom_name, V, n_fg, n_fg_a)
     dom_avg_ms = dom_ms / dom_cnt
     traffic = None
     tf = ROOT / "profiles" / "ncu_traffic.json"     # dram bytes per launch from `ncu --set full` captures
@@ -405,7 +407,7 @@ def main():
         "achieved": (dom_bytes / (dom_avg_ms * 1e-3) / 1e9) if dom_bytes else None, "peak": peak_gbs, "unit": "GB/s",
         "frac": (dom_bytes / (dom_avg_ms * 1e-3) / 1e9 / peak_gbs) if dom_bytes else None,
         "algorithmic_bytes_per_launch": dom_bytes, "traffic": traffic, "peak_source": peak_src,
-        "n_foreground": n_fg,
+        "n_foreground": n_fg, "pass_a_voxels": n_fg_a,
     }
     b_frame = bytes_model.frame_bytes(V, 4, 4, n_fg, stats["n_nodes"], stats["mask_words"], stats["n_overlaps"])
     b_link = bytes_model.link_bytes(tot_links // max(args.steps, 1), tot_pairs // max(args.steps, 1),

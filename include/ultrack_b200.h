@@ -51,6 +51,8 @@ typedef struct ulk_seg_params {
 typedef struct ulk_seg_stats {
     int64_t n_basins, n_rag_edges, plateau_voxels;
     int32_t flow_rounds, k3_rounds;
+    int64_t n_foreground;        /* voxels above the threshold                                    */
+    int64_t pass_a_voxels;       /* voxels of components above max_area (oversegmentation pass)   */
 } ulk_seg_stats;
 
 /* Candidate nodes of one frame, device-resident struct of arrays.  Node order is the

@@ -20,8 +20,7 @@ from typing import Dict, Optional
 
 # kernel name (as reported by ulk_profile_report) -> bytes per frame voxel per launch (float32 inputs)
 DENSE_BYTES_PER_VOXEL: Dict[str, float] = {
-    "K_Threshold": 4 + 4 + 4,            # fg, ct in; component forest out (float32 contours are not staged)
-    "cub::DeviceSelect::If": 4 + 0.3 * 4,   # forest in, list entry out for the foreground fraction
+    "K_Threshold": 4 + 4 + 4 + 0.125,    # fg, ct in; component forest + one foreground bit out (float32 contours are not staged)
 }
 # kernel name -> bytes per FOREGROUND voxel per launch (including the 4-byte list entry)
 LIST_BYTES_PER_FG_VOXEL: Dict[str, float] = {
@@ -54,12 +53,23 @@ def link_bytes(n_links: int, n_pairs: int, mean_mask_words: float) -> int:
     return int(20 * n_links + n_pairs * (2 * 36 + 2 * 4 * mean_mask_words))
 
 
-def kernel_bytes(name: str, voxels: int, n_foreground: int) -> Optional[float]:
+# list kernels of the voxel stage: launched once on the voxels of the components above max_area
+# (oversegmentation pass A) and once on the whole foreground (pass B) per frame
+TWO_PASS = {"K_MinEdge", "K_Hook1", "K_CompressCand", "K_CompressRoots", "K_AssignBasin", "K_BasinAccum",
+            "K_RagInsert", "K_Attach"}
+
+
+def kernel_bytes(name: str, voxels: int, n_foreground: int, pass_a_voxels: Optional[int] = None) -> Optional[float]:
     """Algorithmic bytes of one launch of kernel `name` on a frame of `voxels` voxels of which
-    `n_foreground` are foreground."""
+    `n_foreground` are foreground.  For the two-pass kernels, when `pass_a_voxels` is given, the
+    figure is the AVERAGE over the frame's two launches (pass A on `pass_a_voxels`, pass B on
+    `n_foreground`), matching an average launch duration."""
     base = name.split("<")[0]
     if base in DENSE_BYTES_PER_VOXEL:
         return DENSE_BYTES_PER_VOXEL[base] * voxels
     if base in LIST_BYTES_PER_FG_VOXEL:
-        return LIST_BYTES_PER_FG_VOXEL[base] * n_foreground
+        n = n_foreground
+        if base in TWO_PASS and pass_a_voxels is not None and pass_a_voxels > 0:
+            n = (n_foreground + pass_a_voxels) / 2.0
+        return LIST_BYTES_PER_FG_VOXEL[base] * n
     return None

@@ -610,6 +610,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     // ---- connected components (4/6-connected): union of runs, flatten + sizes + root list
     i32 nfg = 0;
     CHK(ulk_read(&nfg, nfg_dev, 1, st));
+    stats_local.n_foreground = nfg;
     i32 *cnt = A.get<i32>(V);            // sizes at the roots, later the component code at the roots
     i32 *lab2 = P;                       // region labels are written in place over the component forest (-1 stays on the background)
     i32 *ctr = A.get<i32>(4);
@@ -674,6 +675,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         CHK(ulk_select_list_pos_i32(fgl, nfg, labA, fglA, nfgA_dev, st));
         i32 nfgA = 0;
         CHK(ulk_read(&nfgA, nfgA_dev, 1, st));
+        stats_local.pass_a_voxels = nfgA;
         VoxelStage va;
         CHK(voxel_stage(st, AA, dm, fglA, nfgA, ct, labA, n_big, true, false, false, fixscale, va, &stats_local));
         UlkHierScratch S;
