@@ -76,6 +76,13 @@ int ulk_select_list_pos_i32(const i32 *list, i64 n, const i32 *lab, i32 *out, i3
     *count = c;
     return 0;
 }
+int ulk_select_list_split_i32(const i32 *list, i64 n, const i32 *bas, const i32 *nroot, i32 *out, i32 *count, ulk_stream_t)
+{
+    i32 c = 0;
+    for (i64 i = 0; i < n; ++i) if (nroot[bas[list[i]]] > 1) out[c++] = list[i];
+    *count = c;
+    return 0;
+}
 int ulk_sort_keys_u32(const u32 *ki, u32 *ko, i64 n, ulk_stream_t)
 {
     std::vector<u32> k(ki, ki + n);
@@ -442,6 +449,22 @@ int ulk_exclusive_scan_popc_u32(const u32 *words, i32 *out, i64 n, ulk_stream_t 
     if (cub_tmp(need)) return -2;
     ProfScope ps("cub::DeviceScan::ExclusiveSum", s);
     ULK_CUDA(cub::DeviceScan::ExclusiveSum(g_cub_tmp, need, it, out, (int)n, s));
+    ++g_ulk_launches;
+    return 0;
+}
+struct UlkSplitAt {
+    const i32 *bas, *nroot;
+    __device__ bool operator()(const i32 &v) const { return nroot[bas[v]] > 1; }
+};
+int ulk_select_list_split_i32(const i32 *list, i64 n, const i32 *bas, const i32 *nroot, i32 *out, i32 *count_dev, ulk_stream_t s)
+{
+    if (n <= 0) return ulk_memset(count_dev, 0, sizeof(i32), s);
+    UlkSplitAt pred{bas, nroot};
+    size_t need = 0;
+    ULK_CUDA(cub::DeviceSelect::If(nullptr, need, list, out, count_dev, (int)n, pred, s));
+    if (cub_tmp(need)) return -2;
+    ProfScope ps("cub::DeviceSelect::If", s);
+    ULK_CUDA(cub::DeviceSelect::If(g_cub_tmp, need, list, out, count_dev, (int)n, pred, s));
     ++g_ulk_launches;
     return 0;
 }

@@ -287,10 +287,37 @@ ulk_expand_kernel(const u32 *words, const i32 *off, u32 ntask, i32 W, u32 S, Ulk
         if ((wj >> lane) & 1u) list[oj + __popc(wj & ((1u << lane) - 1u))] = bj + lane;
     }
 }
-#endif
-// P (component forest, -1 on the background), *cmax, the foreground list and its length
-static int threshold_and_list(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const K_Threshold &k, i32 *fgl, i32 *nfg_dev)
+// Connected components from the foreground bit words: one thread per 32-voxel row segment.
+// Every x-run inside a segment is already hooked to its first voxel (K_Threshold), so what is
+// left is one union per run of overlap with the row above / the slice above (start bits of
+// w & w_up) and one across the segment boundary; the per-voxel neighbour tests of K_CclUnion
+// become three word loads.  Size counters of all run starts (the only possible roots) are zeroed.
+__global__ void __launch_bounds__(256)
+ulk_ccl_words_kernel(const u32 *words, u32 ntask, i32 W, i32 H, u32 S, UlkFastDiv fS, UlkFastDiv fH, i32 *P, i32 *cnt)
 {
+    const u32 t = blockIdx.x * 256u + threadIdx.x;
+    if (t >= ntask) return;
+    const u32 w = words[t];
+    const u32 r = fS.div(t), sg = t - r * S;          // row (z*H + y), segment of the row
+    const u32 zz = fH.div(r), y = r - zz * (u32)H;
+    const u32 wl = sg > 0 ? words[t - 1] : 0u;
+    const u32 wy = y > 0 ? words[t - S] : 0u;
+    const u32 wz = zz > 0 ? words[t - S * (u32)H] : 0u;
+    if (w == 0) return;
+    const i32 base = (i32)(r * (u32)W + sg * 32u);
+    for (u32 m = w & ~(w << 1); m; m &= m - 1) cnt[base + __ffs(m) - 1] = 0;
+    if ((w & 1u) && (wl >> 31)) ulk_vunion(P, base, base - 1);
+    u32 o = w & wy;
+    for (u32 m = o & ~(o << 1); m; m &= m - 1) { const i32 v = base + __ffs(m) - 1; ulk_vunion(P, v, v - W); }
+    o = w & wz;
+    for (u32 m = o & ~(o << 1); m; m &= m - 1) { const i32 v = base + __ffs(m) - 1; ulk_vunion(P, v, v - W * H); }
+}
+#endif
+// P (component forest, -1 on the background), *cmax, the foreground list and its length; on the
+// GPU also the connected-component unions (they run on the foreground words)
+static int threshold_and_list(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const K_Threshold &k, i32 *fgl, i32 *nfg_dev, i32 *cnt, bool *ccl_done)
+{
+    *ccl_done = false;
 #ifdef ULK_EMU
     ulk_launch_vox_warp(dm.D, dm.H, dm.W, st, k);
     return ulk_select_nonneg_i32(k.P, dm.V, fgl, nfg_dev, st);
@@ -331,6 +358,15 @@ static int threshold_and_list(ulk_stream_t st, UlkArena &A, const UlkDims &dm, c
     ulk_expand_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(words, off, ntask, dm.W, S, fS, fgl, nfg_dev);
     if (g_ulk_prof_on) ulk_prof_end(st);
     ++g_ulk_launches;
+    if (!getenv("ULK_CCL_VOXEL")) {
+        UlkFastDiv fH;
+        fH.init((u32)dm.H);
+        if (g_ulk_prof_on) ulk_prof_begin("K_CclWords", st);
+        ulk_ccl_words_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(words, ntask, dm.W, dm.H, S, fS, fH, k.P, cnt);
+        if (g_ulk_prof_on) ulk_prof_end(st);
+        ++g_ulk_launches;
+        *ccl_done = true;
+    }
     A.release(words); A.release(off);
     return 0;
 #endif
@@ -517,18 +553,31 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
         CHKA(A);
         ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_K3Init{out.bas, out.b_k3, P3});
         ulk_launch_list_phx<4>("K3Union", fgl, nfg, dm, st, K_K3Union{out.bas, dm, out.b_k3, P3});
+        // basins that edges <= K0 leave split (rare) go on with Boruvka rounds on THEIR voxels only
+        const i32 *cur = fgl;
+        i64 ncur = nfg;
+        i32 *sub = nullptr, *nsub_dev = nullptr;
         for (int it = 0;; ++it) {
             CHK(ulk_memset(nroot, 0, (size_t)B * sizeof(i32), st));
             CHK(ulk_memset(ctr, 0, sizeof(i32), st));
-            ulk_launch_list_multi(fgl, nfg, st, K_K3FlattenCount{out.bas, P3, nroot, ctr + 0});
+            ulk_launch_list_multi(cur, ncur, st, K_K3FlattenCount{out.bas, P3, nroot, ctr + 0});
             CHK(ulk_read(hc, ctr, 1, st));
             if (hc[0] == 0) break;
             if (stats) stats->k3_rounds += 1;
-            if (it == 0) ulk_launch_list(fgl, nfg, dm, st, K_FillAt<u32>{best, ULK_NONE32});     // K_K3Hook resets what it used
-            ulk_launch_list(fgl, nfg, dm, st, K_K3FindBest{out.bas, dm, nroot, P3, best});
-            ulk_launch_list(fgl, nfg, dm, st, K_K3Hook{out.bas, dm, P3, best, out.b_k3});
+            if (it == 0) {
+                sub = A.get<i32>(nfg); nsub_dev = A.get<i32>(1);
+                CHKA(A);
+                CHK(ulk_select_list_split_i32(fgl, nfg, out.bas, nroot, sub, nsub_dev, st));
+                i32 nsub = 0;
+                CHK(ulk_read(&nsub, nsub_dev, 1, st));
+                cur = sub; ncur = nsub;
+                ulk_launch_list(cur, ncur, dm, st, K_FillAt<u32>{best, ULK_NONE32});     // K_K3Hook resets what it used
+            }
+            ulk_launch_list(cur, ncur, dm, st, K_K3FindBest{out.bas, dm, nroot, P3, best});
+            ulk_launch_list(cur, ncur, dm, st, K_K3Hook{out.bas, dm, P3, best, out.b_k3});
             if (it > 100000) ULK_FAIL(-4, "bottleneck rounds did not converge");
         }
+        if (sub) { A.release(sub); A.release(nsub_dev); }
         A.release(nroot);
     }
     A.release(pk); A.release(state); A.release(Lr); A.release(best); A.release(fmark);
@@ -606,17 +655,19 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     i32 *fgl = A.get<i32>(V);
     i32 *nfg_dev = A.get<i32>(1);
     CHKA(A);
-    CHK(threshold_and_list(st, A, dm, K_Threshold{fg, fg_dtype, prm->threshold, ctp, ct_dtype, ctf, ctd, P, cmax}, fgl, nfg_dev));
+    i32 *cnt = A.get<i32>(V);            // sizes at the roots, later the component code at the roots
+    CHKA(A);
+    bool ccl_done = false;
+    CHK(threshold_and_list(st, A, dm, K_Threshold{fg, fg_dtype, prm->threshold, ctp, ct_dtype, ctf, ctd, P, cmax}, fgl, nfg_dev, cnt, &ccl_done));
     // ---- connected components (4/6-connected): union of runs, flatten + sizes + root list
     i32 nfg = 0;
     CHK(ulk_read(&nfg, nfg_dev, 1, st));
     stats_local.n_foreground = nfg;
-    i32 *cnt = A.get<i32>(V);            // sizes at the roots, later the component code at the roots
     i32 *lab2 = P;                       // region labels are written in place over the component forest (-1 stays on the background)
     i32 *ctr = A.get<i32>(4);
     u32 *roots0 = A.get<u32>(nfg);
     CHKA(A);
-    ulk_launch_list_phx<2>("CclUnion", fgl, nfg, dm, st, K_CclUnion{P, dm, cnt});
+    if (!ccl_done) ulk_launch_list_phx<2>("CclUnion", fgl, nfg, dm, st, K_CclUnion{P, dm, cnt});
     CHK(ulk_memset(ctr, 0, 4 * sizeof(i32), st));
     ulk_launch_list_multi(fgl, nfg, st, K_FlattenCount{P, cnt, (i32 *)roots0, ctr});
     i32 hc[4];
