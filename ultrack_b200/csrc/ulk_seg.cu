@@ -395,16 +395,18 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     u8 *fmark = A.get<u8>(V + 8);
     i32 *cand = A.get<i32>(V), *cand2 = A.get<i32>(V);
     i32 *groots = A.get<i32>(V);
+    i32 *sroots = A.get<i32>(nfg);   // every supervertex root after the hook round
     i32 *ctr = A.get<i32>(8);        // [0] candidates [1] growing roots [2] scratch flag [4] basins [5] flow edges
     CHKA(A);
     CHK(ulk_memset(fmark, 0, (size_t)V + 8, st));
     CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
     ulk_launch_list_phx<1>("MinEdge", fgl, nfg, dm, st, K_MinEdge{lab, ct, dm, mw, pk});
     ulk_launch_list_phx<4>("Hook1", fgl, nfg, dm, st, K_Hook1{lab, mw, pk, dm, bp, state, Lr, best, ctr + 4});
-    ulk_launch_list_multi(fgl, nfg, st, K_CompressCand{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1});
+    ulk_launch_list_multi(fgl, nfg, st, K_CompressCand{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1, sroots, ctr + 6});
     i32 hc[8];
     CHK(ulk_read(hc, ctr, 8, st));
     i32 ncand = hc[0], ng = hc[1];
+    const i32 nsroots = hc[6];
     // every growing root hooks at most once: that bounds the flow-edge list
     const i32 flow_cap = ng;
     i32 *groots2 = A.get<i32>(ng), *tgt = A.get<i32>(ng);
@@ -438,7 +440,9 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     CHKA(A);
     CHK(ulk_memset(ctr, 0, sizeof(i32), st));
     CHK(ulk_memset(lab_hist, 0, (size_t)(R + 1) * sizeof(i32), st));
-    ulk_launch_list_multi(fgl, nfg, st, K_CompressRoots{bp, lab, rootkeys, ctr + 0});
+    // the flow rounds re-hooked roots only: flattening the root list is enough
+    ulk_launch_list_multi(sroots, nsroots, st, K_CompressRoots{bp, lab, rootkeys, ctr + 0});
+    A.release(sroots);
     CHK(ulk_sort_keys_u64(rootkeys, rootsorted, B, st));
     u32 *gid_at_root = best;         // free after the flow rounds
     ulk_launch(B, st, K_BasinRegroup{rootsorted, Lr, gid_at_root, out.g_root, out.g_lab, out.g_L, lab_hist});

@@ -387,7 +387,7 @@ ULK_D ULK_INLINE void ulk_warp_append(bool flag, i32 value, i32 *list, i32 *coun
 // roots, and candidates = voxels whose steepest weight equals their supervertex level
 struct K_CompressCand {
     i32 *bp; const u32 *mw; const u32 *Lr; const u8 *state;
-    i32 *cand; i32 *ncand; i32 *groots; i32 *ngroots;
+    i32 *cand; i32 *ncand; i32 *groots; i32 *ngroots; i32 *sroots; i32 *nsroots;
 #ifdef ULK_EMU
     void operator()(i64 vv, i32, i32, i32) const
     {
@@ -395,24 +395,11 @@ struct K_CompressCand {
         if (bp[v] < 0) return;
         i32 r = ulk_vfind(bp, v);
         bp[v] = r;
+        if (r == v) sroots[(*nsroots)++] = v;
         if (r == v && state[v] == 0) groots[(*ngroots)++] = v;
         if (state[r] == 0 && mw[v] == Lr[r]) cand[(*ncand)++] = v;
     }
 #else
-    ULK_D void warp(i64 vv, i32, i32, i32, bool valid) const
-    {
-        i32 v = (i32)vv;
-        bool is_groot = false, is_cand = false;
-        if (valid && bp[v] >= 0) {
-            i32 r = ulk_vfind(bp, v);
-            bp[v] = r;
-            bool growing = state[r] == 0;
-            is_groot = r == v && growing;
-            is_cand = growing && mw[v] == Lr[r];
-        }
-        ulk_warp_append(is_groot, v, groots, ngroots);
-        ulk_warp_append(is_cand, v, cand, ncand);
-    }
     ULK_D void multi(const i32 (&v)[ULK_MULTI], const bool (&ok)[ULK_MULTI]) const
     {
         i32 r[ULK_MULTI];
@@ -425,8 +412,10 @@ struct K_CompressCand {
             if (r[u] >= 0) { bp[v[u]] = r[u]; st[u] = state[r[u]]; m[u] = mw[v[u]]; L[u] = Lr[r[u]]; }
 #pragma unroll
         for (int u = 0; u < ULK_MULTI; ++u) {
+            const bool root = r[u] >= 0 && r[u] == v[u];
             const bool growing = r[u] >= 0 && st[u] == 0;
-            ulk_warp_append(growing && r[u] == v[u], v[u], groots, ngroots);
+            ulk_warp_append(root, v[u], sroots, nsroots);
+            ulk_warp_append(growing && root, v[u], groots, ngroots);
             ulk_warp_append(growing && m[u] == L[u], v[u], cand, ncand);
         }
     }
@@ -549,14 +538,16 @@ struct K_BasinRegroup {      // sorted position = global basin id
         ulk_atomic_add(&lab_hist[l - 1], 1);
     }
 };
+// bp[v] is the supervertex root of v (K_CompressCand) and bp[root] the basin root
+// (K_CompressRoots on the root list): two hops, then the basin id
 struct K_AssignBasin {     // background stays at the memset value -1
     const i32 *bp; const u32 *gid_at_root;
     i32 *bas;
     struct S1 { i32 v, r; };
-    struct S2 { i32 v, g; };
+    struct S2 { i32 v, rr; };
     ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32, bool ok) const { S1 s; s.v = ok ? v : -1; s.r = ok ? bp[v] : -1; return s; }
-    ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const { S2 s; s.v = a.v; s.g = a.r < 0 ? -1 : (i32)gid_at_root[a.r]; return s; }
-    ULK_D ULK_INLINE void run(const S2 &s, bool) const { if (s.v >= 0) bas[s.v] = s.g; }
+    ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const { S2 s; s.v = a.v; s.rr = a.r < 0 ? -1 : bp[a.r]; return s; }
+    ULK_D ULK_INLINE void run(const S2 &s, bool) const { if (s.v >= 0) bas[s.v] = s.rr < 0 ? -1 : (i32)gid_at_root[s.rr]; }
 };
 // flow edges are spanning-tree edges of the basin of their supervertex
 struct K_FlowTop {
