@@ -321,6 +321,7 @@ def main():
         n_fg = int(f.stats.n_foreground)
         n_fg_a = int(f.stats.pass_a_voxels)
         stats["n_foreground"], stats["pass_a_voxels"] = n_fg, n_fg_a
+        stats["k3_voxels"] = int(f.stats.k3_voxels)
 
         # ---- e2e: the same steps from pinned HOST buffers through the ingest API segment() uses
         # (ulk_upload_begin of frame i+1 before ulk_segment_frame_uploaded of frame i), node

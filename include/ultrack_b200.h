@@ -53,6 +53,7 @@ typedef struct ulk_seg_stats {
     int32_t flow_rounds, k3_rounds;
     int64_t n_foreground;        /* voxels above the threshold                                    */
     int64_t pass_a_voxels;       /* voxels of components above max_area (oversegmentation pass)   */
+    int64_t k3_voxels;           /* voxels of basins whose raster-key bottleneck needed a check   */
 } ulk_seg_stats;
 
 /* Candidate nodes of one frame, device-resident struct of arrays.  Node order is the

@@ -38,8 +38,8 @@ def test_struct_layouts_match_header():
     assert C.sizeof(_lib.SegParams) == 48
     assert C.sizeof(_lib.LinkParams) == 48
     assert C.sizeof(_lib.Links) == 40
-    assert C.sizeof(_lib.SegStats) == 48
-    assert C.sizeof(_lib.FrameNodes) == 40 + 12 * 8 + 48
+    assert C.sizeof(_lib.SegStats) == 56
+    assert C.sizeof(_lib.FrameNodes) == 40 + 12 * 8 + 56
 
 
 def test_product_path_fails_loudly_without_gpu(monkeypatch):

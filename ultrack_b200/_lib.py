@@ -32,7 +32,8 @@ class SegParams(C.Structure):
 class SegStats(C.Structure):
     _fields_ = [("n_basins", C.c_int64), ("n_rag_edges", C.c_int64), ("plateau_voxels", C.c_int64),
                 ("flow_rounds", C.c_int32), ("k3_rounds", C.c_int32),
-                ("n_foreground", C.c_int64), ("pass_a_voxels", C.c_int64)]
+                ("n_foreground", C.c_int64), ("pass_a_voxels", C.c_int64),
+                ("k3_voxels", C.c_int64)]
 
 
 class FrameNodes(C.Structure):

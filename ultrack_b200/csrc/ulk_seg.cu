@@ -458,13 +458,14 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     i32 *hp = nullptr;
     out.mw = mw;
     if (need_join) { out.jk = A.get<u32>(V); hp = A.get<i32>(V); }
-    if (need_k3) out.b_k3 = A.get<u32>(B);
+    u32 *Tk = nullptr;
+    if (need_k3) { out.b_k3 = A.get<u32>(B); Tk = A.get<u32>(B); }
     CHKA(A);
     CHK(ulk_memset(out.b_size, 0, (size_t)B * sizeof(i32), st));
     CHK(ulk_memset(out.b_top, 0, (size_t)B * sizeof(u64), st));
     CHK(ulk_memset(ncross, 0, sizeof(u64), st));
     CHK(ulk_memset(ctr, 0, 4 * sizeof(i32), st));
-    if (need_k3) CHK(ulk_memset(out.b_k3, 0, (size_t)B * sizeof(u32), st));
+    if (need_k3) { CHK(ulk_memset(out.b_k3, 0, (size_t)B * sizeof(u32), st)); CHK(ulk_memset(Tk, 0, (size_t)B * sizeof(u32), st)); }
     if (need_stats) {
         ulk_fill<i32>(out.bbmin, 0x7fffffff, 3 * (i64)B, st);
         ulk_fill<i32>(out.bbmax, -0x7fffffff, 3 * (i64)B, st);
@@ -473,8 +474,8 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     ulk_launch_list_phx<2>("BasinAccum", fgl, nfg, dm, st, K_BasinAccum{out.bas, lab, mw, pk, dm, out.b_size, out.b_top, ncross,
                                         need_stats ? 1 : 0, out.bbmin, out.bbmax, out.csum,
                                         need_join ? 1 : 0, out.g_L, out.jk, hp, ctr + 0,
-                                        need_k3 ? 1 : 0, out.b_k3});
-    ulk_launch(nflow, st, K_FlowTop{flow_root, flow_key, out.bas, ct, dm, out.b_top});
+                                        need_k3 ? 1 : 0, out.b_k3, Tk});
+    ulk_launch(nflow, st, K_FlowTop{flow_root, flow_key, out.bas, ct, dm, out.b_top, Tk});
     A.release(flow_root); A.release(flow_key);
     u64 h_ncross = 0;
     CHK(ulk_read(&h_ncross, ncross, 1, st));
@@ -555,13 +556,30 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
         i32 *P3 = bp;          // basin forest no longer needed
         i32 *nroot = A.get<i32>(B);
         CHKA(A);
-        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_K3Init{out.bas, out.b_k3, P3});
-        ulk_launch_list_phx<4>("K3Union", fgl, nfg, dm, st, K_K3Union{out.bas, dm, out.b_k3, P3});
+        // only basins with a spanning-tree edge above K0 need the connectivity check; their voxels
+        // form the list the check runs on (K_K3Need writes its marks into nroot)
+        CHK(ulk_memset(ctr, 0, sizeof(i32), st));
+        ulk_launch(B, st, K_K3Need{Tk, out.b_k3, nroot, ctr + 0});
+        CHK(ulk_read(hc, ctr, 1, st));
+        const i32 *kl = fgl;
+        i64 nkl = hc[0] > 0 ? nfg : 0;
+        i32 *klist = nullptr, *nkl_dev = nullptr;
+        if (hc[0] > 0 && hc[0] < B && !getenv("ULK_K3_ALL")) {
+            klist = A.get<i32>(nfg); nkl_dev = A.get<i32>(1);
+            CHKA(A);
+            CHK(ulk_select_list_split_i32(fgl, nfg, out.bas, nroot, klist, nkl_dev, st));
+            i32 n = 0;
+            CHK(ulk_read(&n, nkl_dev, 1, st));
+            kl = klist; nkl = n;
+        }
+        if (stats) stats->k3_voxels += nkl;
+        ulk_launch_list_ph<4>(kl, nkl, dm, st, K_K3Init{out.bas, out.b_k3, P3});
+        ulk_launch_list_phx<4>("K3Union", kl, nkl, dm, st, K_K3Union{out.bas, dm, out.b_k3, P3});
         // basins that edges <= K0 leave split (rare) go on with Boruvka rounds on THEIR voxels only
-        const i32 *cur = fgl;
-        i64 ncur = nfg;
+        const i32 *cur = kl;
+        i64 ncur = nkl;
         i32 *sub = nullptr, *nsub_dev = nullptr;
-        for (int it = 0;; ++it) {
+        for (int it = 0; nkl > 0; ++it) {
             CHK(ulk_memset(nroot, 0, (size_t)B * sizeof(i32), st));
             CHK(ulk_memset(ctr, 0, sizeof(i32), st));
             ulk_launch_list_multi(cur, ncur, st, K_K3FlattenCount{out.bas, P3, nroot, ctr + 0});
@@ -571,7 +589,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
             if (it == 0) {
                 sub = A.get<i32>(nfg); nsub_dev = A.get<i32>(1);
                 CHKA(A);
-                CHK(ulk_select_list_split_i32(fgl, nfg, out.bas, nroot, sub, nsub_dev, st));
+                CHK(ulk_select_list_split_i32(kl, nkl, out.bas, nroot, sub, nsub_dev, st));
                 i32 nsub = 0;
                 CHK(ulk_read(&nsub, nsub_dev, 1, st));
                 cur = sub; ncur = nsub;
@@ -582,6 +600,8 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
             if (it > 100000) ULK_FAIL(-4, "bottleneck rounds did not converge");
         }
         if (sub) { A.release(sub); A.release(nsub_dev); }
+        if (klist) { A.release(klist); A.release(nkl_dev); }
+        A.release(Tk);
         A.release(nroot);
     }
     A.release(pk); A.release(state); A.release(Lr); A.release(best); A.release(fmark);

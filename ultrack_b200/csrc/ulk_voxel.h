@@ -551,12 +551,26 @@ struct K_AssignBasin {     // background stays at the memset value -1
 };
 // flow edges are spanning-tree edges of the basin of their supervertex
 struct K_FlowTop {
-    const i32 *flow_root; const u32 *flow_key; const i32 *bas; UlkCt ct; UlkDims dm; u64 *b_top;
+    const i32 *flow_root; const u32 *flow_key; const i32 *bas; UlkCt ct; UlkDims dm; u64 *b_top; u32 *Tk;
     ULK_D void operator()(i64 j) const
     {
         u32 fk = flow_key[j];
         i32 a = (i32)(fk / 3u), e = a + dm.stride((int)(fk % 3u));
-        ulk_atomic_max(&b_top[bas[flow_root[j]]], ((u64)ulk_f2ord(ct.w(a, e)) << 32) | fk);
+        i32 b = bas[flow_root[j]];
+        ulk_atomic_max(&b_top[b], ((u64)ulk_f2ord(ct.w(a, e)) << 32) | fk);
+        if (Tk) ulk_atomic_max(&Tk[b], fk);
+    }
+};
+// A basin whose spanning-tree edges (steepest edges + flow edges) all carry raster keys <= K0 is
+// connected by edges <= K0: its bottleneck IS K0 and it needs no union-find check.  need[b] = 2
+// marks the others (the value the split-list selection tests for).
+struct K_K3Need {
+    const u32 *Tk, *K0; i32 *need; i32 *nneed;
+    ULK_D void operator()(i64 b) const
+    {
+        bool n = Tk[b] > K0[b];
+        need[b] = n ? 2 : 0;
+        if (n) ulk_atomic_add(nneed, 1);
     }
 };
 // One pass over the voxels once basin ids exist:
@@ -572,7 +586,7 @@ struct K_BasinAccum {
     i32 *b_size; u64 *b_top; u64 *ncross;
     int want_stats; i32 *bbmin, *bbmax; i64 *csum;
     int want_join; const u32 *b_L; u32 *jk; i32 *hp; i32 *nhp;
-    int want_k0; u32 *K0;
+    int want_k0; u32 *K0; u32 *Tk;      // Tk: largest raster key among the basin's steepest edges
     // phase 1: the voxel's own entries and its neighbours' basins (indices clamped at the border)
     struct S1 { i32 v, z, y, x, b, l; u32 m, k; i32 a[3], c[3]; };
     // phase 2: what depends on them -- the basin level, the weight across the steepest edge, the
@@ -637,6 +651,7 @@ struct K_BasinAccum {
         *ncross += o.nc;
         if (o.plateau) hp[(*nhp)++] = o.v;
         if (want_k0 && o.kmin != ULK_NONE32 && o.kmin > K0[b]) K0[b] = o.kmin;
+        if (want_k0 && o.top != 0 && (u32)o.top > Tk[b]) Tk[b] = (u32)o.top;
         if (want_stats) {
             const i32 c[3] = {o.z, o.y, o.x};
             for (int d = 0; d < 3; ++d) {
@@ -670,11 +685,11 @@ struct K_BasinAccum {
         const i32 n = __popc(grp);
         // the leader reads the accumulators it may have to update before the reductions start,
         // so those loads overlap them
-        u64 cur_top = 0; u32 cur_k0 = 0;
+        u64 cur_top = 0; u32 cur_k0 = 0, cur_tk = 0;
         i32 clo[3] = {0, 0, 0}, chi[3] = {0, 0, 0};
         if (lead) {
             cur_top = b_top[b];
-            if (want_k0) cur_k0 = K0[b];
+            if (want_k0) { cur_k0 = K0[b]; cur_tk = Tk[b]; }
             if (want_stats) {
                 clo[0] = bbmin[3 * b]; clo[1] = bbmin[3 * b + 1]; clo[2] = bbmin[3 * b + 2];
                 chi[0] = bbmax[3 * b]; chi[1] = bbmax[3 * b + 1]; chi[2] = bbmax[3 * b + 2];
@@ -682,8 +697,11 @@ struct K_BasinAccum {
         }
         u32 thi = __reduce_max_sync(grp, (u32)(o.top >> 32));
         u32 tlo = __reduce_max_sync(grp, (u32)(o.top >> 32) == thi ? (u32)o.top : 0u);
-        u32 km = 0;
-        if (want_k0) km = __reduce_max_sync(grp, o.kmin == ULK_NONE32 ? 0u : o.kmin);
+        u32 km = 0, tk = 0;
+        if (want_k0) {
+            km = __reduce_max_sync(grp, o.kmin == ULK_NONE32 ? 0u : o.kmin);
+            tk = __reduce_max_sync(grp, o.top != 0 ? (u32)o.top : 0u);
+        }
         i32 x1 = x; u32 sx = 0;
         if (want_stats) {
             x1 = __shfl_sync(grp, x, 31 - __clz(grp));                 // x of the run's last lane
@@ -695,6 +713,7 @@ struct K_BasinAccum {
         const u64 t = ((u64)thi << 32) | tlo;
         if (t > cur_top) atomicMax((unsigned long long *)&b_top[b], (unsigned long long)t);
         if (want_k0 && km > cur_k0) atomicMax(&K0[b], km);
+        if (want_k0 && tk > cur_tk) atomicMax(&Tk[b], tk);
         if (want_stats) {
             const i32 z = o.z, y = o.y;
             i32 *lo = bbmin + 3 * b, *hi = bbmax + 3 * b;
