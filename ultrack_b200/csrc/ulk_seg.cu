@@ -458,6 +458,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     i32 *hp = nullptr;
     out.mw = mw;
     if (need_join) { out.jk = A.get<u32>(V); hp = A.get<i32>(V); }
+    i32 *xl = A.get<i32>(nfg);       // voxels on a boundary between basins of one region
     u32 *Tk = nullptr;
     if (need_k3) { out.b_k3 = A.get<u32>(B); Tk = A.get<u32>(B); }
     CHKA(A);
@@ -474,14 +475,15 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     ulk_launch_list_phx<2>("BasinAccum", fgl, nfg, dm, st, K_BasinAccum{out.bas, lab, mw, pk, dm, out.b_size, out.b_top, ncross,
                                         need_stats ? 1 : 0, out.bbmin, out.bbmax, out.csum,
                                         need_join ? 1 : 0, out.g_L, out.jk, hp, ctr + 0,
-                                        need_k3 ? 1 : 0, out.b_k3, Tk});
+                                        need_k3 ? 1 : 0, out.b_k3, Tk, xl, ctr + 1});
     ulk_launch(nflow, st, K_FlowTop{flow_root, flow_key, out.bas, ct, dm, out.b_top, Tk});
     A.release(flow_root); A.release(flow_key);
     u64 h_ncross = 0;
     CHK(ulk_read(&h_ncross, ncross, 1, st));
+    CHK(ulk_read(hc, ctr, 4, st));
+    const i32 nxl = hc[1];
     if (need_join) {
         // plateau voxels above their basin level: minimax relaxation along spanning-tree edges
-        CHK(ulk_read(hc, ctr, 4, st));
         i32 nhp = hc[0];
         if (stats) stats->plateau_voxels += nhp;
         int it = 0;
@@ -509,7 +511,8 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     CHK(ulk_memset(T.cnt, 0, cap * 4, st));
     CHK(ulk_memset(T.shi, 0, cap * 8, st));
     CHK(ulk_memset(T.slo, 0, cap * 8, st));
-    ulk_launch_list_phx<1>("RagInsert", fgl, nfg, dm, st, K_RagInsert{out.bas, lab, ct, dm, T, fixscale});
+    ulk_launch_list_phx<1>("RagInsert", xl, nxl, dm, st, K_RagInsert{out.bas, lab, ct, dm, T, fixscale});
+    A.release(xl);
     i32 *eflag = A.get<i32>((i64)cap + 1), *epre = A.get<i32>((i64)cap + 1);
     CHKA(A);
     ulk_launch((i64)cap, st, K_RagFlag{T.key, eflag});

@@ -587,6 +587,7 @@ struct K_BasinAccum {
     int want_stats; i32 *bbmin, *bbmax; i64 *csum;
     int want_join; const u32 *b_L; u32 *jk; i32 *hp; i32 *nhp;
     int want_k0; u32 *K0; u32 *Tk;      // Tk: largest raster key among the basin's steepest edges
+    i32 *xl; i32 *nxl;                  // voxels with a forward edge into another basin of their region
     // phase 1: the voxel's own entries and its neighbours' basins (indices clamped at the border)
     struct S1 { i32 v, z, y, x, b, l; u32 m, k; i32 a[3], c[3]; };
     // phase 2: what depends on them -- the basin level, the weight across the steepest edge, the
@@ -649,6 +650,7 @@ struct K_BasinAccum {
         b_size[b] += 1;
         if (o.top > b_top[b]) b_top[b] = o.top;
         *ncross += o.nc;
+        if (o.nc) xl[(*nxl)++] = o.v;
         if (o.plateau) hp[(*nhp)++] = o.v;
         if (want_k0 && o.kmin != ULK_NONE32 && o.kmin > K0[b]) K0[b] = o.kmin;
         if (want_k0 && o.top != 0 && (u32)o.top > Tk[b]) Tk[b] = (u32)o.top;
@@ -672,6 +674,7 @@ struct K_BasinAccum {
         const i32 b = o.b, v = o.v, x = o.x;
         u32 nct = __reduce_add_sync(0xffffffffu, o.nc);
         if (lane == 0 && nct) atomicAdd((unsigned long long *)ncross, (unsigned long long)nct);
+        if (nct) ulk_warp_append(o.nc > 0, v, xl, nxl);
         if (want_join) {
             if (b >= 0) jk[v] = o.jkv;
             ulk_warp_append(o.plateau, v, hp, nhp);
