@@ -20,7 +20,7 @@ from typing import Dict, Optional
 
 # kernel name (as reported by ulk_profile_report) -> bytes per frame voxel per launch (float32 inputs)
 DENSE_BYTES_PER_VOXEL: Dict[str, float] = {
-    "K_Threshold": 4 + 4 + 4 + 0.125,    # fg, ct in; component forest + one foreground bit out (float32 contours are not staged)
+    "K_Threshold": 4 + 4 + 0.125,        # fg in; component forest + one foreground bit out (float32 contours are neither staged nor read here)
 }
 # kernel name -> bytes per FOREGROUND voxel per launch (including the 4-byte list entry)
 LIST_BYTES_PER_FG_VOXEL: Dict[str, float] = {

@@ -190,7 +190,7 @@ ulk_threshold_kernel(K_Threshold k, i32 W, u32 S, u32 ntask, u32 *words)
         i32 x = (i32)sg * 32 + lane;
         valid[u] = t0 + u < ntask && x < W;
         v[u] = (i64)r * W + x;
-        if (F32 && valid[u]) { f[u] = ((const float *)k.fg)[v[u]]; c[u] = ((const float *)k.ct)[v[u]]; }
+        if (F32 && valid[u]) { f[u] = ((const float *)k.fg)[v[u]]; c[u] = k.skip_ct ? 0.f : ((const float *)k.ct)[v[u]]; }
         if (++sg == S) { sg = 0; ++r; }
     }
     u32 mx = 0;
@@ -202,7 +202,7 @@ ulk_threshold_kernel(K_Threshold k, i32 W, u32 S, u32 ntask, u32 *words)
             if (F32) {
                 on = (double)f[u] > k.thr;
                 float a = fabsf(c[u]);
-                if (a <= 3.0e38f) bits = __float_as_uint(a);
+                if (!k.skip_ct && a <= 3.0e38f) bits = __float_as_uint(a);
             } else on = k.stage(v[u], bits);
         }
         mx = bits > mx ? bits : mx;
@@ -219,7 +219,7 @@ ulk_threshold_kernel(K_Threshold k, i32 W, u32 S, u32 ntask, u32 *words)
 // voxels of each volume with one 128-bit load, a warp covers four 32-voxel row segments; the
 // foreground word of a segment is the OR of its eight lanes' nibbles, and the run starts of a
 // lane's voxels follow from that word alone (linked = word & word << 1)
-template <int U> __global__ void __launch_bounds__(256)
+template <int U, bool CT> __global__ void __launch_bounds__(256)
 ulk_threshold_kernel_v4(K_Threshold k, i32 W, u32 S, u32 T, u32 ntask4, u32 *words)
 {
     const int lane = threadIdx.x & 31;
@@ -233,7 +233,10 @@ ulk_threshold_kernel_v4(K_Threshold k, i32 W, u32 S, u32 T, u32 ntask4, u32 *wor
         valid[u] = t0 + u < ntask4 && x < W;
         v[u] = (i64)r * W + x;
         wbase[u] = r * S + q * 4u;
-        if (valid[u]) { f[u] = *(const float4 *)((const float *)k.fg + v[u]); c[u] = *(const float4 *)((const float *)k.ct + v[u]); }
+        if (valid[u]) {
+            f[u] = *(const float4 *)((const float *)k.fg + v[u]);
+            if (CT) c[u] = *(const float4 *)((const float *)k.ct + v[u]);
+        }
         if (++q == T) { q = 0; ++r; }
     }
     u32 mx = 0;
@@ -242,12 +245,14 @@ ulk_threshold_kernel_v4(K_Threshold k, i32 W, u32 S, u32 T, u32 ntask4, u32 *wor
         u32 nib = 0;
         if (valid[u]) {
             nib = ((double)f[u].x > k.thr ? 1u : 0u) | ((double)f[u].y > k.thr ? 2u : 0u) | ((double)f[u].z > k.thr ? 4u : 0u) | ((double)f[u].w > k.thr ? 8u : 0u);
-            const float a0 = fabsf(c[u].x), a1 = fabsf(c[u].y), a2 = fabsf(c[u].z), a3 = fabsf(c[u].w);
-            u32 b;
-            b = a0 <= 3.0e38f ? __float_as_uint(a0) : 0u; mx = b > mx ? b : mx;
-            b = a1 <= 3.0e38f ? __float_as_uint(a1) : 0u; mx = b > mx ? b : mx;
-            b = a2 <= 3.0e38f ? __float_as_uint(a2) : 0u; mx = b > mx ? b : mx;
-            b = a3 <= 3.0e38f ? __float_as_uint(a3) : 0u; mx = b > mx ? b : mx;
+            if (CT) {
+                const float a0 = fabsf(c[u].x), a1 = fabsf(c[u].y), a2 = fabsf(c[u].z), a3 = fabsf(c[u].w);
+                u32 b;
+                b = a0 <= 3.0e38f ? __float_as_uint(a0) : 0u; mx = b > mx ? b : mx;
+                b = a1 <= 3.0e38f ? __float_as_uint(a1) : 0u; mx = b > mx ? b : mx;
+                b = a2 <= 3.0e38f ? __float_as_uint(a2) : 0u; mx = b > mx ? b : mx;
+                b = a3 <= 3.0e38f ? __float_as_uint(a3) : 0u; mx = b > mx ? b : mx;
+            }
         }
         const int sub = lane >> 3, pos = (lane & 7) * 4;
         const u32 word = __reduce_or_sync(0xffu << (sub * 8), nib << pos);
@@ -263,8 +268,10 @@ ulk_threshold_kernel_v4(K_Threshold k, i32 W, u32 S, u32 T, u32 ntask4, u32 *wor
             if ((lane & 7) == 0) words[wbase[u] + sub] = word;
         }
     }
-    u32 m = __reduce_max_sync(0xffffffffu, mx);
-    if (lane == 0 && m > *k.cmax) atomicMax(k.cmax, m);
+    if (CT) {
+        u32 m = __reduce_max_sync(0xffffffffu, mx);
+        if (lane == 0 && m > *k.cmax) atomicMax(k.cmax, m);
+    }
 }
 __global__ void __launch_bounds__(256)
 ulk_expand_kernel(const u32 *words, const i32 *off, u32 ntask, i32 W, u32 S, UlkFastDiv fS, i32 *list, i32 *count)
@@ -339,7 +346,9 @@ static int threshold_and_list(ulk_stream_t st, UlkArena &A, const UlkDims &dm, c
         const i64 nt4 = (i64)dm.D * dm.H * T;
         const int U4 = 2;
         const i64 warps4 = (nt4 + U4 - 1) / U4;
-        ulk_threshold_kernel_v4<U4><<<(unsigned)((warps4 + 7) / 8), 256, 0, st>>>(k, dm.W, S, T, (u32)nt4, words);
+        const i64 warps4b = (nt4 + 3) / 4;
+        if (k.skip_ct) ulk_threshold_kernel_v4<4, false><<<(unsigned)((warps4b + 7) / 8), 256, 0, st>>>(k, dm.W, S, T, (u32)nt4, words);
+        else ulk_threshold_kernel_v4<U4, true><<<(unsigned)((warps4 + 7) / 8), 256, 0, st>>>(k, dm.W, S, T, (u32)nt4, words);
     } else if (k.fgt == ULK_F32 && k.ctt == ULK_F32) {
         if (U == 8) ulk_threshold_kernel<8, true><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
         else if (U == 2) ulk_threshold_kernel<2, true><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
@@ -372,6 +381,16 @@ static int threshold_and_list(ulk_stream_t st, UlkArena &A, const UlkDims &dm, c
 #endif
 }
 
+// fixed-point position for the frontier sums: 2^e2 > max |contour| + 1, sums scaled by 2^(62-e2)
+static int ulk_fix_shift_for(u32 cmax_bits)
+{
+    float cmaxf;
+    memcpy(&cmaxf, &cmax_bits, 4);
+    int e2 = 0;
+    while (ldexp(1.0, e2) <= (double)cmaxf + 1.0) ++e2;
+    return 62 - e2;
+}
+
 // ------------------------------------------------------------------ voxel stage
 struct VoxelStage {
     i32 *bas = nullptr; i32 B = 0; i32 Eg = 0;
@@ -384,9 +403,12 @@ struct VoxelStage {
 };
 
 static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i32 *fgl, i64 nfg, const UlkCt &ct, const i32 *lab,
-                       i32 R, bool need_join, bool need_k3, bool need_stats, double fixscale,
+                       i32 R, bool need_join, bool need_k3, bool need_stats, u32 *cmax_late, int *fix_shift,
                        VoxelStage &out, ulk_seg_stats *stats)
 {
+    // cmax_late != null: max |ct| over this stage's voxels is found by K_MinEdge and *fix_shift is
+    // derived from it here; otherwise *fix_shift comes from the caller (K_Threshold saw every voxel)
+    double fixscale = ldexp(1.0, *fix_shift);
     const i64 V = dm.V;
     u32 *mw = A.get<u32>(V), *pk = A.get<u32>(V);
     i32 *bp = A.get<i32>(V);
@@ -400,13 +422,20 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     CHKA(A);
     CHK(ulk_memset(fmark, 0, (size_t)V + 8, st));
     CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
-    ulk_launch_list_phx<1>("MinEdge", fgl, nfg, dm, st, K_MinEdge{lab, ct, dm, mw, pk});
+    if (cmax_late) CHK(ulk_memset(cmax_late, 0, sizeof(u32), st));
+    ulk_launch_list_phx<1>("MinEdge", fgl, nfg, dm, st, K_MinEdge{lab, ct, dm, mw, pk, cmax_late});
     ulk_launch_list_phx<4>("Hook1", fgl, nfg, dm, st, K_Hook1{lab, mw, pk, dm, bp, state, Lr, best, ctr + 4});
     ulk_launch_list_multi(fgl, nfg, st, K_CompressCand{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1, sroots, ctr + 6});
     i32 hc[8];
     CHK(ulk_read(hc, ctr, 8, st));
     i32 ncand = hc[0], ng = hc[1];
     const i32 nsroots = hc[6];
+    if (cmax_late) {
+        u32 h_cmax = 0;
+        CHK(ulk_read(&h_cmax, cmax_late, 1, st));
+        *fix_shift = ulk_fix_shift_for(h_cmax);
+        fixscale = ldexp(1.0, *fix_shift);
+    }
     // every growing root hooks at most once: that bounds the flow-edge list
     const i32 flow_cap = ng;
     i32 *groots2 = A.get<i32>(ng), *tgt = A.get<i32>(ng);
@@ -447,7 +476,8 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     u32 *gid_at_root = best;         // free after the flow rounds
     ulk_launch(B, st, K_BasinRegroup{rootsorted, Lr, gid_at_root, out.g_root, out.g_lab, out.g_L, lab_hist});
     CHK(ulk_exclusive_scan_i32(lab_hist, out.bs, R + 1, st));
-    CHK(ulk_memset(out.bas, 0xff, (size_t)V * sizeof(i32), st));
+    if (nfg * 8 < V) ulk_launch_list(fgl, nfg, dm, st, K_ClearHalo{lab, dm, out.bas});   // short list (pass A): clear its halo only
+    else CHK(ulk_memset(out.bas, 0xff, (size_t)V * sizeof(i32), st));
     ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_AssignBasin{bp, gid_at_root, out.bas});
     A.release(rootkeys); A.release(rootsorted);
 
@@ -685,7 +715,10 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     i32 *cnt = A.get<i32>(V);            // sizes at the roots, later the component code at the roots
     CHKA(A);
     bool ccl_done = false;
-    CHK(threshold_and_list(st, A, dm, K_Threshold{fg, fg_dtype, prm->threshold, ctp, ct_dtype, ctf, ctd, P, cmax}, fgl, nfg_dev, cnt, &ccl_done));
+    // float32 contours are never staged: K_Threshold does not read them at all, the bound on the
+    // edge weights comes from K_MinEdge (region voxels only)
+    const bool late_cmax = ct_dtype == ULK_F32 && !getenv("ULK_CMAX_EARLY");
+    CHK(threshold_and_list(st, A, dm, K_Threshold{fg, fg_dtype, prm->threshold, ctp, ct_dtype, ctf, ctd, P, cmax, late_cmax ? 1 : 0}, fgl, nfg_dev, cnt, &ccl_done));
     // ---- connected components (4/6-connected): union of runs, flatten + sizes + root list
     i32 nfg = 0;
     CHK(ulk_read(&nfg, nfg_dev, 1, st));
@@ -703,12 +736,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     CHK(ulk_read(&h_cmax, cmax, 1, st));
     const i32 n_roots = hc[0];
     const i32 max_area_i = prm->max_area > 2147483646.0 ? 2147483646 : (i32)prm->max_area;
-    float cmaxf;
-    memcpy(&cmaxf, &h_cmax, 4);
-    int e2 = 0;
-    while (ldexp(1.0, e2) <= (double)cmaxf + 1.0) ++e2;
-    const int fix_shift = 62 - e2;
-    const double fixscale = ldexp(1.0, fix_shift);
+    int fix_shift = ulk_fix_shift_for(h_cmax);
     F->fix_shift = fix_shift;
     if (n_roots == 0) { F->n_nodes = 0; F->stats = stats_local; return 0; }
     // ---- per-component decisions on the (sorted) root list: small-object removal
@@ -755,7 +783,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         CHK(ulk_read(&nfgA, nfgA_dev, 1, st));
         stats_local.pass_a_voxels = nfgA;
         VoxelStage va;
-        CHK(voxel_stage(st, AA, dm, fglA, nfgA, ct, labA, n_big, true, false, false, fixscale, va, &stats_local));
+        CHK(voxel_stage(st, AA, dm, fglA, nfgA, ct, labA, n_big, true, false, false, late_cmax ? cmax : nullptr, &fix_shift, va, &stats_local));
         UlkHierScratch S;
         CHK(alloc_scratch(AA, va.B, va.Eg, S));
         UlkBasins Bv{va.b_size, va.g_L, va.b_top, nullptr, nullptr, nullptr, nullptr};
@@ -802,7 +830,8 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     // ---- pass B: the configured hierarchy on every region
     const bool area_mode = prm->ws_hierarchy == 0;
     VoxelStage vb;
-    CHK(voxel_stage(st, A, dm, fgl, nfg, ct, lab2, R, area_mode, true, true, fixscale, vb, &stats_local));
+    CHK(voxel_stage(st, A, dm, fgl, nfg, ct, lab2, R, area_mode, true, true, late_cmax ? cmax : nullptr, &fix_shift, vb, &stats_local));
+    F->fix_shift = fix_shift;
     UlkHierScratch S;
     CHK(alloc_scratch(A, vb.B, vb.Eg, S));
     UlkBasins Bv{vb.b_size, vb.g_L, vb.b_top, vb.b_k3, vb.bbmin, vb.bbmax, vb.csum};

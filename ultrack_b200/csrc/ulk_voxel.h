@@ -91,13 +91,16 @@ struct K_Threshold {
     const void *ct; int ctt;
     float *ctf; double *ctd;
     i32 *P; u32 *cmax;
+    int skip_ct;      // float32 contours are read in place later: K_MinEdge finds max |ct| over the regions
     ULK_D ULK_INLINE bool stage(i64 v, u32 &bits) const
     {
         double f = ulk_load_as_double(fg, fgt, v);
         bits = 0;
         if (ctt == ULK_F32) {       // read in place, never staged
-            float a = fabsf(((const float *)ct)[v]);
-            if (a <= 3.0e38f) memcpy(&bits, &a, 4);
+            if (!skip_ct) {
+                float a = fabsf(((const float *)ct)[v]);
+                if (a <= 3.0e38f) memcpy(&bits, &a, 4);
+            }
             return f > thr;
         }
         double c = ulk_load_as_double(ct, ctt, v);
@@ -271,6 +274,7 @@ struct K_FlagRoots {
 struct K_MinEdge {
     const i32 *lab; UlkCt ct; UlkDims dm;
     u32 *mw, *pk;
+    u32 *cmax;        // when set (float32 contours): max |ct| over the voxels of the regions, as float bits
     // neighbour indices clamped to v at the frame border: all loads are issued together
     struct S1 { i32 v, l; u32 h; i32 ln[6]; float c, cn[6]; };
     typedef S1 S2;
@@ -283,7 +287,7 @@ struct K_MinEdge {
     ULK_D ULK_INLINE S1 load1(i32 v, i32 z, i32 y, i32 x, bool ok) const
     {
         S1 s;
-        s.v = v; s.l = 0; s.h = 0;
+        s.v = v; s.l = 0; s.h = 0; s.c = 0.f;
         if (!ok) return s;
         s.h = (z > 0 ? 1u : 0u) | (y > 0 ? 2u : 0u) | (x > 0 ? 4u : 0u) | (x + 1 < dm.W ? 8u : 0u) | (y + 1 < dm.H ? 16u : 0u) | (z + 1 < dm.D ? 32u : 0u);
         s.l = lab[v];
@@ -305,6 +309,16 @@ struct K_MinEdge {
     ULK_D ULK_INLINE void run(const S2 &s, bool) const
     {
         const i32 v = s.v, l = s.l;
+        if (cmax) {
+            u32 bits = 0;
+            if (l > 0) { float a = fabsf(s.c); if (a <= 3.0e38f) memcpy(&bits, &a, 4); }
+#ifdef ULK_EMU
+            if (bits > *cmax) *cmax = bits;
+#else
+            const u32 m = __reduce_max_sync(0xffffffffu, bits);
+            if ((threadIdx.x & 31) == 0 && m > *cmax) atomicMax(cmax, m);
+#endif
+        }
         if (l <= 0) return;          // mw / pk are only ever read where lab > 0
         u32 bw = ULK_NONE32, bk = ULK_NONE32;
 #ifndef ULK_EMU
@@ -548,6 +562,20 @@ struct K_AssignBasin {     // background stays at the memset value -1
     ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32, bool ok) const { S1 s; s.v = ok ? v : -1; s.r = ok ? bp[v] : -1; return s; }
     ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const { S2 s; s.v = a.v; s.rr = a.r < 0 ? -1 : bp[a.r]; return s; }
     ULK_D ULK_INLINE void run(const S2 &s, bool) const { if (s.v >= 0) bas[s.v] = s.rr < 0 ? -1 : (i32)gid_at_root[s.rr]; }
+};
+// instead of a memset of the whole basin-id volume: -1 on the neighbours of the list's voxels
+// that are outside every region (the only entries outside the list a stencil kernel reads)
+struct K_ClearHalo {
+    const i32 *lab; UlkDims dm; i32 *bas;
+    ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
+    {
+        const i32 v = (i32)vv;
+        for (int d = 0; d < 3; ++d) {
+            const i32 st = dm.stride(d);
+            if (dm.bwd(d, z, y, x) && lab[v - st] <= 0) bas[v - st] = -1;
+            if (dm.fwd(d, z, y, x) && lab[v + st] <= 0) bas[v + st] = -1;
+        }
+    }
 };
 // flow edges are spanning-tree edges of the basin of their supervertex
 struct K_FlowTop {
