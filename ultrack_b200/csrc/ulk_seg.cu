@@ -592,7 +592,9 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
         // only basins with a spanning-tree edge above K0 need the connectivity check; their voxels
         // form the list the check runs on (K_K3Need writes its marks into nroot)
         CHK(ulk_memset(ctr, 0, sizeof(i32), st));
-        ulk_launch(B, st, K_K3Need{Tk, out.b_k3, nroot, ctr + 0});
+        i32 *needlist = A.get<i32>(B);
+        CHKA(A);
+        ulk_launch(B, st, K_K3Need{Tk, out.b_k3, nroot, ctr + 0, needlist});
         CHK(ulk_read(hc, ctr, 1, st));
         const i32 *kl = fgl;
         i64 nkl = hc[0] > 0 ? nfg : 0;
@@ -600,7 +602,12 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
         if (hc[0] > 0 && hc[0] < B && !getenv("ULK_K3_ALL")) {
             klist = A.get<i32>(nfg); nkl_dev = A.get<i32>(1);
             CHKA(A);
+#ifdef ULK_EMU
             CHK(ulk_select_list_split_i32(fgl, nfg, out.bas, nroot, klist, nkl_dev, st));
+#else
+            CHK(ulk_memset(nkl_dev, 0, sizeof(i32), st));
+            ulk_launch_warp((i64)hc[0] * 32, st, K_K3Collect{needlist, hc[0], out.bas, out.bbmin, out.bbmax, dm, klist, nkl_dev});
+#endif
             i32 n = 0;
             CHK(ulk_read(&n, nkl_dev, 1, st));
             kl = klist; nkl = n;
@@ -634,6 +641,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
         }
         if (sub) { A.release(sub); A.release(nsub_dev); }
         if (klist) { A.release(klist); A.release(nkl_dev); }
+        A.release(needlist);
         A.release(Tk);
         A.release(nroot);
     }
@@ -766,19 +774,20 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     // ---- region labels: components, oversegmented where area > max_area
     i32 R = n_cc;
     if (n_big == 0) {
-        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_LabelCc{code, cc_big, 0, lab2});
+        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_LabelCc{code, cc_big, 0, lab2, nullptr, nullptr});
     } else {
         UlkArena AA;
         // the labels of the oversegmentation pass live in place too: > 0 on the components above
         // max_area, negative everywhere else
         i32 *labA = lab2;
-        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_LabelCc{code, cc_big, 1, labA});
         // pass A only ever touches the voxels of the components above max_area: its kernels run
-        // on that sub-list (raster order kept), not on the whole foreground
+        // on that sub-list, collected while the labels are written (chunks of up to 32 raster-
+        // ordered voxels in arbitrary order: order only matters for coalescing)
         i32 *fglA = AA.get<i32>(nfg);
         i32 *nfgA_dev = AA.get<i32>(1);
         CHKA(AA);
-        CHK(ulk_select_list_pos_i32(fgl, nfg, labA, fglA, nfgA_dev, st));
+        CHK(ulk_memset(nfgA_dev, 0, sizeof(i32), st));
+        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_LabelCc{code, cc_big, 1, labA, fglA, nfgA_dev});
         i32 nfgA = 0;
         CHK(ulk_read(&nfgA, nfgA_dev, 1, st));
         stats_local.pass_a_voxels = nfgA;

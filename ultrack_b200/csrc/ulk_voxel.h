@@ -44,6 +44,19 @@ ULK_D ULK_INLINE void ulk_vunion(i32 *P, i32 a, i32 b)
 }
 
 #ifndef ULK_EMU
+// appends `value` of every lane with `flag` to a list: one atomic per warp
+ULK_D ULK_INLINE void ulk_warp_append(bool flag, i32 value, i32 *list, i32 *counter)
+{
+    u32 m = __ballot_sync(0xffffffffu, flag);
+    if (!m) return;
+    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+    i32 base = 0;
+    if (lane == leader) base = atomicAdd(counter, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (flag) list[base + __popc(m & ((1u << lane) - 1u))] = value;
+}
+#endif
+#ifndef ULK_EMU
 // lanes hold consecutive entries of a raster-ordered list, so lanes that share a key are almost
 // always neighbours: `heads` has a bit for every lane whose key differs from the lane below it;
 // returns the lane mask of the caller's run (runs need not be maximal groups -- a key that
@@ -246,6 +259,7 @@ struct K_RootCode {
 // of the oversegmentation pass), the other kept components -(index + 2), dropped ones -1.
 struct K_LabelCc {
     const i32 *code; const i32 *cc_big; int mode; i32 *lab;
+    i32 *biglist; i32 *nbig;       // mode 1: the voxels of the components above max_area (32-entry chunks in raster order)
     struct S1 { i32 v, r; };
     struct S2 { i32 v, c; };
     ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32, bool ok) const { S1 s; s.v = v; s.r = ok ? lab[v] : -1; return s; }
@@ -253,11 +267,22 @@ struct K_LabelCc {
     ULK_D ULK_INLINE void run(const S2 &s, bool) const
     {
         const i32 c = s.c;
-        if (c < 0) return;
-        if (mode == 0) { lab[s.v] = c; return; }
-        if (c == 0) { lab[s.v] = -1; return; }
-        i32 g = cc_big[c - 1];
-        lab[s.v] = g >= 0 ? g + 1 : -(c - 1) - 2;
+        i32 g = -1;
+        if (c >= 0) {
+            if (mode == 0) lab[s.v] = c;
+            else if (c == 0) lab[s.v] = -1;
+            else {
+                g = cc_big[c - 1];
+                lab[s.v] = g >= 0 ? g + 1 : -(c - 1) - 2;
+            }
+        }
+        if (mode == 1) {
+#ifdef ULK_EMU
+            if (g >= 0) biglist[(*nbig)++] = s.v;
+#else
+            ulk_warp_append(g >= 0, s.v, biglist, nbig);
+#endif
+        }
     }
 };
 struct K_FlagRoots {
@@ -384,19 +409,6 @@ struct K_Compress {
     i32 *bp;
     ULK_D void operator()(i64 v) const { if (bp[v] >= 0) bp[v] = ulk_vfind(bp, (i32)v); }
 };
-#ifndef ULK_EMU
-// appends `value` of every lane with `flag` to a list: one atomic per warp
-ULK_D ULK_INLINE void ulk_warp_append(bool flag, i32 value, i32 *list, i32 *counter)
-{
-    u32 m = __ballot_sync(0xffffffffu, flag);
-    if (!m) return;
-    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
-    i32 base = 0;
-    if (lane == leader) base = atomicAdd(counter, __popc(m));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (flag) list[base + __popc(m & ((1u << lane) - 1u))] = value;
-}
-#endif
 // path compression of the hook forest, fused with the lists of the flow rounds: growing
 // roots, and candidates = voxels whose steepest weight equals their supervertex level
 struct K_CompressCand {
@@ -593,14 +605,40 @@ struct K_FlowTop {
 // connected by edges <= K0: its bottleneck IS K0 and it needs no union-find check.  need[b] = 2
 // marks the others (the value the split-list selection tests for).
 struct K_K3Need {
-    const u32 *Tk, *K0; i32 *need; i32 *nneed;
+    const u32 *Tk, *K0; i32 *need; i32 *nneed; i32 *needlist;
     ULK_D void operator()(i64 b) const
     {
         bool n = Tk[b] > K0[b];
         need[b] = n ? 2 : 0;
-        if (n) ulk_atomic_add(nneed, 1);
+        if (n) needlist[ulk_atomic_add(nneed, 1)] = (i32)b;
     }
 };
+#ifndef ULK_EMU
+// the voxels of the basins that need the check, one warp per basin scanning its bounding box
+// row by row (x-runs of a basin stay contiguous in the list, which is all K_K3Init relies on)
+struct K_K3Collect {
+    const i32 *needlist; i64 nneed; const i32 *bas; const i32 *bbmin, *bbmax; UlkDims dm;
+    i32 *list; i32 *count;
+    ULK_D void warp(i64 ii, bool) const
+    {
+        const int lane = threadIdx.x & 31;
+        const i64 i = ii >> 5;
+        if (i >= nneed) return;
+        const i32 b = needlist[i];
+        const i32 z0 = bbmin[3 * b], y0 = bbmin[3 * b + 1], x0 = bbmin[3 * b + 2];
+        const i32 z1 = bbmax[3 * b], y1 = bbmax[3 * b + 1], x1 = bbmax[3 * b + 2];
+        for (i32 z = z0; z <= z1; ++z)
+            for (i32 y = y0; y <= y1; ++y) {
+                const i32 row = (z * dm.H + y) * dm.W;
+                for (i32 xb = x0; xb <= x1; xb += 32) {
+                    const i32 x = xb + lane;
+                    const bool hit = x <= x1 && bas[row + x] == b;
+                    ulk_warp_append(hit, row + x, list, count);
+                }
+            }
+    }
+};
+#endif
 // One pass over the voxels once basin ids exist:
 //  * per-basin size, largest spanning-tree key, bbox / coordinate sums, and the number of
 //    voxel edges between different basins of a region (sizes the adjacency hash table);
