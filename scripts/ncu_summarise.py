@@ -22,10 +22,17 @@ src = Path(sys.argv[2]) if len(sys.argv) > 2 else ROOT / "gpurun_out"
 prof = ROOT / "profiles"
 
 
+ALIAS = {"ulk_ccl_words_kernel": "K_CclWords", "ulk_expand_kernel": "K_ExpandForeground",
+         "ulk_threshold_kernel": "K_Threshold", "ulk_threshold_kernel_v4": "K_Threshold"}
+
+
 def short(name):
     m = re.search(r"(K_\w+(?:<[^>]*>)?)", name)
     if m:
         return m.group(1)
+    for k, v in ALIAS.items():
+        if re.search(r"\b" + k + r"\b", name):
+            return v
     return re.sub(r"^void |\(.*$", "", name)[:70]
 
 
