@@ -218,6 +218,8 @@ def main():
 
     torch.cuda.set_device(local_rank)
     if world > 1:
+        # NCCL's version / debug lines go to stderr: stdout carries exactly one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     lib = _lib.get_lib()
     _lib.check(lib, lib.ulk_set_device(local_rank))
