@@ -273,3 +273,47 @@ def test_full_size_properties(cuda_lib):
     assert np.bincount(t, minlength=n).max() <= 5
     cuda_lib.ulk_frame_nodes_free(h0)
     cuda_lib.ulk_frame_nodes_free(h1)
+
+
+def test_bench_recipe_against_oracle(cuda_lib):
+    """The bench's own recipe and parameters (variant S, radius 8, fill 0.3, min_area 100,
+    max_area 10000) on the sub-volume the CPU arm times: oversegmentation pass, 128-bit threshold
+    path (W % 4 == 0), bottleneck shortcut and boundary-voxel RAG all active, bit-exact vs oracle."""
+    from ultrack_b200 import synth
+    fg, ct, _ = synth.make_frame((40, 128, 128), t=3, seed=7, variant="S", radius=8.0, fill=0.3, motion=3.0, noise=1e-3)
+    n = cases.run_and_compare(cuda_lib, _seg_host, fg, ct, 3, min_area=100, max_area=10000, min_frontier=0.0)
+    assert n > 20
+
+
+def test_shortcuts_equal_exhaustive_forms(cuda_lib, monkeypatch):
+    """The data-dependent shortcuts (bottleneck check only where a spanning-tree key exceeds K0,
+    components from the foreground bit words, weight bound from K_MinEdge, 128-bit threshold) give
+    the same node tables as the exhaustive per-voxel forms they replace, on a frame far beyond the
+    oracle's reach (128x256x256)."""
+    import torch
+    from tests.emu_harness import seg_params
+    from ultrack_b200 import _lib
+    from ultrack_b200.segment import segment_frame_device
+    shape = (128, 256, 256)
+    fg = torch.empty(shape, dtype=torch.float32, device="cuda")
+    ct = torch.empty(shape, dtype=torch.float32, device="cuda")
+    shp = (C.c_int64 * 3)(*shape)
+    _lib.check(cuda_lib, cuda_lib.ulk_synth_frame(shp, 1, 11, 8.0, 0.3, 3.0, 1e-3, C.c_void_p(fg.data_ptr()),
+                                                  C.c_void_p(ct.data_ptr()), None))
+    prm = seg_params(fg_dtype=np.float32, min_area=100, max_area=10000, min_frontier=0.0)
+
+    def run():
+        h = segment_frame_device(cuda_lib, fg, ct, prm, keep_labels=True)
+        out = _lib.nodes_to_host(cuda_lib, h, with_labels=True)
+        cuda_lib.ulk_frame_nodes_free(h)
+        return out
+
+    a = run()
+    assert 0 < a["stats"]["k3_voxels"] < a["stats"]["n_foreground"]
+    for var in ("ULK_K3_ALL", "ULK_CCL_VOXEL", "ULK_CMAX_EARLY", "ULK_THR_SCALAR"):
+        monkeypatch.setenv(var, "1")
+    b = run()
+    assert b["stats"]["k3_voxels"] == b["stats"]["n_foreground"]
+    for key in ("bbox", "centroid", "area", "height", "hier_id", "parent", "hidx", "mask_off", "mask", "overlaps", "labels"):
+        assert np.array_equal(a[key], b[key]), key
+    assert np.allclose(a["frontier"], b["frontier"], rtol=1e-12, atol=0)

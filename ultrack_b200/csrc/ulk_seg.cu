@@ -424,7 +424,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
     if (cmax_late) CHK(ulk_memset(cmax_late, 0, sizeof(u32), st));
     ulk_launch_list_phx<1>("MinEdge", fgl, nfg, dm, st, K_MinEdge{lab, ct, dm, mw, pk, cmax_late});
-    ulk_launch_list_phx<4>("Hook1", fgl, nfg, dm, st, K_Hook1{lab, mw, pk, dm, bp, state, Lr, best, ctr + 4});
+    ulk_launch_list_phx<4>("Hook1", fgl, nfg, dm, st, K_Hook1{mw, pk, dm, bp, state, Lr, best, ctr + 4});
     ulk_launch_list_multi(fgl, nfg, st, K_CompressCand{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1, sroots, ctr + 6});
     i32 hc[8];
     CHK(ulk_read(hc, ctr, 8, st));

@@ -9,6 +9,7 @@
 #include "ulk_common.h"
 
 #define ULK_JK_CORE 0xFFFFFFFEu   // join key of voxels inside the regional minimum
+#define ULK_PK_OUT 0xFFFFFFFEu    // steepest-edge key of a list voxel outside every region (dropped component)
 
 // ------------------------------------------------------------------ union-find on voxels
 ULK_D ULK_INLINE i32 ulk_vfind(const i32 *P, i32 x)
@@ -344,7 +345,7 @@ struct K_MinEdge {
             if ((threadIdx.x & 31) == 0 && m > *cmax) atomicMax(cmax, m);
 #endif
         }
-        if (l <= 0) return;          // mw / pk are only ever read where lab > 0
+        if (l <= 0) { pk[v] = ULK_PK_OUT; return; }     // K_Hook1 reads the key instead of the label
         u32 bw = ULK_NONE32, bk = ULK_NONE32;
 #ifndef ULK_EMU
 #pragma unroll
@@ -371,37 +372,38 @@ ULK_HD ULK_INLINE i32 ulk_edge_other(u32 key, i32 v, const UlkDims &dm)
 }
 // first Boruvka round: every voxel hooks along its steepest edge; mutual pairs keep the
 // smaller voxel as root.  state: 0 growing, 1 minimum (basin seed)
+// reads only the steepest-edge keys (its own and the other endpoint's); the level of a root is
+// fetched by the roots alone, and `state` only exists at roots (nothing reads it elsewhere)
 struct K_Hook1 {
-    const i32 *lab; const u32 *mw, *pk; UlkDims dm;
+    const u32 *mw, *pk; UlkDims dm;
     i32 *bp; u8 *state; u32 *Lr; u32 *best; i32 *nbasins;
-    struct S1 { i32 v, l; u32 k, m; };
-    struct S2 { i32 v, l, u; u32 k, m, ku; };
+    struct S1 { i32 v; u32 k; };
+    struct S2 { i32 v, u; u32 k, ku; };
     ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32, bool ok) const
     {
         S1 s;
-        s.v = v; s.l = 0; s.k = ULK_NONE32; s.m = 0;
-        if (ok) { s.l = lab[v]; s.k = pk[v]; s.m = mw[v]; }   // pk / mw hold stale values where lab <= 0: never used
+        s.v = v; s.k = ULK_PK_OUT;
+        if (ok) s.k = pk[v];
         return s;
     }
     ULK_D ULK_INLINE S2 load2(const S1 &a, bool ok) const
     {
         S2 s;
-        s.v = a.v; s.l = a.l; s.k = a.k; s.m = a.m; s.u = a.v; s.ku = ULK_NONE32;
-        if (ok && a.l > 0 && a.k != ULK_NONE32) { s.u = ulk_edge_other(a.k, a.v, dm); s.ku = pk[s.u]; }
+        s.v = a.v; s.k = a.k; s.u = a.v; s.ku = ULK_NONE32;
+        if (ok && a.k < ULK_PK_OUT) { s.u = ulk_edge_other(a.k, a.v, dm); s.ku = pk[s.u]; }
         return s;
     }
     ULK_D ULK_INLINE void run(const S2 &s, bool ok) const
     {
         if (!ok) return;
         const i32 v = s.v;
-        state[v] = 0;
-        if (s.l <= 0) { bp[v] = -1; return; }
+        if (s.k == ULK_PK_OUT) { bp[v] = -1; return; }
         if (s.k == ULK_NONE32) {
             bp[v] = v; state[v] = 1; Lr[v] = ULK_NONE32; best[v] = ULK_NONE32;
             ulk_atomic_add(nbasins, 1);
             return;
         }
-        if (s.ku == s.k && v < s.u) { bp[v] = v; Lr[v] = s.m; best[v] = ULK_NONE32; }
+        if (s.ku == s.k && v < s.u) { bp[v] = v; state[v] = 0; Lr[v] = mw[v]; best[v] = ULK_NONE32; }
         else bp[v] = s.u;
     }
 };
