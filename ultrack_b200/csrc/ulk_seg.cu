@@ -132,20 +132,33 @@ struct K_MaskPaint {
             n = r.parent;
         }
 #else
+        // all lanes stay in the loop until the deepest chain of the warp ends (full-mask
+        // collectives); adjacent lanes that hit the same mask word merge their bits with a
+        // segmented shuffle OR and the run's first lane issues the atomic
         const int lane = threadIdx.x & 31;
-        const i32 bprev = __shfl_up_sync(0xffffffffu, s.b, 1);
-        const u32 grp = ulk_run_mask(__ballot_sync(0xffffffffu, lane == 0 || bprev != s.b), lane);
-        if (s.b < 0) return;
-        const bool first = lane == __ffs(grp) - 1;
-        for (i32 n = s.n; n >= 0;) {
-            const UlkPaintInfo r = load(n);
-            i32 rx = s.x - r.x0;
-            i64 word = r.moff + ((i64)(s.z - r.z0) * r.bh + (s.y - r.y0)) * r.wpr + (rx >> 5);
-            const i64 wprev = __shfl_up_sync(grp, word, 1);
-            const u32 sub = ulk_run_mask(__ballot_sync(grp, first || wprev != word) | ~grp, lane) & grp;
-            u32 bits = __reduce_or_sync(sub, 1u << (rx & 31));
-            if (lane == __ffs(sub) - 1) atomicOr(&mask[word], bits);
-            n = r.parent;
+        i32 n = s.b >= 0 ? s.n : -1;
+        while (__any_sync(0xffffffffu, n >= 0)) {
+            const bool act = n >= 0;
+            i64 word = -1 - lane;
+            u32 bits = 0;
+            i32 parent = -1;
+            if (act) {
+                const UlkPaintInfo r = load(n);
+                const i32 rx = s.x - r.x0;
+                word = r.moff + ((i64)(s.z - r.z0) * r.bh + (s.y - r.y0)) * r.wpr + (rx >> 5);
+                bits = 1u << (rx & 31);
+                parent = r.parent;
+            }
+            const i64 wprev = __shfl_up_sync(0xffffffffu, word, 1);
+            const u32 run = ulk_run_mask(__ballot_sync(0xffffffffu, lane == 0 || wprev != word), lane);
+            const int first = __ffs(run) - 1, last = 31 - __clz(run);
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const u32 b2 = __shfl_down_sync(0xffffffffu, bits, off);
+                if (lane + off <= last) bits |= b2;
+            }
+            if (act && lane == first) atomicOr(&mask[word], bits);
+            n = parent;
         }
 #endif
     }

@@ -736,6 +736,9 @@ struct K_BasinAccum {
     // two per warp): z and y are uniform in it and x grows with the lane, so the bounding box and
     // the coordinate sums need no reduction; one lane per group issues the atomics, and only
     // those that can still change the accumulator (a stale cached value only costs an atomic)
+    // Every lane stays in the collectives (full mask): a reduction over a run is a segmented
+    // shuffle reduction towards the run's first lane (partial-mask __reduce_*_sync serialises
+    // over the distinct masks of a warp).
     ULK_D ULK_INLINE void run(const S2 &o, bool) const
     {
         const int lane = threadIdx.x & 31;
@@ -750,12 +753,10 @@ struct K_BasinAccum {
         const i32 row = v - x;
         const i32 bp_ = __shfl_up_sync(0xffffffffu, b, 1), rp_ = __shfl_up_sync(0xffffffffu, row, 1);
         const u32 grp = ulk_run_mask(__ballot_sync(0xffffffffu, lane == 0 || bp_ != b || rp_ != row), lane);
-        if (b < 0) return;
-        const int first = __ffs(grp) - 1;
-        const bool lead = lane == first;
-        const i32 n = __popc(grp);
-        // the leader reads the accumulators it may have to update before the reductions start,
-        // so those loads overlap them
+        const int first = __ffs(grp) - 1, last = 31 - __clz(grp);
+        const bool lead = lane == first && b >= 0;
+        const i32 n = last - first + 1;
+        // the leader reads the accumulators it may have to update before the reductions start
         u64 cur_top = 0; u32 cur_k0 = 0, cur_tk = 0;
         i32 clo[3] = {0, 0, 0}, chi[3] = {0, 0, 0};
         if (lead) {
@@ -766,22 +767,28 @@ struct K_BasinAccum {
                 chi[0] = bbmax[3 * b]; chi[1] = bbmax[3 * b + 1]; chi[2] = bbmax[3 * b + 2];
             }
         }
-        u32 thi = __reduce_max_sync(grp, (u32)(o.top >> 32));
-        u32 tlo = __reduce_max_sync(grp, (u32)(o.top >> 32) == thi ? (u32)o.top : 0u);
-        u32 km = 0, tk = 0;
-        if (want_k0) {
-            km = __reduce_max_sync(grp, o.kmin == ULK_NONE32 ? 0u : o.kmin);
-            tk = __reduce_max_sync(grp, o.top != 0 ? (u32)o.top : 0u);
-        }
-        i32 x1 = x; u32 sx = 0;
-        if (want_stats) {
-            x1 = __shfl_sync(grp, x, 31 - __clz(grp));                 // x of the run's last lane
-            sx = (x1 - x + 1 == n) ? (u32)(((i64)(x + x1) * n) >> 1) : 0u;   // meaningful in the first lane
-            if (__shfl_sync(grp, x1 - x + 1 != n ? 1 : 0, first)) sx = __reduce_add_sync(grp, (u32)x);
+        u64 t = o.top;
+        u32 km = o.kmin == ULK_NONE32 ? 0u : o.kmin, tk = o.top != 0 ? (u32)o.top : 0u;
+        const i32 x1 = __shfl_sync(0xffffffffu, x, last);      // x of the run's last lane
+        u32 sx = (u32)x;
+        const bool contig = __shfl_sync(0xffffffffu, x1 - x + 1 == n ? 1 : 0, first) != 0;   // the leader's view
+        const bool any_gap = __any_sync(0xffffffffu, b >= 0 && want_stats && !contig);
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const u64 t2 = __shfl_down_sync(0xffffffffu, t, off);
+            const u32 km2 = __shfl_down_sync(0xffffffffu, km, off), tk2 = __shfl_down_sync(0xffffffffu, tk, off);
+            u32 sx2 = 0;
+            if (any_gap) sx2 = __shfl_down_sync(0xffffffffu, sx, off);
+            if (lane + off <= last) {
+                t = t2 > t ? t2 : t;
+                km = km2 > km ? km2 : km;
+                tk = tk2 > tk ? tk2 : tk;
+                sx += sx2;
+            }
         }
         if (!lead) return;
+        if (contig) sx = (u32)(((i64)(x + x1) * n) >> 1);
         atomicAdd(&b_size[b], n);
-        const u64 t = ((u64)thi << 32) | tlo;
         if (t > cur_top) atomicMax((unsigned long long *)&b_top[b], (unsigned long long)t);
         if (want_k0 && km > cur_k0) atomicMax(&K0[b], km);
         if (want_k0 && tk > cur_tk) atomicMax(&Tk[b], tk);
