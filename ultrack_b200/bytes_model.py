@@ -29,7 +29,7 @@ LIST_BYTES_PER_FG_VOXEL: Dict[str, float] = {
     "K_LabelCc": 4 + 4 + 4,
     "K_WriteLabels": 4 + 4 + 4 + 4,      # list, forest, basin, label out
     "K_MinEdge": 4 + 4 + 4 + 4 + 4,      # list, label, contour in; min weight, min key out
-    "K_Hook1": 4 + 4 + 4 + 4 + 4 + 1,    # list, label, weight, key in; forest, state out
+    "K_Hook1": 4 + 4 + 4 + 4,            # list, key, the other endpoint's key in; forest out
     "K_CompressCand": 4 + 4 + 4 + 4,     # list, forest in/out, weight
     "K_CompressRoots": 4 + 4 + 4,
     "K_AssignBasin": 4 + 4 + 4,
