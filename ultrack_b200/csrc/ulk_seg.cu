@@ -518,7 +518,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     ulk_launch_list_phx<1>("BasinAccum", fgl, nfg, dm, st, K_BasinAccum{out.bas, lab, mw, pk, dm, out.b_size, out.b_top, ncross,
                                         need_stats ? 1 : 0, out.bbmin, out.bbmax, out.csum,
                                         need_join ? 1 : 0, out.g_L, out.jk, hp, ctr + 0,
-                                        need_k3 ? 1 : 0, out.b_k3, Tk, xl, ctr + 1});
+                                        need_k3 ? 1 : 0, out.b_k3, Tk, xl, ctr + 1, out.g_lab});
     ulk_launch(nflow, st, K_FlowTop{flow_root, flow_key, out.bas, ct, dm, out.b_top, Tk});
     A.release(flow_root); A.release(flow_key);
     u64 h_ncross = 0;

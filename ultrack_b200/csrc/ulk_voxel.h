@@ -656,6 +656,7 @@ struct K_BasinAccum {
     int want_join; const u32 *b_L; u32 *jk; i32 *hp; i32 *nhp;
     int want_k0; u32 *K0; u32 *Tk;      // Tk: largest raster key among the basin's steepest edges
     i32 *xl; i32 *nxl;                  // voxels with a forward edge into another basin of their region
+    const i32 *g_lab;                   // region label of a basin (the voxel's own label is not read)
     // phase 1: the voxel's own entries and its neighbours' basins (indices clamped at the border)
     struct S1 { i32 v, z, y, x, b, l; u32 m, k; i32 a[3], c[3]; };
     // phase 2: what depends on them -- the basin level, the weight across the steepest edge, the
@@ -671,7 +672,7 @@ struct K_BasinAccum {
         s.a[0] = bas[x + 1 < dm.W ? v + 1 : v]; s.a[1] = bas[y + 1 < dm.H ? v + sy : v]; s.a[2] = bas[z + 1 < dm.D ? v + sz : v];
         s.c[0] = s.c[1] = s.c[2] = -1;
         if (want_k0) { s.c[0] = bas[x > 0 ? v - 1 : v]; s.c[1] = bas[y > 0 ? v - sy : v]; s.c[2] = bas[z > 0 ? v - sz : v]; }
-        s.m = mw[v]; s.k = pk[v]; s.l = lab[v];
+        s.m = mw[v]; s.k = pk[v]; s.l = 0;
         return s;
     }
     ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const
@@ -686,13 +687,14 @@ struct K_BasinAccum {
         // issue the dependent loads first
         const bool q0 = f0 && a.a[0] != b, q1 = f1 && a.a[1] != b, q2 = f2 && a.a[2] != b;
         const i32 l0 = q0 ? lab[v + 1] : 0, l1 = q1 ? lab[v + sy] : 0, l2 = q2 ? lab[v + sz] : 0;
+        const i32 lown = (q0 || q1 || q2) ? g_lab[b] : 0;
         u32 bl = 0, mo = 0;
         const bool has_edge = a.k != ULK_NONE32;
         if (want_join) { bl = b_L[b]; if (has_edge) mo = mw[ulk_edge_other(a.k, v, dm)]; }
         o.top = has_edge ? ((u64)a.m << 32) | a.k : 0;
-        if (q0 && l0 == a.l) ++o.nc;
-        if (q1 && l1 == a.l) ++o.nc;
-        if (q2 && l2 == a.l) ++o.nc;
+        if (q0 && l0 == lown) ++o.nc;
+        if (q1 && l1 == lown) ++o.nc;
+        if (q2 && l2 == lown) ++o.nc;
         u32 kk;
         if (f0 && a.a[0] == b) { kk = 3u * (u32)v; if (kk < o.kmin) o.kmin = kk; }
         if (f1 && a.a[1] == b) { kk = 3u * (u32)v + 1u; if (kk < o.kmin) o.kmin = kk; }
