@@ -14,6 +14,7 @@
  *   ulk_link_frames      <- core/linking/processing.py:172-291        (compute_spatial_neighbors:
  *                           KD-tree k-NN, IoU, top-k) and core/segmentation/node.py:23-118
  *   ulk_labels_to_contours <- utils/edge.py:18-96                      (labels_to_contours)
+ *   ulk_node_shifts      <- imgproc/flow.py:639-751                   (add_flow, per timepoint)
  *
  * Conventions: every function returns 0 on success and a negative code on failure and never
  * throws; ulk_last_error() gives the message of the calling thread's last failure.  Code -10
@@ -163,6 +164,15 @@ ULK_API void ulk_links_free(ulk_links *links);
  * foreground uint8 [D,H,W] and contours float32 [D,H,W] (sigma = None path) */
 ULK_API int ulk_labels_to_contours(const int32_t *labels, int32_t n_sets, const int64_t shape[3],
                            uint8_t *foreground, float *contours, void *stream);
+
+/* add_flow (imgproc/flow.py:639-751), the per-timepoint kernel: for every node of `nodes` the
+ * vector field sampled at its centroid mapped into field coordinates (round half to even of
+ * centroid * (field_dim - 1) / (image_dim - 1), clipped: flow.py:716-720), scaled to voxels
+ * (flow.py:737).  `field` is a device array [n_vec, FD, FH, FW] of `field_dtype` for ONE
+ * timepoint; with fewer vectors than dimensions the last axes have priority (the last vector is
+ * x).  shift_host receives [n,3] doubles (z, y, x), the layout ulk_link_frames takes. */
+ULK_API int ulk_node_shifts(const ulk_frame_nodes *nodes, const void *field, int field_dtype, int32_t n_vec,
+                    const int64_t field_shape[3], double *shift_host, void *stream);
 
 /* seeded synthetic frame on the device (ultrack_b200/synth.py recipe, variant "S"):
  * foreground float32 and contours float32 [D,H,W] */

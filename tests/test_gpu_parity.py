@@ -317,3 +317,91 @@ def test_shortcuts_equal_exhaustive_forms(cuda_lib, monkeypatch):
     for key in ("bbox", "centroid", "area", "height", "hier_id", "parent", "hidx", "mask_off", "mask", "overlaps", "labels"):
         assert np.array_equal(a[key], b[key]), key
     assert np.allclose(a["frontier"], b["frontier"], rtol=1e-12, atol=0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ndim,nvecs,fdtype", [(3, 3, np.float32), (3, 2, np.float32), (2, 2, np.float64), (3, 3, np.float16)])
+def test_node_shifts_parity(cuda_lib, ndim, nvecs, fdtype):
+    """ulk_node_shifts vs the restated add_flow arithmetic (imgproc/flow.py:700-737): field coarser
+    than the image, fewer vectors than dimensions, half-way coordinates (round half to even)."""
+    import torch
+    from oracle.flow_oracle import node_shifts
+    from ultrack_b200 import _lib
+    shape = (20, 48, 40) if ndim == 3 else (96, 80)
+    fshape = (5, 13, 11) if ndim == 3 else (25, 21)
+    fg, ct = cases.blob_frame(shape, 3, "smooth")
+    h, nodes = _seg_host(cuda_lib, fg, ct, min_area=30, max_area=2000)
+    rng = np.random.default_rng(5)
+    field = (rng.random((nvecs,) + fshape) - 0.5).astype(fdtype)
+    cen = nodes["centroid"][:, 3 - ndim:]
+    exp = node_shifts(cen, field, shape)
+    dev = torch.from_numpy(field.view(np.uint8).reshape(-1).copy()).cuda()
+    fs3 = fshape if ndim == 3 else (1,) + fshape
+    out = np.zeros((len(cen), 3), np.float64)
+    _lib.check(cuda_lib, cuda_lib.ulk_node_shifts(h, C.c_void_p(dev.data_ptr()), _lib.dtype_code(field.dtype), nvecs,
+                                                  (C.c_int64 * 3)(*fs3), out.ctypes.data_as(C.c_void_p), None))
+    assert len(cen) > 5 and np.array_equal(out, exp)
+    cuda_lib.ulk_frame_nodes_free(h)
+
+
+def test_add_flow_api_on_gpu(cuda_lib, tmp_path):
+    """segment() -> add_flow() -> link() through the public API: the shift columns equal the
+    restated reference arithmetic and link() consumes them (imgproc/flow.py:639-751,
+    core/linking/processing.py:140-148,211-213)."""
+    from oracle.flow_oracle import node_shifts
+    from oracle.link_oracle import link_pair
+    from oracle.segment_oracle import SegParams, segment_frame as o_seg
+    from ultrack_b200 import MainConfig, add_flow, database, link, segment, synth
+    cfg = MainConfig.model_validate({"data": {"working_dir": str(tmp_path)},
+                                     "segmentation": {"min_area": 60, "max_area": 2000},
+                                     "linking": {"max_distance": 10, "max_neighbors": 3}})
+    T, shape = 3, (16, 64, 64)
+    fg, ct = synth.make_timelapse(shape, T, seed=4, variant="S", radius=5.0, motion=2.0)
+    segment(fg, ct, cfg)
+    rng = np.random.default_rng(1)
+    field = ((rng.random((T, 3, 4, 16, 16)) - 0.5) * 0.2).astype(np.float32)
+    add_flow(cfg, field)
+    with pytest.raises(ValueError, match="normalized"):
+        add_flow(cfg, field * 100)
+    with database.connect(cfg.data_config.database_path) as conn:
+        rows = conn.execute("select t, z, y, x, z_shift, y_shift, x_shift from nodes order by id").fetchall()
+        links = {(s, t): w for s, t, w in conn.execute("select source_id,target_id,weight from links")}
+    assert not links
+    rows = np.array(rows, float)
+    for t in range(T):
+        sel = rows[:, 0] == t
+        exp = node_shifts(rows[sel, 1:4], field[t], shape)
+        assert sel.sum() > 5 and np.array_equal(rows[sel, 4:7], exp) and np.abs(exp).max() > 0
+    link(cfg)
+    with database.connect(cfg.data_config.database_path) as conn:
+        links = {(s, t): w for s, t, w in conn.execute("select source_id,target_id,weight from links")}
+    prm = SegParams(min_area=60, max_area=2000)
+    ref = [o_seg(fg[t], ct[t], prm, time=t) for t in range(T)]
+    exp_links = {}
+    for t in range(T - 1):
+        sh = rows[rows[:, 0] == t + 1, 4:7]
+        for w, s, d in link_pair(ref[t]["nodes"], ref[t + 1]["nodes"], 10, 3, time=t, target_shift=sh):
+            exp_links[(int(s), int(d))] = w
+    assert set(links) == set(exp_links) and len(links) > 10
+    for k in exp_links:
+        assert links[k] == pytest.approx(exp_links[k], rel=RTOL)
+
+
+def test_repeated_runs_stay_exact(cuda_lib):
+    """Races show up as rare mismatches: the same frames segmented many times in one process
+    (lists shorter than the grid, lanes past the list end, stale scratch from earlier frames)
+    must match the oracle every time.  scripts/gpu_hammer.py is the long form."""
+    from oracle.segment_oracle import SegParams, segment_frame as o_seg
+    from tests.emu_harness import compare_nodes
+    todo = []
+    for kind, hier in (("smooth", "dynamics"), ("quant", "area")):
+        fg, ct = cases.blob_frame((24, 48, 48), 1, kind)
+        kw = dict(min_area=40, max_area=1350, ws_hierarchy=hier, min_frontier=0.25 if hier == "dynamics" else 0.0)
+        todo.append((fg, ct, kw, o_seg(fg, ct, SegParams(**kw))))
+    for rep in range(40):
+        for fg, ct, kw, ref in todo:
+            h, nodes = _seg_host(cuda_lib, fg, ct, **kw)
+            assert np.array_equal(nodes["labels"].reshape(ref["labels"].shape), ref["labels"]), f"labels differ at repetition {rep}"
+            if rep % 10 == 0:
+                compare_nodes(nodes, ref, 3)
+            cuda_lib.ulk_frame_nodes_free(h)

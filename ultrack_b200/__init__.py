@@ -12,8 +12,9 @@ from ultrack_b200.config import (  # noqa: F401
     save_config,
 )
 from ultrack_b200.edge import labels_to_contours  # noqa: F401
+from ultrack_b200.flow import add_flow  # noqa: F401
 from ultrack_b200.link import link  # noqa: F401
 from ultrack_b200.segment import segment  # noqa: F401
 
-__all__ = ["segment", "link", "labels_to_contours", "MainConfig", "DataConfig", "SegmentationConfig",
+__all__ = ["segment", "link", "add_flow", "labels_to_contours", "MainConfig", "DataConfig", "SegmentationConfig",
            "LinkingConfig", "load_config", "save_config"]

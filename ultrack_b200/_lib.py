@@ -62,7 +62,7 @@ EXPORTS = [
     "ulk_profile_enable", "ulk_profile_reset", "ulk_profile_report", "ulk_segment_frame",
     "ulk_segment_frame_host", "ulk_frame_nodes_free", "ulk_frame_nodes_to_host",
     "ulk_frame_nodes_from_host", "ulk_frame_nodes_to_device", "ulk_frame_nodes_from_device", "ulk_link_frames", "ulk_links_to_host", "ulk_links_free",
-    "ulk_labels_to_contours", "ulk_synth_frame",
+    "ulk_labels_to_contours", "ulk_node_shifts", "ulk_synth_frame",
     "ulk_upload_begin", "ulk_segment_frame_uploaded", "ulk_upload_free",
 ]
 
@@ -99,6 +99,7 @@ def bind(lib: C.CDLL) -> C.CDLL:
     lib.ulk_links_free.argtypes = [PL]
     lib.ulk_links_free.restype = None
     lib.ulk_labels_to_contours.argtypes = [vp, i32, C.POINTER(i64), vp, vp, vp]
+    lib.ulk_node_shifts.argtypes = [PF, vp, C.c_int, i32, C.POINTER(i64), vp, vp]
     lib.ulk_synth_frame.argtypes = [C.POINTER(i64), i32, C.c_uint64, dbl, dbl, dbl, dbl, vp, vp, vp]
     return lib
 

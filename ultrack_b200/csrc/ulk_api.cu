@@ -307,6 +307,16 @@ int ulk_labels_to_contours(const int32_t *labels, int32_t n_sets, const int64_t 
     return ulk_labels_to_contours_impl(st, labels, n_sets, shape, foreground, contours);
 }
 
+int ulk_node_shifts(const ulk_frame_nodes *nodes, const void *field, int field_dtype, int32_t n_vec,
+                    const int64_t field_shape[3], double *shift_host, void *stream)
+{
+    if (!nodes || !field || !field_shape || !shift_host) ULK_FAIL(-1, "null argument");
+    if (n_vec < 1 || n_vec > 3) ULK_FAIL(-1, "n_vec must be 1, 2 or 3");
+    ulk_stream_t st = (ulk_stream_t)stream;
+    ulk_set_alloc_stream(st);
+    return ulk_node_shifts_impl(st, nodes, field, field_dtype, n_vec, field_shape, shift_host);
+}
+
 int ulk_synth_frame(const int64_t shape[3], int32_t t, uint64_t seed, double radius, double fill,
                     double motion, double noise, float *foreground, float *contours, void *stream)
 {

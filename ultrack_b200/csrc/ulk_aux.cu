@@ -154,3 +154,49 @@ int ulk_synth_frame_impl(ulk_stream_t st, const int64_t shape[3], int32_t t, uin
     ulk_launch(k.dm.V, st, k);
     return ulk_sync(st);
 }
+
+// ------------------------------------------------------------------ add_flow (imgproc/flow.py:639-751)
+// coords = clip(round(centroid * (field_dim - 1) / (image_dim - 1)), 0, field_dim - 1)
+// (flow.py:716-720); column j of (x, y, z) takes vector n_vec-1-j (flow.py:711,726-731) times the
+// image extent of that axis (flow.py:713,737).  Output rows are (z, y, x).
+struct K_NodeShifts {
+    const i32 *cen; const void *field; int dt; i32 nvec;
+    i64 fd, fh, fw; double cs[3]; double vs[3];      // cs: coordinate scaling z,y,x; vs: extent of x, y, z
+    double *out;
+    ULK_D void operator()(i64 n) const
+    {
+        i64 c[3];
+        const i64 lim[3] = {fd, fh, fw};
+        for (int d = 0; d < 3; ++d) {
+            double q = rint((double)cen[3 * n + d] * cs[d]);
+            i64 k = (i64)q;
+            if (k < 0) k = 0;
+            if (k > lim[d] - 1) k = lim[d] - 1;
+            c[d] = k;
+        }
+        const i64 idx = (c[0] * fh + c[1]) * fw + c[2], fv = fd * fh * fw;
+        out[3 * n] = out[3 * n + 1] = out[3 * n + 2] = 0.0;
+        for (i32 j = 0; j < nvec; ++j)
+            out[3 * n + (2 - j)] = ulk_load_as_double(field, dt, (i64)(nvec - 1 - j) * fv + idx) * vs[j];
+    }
+};
+int ulk_node_shifts_impl(ulk_stream_t st, const ulk_frame_nodes *nodes, const void *field, int field_dtype, int32_t n_vec,
+                         const int64_t field_shape[3], double *shift_host)
+{
+    const i32 N = nodes->n_nodes;
+    if (N <= 0) return 0;
+    UlkArena A;
+    double *out = A.get<double>(3 * (i64)N);
+    if (A.failed) ULK_FAIL(-3, "device allocation failed");
+    K_NodeShifts k;
+    k.cen = nodes->centroid; k.field = field; k.dt = field_dtype; k.nvec = n_vec;
+    k.fd = field_shape[0]; k.fh = field_shape[1]; k.fw = field_shape[2];
+    for (int d = 0; d < 3; ++d) {
+        const i64 img = nodes->shape[d];
+        k.cs[d] = img > 1 ? (double)(field_shape[d] - 1) / (double)(img - 1) : 0.0;
+    }
+    k.vs[0] = (double)nodes->shape[2]; k.vs[1] = (double)nodes->shape[1]; k.vs[2] = (double)nodes->shape[0];
+    k.out = out;
+    ulk_launch(N, st, k);
+    return ulk_d2h(shift_host, out, (size_t)N * 3 * sizeof(double), st);
+}

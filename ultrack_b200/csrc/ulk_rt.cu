@@ -107,6 +107,13 @@ int ulk_sort_keys_u64(const u64 *ki, u64 *ko, i64 n, ulk_stream_t)
 #include <map>
 #include <vector>
 bool g_ulk_prof_on = false;
+int g_ulk_debug_sync = getenv("ULK_DEBUG_SYNC") ? atoi(getenv("ULK_DEBUG_SYNC")) : 0;
+void ulk_debug_after_launch(const char *name, ulk_stream_t s)
+{
+    cudaError_t e = cudaStreamSynchronize(s);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) { fprintf(stderr, "ULK_DEBUG_SYNC: %s failed: %s\n", name, cudaGetErrorString(e)); fflush(stderr); }
+}
 struct ProfRec { const char *name; cudaEvent_t a, b; };
 static std::vector<ProfRec> g_prof_recs;
 static std::vector<cudaEvent_t> g_prof_free;

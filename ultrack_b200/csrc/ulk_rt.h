@@ -124,6 +124,10 @@ template <class F> __global__ void __launch_bounds__(256) ulk_kernel(i64 n, F f)
     if (i < n) f(i);
 }
 extern long long g_ulk_launches;
+// ULK_DEBUG_SYNC=1: every launch is followed by a stream synchronize; the first failing kernel
+// is named on stderr (debugging aid, off by default)
+extern int g_ulk_debug_sync;
+void ulk_debug_after_launch(const char *name, ulk_stream_t s);
 // optional per-kernel timing (CUDA events on the launching stream), see ulk_profile_* in the C ABI
 extern bool g_ulk_prof_on;
 void ulk_prof_begin(const char *name, ulk_stream_t s);
@@ -136,6 +140,7 @@ template <class F> void ulk_launch(i64 n, ulk_stream_t s, const F &f)
     ulk_kernel<F><<<(unsigned)grid, 256, 0, s>>>(n, f);
     if (g_ulk_prof_on) ulk_prof_end(s);
     ++g_ulk_launches;
+    if (g_ulk_debug_sync) ulk_debug_after_launch(typeid(F).name(), s);
 }
 // warp-cooperative kernels: every thread of the grid calls F::warp(i, i < n), so the body may
 // use full-mask warp collectives; lane l of a warp holds element 32*k + l.
@@ -152,6 +157,7 @@ template <class F> void ulk_launch_warp(i64 n, ulk_stream_t s, const F &f)
     ulk_kernel_warp<F><<<(unsigned)grid, 256, 0, s>>>(n, f);
     if (g_ulk_prof_on) ulk_prof_end(s);
     ++g_ulk_launches;
+    if (g_ulk_debug_sync) ulk_debug_after_launch(typeid(F).name(), s);
 }
 // voxel kernels that need coordinates: 3-D grid (x blocks, y, z), no index division; lane l of a
 // warp holds x = 32*k + l of one row.  The _warp form calls F::warp(v, z, y, x, valid) from
@@ -175,6 +181,7 @@ template <class F> void ulk_launch_vox(i32 D, i32 H, i32 W, ulk_stream_t s, cons
     ulk_kernel_vox<F><<<grid, ULK_VOX_BX, 0, s>>>(H, W, f);
     if (g_ulk_prof_on) ulk_prof_end(s);
     ++g_ulk_launches;
+    if (g_ulk_debug_sync) ulk_debug_after_launch(typeid(F).name(), s);
 }
 template <class F> void ulk_launch_vox_warp(i32 D, i32 H, i32 W, ulk_stream_t s, const F &f)
 {
@@ -184,6 +191,7 @@ template <class F> void ulk_launch_vox_warp(i32 D, i32 H, i32 W, ulk_stream_t s,
     ulk_kernel_vox_warp<F><<<grid, ULK_VOX_BX, 0, s>>>(H, W, f);
     if (g_ulk_prof_on) ulk_prof_end(s);
     ++g_ulk_launches;
+    if (g_ulk_debug_sync) ulk_debug_after_launch(typeid(F).name(), s);
 }
 // list kernels: one thread per entry of a voxel list (the foreground voxels of a frame, in
 // raster order): every lane does useful work, and consecutive entries are mostly consecutive
@@ -211,6 +219,7 @@ template <class F, class DM> void ulk_launch_list(const i32 *list, i64 n, const 
     ulk_kernel_list<F, DM><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(list, n, dm, f);
     if (g_ulk_prof_on) ulk_prof_end(s);
     ++g_ulk_launches;
+    if (g_ulk_debug_sync) ulk_debug_after_launch(typeid(F).name(), s);
 }
 template <class F, class DM> void ulk_launch_list_warp(const i32 *list, i64 n, const DM &dm, ulk_stream_t s, const F &f)
 {
@@ -219,6 +228,7 @@ template <class F, class DM> void ulk_launch_list_warp(const i32 *list, i64 n, c
     ulk_kernel_list_warp<F, DM><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(list, n, dm, f);
     if (g_ulk_prof_on) ulk_prof_end(s);
     ++g_ulk_launches;
+    if (g_ulk_debug_sync) ulk_debug_after_launch(typeid(F).name(), s);
 }
 // pointer-chasing list kernels: a thread takes ULK_MULTI entries (256 apart, so every load of
 // the list stays coalesced) and calls F::multi(v[], valid[]) from every thread of the block; the
@@ -268,6 +278,7 @@ template <int U, class F, class DM> void ulk_launch_list_ph(const i32 *list, i64
     ulk_kernel_list_ph<U, F, DM><<<(unsigned)((n + 256 * U - 1) / (256 * U)), 256, 0, s>>>(list, n, dm, f);
     if (g_ulk_prof_on) ulk_prof_end(s);
     ++g_ulk_launches;
+    if (g_ulk_debug_sync) ulk_debug_after_launch(typeid(F).name(), s);
 }
 // tuning aid: entries per thread from the environment (ULK_U_<tag> = 1, 2 or 4), else the default
 template <int UDEF, class F, class DM> void ulk_launch_list_phx(const char *tag, const i32 *list, i64 n, const DM &dm, ulk_stream_t s, const F &f)
@@ -287,6 +298,7 @@ template <class F> void ulk_launch_list_multi(const i32 *list, i64 n, ulk_stream
     ulk_kernel_list_multi<F><<<(unsigned)((n + 256 * ULK_MULTI - 1) / (256 * ULK_MULTI)), 256, 0, s>>>(list, n, f);
     if (g_ulk_prof_on) ulk_prof_end(s);
     ++g_ulk_launches;
+    if (g_ulk_debug_sync) ulk_debug_after_launch(typeid(F).name(), s);
 }
 #endif
 int ulk_prof_report(char *buf, i64 cap);   // "name\tlaunches\ttotal_ms\n" per kernel; returns bytes needed

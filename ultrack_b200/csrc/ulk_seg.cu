@@ -373,6 +373,7 @@ static int threshold_and_list(ulk_stream_t st, UlkArena &A, const UlkDims &dm, c
     }
     if (g_ulk_prof_on) ulk_prof_end(st);
     ++g_ulk_launches;
+    if (g_ulk_debug_sync) ulk_debug_after_launch("K_Threshold", st);
     CHK(ulk_exclusive_scan_popc_u32(words, off, nt, st));
     UlkFastDiv fS;
     fS.init(S);
@@ -380,6 +381,7 @@ static int threshold_and_list(ulk_stream_t st, UlkArena &A, const UlkDims &dm, c
     ulk_expand_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(words, off, ntask, dm.W, S, fS, fgl, nfg_dev);
     if (g_ulk_prof_on) ulk_prof_end(st);
     ++g_ulk_launches;
+    if (g_ulk_debug_sync) ulk_debug_after_launch("K_ExpandForeground", st);
     if (!getenv("ULK_CCL_VOXEL")) {
         UlkFastDiv fH;
         fH.init((u32)dm.H);
@@ -387,6 +389,7 @@ static int threshold_and_list(ulk_stream_t st, UlkArena &A, const UlkDims &dm, c
         ulk_ccl_words_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(words, ntask, dm.W, dm.H, S, fS, fH, k.P, cnt);
         if (g_ulk_prof_on) ulk_prof_end(st);
         ++g_ulk_launches;
+        if (g_ulk_debug_sync) ulk_debug_after_launch("K_CclWords", st);
         *ccl_done = true;
     }
     A.release(words); A.release(off);

@@ -332,7 +332,7 @@ struct K_MinEdge {
         return s;
     }
     ULK_D ULK_INLINE S2 load2(const S1 &s, bool) const { return s; }
-    ULK_D ULK_INLINE void run(const S2 &s, bool) const
+    ULK_D ULK_INLINE void run(const S2 &s, bool ok) const
     {
         const i32 v = s.v, l = s.l;
         if (cmax) {
@@ -345,7 +345,10 @@ struct K_MinEdge {
             if ((threadIdx.x & 31) == 0 && m > *cmax) atomicMax(cmax, m);
 #endif
         }
-        if (l <= 0) { pk[v] = ULK_PK_OUT; return; }     // K_Hook1 reads the key instead of the label
+        if (l <= 0) {          // K_Hook1 reads the key instead of the label; lanes past the list end write nothing
+            if (ok) pk[v] = ULK_PK_OUT;
+            return;
+        }
         u32 bw = ULK_NONE32, bk = ULK_NONE32;
 #ifndef ULK_EMU
 #pragma unroll

@@ -179,6 +179,18 @@ def insert_links(database_path: str, weight: np.ndarray, source_id: np.ndarray, 
         conn.close()
 
 
+def update_shifts(database_path: str, ids: np.ndarray, shifts_zyx: np.ndarray) -> None:
+    """UPDATE nodes SET z_shift, y_shift, x_shift WHERE id = ... (imgproc/flow.py:740-751)."""
+    rows = [(float(s[0]), float(s[1]), float(s[2]), int(i)) for i, s in zip(ids, shifts_zyx)]
+    conn = connect(database_path)
+    try:
+        with conn:
+            conn.execute("BEGIN IMMEDIATE")
+            conn.executemany("UPDATE nodes SET z_shift = ?, y_shift = ?, x_shift = ? WHERE id = ?", rows)
+    finally:
+        conn.close()
+
+
 def load_frame_nodes(database_path: str, t: int) -> List[Tuple]:
     """SELECT id, pickle, z_shift, y_shift, x_shift FROM nodes WHERE t = ? (linking/processing.py:136-148)."""
     with connect(database_path) as conn:
