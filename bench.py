@@ -217,6 +217,16 @@ def main():
     from ultrack_b200 import _lib, bytes_model
 
     torch.cuda.set_device(local_rank)
+    # the rank's host threads (and so its pinned staging buffers) stay on the NUMA node next to
+    # its GPU: the end-to-end figure is bound by host->device copies
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        phys = int(vis.split(",")[local_rank]) if vis and vis.split(",")[local_rank].isdigit() else local_rank
+        pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(phys))
+    except Exception:  # noqa: BLE001
+        pass
     if world > 1:
         # NCCL's version / debug lines go to stderr: stdout carries exactly one JSON line
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
