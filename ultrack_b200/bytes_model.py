@@ -24,7 +24,8 @@ DENSE_BYTES_PER_VOXEL: Dict[str, float] = {
 }
 # kernel name -> bytes per FOREGROUND voxel per launch (including the 4-byte list entry)
 LIST_BYTES_PER_FG_VOXEL: Dict[str, float] = {
-    "K_CclUnion": 4 + 4 + 4,             # list, forest in / out
+    "K_CclUnion": 4 + 4 + 4,             # list, forest in / out (per-voxel form)
+    "K_CclWords": 0.5 + 4 + 4,           # foreground words in (4 per 32-voxel segment), forest in / out
     "K_FlattenCount": 4 + 4 + 4,
     "K_LabelCc": 4 + 4 + 4,
     "K_WriteLabels": 4 + 4 + 4 + 4,      # list, forest, basin, label out

@@ -69,13 +69,6 @@ int ulk_select_nonneg_i32(const i32 *in, i64 n, i32 *out, i32 *count, ulk_stream
     *count = c;
     return 0;
 }
-int ulk_select_list_pos_i32(const i32 *list, i64 n, const i32 *lab, i32 *out, i32 *count, ulk_stream_t)
-{
-    i32 c = 0;
-    for (i64 i = 0; i < n; ++i) if (lab[list[i]] > 0) out[c++] = list[i];
-    *count = c;
-    return 0;
-}
 int ulk_select_list_split_i32(const i32 *list, i64 n, const i32 *bas, const i32 *nroot, i32 *out, i32 *count, ulk_stream_t)
 {
     i32 c = 0;
@@ -467,22 +460,6 @@ int ulk_select_list_split_i32(const i32 *list, i64 n, const i32 *bas, const i32 
 {
     if (n <= 0) return ulk_memset(count_dev, 0, sizeof(i32), s);
     UlkSplitAt pred{bas, nroot};
-    size_t need = 0;
-    ULK_CUDA(cub::DeviceSelect::If(nullptr, need, list, out, count_dev, (int)n, pred, s));
-    if (cub_tmp(need)) return -2;
-    ProfScope ps("cub::DeviceSelect::If", s);
-    ULK_CUDA(cub::DeviceSelect::If(g_cub_tmp, need, list, out, count_dev, (int)n, pred, s));
-    ++g_ulk_launches;
-    return 0;
-}
-struct UlkPosAt {
-    const i32 *p;
-    __device__ bool operator()(const i32 &v) const { return p[v] > 0; }
-};
-int ulk_select_list_pos_i32(const i32 *list, i64 n, const i32 *lab, i32 *out, i32 *count_dev, ulk_stream_t s)
-{
-    if (n <= 0) return ulk_memset(count_dev, 0, sizeof(i32), s);
-    UlkPosAt pred{lab};
     size_t need = 0;
     ULK_CUDA(cub::DeviceSelect::If(nullptr, need, list, out, count_dev, (int)n, pred, s));
     if (cub_tmp(need)) return -2;

@@ -336,8 +336,6 @@ int ulk_sort_pairs_u32(const u32 *keys_in, u32 *keys_out, const u32 *vals_in, u3
 int ulk_sort_keys_u32(const u32 *keys_in, u32 *keys_out, i64 n, ulk_stream_t s);
 // indices i (ascending) with in[i] >= 0 -> out; *count_dev receives how many
 int ulk_select_nonneg_i32(const i32 *in, i64 n, i32 *out, i32 *count_dev, ulk_stream_t s);
-// entries v of a voxel list (order kept) with lab[v] > 0 -> out; *count_dev receives how many
-int ulk_select_list_pos_i32(const i32 *list, i64 n, const i32 *lab, i32 *out, i32 *count_dev, ulk_stream_t s);
 int ulk_sort_keys_u64(const u64 *keys_in, u64 *keys_out, i64 n, ulk_stream_t s);
 // entries v of a voxel list (order kept) whose basin still has more than one root
 int ulk_select_list_split_i32(const i32 *list, i64 n, const i32 *bas, const i32 *nroot, i32 *out, i32 *count_dev, ulk_stream_t s);
