@@ -803,7 +803,11 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         i32 *nfgA_dev = AA.get<i32>(1);
         CHKA(AA);
         CHK(ulk_memset(nfgA_dev, 0, sizeof(i32), st));
+#ifdef ULK_EMU
         ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_LabelCc{code, cc_big, 1, labA, fglA, nfgA_dev});
+#else
+        ulk_launch_list_multi(fgl, nfg, st, K_LabelCc{code, cc_big, 1, labA, fglA, nfgA_dev});
+#endif
         i32 nfgA = 0;
         CHK(ulk_read(&nfgA, nfgA_dev, 1, st));
         stats_local.pass_a_voxels = nfgA;

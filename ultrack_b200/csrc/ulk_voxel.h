@@ -285,6 +285,38 @@ struct K_LabelCc {
 #endif
         }
     }
+#ifndef ULK_EMU
+    // mode 1, ULK_MULTI entries per thread: the three dependent loads of all entries in lockstep
+    // and ONE list reservation per warp for all of them
+    ULK_D void multi(const i32 (&v)[ULK_MULTI], const bool (&ok)[ULK_MULTI]) const
+    {
+        i32 r[ULK_MULTI], c[ULK_MULTI], g[ULK_MULTI];
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u) r[u] = ok[u] ? lab[v[u]] : -1;
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u) c[u] = r[u] >= 0 ? code[r[u]] : -1;
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u) g[u] = c[u] > 0 ? cc_big[c[u] - 1] : -1;
+        const int lane = threadIdx.x & 31;
+        u32 m[ULK_MULTI];
+        i32 total = 0;
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u) {
+            if (c[u] >= 0) lab[v[u]] = c[u] == 0 ? -1 : (g[u] >= 0 ? g[u] + 1 : -(c[u] - 1) - 2);
+            m[u] = __ballot_sync(0xffffffffu, g[u] >= 0);
+            total += __popc(m[u]);
+        }
+        if (total == 0) return;
+        i32 base = 0;
+        if (lane == 0) base = atomicAdd(nbig, total);
+        base = __shfl_sync(0xffffffffu, base, 0);
+#pragma unroll
+        for (int u = 0; u < ULK_MULTI; ++u) {
+            if (g[u] >= 0) biglist[base + __popc(m[u] & ((1u << lane) - 1u))] = v[u];
+            base += __popc(m[u]);
+        }
+    }
+#endif
 };
 struct K_FlagRoots {
     const i32 *P; i32 *flag;
