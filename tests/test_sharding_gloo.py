@@ -15,6 +15,15 @@ from ultrack_b200 import sharding
 ROOT = Path(__file__).resolve().parent.parent
 
 
+def test_link_pairs_follow_segment_partition():
+    for T in (2, 5, 7, 10, 50):
+        for world in (2, 3, 4, 8):
+            for r in range(world):
+                seg = sharding.owned(range(T), T, world, r)
+                lnk = sharding.owned(range(T - 1), T, world, r)
+                assert lnk == [t for t in seg if t < T - 1]
+
+
 def test_block_bounds_partition():
     for n in (0, 1, 5, 8, 50, 400):
         for world in (1, 2, 3, 8):
@@ -49,6 +58,12 @@ WORKER = textwrap.dedent("""
     segment(fg, ct, cfg)
     if {drop_store}:
         frames.STORE.clear()       # link() then rebuilds tables from the database blobs
+    else:
+        # link pairs follow segment()'s partition: every table link() needs is resident or
+        # arrives through the boundary exchange, never through the database blobs
+        def _no_db(*a, **k):
+            raise AssertionError("link() fell back to frame_from_database")
+        frames.frame_from_database = _no_db
     link(cfg)
     dist.barrier()
     dist.destroy_process_group()
@@ -73,10 +88,11 @@ def _run(tmp_path, world, T, drop_store=False):
     return nodes, ov, links
 
 
-@pytest.mark.parametrize("T", [5, 2])
-def test_two_ranks_equal_one(tmp_path, T):
+@pytest.mark.parametrize("world,T", [(2, 5), (2, 2), (3, 7)])
+def test_ranks_equal_one(tmp_path, world, T):
+    """T is not a multiple of the world size: segment and link must still agree on who owns what."""
     one = _run(tmp_path, 1, T)
-    two = _run(tmp_path, 2, T)
+    two = _run(tmp_path, world, T)
     assert one[0] == two[0] and len(one[0]) > 0
     assert one[1] == two[1]
     assert one[2] == two[2] and len(one[2]) > 0

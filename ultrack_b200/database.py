@@ -12,7 +12,10 @@ Only sqlite (file and shared-cache memory) is implemented; a postgresql URL rais
 """
 from __future__ import annotations
 
+import contextlib
+import fcntl
 import logging
+import os
 import sqlite3
 from typing import Iterable, List, Optional, Sequence, Tuple
 
@@ -110,6 +113,25 @@ def connect(database_path: str, timeout: float = 45.0) -> sqlite3.Connection:
     return sqlite3.connect(target, timeout=timeout, uri=uri)
 
 
+@contextlib.contextmanager
+def write_lock(database_path: str):
+    """Inter-process write lock for file-backed sqlite databases: the ranks of a multi-GPU
+    run (one process per GPU) append to ONE file.  The reference serialises its workers with a
+    `fasteners.InterProcessLock` file in the working directory (utils/multiprocessing.py:59-79);
+    this is the same idea with `fcntl.flock` on `<database file>.lock`."""
+    target = database_path[len("sqlite:///"):] if database_path.startswith("sqlite:///") else ""
+    if not target or target.startswith("file:") or target == ":memory:":
+        yield
+        return
+    fd = os.open(target + ".lock", os.O_CREAT | os.O_RDWR, 0o644)
+    try:
+        fcntl.flock(fd, fcntl.LOCK_EX)
+        yield
+    finally:
+        fcntl.flock(fd, fcntl.LOCK_UN)
+        os.close(fd)
+
+
 def create_all(database_path: str) -> None:
     """Base.metadata.create_all(engine) (processing.py:459)."""
     with connect(database_path) as conn:
@@ -157,7 +179,7 @@ def insert_nodes(database_path: str, nodes: Sequence[Tuple], overlaps: Iterable[
     """_insert_db (processing.py:62-87): one transaction per frame."""
     conn = connect(database_path)
     try:
-        with conn:
+        with write_lock(database_path), conn:
             conn.execute("BEGIN IMMEDIATE")
             conn.executemany(_NODE_INSERT, nodes)
             conn.executemany("INSERT INTO overlaps (node_id, ancestor_id) VALUES (?, ?)", overlaps)
@@ -172,7 +194,7 @@ def insert_links(database_path: str, weight: np.ndarray, source_id: np.ndarray, 
     rows = zip((float(w) for w in weight), (float(s) for s in source_id), (float(t) for t in target_id))
     conn = connect(database_path)
     try:
-        with conn:
+        with write_lock(database_path), conn:
             conn.execute("BEGIN IMMEDIATE")
             conn.executemany("INSERT INTO links (weight, source_id, target_id) VALUES (?, ?, ?)", rows)
     finally:
@@ -184,7 +206,7 @@ def update_shifts(database_path: str, ids: np.ndarray, shifts_zyx: np.ndarray) -
     rows = [(float(s[0]), float(s[1]), float(s[2]), int(i)) for i, s in zip(ids, shifts_zyx)]
     conn = connect(database_path)
     try:
-        with conn:
+        with write_lock(database_path), conn:
             conn.execute("BEGIN IMMEDIATE")
             conn.executemany("UPDATE nodes SET z_shift = ?, y_shift = ?, x_shift = ? WHERE id = ?", rows)
     finally:

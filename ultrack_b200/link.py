@@ -26,10 +26,11 @@ def link_params(config, scale: Optional[Sequence[float]], ndim: int) -> _lib.Lin
     """LinkingConfig (+ scale) -> ulk_link_params; `scale[-ndim:]` as in processing.py:215-219."""
     sc = [1.0, 1.0, 1.0]
     if scale is not None:
+        # the reference keeps the last min(n_dim, len(scale)) axes of BOTH position arrays
+        # (processing.py:215-219): a short scale drops the leading axes from the distance, which
+        # a zero scale factor on those axes reproduces exactly
         m = min(ndim, len(scale))
-        if m < ndim:
-            raise ValueError(f"`scale` must cover the {ndim} spatial axes, found {scale}")
-        sc[3 - m:] = [float(v) for v in list(scale)[-m:]]
+        sc = [0.0] * (3 - m) + [float(v) for v in list(scale)[-m:]] if m > 0 else [0.0, 0.0, 0.0]
     return _lib.LinkParams(float(config.max_distance), float(config.distance_weight), int(config.max_neighbors),
                            int(scale is not None), (C.c_double * 3)(*sc))
 
@@ -60,6 +61,9 @@ def link_frames_device(lib, src: frames.DeviceFrame, dst: frames.DeviceFrame, pr
 def _frame(lib, db: str, t: int, shape3, ndim: int) -> Optional[frames.DeviceFrame]:
     f = frames.STORE.get(db, t)
     if f is None:
+        if sharding.dist_info()[1] > 1:
+            LOG.warning(f"node table of t={t} is not resident on rank {sharding.dist_info()[0]}: rebuilding it from "
+                        "the database blobs (slow path; segment() and link() should run in the same processes)")
         f, _ = frames.frame_from_database(lib, db, t, shape3, ndim)
         if f is not None:
             frames.STORE.put(db, t, f)
@@ -123,31 +127,32 @@ def link(
     ndim = len(shape) - 1
     shape3 = tuple(shape[1:]) if ndim == 3 else (1,) + tuple(shape[1:])
 
-    mine = sharding.shard(time_points, world, rank)
+    # pairs follow their SOURCE frame under segment()'s partition of the max_t + 1 frames
+    mine = sharding.owned(time_points, max_t + 1, world, rank)
     boundary = None
     if world > 1:
-        boundary = _exchange_boundary(lib, db_path, time_points, world, rank, shape3, ndim)
+        boundary = _exchange_boundary(lib, db_path, time_points, max_t + 1, world, rank, shape3, ndim)
     for time in mine:
         nxt = boundary if (boundary is not None and time == mine[-1]) else None
         _process(time, config.linking_config, db_path, scale, lib, shape3, ndim, next_frame=nxt)
     sharding.barrier()
 
 
-def _exchange_boundary(lib, db_path: str, time_points: Sequence[int], world: int, rank: int, shape3, ndim: int):
-    """Every rank with a non-empty block needs the target frame of its last pair; when that
-    frame is the first source frame of a later rank's block that rank sends it.  All ranks walk
-    the same schedule, so sends and receives pair up without a handshake."""
-    n = len(time_points)
+def _exchange_boundary(lib, db_path: str, time_points: Sequence[int], total: int, world: int, rank: int, shape3, ndim: int):
+    """The target frame of a rank's last pair belongs to the next rank's block: its owner sends
+    the node table (frames.send_frame / recv_frame, NCCL over NVLink on a GPU group).  All ranks
+    walk the same schedule, so sends and receives pair up without a handshake."""
     received = None
     for r in range(world):
-        lo, hi = sharding.block_bounds(n, world, r)
-        if lo == hi or hi >= n:
-            continue  # empty block, or the last pair's target lies past every source block
-        sender = sharding.owner_of(hi, n, world)
+        pairs = sharding.owned(time_points, total, world, r)
+        if not pairs:
+            continue
+        target = pairs[-1] + 1
+        sender = sharding.owner_of(target, total, world)
         if sender == r:
             continue
         if rank == sender:
-            frames.send_frame(_frame(lib, db_path, time_points[hi], shape3, ndim), r)
+            frames.send_frame(_frame(lib, db_path, target, shape3, ndim), r)
         elif rank == r:
             received = frames.recv_frame(lib, sender)
     return received

@@ -163,7 +163,8 @@ def frame_rows(nodes: Dict[str, np.ndarray], time: int, ndim: int, max_segments_
     """Node table -> (`nodes` rows, `overlaps` rows) exactly as _process emits them
     (processing.py:235-300)."""
     n = len(nodes["area"])
-    if n > max_segments_per_time:
+    # the reference's running index ends at n + 1 and it raises when index > max (processing.py:305-308)
+    if n + 1 > max_segments_per_time:
         raise ValueError(f"Number of segments exceeds upper bound of {max_segments_per_time} per time.")
     index = np.arange(1, n + 1, dtype=np.int64)
     ids = _generate_id(index, time, max_segments_per_time)
@@ -288,7 +289,7 @@ def segment(
         frames.STORE.clear(db_path)
     sharding.barrier()
     # the host->device copy of the next frame overlaps the kernels of the current one
-    mine = list(sharding.shard(time_points, world, rank))
+    mine = sharding.owned(time_points, length, world, rank)
     staged = _stage(mine[0], foreground, contours, config.segmentation_config, lib) if mine else None
     for k, time in enumerate(mine):
         nxt = _stage(mine[k + 1], foreground, contours, config.segmentation_config, lib) if k + 1 < len(mine) else None

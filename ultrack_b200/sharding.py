@@ -56,6 +56,14 @@ def owner_of(index: int, n: int, world: int) -> int:
     raise IndexError(index)
 
 
+def owned(points: Sequence[int], total: int, world: int, rank: int) -> list:
+    """The members of `points` (timepoints of one call, possibly a `batch_index` window) that
+    fall into `rank`'s block of the `total` frames of the timelapse.  `segment` and `link` both
+    use this rule, so the rank that links the pair (t, t+1) is the one that segmented frame t."""
+    lo, hi = block_bounds(total, world, rank)
+    return [t for t in points if lo <= t < hi]
+
+
 def barrier() -> None:
     rank, world = dist_info()
     if world > 1:
