@@ -266,8 +266,8 @@ def main():
     import torch
     import torch.distributed as dist
 
-    from tests.emu_harness import seg_params
     from ultrack_b200 import _lib, bytes_model
+    from ultrack_b200.capi import seg_params
 
     torch.cuda.set_device(local_rank)
     # the rank's host threads (and so its pinned staging buffers) stay on the NUMA node next to

@@ -18,28 +18,24 @@ from __future__ import annotations
 
 from typing import Dict, Optional
 
-# kernel name (as reported by ulk_profile_report) -> bytes per frame voxel per launch (float32 inputs)
+# kernel name (as reported by ulk_profile_report) -> bytes per frame voxel per launch (float32 foreground)
 DENSE_BYTES_PER_VOXEL: Dict[str, float] = {
-    "K_Threshold": 4 + 4 + 0.125,        # fg in; component forest + one foreground bit out (float32 contours are neither staged nor read here)
+    "K_Threshold": 4 + 0.125,            # foreground in; one foreground bit out (contours are not touched here)
 }
-# kernel name -> bytes per FOREGROUND voxel per launch (including the 4-byte list entry)
+# kernel name -> bytes per FOREGROUND voxel per launch.  Every array is rank-indexed (n_fg long);
+# an entry is what the kernel must read or write once for its own voxel.
 LIST_BYTES_PER_FG_VOXEL: Dict[str, float] = {
-    "K_CclUnion": 4 + 4 + 4,             # list, forest in / out (per-voxel form)
-    "K_CclWords": 0.5 + 4 + 4,           # foreground words in (4 per 32-voxel segment), forest in / out
-    "K_FlattenCount": 4 + 4 + 4,
-    "K_LabelCc": 4 + 4 + 4,
-    "K_WriteLabels": 4 + 4 + 4 + 4,      # list, forest, basin, label out
-    "K_MinEdge": 4 + 4 + 4 + 4 + 4,      # list, label, contour in; min weight, min key out
-    "K_Hook1": 4 + 4 + 4 + 4,            # list, key, the other endpoint's key in; forest out
-    "K_CompressCand": 4 + 4 + 4 + 4,     # list, forest in/out, weight
-    "K_CompressRoots": 4 + 4 + 4,
-    "K_AssignBasin": 4 + 4 + 4,
-    "K_BasinAccum": 4 + 4 + 4 + 4 + 4 + 4,   # list, basin, label, weight, key in; join key out
-    "K_RagInsert": 4 + 4 + 4 + 4,        # list, basin, label, contour
-    "K_Attach": 4 + 4 + 4 + 4,           # list, basin, weight, join key
-    "K_K3Init": 4 + 4 + 4,
-    "K_K3Union": 4 + 4 + 4 + 4,
-    "K_K3FlattenCount": 4 + 4 + 4 + 4,
+    "K_Expand": 4 + 4 + 4 + 4,           # contour in (from the volume); list, rank-space contour, forest out
+    "K_CclWords": 0.5 + 4 + 4,           # segment records in, forest in / out
+    "K_FlattenCount": 4 + 4,             # forest in / out
+    "K_LabelCc": 4 + 4,                  # forest in, label out (in place)
+    "K_WriteLabels": 4 + 4 + 4,          # label, pass-A basin in; label out
+    "K_MinEdge": 4 + 4 + 4 + 4 + 4 + 4,  # list, label, contour in; min weight, min key, other endpoint out
+    "K_Hook1": 4 + 4 + 4,                # endpoint, the endpoint's endpoint in; forest out
+    "K_CompressCand": 4 + 4 + 4,         # forest in / out, weight
+    "K_AssignBasin": 4 + 4 + 4,          # forest (two hops) in; basin out
+    "K_BasinAccum": 4 + 4 + 4 + 4 + 4 + 4,   # list, basin, weight, key, endpoint in; join key out
+    "K_Attach": 4 + 4 + 4,               # basin, weight, join key
     "K_MaskPaint": 4 + 4 + 0.125,        # list, basin in; one mask bit out (per emitted ancestor)
 }
 
@@ -56,8 +52,7 @@ def link_bytes(n_links: int, n_pairs: int, mean_mask_words: float) -> int:
 
 # list kernels of the voxel stage: launched once on the voxels of the components above max_area
 # (oversegmentation pass A) and once on the whole foreground (pass B) per frame
-TWO_PASS = {"K_MinEdge", "K_Hook1", "K_CompressCand", "K_CompressRoots", "K_AssignBasin", "K_BasinAccum",
-            "K_RagInsert", "K_Attach"}
+TWO_PASS = {"K_MinEdge", "K_Hook1", "K_CompressCand", "K_AssignBasin", "K_BasinAccum", "K_Attach"}
 
 
 def kernel_bytes(name: str, voxels: int, n_foreground: int, pass_a_voxels: Optional[int] = None) -> Optional[float]:

@@ -72,8 +72,14 @@ int ulk_select_nonneg_i32(const i32 *in, i64 n, i32 *out, i32 *count, ulk_stream
 int ulk_select_list_split_i32(const i32 *list, i64 n, const i32 *bas, const i32 *nroot, i32 *out, i32 *count, ulk_stream_t)
 {
     i32 c = 0;
-    for (i64 i = 0; i < n; ++i) if (nroot[bas[list[i]]] > 1) out[c++] = list[i];
+    for (i64 i = 0; i < n; ++i) { i32 r = list ? list[i] : (i32)i; if (bas[r] >= 0 && nroot[bas[r]] > 1) out[c++] = r; }
     *count = c;
+    return 0;
+}
+int ulk_exclusive_scan_popc_u32(const u32 *words, i32 *out, i64 n, ulk_stream_t)
+{
+    i32 acc = 0;
+    for (i64 i = 0; i < n; ++i) { out[i] = acc; acc += __builtin_popcount(words[i]); }
     return 0;
 }
 int ulk_sort_keys_u32(const u32 *ki, u32 *ko, i64 n, ulk_stream_t)
@@ -454,13 +460,22 @@ int ulk_exclusive_scan_popc_u32(const u32 *words, i32 *out, i64 n, ulk_stream_t 
 }
 struct UlkSplitAt {
     const i32 *bas, *nroot;
-    __device__ bool operator()(const i32 &v) const { return nroot[bas[v]] > 1; }
+    __device__ bool operator()(const i32 &v) const { const i32 b = bas[v]; return b >= 0 && nroot[b] > 1; }
 };
 int ulk_select_list_split_i32(const i32 *list, i64 n, const i32 *bas, const i32 *nroot, i32 *out, i32 *count_dev, ulk_stream_t s)
 {
     if (n <= 0) return ulk_memset(count_dev, 0, sizeof(i32), s);
     UlkSplitAt pred{bas, nroot};
     size_t need = 0;
+    if (!list) {      // the identity list: every foreground rank
+        thrust::counting_iterator<i32> it(0);
+        ULK_CUDA(cub::DeviceSelect::If(nullptr, need, it, out, count_dev, (int)n, pred, s));
+        if (cub_tmp(need)) return -2;
+        ProfScope ps("cub::DeviceSelect::If", s);
+        ULK_CUDA(cub::DeviceSelect::If(g_cub_tmp, need, it, out, count_dev, (int)n, pred, s));
+        ++g_ulk_launches;
+        return 0;
+    }
     ULK_CUDA(cub::DeviceSelect::If(nullptr, need, list, out, count_dev, (int)n, pred, s));
     if (cub_tmp(need)) return -2;
     ProfScope ps("cub::DeviceSelect::If", s);

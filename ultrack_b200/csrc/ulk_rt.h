@@ -117,6 +117,33 @@ template <class F> void ulk_launch_list_multi(const i32 *list, i64 n, ulk_stream
 {
     for (i64 i = 0; i < n; ++i) f((i64)list[i], 0, 0, 0);
 }
+// rank-space list kernels (see the CUDA forms below): entry i of a list is the foreground rank
+// r = rl ? rl[i] : i, its voxel is fgl[r]
+template <int U, class F, class DM> void ulk_launch_rk(const i32 *rl, const i32 *fgl, i64 m, const DM &dm, ulk_stream_t, const F &f)
+{
+    for (i64 i = 0; i < m; ++i) {
+        i32 r = rl ? rl[i] : (i32)i, v = fgl[r], z, y, x;
+        dm.coords(v, z, y, x);
+        f.run(f.load2(f.load1(r, v, z, y, x, true), true), true);
+    }
+}
+template <int UDEF, class F, class DM> void ulk_launch_rkx(const char *, const i32 *rl, const i32 *fgl, i64 m, const DM &dm, ulk_stream_t s, const F &f) { ulk_launch_rk<UDEF>(rl, fgl, m, dm, s, f); }
+template <int U, class F> void ulk_launch_rkn(const i32 *rl, i64 m, ulk_stream_t, const F &f)
+{
+    for (i64 i = 0; i < m; ++i) { i32 r = rl ? rl[i] : (i32)i; f.run(f.load2(f.load1(r, true), true), true); }
+}
+template <class F> void ulk_launch_rk_multi(const i32 *rl, i64 m, ulk_stream_t, const F &f)
+{
+    for (i64 i = 0; i < m; ++i) f(rl ? rl[i] : (i32)i);
+}
+template <class F, class DM> void ulk_launch_rk1(const i32 *rl, const i32 *fgl, i64 m, const DM &dm, ulk_stream_t, const F &f)
+{
+    for (i64 i = 0; i < m; ++i) {
+        i32 r = rl ? rl[i] : (i32)i, v = fgl[r], z, y, x;
+        dm.coords(v, z, y, x);
+        f(r, v, z, y, x);
+    }
+}
 #else
 template <class F> __global__ void __launch_bounds__(256) ulk_kernel(i64 n, F f)
 {
@@ -300,6 +327,120 @@ template <class F> void ulk_launch_list_multi(const i32 *list, i64 n, ulk_stream
     ++g_ulk_launches;
     if (g_ulk_debug_sync) ulk_debug_after_launch(typeid(F).name(), s);
 }
+// ---- rank-space list kernels.  Every per-voxel array of the voxel stage is indexed by the
+// foreground RANK of the voxel (its position in the raster-ordered foreground list fgl), so a
+// kernel's own accesses are dense whatever the foreground fraction.  A list entry i is the rank
+// r = rl ? rl[i] : i (rl == nullptr: the whole foreground); its voxel is fgl[r].  Lane l of a warp
+// holds entry 32k + l: x-neighbours in the frame are neighbours in the warp.
+// phased, with coordinates: S1 load1(r, v, z, y, x, ok) -> S2 load2(S1, ok) -> run(S2, ok)
+template <int U, class F, class DM> __global__ void __launch_bounds__(256) ulk_kernel_rk(const i32 *rl, const i32 *fgl, i64 m, DM dm, F f)
+{
+    const i64 base = (i64)blockIdx.x * (256 * U) + threadIdx.x;
+    typename F::S1 a[U];
+    typename F::S2 b[U];
+    bool ok[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        const i64 i = base + u * 256;
+        ok[u] = i < m;
+        i32 r = 0, v = 0, z = 0, y = 0, x = 0;
+        if (ok[u]) { r = rl ? rl[i] : (i32)i; v = fgl[r]; dm.coords(v, z, y, x); }
+        a[u] = f.load1(r, v, z, y, x, ok[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) b[u] = f.load2(a[u], ok[u]);
+#pragma unroll
+    for (int u = 0; u < U; ++u) f.run(b[u], ok[u]);
+}
+template <int U, class F, class DM> void ulk_launch_rk(const i32 *rl, const i32 *fgl, i64 m, const DM &dm, ulk_stream_t s, const F &f)
+{
+    if (m <= 0) return;
+    if (g_ulk_prof_on) ulk_prof_begin(typeid(F).name(), s);
+    ulk_kernel_rk<U, F, DM><<<(unsigned)((m + 256 * U - 1) / (256 * U)), 256, 0, s>>>(rl, fgl, m, dm, f);
+    if (g_ulk_prof_on) ulk_prof_end(s);
+    ++g_ulk_launches;
+    if (g_ulk_debug_sync) ulk_debug_after_launch(typeid(F).name(), s);
+}
+template <int UDEF, class F, class DM> void ulk_launch_rkx(const char *tag, const i32 *rl, const i32 *fgl, i64 m, const DM &dm, ulk_stream_t s, const F &f)
+{
+    char name[64];
+    snprintf(name, sizeof(name), "ULK_U_%s", tag);
+    const char *e = getenv(name);
+    int U = e ? atoi(e) : UDEF;
+    if (U == 1) ulk_launch_rk<1>(rl, fgl, m, dm, s, f);
+    else if (U == 2) ulk_launch_rk<2>(rl, fgl, m, dm, s, f);
+    else ulk_launch_rk<4>(rl, fgl, m, dm, s, f);
+}
+// phased, rank only (no voxel index, no coordinates): S1 load1(r, ok) -> S2 load2(S1, ok) -> run(S2, ok)
+template <int U, class F> __global__ void __launch_bounds__(256) ulk_kernel_rkn(const i32 *rl, i64 m, F f)
+{
+    const i64 base = (i64)blockIdx.x * (256 * U) + threadIdx.x;
+    typename F::S1 a[U];
+    typename F::S2 b[U];
+    bool ok[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        const i64 i = base + u * 256;
+        ok[u] = i < m;
+        const i32 r = ok[u] ? (rl ? rl[i] : (i32)i) : 0;
+        a[u] = f.load1(r, ok[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) b[u] = f.load2(a[u], ok[u]);
+#pragma unroll
+    for (int u = 0; u < U; ++u) f.run(b[u], ok[u]);
+}
+template <int U, class F> void ulk_launch_rkn(const i32 *rl, i64 m, ulk_stream_t s, const F &f)
+{
+    if (m <= 0) return;
+    if (g_ulk_prof_on) ulk_prof_begin(typeid(F).name(), s);
+    ulk_kernel_rkn<U, F><<<(unsigned)((m + 256 * U - 1) / (256 * U)), 256, 0, s>>>(rl, m, f);
+    if (g_ulk_prof_on) ulk_prof_end(s);
+    ++g_ulk_launches;
+    if (g_ulk_debug_sync) ulk_debug_after_launch(typeid(F).name(), s);
+}
+// pointer chasing: ULK_MULTI ranks per thread, F::multi(r[], ok[]) from every thread of the block
+template <class F> __global__ void __launch_bounds__(256) ulk_kernel_rk_multi(const i32 *rl, i64 m, F f)
+{
+    const i64 base = (i64)blockIdx.x * (256 * ULK_MULTI) + threadIdx.x;
+    i32 r[ULK_MULTI];
+    bool ok[ULK_MULTI];
+#pragma unroll
+    for (int u = 0; u < ULK_MULTI; ++u) {
+        const i64 i = base + u * 256;
+        ok[u] = i < m;
+        r[u] = ok[u] ? (rl ? rl[i] : (i32)i) : -1;
+    }
+    f.multi(r, ok);
+}
+template <class F> void ulk_launch_rk_multi(const i32 *rl, i64 m, ulk_stream_t s, const F &f)
+{
+    if (m <= 0) return;
+    if (g_ulk_prof_on) ulk_prof_begin(typeid(F).name(), s);
+    ulk_kernel_rk_multi<F><<<(unsigned)((m + 256 * ULK_MULTI - 1) / (256 * ULK_MULTI)), 256, 0, s>>>(rl, m, f);
+    if (g_ulk_prof_on) ulk_prof_end(s);
+    ++g_ulk_launches;
+    if (g_ulk_debug_sync) ulk_debug_after_launch(typeid(F).name(), s);
+}
+// one thread per entry, with coordinates: f(r, v, z, y, x)   (short lists)
+template <class F, class DM> __global__ void __launch_bounds__(256) ulk_kernel_rk1(const i32 *rl, const i32 *fgl, i64 m, DM dm, F f)
+{
+    const i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const i32 r = rl ? rl[i] : (i32)i, v = fgl[r];
+    i32 z, y, x;
+    dm.coords(v, z, y, x);
+    f(r, v, z, y, x);
+}
+template <class F, class DM> void ulk_launch_rk1(const i32 *rl, const i32 *fgl, i64 m, const DM &dm, ulk_stream_t s, const F &f)
+{
+    if (m <= 0) return;
+    if (g_ulk_prof_on) ulk_prof_begin(typeid(F).name(), s);
+    ulk_kernel_rk1<F, DM><<<(unsigned)((m + 255) / 256), 256, 0, s>>>(rl, fgl, m, dm, f);
+    if (g_ulk_prof_on) ulk_prof_end(s);
+    ++g_ulk_launches;
+    if (g_ulk_debug_sync) ulk_debug_after_launch(typeid(F).name(), s);
+}
 #endif
 int ulk_prof_report(char *buf, i64 cap);   // "name\tlaunches\ttotal_ms\n" per kernel; returns bytes needed
 void ulk_prof_enable(int on);
@@ -339,10 +480,8 @@ int ulk_select_nonneg_i32(const i32 *in, i64 n, i32 *out, i32 *count_dev, ulk_st
 int ulk_sort_keys_u64(const u64 *keys_in, u64 *keys_out, i64 n, ulk_stream_t s);
 // entries v of a voxel list (order kept) whose basin still has more than one root
 int ulk_select_list_split_i32(const i32 *list, i64 n, const i32 *bas, const i32 *nroot, i32 *out, i32 *count_dev, ulk_stream_t s);
-#ifndef ULK_EMU
 // exclusive prefix sum of the population counts of n 32-bit words
 int ulk_exclusive_scan_popc_u32(const u32 *words, i32 *out, i64 n, ulk_stream_t s);
-#endif
 
 // ---------------------------------------------------------------- numerics
 // order-preserving map float32 -> uint32 (handles negatives)

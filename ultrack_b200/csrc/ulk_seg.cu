@@ -117,7 +117,7 @@ struct K_MaskPaint {
     }
     struct S1 { i32 z, y, x, b; };
     struct S2 { i32 z, y, x, b, n; };
-    ULK_D ULK_INLINE S1 load1(i32 v, i32 z, i32 y, i32 x, bool ok) const { S1 s; s.z = z; s.y = y; s.x = x; s.b = ok ? bas[v] : -1; return s; }
+    ULK_D ULK_INLINE S1 load1(i32 r, i32, i32 z, i32 y, i32 x, bool ok) const { S1 s; s.z = z; s.y = y; s.x = x; s.b = ok ? bas[r] : -1; return s; }
     ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const { S2 s; s.z = a.z; s.y = a.y; s.x = a.x; s.b = a.b; s.n = a.b >= 0 ? bnode[a.b] : -1; return s; }
     // lanes of one basin climb the same ancestor chain in lockstep; those that fall into the
     // same mask word (consecutive x of one row) merge their bits and issue one atomic
@@ -183,217 +183,166 @@ struct K_OverlapWrite {
 struct K_Iota { u32 *p; ULK_D void operator()(i64 i) const { p[i] = (u32)i; } };
 struct K_Valid { const u32 *c; i32 *f; ULK_D void operator()(i64 i) const { f[i] = c[i] != ULK_NONE32; } };
 
-// ------------------------------------------------------------------ threshold + foreground list
-// K_Threshold streams the two input volumes once: a warp takes U consecutive 32-voxel row
-// segments, issues all its loads first, then writes the component forest (runs hooked to
-// their first voxel) and one foreground bit word per segment.  The raster-ordered foreground
-// list comes from those words (prefix sum of their population counts + one expansion pass),
-// not from a second pass over the voxels.
+// ------------------------------------------------------------------ threshold + foreground map
+// The dense front end streams the foreground volume ONCE and writes one bit per voxel (a 32-bit
+// word per 32-voxel row segment); nothing V-sized is written.  A prefix sum of the words'
+// population counts gives every segment the rank of its first foreground voxel, and one
+// expansion pass builds the rank-space arrays every later kernel works on (K_Expand).
 #ifndef ULK_EMU
-template <int U, bool F32> __global__ void __launch_bounds__(256)
-ulk_threshold_kernel(K_Threshold k, i32 W, u32 S, u32 ntask, u32 *words)
+// generic dtype / ragged width: a warp takes U consecutive row segments, lane l tests voxel l
+template <int U> __global__ void __launch_bounds__(256)
+ulk_threshold_kernel(K_Threshold k, u32 ntask)
 {
     const int lane = threadIdx.x & 31;
     const u32 t0 = (u32)((((i64)blockIdx.x * 256 + threadIdx.x) >> 5) * U);
     if (t0 >= ntask) return;                  // the whole warp leaves together
+    const u32 S = (u32)k.S;
     u32 r = t0 / S, sg = t0 - r * S;
-    i64 v[U]; bool valid[U]; float f[U], c[U];
+    double f[U]; bool valid[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-        i32 x = (i32)sg * 32 + lane;
-        valid[u] = t0 + u < ntask && x < W;
-        v[u] = (i64)r * W + x;
-        if (F32 && valid[u]) { f[u] = ((const float *)k.fg)[v[u]]; c[u] = k.skip_ct ? 0.f : ((const float *)k.ct)[v[u]]; }
+        const i32 x = (i32)sg * 32 + lane;
+        valid[u] = t0 + u < ntask && x < k.dm.W;
+        f[u] = valid[u] ? ulk_load_as_double(k.fg, k.fgt, (i64)r * k.dm.W + x) : 0.0;
         if (++sg == S) { sg = 0; ++r; }
     }
-    u32 mx = 0;
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-        bool on = false;
-        u32 bits = 0;
-        if (valid[u]) {
-            if (F32) {
-                on = (double)f[u] > k.thr;
-                float a = fabsf(c[u]);
-                if (!k.skip_ct && a <= 3.0e38f) bits = __float_as_uint(a);
-            } else on = k.stage(v[u], bits);
-        }
-        mx = bits > mx ? bits : mx;
-        bool prev = __shfl_up_sync(0xffffffffu, on ? 1 : 0, 1) != 0;
-        u32 linked = __ballot_sync(0xffffffffu, on && prev && lane > 0);
-        u32 fgm = __ballot_sync(0xffffffffu, on);
-        if (valid[u]) k.P[v[u]] = on ? (i32)v[u] - (lane - ulk_run_start(linked, lane)) : -1;
-        if (lane == 0 && t0 + u < ntask) words[t0 + u] = fgm;
+        const u32 word = __ballot_sync(0xffffffffu, valid[u] && f[u] > k.thr);
+        if (lane == 0 && t0 + u < ntask) k.words[t0 + u] = word;
     }
-    u32 m = __reduce_max_sync(0xffffffffu, mx);
-    if (lane == 0 && m > *k.cmax) atomicMax(k.cmax, m);
 }
-// float32 + float32 inputs, W % 4 == 0, 16-byte aligned volumes: a lane loads four consecutive
-// voxels of each volume with one 128-bit load, a warp covers four 32-voxel row segments; the
-// foreground word of a segment is the OR of its eight lanes' nibbles, and the run starts of a
-// lane's voxels follow from that word alone (linked = word & word << 1)
-template <int U, bool CT> __global__ void __launch_bounds__(256)
-ulk_threshold_kernel_v4(K_Threshold k, i32 W, u32 S, u32 T, u32 ntask4, u32 *words)
+// W % 4 == 0 and aligned volumes: a lane loads four consecutive voxels with one vector load, a warp
+// covers four 32-voxel row segments per task; the foreground word of a segment is the OR of its
+// eight lanes' nibbles.  All U loads of a thread are issued before the first is used.
+struct UlkLoadF32 {
+    typedef float4 Raw;
+    static __device__ __forceinline__ Raw load(const void *p, i64 v) { return __ldcs((const float4 *)((const float *)p + v)); }
+    static __device__ __forceinline__ u32 nib(const Raw &f, double thr)
+    {
+        return ((double)f.x > thr ? 1u : 0u) | ((double)f.y > thr ? 2u : 0u) | ((double)f.z > thr ? 4u : 0u) | ((double)f.w > thr ? 8u : 0u);
+    }
+};
+struct UlkLoadU8 {
+    typedef u32 Raw;
+    static __device__ __forceinline__ Raw load(const void *p, i64 v) { return __ldcs((const u32 *)((const u8 *)p + v)); }
+    static __device__ __forceinline__ u32 nib(const Raw &q, double thr)
+    {
+        return ((double)(q & 0xffu) > thr ? 1u : 0u) | ((double)((q >> 8) & 0xffu) > thr ? 2u : 0u) |
+               ((double)((q >> 16) & 0xffu) > thr ? 4u : 0u) | ((double)(q >> 24) > thr ? 8u : 0u);
+    }
+};
+struct UlkLoadF16 {
+    typedef uint2 Raw;
+    static __device__ __forceinline__ Raw load(const void *p, i64 v) { return __ldcs((const uint2 *)((const uint16_t *)p + v)); }
+    static __device__ __forceinline__ u32 nib(const Raw &q, double thr)
+    {
+        const float a = ulk_half_to_float((uint16_t)(q.x & 0xffffu)), b = ulk_half_to_float((uint16_t)(q.x >> 16));
+        const float c = ulk_half_to_float((uint16_t)(q.y & 0xffffu)), d = ulk_half_to_float((uint16_t)(q.y >> 16));
+        return ((double)a > thr ? 1u : 0u) | ((double)b > thr ? 2u : 0u) | ((double)c > thr ? 4u : 0u) | ((double)d > thr ? 8u : 0u);
+    }
+};
+template <int U, class L> __global__ void __launch_bounds__(256)
+ulk_threshold_kernel_v4(const void *fg, double thr, i32 W, u32 S, u32 T, u32 ntask4, u32 *words)
 {
     const int lane = threadIdx.x & 31;
     const u32 t0 = (u32)((((i64)blockIdx.x * 256 + threadIdx.x) >> 5) * U);
     if (t0 >= ntask4) return;                 // the whole warp leaves together
     u32 r = t0 / T, q = t0 - r * T;           // row, 128-voxel chunk of the row
-    float4 f[U], c[U]; i64 v[U]; bool valid[U]; u32 wbase[U];
+    typename L::Raw f[U]; bool valid[U]; u32 wbase[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
         const i32 x = (i32)q * 128 + lane * 4;
         valid[u] = t0 + u < ntask4 && x < W;
-        v[u] = (i64)r * W + x;
         wbase[u] = r * S + q * 4u;
-        if (valid[u]) {
-            f[u] = *(const float4 *)((const float *)k.fg + v[u]);
-            if (CT) c[u] = *(const float4 *)((const float *)k.ct + v[u]);
-        }
+        if (valid[u]) f[u] = L::load(fg, (i64)r * W + x);
         if (++q == T) { q = 0; ++r; }
     }
-    u32 mx = 0;
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-        u32 nib = 0;
-        if (valid[u]) {
-            nib = ((double)f[u].x > k.thr ? 1u : 0u) | ((double)f[u].y > k.thr ? 2u : 0u) | ((double)f[u].z > k.thr ? 4u : 0u) | ((double)f[u].w > k.thr ? 8u : 0u);
-            if (CT) {
-                const float a0 = fabsf(c[u].x), a1 = fabsf(c[u].y), a2 = fabsf(c[u].z), a3 = fabsf(c[u].w);
-                u32 b;
-                b = a0 <= 3.0e38f ? __float_as_uint(a0) : 0u; mx = b > mx ? b : mx;
-                b = a1 <= 3.0e38f ? __float_as_uint(a1) : 0u; mx = b > mx ? b : mx;
-                b = a2 <= 3.0e38f ? __float_as_uint(a2) : 0u; mx = b > mx ? b : mx;
-                b = a3 <= 3.0e38f ? __float_as_uint(a3) : 0u; mx = b > mx ? b : mx;
-            }
-        }
+        const u32 nib = valid[u] ? L::nib(f[u], thr) : 0u;
         const int sub = lane >> 3, pos = (lane & 7) * 4;
         const u32 word = __reduce_or_sync(0xffu << (sub * 8), nib << pos);
-        const u32 linked = word & (word << 1);
-        if (valid[u]) {
-            int4 o;
-            const i32 vb = (i32)v[u] - pos;        // first voxel of this 32-voxel segment
-            o.x = (nib & 1u) ? vb + ulk_run_start(linked, pos) : -1;
-            o.y = (nib & 2u) ? vb + ulk_run_start(linked, pos + 1) : -1;
-            o.z = (nib & 4u) ? vb + ulk_run_start(linked, pos + 2) : -1;
-            o.w = (nib & 8u) ? vb + ulk_run_start(linked, pos + 3) : -1;
-            *(int4 *)(k.P + v[u]) = o;
-            if ((lane & 7) == 0) words[wbase[u] + sub] = word;
-        }
-    }
-    if (CT) {
-        u32 m = __reduce_max_sync(0xffffffffu, mx);
-        if (lane == 0 && m > *k.cmax) atomicMax(k.cmax, m);
+        if (valid[u] && (lane & 7) == 0) words[wbase[u] + sub] = word;
     }
 }
+// expansion, warp cooperative: a thread owns one segment record; the warp then walks its
+// non-empty segments and lane l emits voxel l of the segment
 __global__ void __launch_bounds__(256)
-ulk_expand_kernel(const u32 *words, const i32 *off, u32 ntask, i32 W, u32 S, UlkFastDiv fS, i32 *list, i32 *count)
+ulk_expand_kernel(K_Expand k, u32 ntask, UlkFastDiv fS)
 {
     const int lane = threadIdx.x & 31;
     const u32 t = blockIdx.x * 256u + threadIdx.x;
     u32 w = 0; i32 o = 0, base = 0;
     if (t < ntask) {
-        w = words[t]; o = off[t];
-        u32 r = fS.div(t);
-        base = (i32)(r * (u32)W + (t - r * S) * 32u);
+        w = k.words[t]; o = k.off[t];
+        const u32 r = fS.div(t);
+        base = (i32)(r * (u32)k.dm.W + (t - r * (u32)k.S) * 32u);
+        UlkOW e;
+        e.w = w; e.o = o;
+        k.ow[t] = e;
     }
-    if (t == ntask - 1) *count = o + __popc(w);
     u32 m = __ballot_sync(0xffffffffu, w != 0);
+    u32 mx = 0;
     while (m) {
-        int j = __ffs(m) - 1;
+        const int j = __ffs(m) - 1;
         m &= m - 1;
-        u32 wj = __shfl_sync(0xffffffffu, w, j);
-        i32 oj = __shfl_sync(0xffffffffu, o, j), bj = __shfl_sync(0xffffffffu, base, j);
-        if ((wj >> lane) & 1u) list[oj + __popc(wj & ((1u << lane) - 1u))] = bj + lane;
+        const u32 wj = __shfl_sync(0xffffffffu, w, j);
+        const i32 oj = __shfl_sync(0xffffffffu, o, j), bj = __shfl_sync(0xffffffffu, base, j);
+        if ((wj >> lane) & 1u) {
+            const int st = ulk_run_start(wj & (wj << 1), lane);
+            const u32 bits = k.emit(oj + __popc(wj & ((1u << lane) - 1u)), bj + lane, oj + __popc(wj & ((1u << st) - 1u)));
+            mx = bits > mx ? bits : mx;
+        }
     }
-}
-// Connected components from the foreground bit words: one thread per 32-voxel row segment.
-// Every x-run inside a segment is already hooked to its first voxel (K_Threshold), so what is
-// left is one union per run of overlap with the row above / the slice above (start bits of
-// w & w_up) and one across the segment boundary; the per-voxel neighbour tests of K_CclUnion
-// become three word loads.  Size counters of all run starts (the only possible roots) are zeroed.
-__global__ void __launch_bounds__(256)
-ulk_ccl_words_kernel(const u32 *words, u32 ntask, i32 W, i32 H, u32 S, UlkFastDiv fS, UlkFastDiv fH, i32 *P, i32 *cnt)
-{
-    const u32 t = blockIdx.x * 256u + threadIdx.x;
-    if (t >= ntask) return;
-    const u32 w = words[t];
-    const u32 r = fS.div(t), sg = t - r * S;          // row (z*H + y), segment of the row
-    const u32 zz = fH.div(r), y = r - zz * (u32)H;
-    const u32 wl = sg > 0 ? words[t - 1] : 0u;
-    const u32 wy = y > 0 ? words[t - S] : 0u;
-    const u32 wz = zz > 0 ? words[t - S * (u32)H] : 0u;
-    if (w == 0) return;
-    const i32 base = (i32)(r * (u32)W + sg * 32u);
-    for (u32 m = w & ~(w << 1); m; m &= m - 1) cnt[base + __ffs(m) - 1] = 0;
-    if ((w & 1u) && (wl >> 31)) ulk_vunion(P, base, base - 1);
-    u32 o = w & wy;
-    for (u32 m = o & ~(o << 1); m; m &= m - 1) { const i32 v = base + __ffs(m) - 1; ulk_vunion(P, v, v - W); }
-    o = w & wz;
-    for (u32 m = o & ~(o << 1); m; m &= m - 1) { const i32 v = base + __ffs(m) - 1; ulk_vunion(P, v, v - W * H); }
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    if (lane == 0 && mx > *k.cmax) atomicMax(k.cmax, mx);
 }
 #endif
-// P (component forest, -1 on the background), *cmax, the foreground list and its length; on the
-// GPU also the connected-component unions (they run on the foreground words)
-static int threshold_and_list(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const K_Threshold &k, i32 *fgl, i32 *nfg_dev, i32 *cnt, bool *ccl_done)
+// foreground words of the frame (one per 32-voxel row segment)
+static int threshold_words(ulk_stream_t st, const UlkDims &dm, const void *fg, int fgt, double thr, i32 S, i64 nt, u32 *words)
 {
-    *ccl_done = false;
+    K_Threshold k{fg, fgt, thr, dm, S, words};
 #ifdef ULK_EMU
-    ulk_launch_vox_warp(dm.D, dm.H, dm.W, st, k);
-    return ulk_select_nonneg_i32(k.P, dm.V, fgl, nfg_dev, st);
+    ulk_launch(nt, st, k);
 #else
-    const u32 S = (u32)((dm.W + 31) / 32);
-    const i64 nt = (i64)dm.D * dm.H * S;
-    const u32 ntask = (u32)nt;
-    u32 *words = A.get<u32>(nt);
-    i32 *off = A.get<i32>(nt);
-    CHKA(A);
-    static const int U = getenv("ULK_THR_U") ? atoi(getenv("ULK_THR_U")) : 4;
-    const i64 warps = (nt + U - 1) / U;
-    const unsigned grid = (unsigned)((warps + 7) / 8);
     if (g_ulk_prof_on) ulk_prof_begin(typeid(K_Threshold).name(), st);
-    const bool vec4 = k.fgt == ULK_F32 && k.ctt == ULK_F32 && dm.W % 4 == 0 && !getenv("ULK_THR_SCALAR") &&
-                      (((uintptr_t)k.fg | (uintptr_t)k.ct | (uintptr_t)k.P) & 15u) == 0;
+    const int esz = ulk_dtype_size(fgt);
+    const bool vec4 = (fgt == ULK_F32 || fgt == ULK_U8 || fgt == ULK_F16) && dm.W % 4 == 0 && !getenv("ULK_THR_SCALAR") &&
+                      ((uintptr_t)fg & (uintptr_t)(4 * esz - 1)) == 0;
     if (vec4) {
         const u32 T = (u32)((dm.W + 127) / 128);
         const i64 nt4 = (i64)dm.D * dm.H * T;
-        const int U4 = 2;
-        const i64 warps4 = (nt4 + U4 - 1) / U4;
-        const i64 warps4b = (nt4 + 3) / 4;
-        if (k.skip_ct) ulk_threshold_kernel_v4<4, false><<<(unsigned)((warps4b + 7) / 8), 256, 0, st>>>(k, dm.W, S, T, (u32)nt4, words);
-        else ulk_threshold_kernel_v4<U4, true><<<(unsigned)((warps4 + 7) / 8), 256, 0, st>>>(k, dm.W, S, T, (u32)nt4, words);
-    } else if (k.fgt == ULK_F32 && k.ctt == ULK_F32) {
-        if (U == 8) ulk_threshold_kernel<8, true><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
-        else if (U == 2) ulk_threshold_kernel<2, true><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
-        else ulk_threshold_kernel<4, true><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
+        static const int U4 = getenv("ULK_THR_U") ? atoi(getenv("ULK_THR_U")) : 4;
+        const i64 warps = (nt4 + U4 - 1) / U4;
+        const unsigned grid = (unsigned)((warps + 7) / 8);
+#define ULK_THR_LAUNCH(UU, LL) ulk_threshold_kernel_v4<UU, LL><<<grid, 256, 0, st>>>(fg, thr, dm.W, (u32)S, T, (u32)nt4, words)
+        if (fgt == ULK_F32) { if (U4 == 8) ULK_THR_LAUNCH(8, UlkLoadF32); else if (U4 == 2) ULK_THR_LAUNCH(2, UlkLoadF32); else ULK_THR_LAUNCH(4, UlkLoadF32); }
+        else if (fgt == ULK_U8) { if (U4 == 8) ULK_THR_LAUNCH(8, UlkLoadU8); else if (U4 == 2) ULK_THR_LAUNCH(2, UlkLoadU8); else ULK_THR_LAUNCH(4, UlkLoadU8); }
+        else { if (U4 == 8) ULK_THR_LAUNCH(8, UlkLoadF16); else if (U4 == 2) ULK_THR_LAUNCH(2, UlkLoadF16); else ULK_THR_LAUNCH(4, UlkLoadF16); }
+#undef ULK_THR_LAUNCH
     } else {
-        if (U == 8) ulk_threshold_kernel<8, false><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
-        else if (U == 2) ulk_threshold_kernel<2, false><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
-        else ulk_threshold_kernel<4, false><<<grid, 256, 0, st>>>(k, dm.W, S, ntask, words);
+        const i64 warps = (nt + 3) / 4;
+        ulk_threshold_kernel<4><<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(k, (u32)nt);
     }
     if (g_ulk_prof_on) ulk_prof_end(st);
     ++g_ulk_launches;
     if (g_ulk_debug_sync) ulk_debug_after_launch("K_Threshold", st);
-    CHK(ulk_exclusive_scan_popc_u32(words, off, nt, st));
+#endif
+    return 0;
+}
+static void expand_words(ulk_stream_t st, const K_Expand &k, i64 nt)
+{
+#ifdef ULK_EMU
+    ulk_launch(nt, st, k);
+#else
     UlkFastDiv fS;
-    fS.init(S);
-    if (g_ulk_prof_on) ulk_prof_begin("K_ExpandForeground", st);
-    ulk_expand_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(words, off, ntask, dm.W, S, fS, fgl, nfg_dev);
+    fS.init((u32)k.S);
+    if (g_ulk_prof_on) ulk_prof_begin(typeid(K_Expand).name(), st);
+    ulk_expand_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(k, (u32)nt, fS);
     if (g_ulk_prof_on) ulk_prof_end(st);
     ++g_ulk_launches;
-    if (g_ulk_debug_sync) ulk_debug_after_launch("K_ExpandForeground", st);
-    if (!getenv("ULK_CCL_VOXEL")) {
-        UlkFastDiv fH;
-        fH.init((u32)dm.H);
-        if (g_ulk_prof_on) ulk_prof_begin("K_CclWords", st);
-        ulk_ccl_words_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(words, ntask, dm.W, dm.H, S, fS, fH, k.P, cnt);
-        if (g_ulk_prof_on) ulk_prof_end(st);
-        ++g_ulk_launches;
-        if (g_ulk_debug_sync) ulk_debug_after_launch("K_CclWords", st);
-        *ccl_done = true;
-    }
-    A.release(words); A.release(off);
-    return 0;
+    if (g_ulk_debug_sync) ulk_debug_after_launch("K_Expand", st);
 #endif
 }
 
@@ -418,53 +367,48 @@ struct VoxelStage {
     u32 *mw = nullptr, *jk = nullptr;
 };
 
-static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i32 *fgl, i64 nfg, const UlkCt &ct, const i32 *lab,
-                       i32 R, bool need_join, bool need_k3, bool need_stats, u32 *cmax_late, int *fix_shift,
+// One watershed-collapse pass over a list of foreground voxels: `rl` holds the ranks of the
+// list (nullptr: every foreground voxel), m its length; every array is indexed by rank.
+static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkFg &fg, const i32 *rl, i64 m, const UlkCt &ct, const i32 *lab,
+                       i32 R, bool need_join, bool need_k3, bool need_stats, int fix_shift,
                        VoxelStage &out, ulk_seg_stats *stats)
 {
-    // cmax_late != null: max |ct| over this stage's voxels is found by K_MinEdge and *fix_shift is
-    // derived from it here; otherwise *fix_shift comes from the caller (K_Threshold saw every voxel)
-    double fixscale = ldexp(1.0, *fix_shift);
-    const i64 V = dm.V;
-    u32 *mw = A.get<u32>(V), *pk = A.get<u32>(V);
-    i32 *bp = A.get<i32>(V);
-    u8 *state = A.get<u8>(V + 4);
-    u32 *Lr = A.get<u32>(V), *best = A.get<u32>(V);
-    u8 *fmark = A.get<u8>(V + 8);
-    i32 *cand = A.get<i32>(V), *cand2 = A.get<i32>(V);
-    i32 *groots = A.get<i32>(V);
-    i32 *sroots = A.get<i32>(nfg);   // every supervertex root after the hook round
-    i32 *ctr = A.get<i32>(8);        // [0] candidates [1] growing roots [2] scratch flag [4] basins [5] flow edges
+    const double fixscale = ldexp(1.0, fix_shift);
+    const UlkDims &dm = fg.dm;
+    const i64 n = fg.n;
+    u32 *mw = A.get<u32>(n), *pk = A.get<u32>(n);
+    i32 *po = A.get<i32>(n);
+    i32 *bp = A.get<i32>(n);
+    u8 *state = A.get<u8>(n + 4);
+    u32 *Lr = A.get<u32>(n), *best = A.get<u32>(n);
+    u8 *fmark = A.get<u8>(n + 8);
+    i32 *cand = A.get<i32>(m), *cand2 = A.get<i32>(m);
+    i32 *groots = A.get<i32>(m);
+    i32 *sroots = A.get<i32>(m);     // every supervertex root after the hook round
+    i32 *ctr = A.get<i32>(8);        // [0] candidates [1] growing roots [2] scratch flag [4] basins [5] flow edges [6] supervertex roots
     CHKA(A);
-    CHK(ulk_memset(fmark, 0, (size_t)V + 8, st));
+    CHK(ulk_memset(fmark, 0, (size_t)n + 8, st));
     CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
-    if (cmax_late) CHK(ulk_memset(cmax_late, 0, sizeof(u32), st));
-    ulk_launch_list_phx<1>("MinEdge", fgl, nfg, dm, st, K_MinEdge{lab, ct, dm, mw, pk, cmax_late});
-    ulk_launch_list_phx<4>("Hook1", fgl, nfg, dm, st, K_Hook1{mw, pk, dm, bp, state, Lr, best, ctr + 4});
-    ulk_launch_list_multi(fgl, nfg, st, K_CompressCand{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1, sroots, ctr + 6});
+    ulk_launch_rkx<1>("MinEdge", rl, fg.fgl, m, dm, st, K_MinEdge{lab, ct, fg, mw, pk, po});
+    ulk_launch_rkn<4>(rl, m, st, K_Hook1{mw, po, bp, state, Lr, best, ctr + 4});
+    ulk_launch_rk_multi(rl, m, st, K_CompressCand{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1, sroots, ctr + 6});
     i32 hc[8];
     CHK(ulk_read(hc, ctr, 8, st));
     i32 ncand = hc[0], ng = hc[1];
     const i32 nsroots = hc[6];
-    if (cmax_late) {
-        u32 h_cmax = 0;
-        CHK(ulk_read(&h_cmax, cmax_late, 1, st));
-        *fix_shift = ulk_fix_shift_for(h_cmax);
-        fixscale = ldexp(1.0, *fix_shift);
-    }
     // every growing root hooks at most once: that bounds the flow-edge list
     const i32 flow_cap = ng;
-    i32 *groots2 = A.get<i32>(ng), *tgt = A.get<i32>(ng);
-    i32 *flow_root = A.get<i32>(flow_cap);
+    i32 *groots2 = A.get<i32>(ng), *tgt = A.get<i32>(ng), *srcr = A.get<i32>(ng);
+    i32 *flow_root = A.get<i32>(flow_cap), *flow_src = A.get<i32>(flow_cap);
     u32 *flow_key = A.get<u32>(flow_cap);
     CHKA(A);
     int rounds = 0;
     while (ng > 0) {
         CHK(ulk_memset(ctr, 0, 2 * sizeof(i32), st));
-        ulk_launch(ncand, st, K_FindFlow{cand, lab, bp, mw, Lr, state, ct, dm, best, cand2, ctr + 0});
-        ulk_launch(ng, st, K_Decide1{groots, bp, best, dm, tgt});
-        ulk_launch(ng, st, K_Decide2{groots, tgt, bp, state, best, fmark, groots2, ctr + 1,
-                                     flow_root, flow_key, ctr + 5, ctr + 4});
+        ulk_launch(ncand, st, K_FindFlow{cand, lab, bp, mw, Lr, state, ct, fg, best, cand2, ctr + 0});
+        ulk_launch(ng, st, K_Decide1{groots, bp, best, fg, tgt, srcr});
+        ulk_launch(ng, st, K_Decide2{groots, tgt, srcr, bp, state, best, fmark, groots2, ctr + 1,
+                                     flow_root, flow_key, flow_src, ctr + 5, ctr + 4});
         CHK(ulk_read(hc, ctr, 8, st));
         ncand = hc[0]; ng = hc[1];
         i32 *t = cand; cand = cand2; cand2 = t;
@@ -474,27 +418,27 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     if (stats) stats->flow_rounds += rounds;
     const i32 B = hc[4], nflow = hc[5];
     out.B = B;
-    A.release(cand); A.release(cand2); A.release(groots); A.release(groots2); A.release(tgt);
+    A.release(cand); A.release(cand2); A.release(groots); A.release(groots2); A.release(tgt); A.release(srcr);
 
-    // ---- basin ids, grouped by region label: sort of the (label, root voxel) keys
+    // ---- basin ids, grouped by region label: sort of the (label, root rank) keys
     u64 *rootkeys = A.get<u64>(B), *rootsorted = A.get<u64>(B);
     out.g_root = A.get<i32>(B); out.g_lab = A.get<i32>(B); out.g_L = A.get<u32>(B);
     out.bs = A.get<i32>(R + 1);
     i32 *lab_hist = A.get<i32>(R + 1);
-    out.bas = A.get<i32>(V);
+    out.bas = A.get<i32>(n);
     CHKA(A);
     CHK(ulk_memset(ctr, 0, sizeof(i32), st));
     CHK(ulk_memset(lab_hist, 0, (size_t)(R + 1) * sizeof(i32), st));
     // the flow rounds re-hooked roots only: flattening the root list is enough
-    ulk_launch_list_multi(sroots, nsroots, st, K_CompressRoots{bp, lab, rootkeys, ctr + 0});
+    ulk_launch_rk_multi(sroots, nsroots, st, K_CompressRoots{bp, lab, rootkeys, ctr + 0});
     A.release(sroots);
     CHK(ulk_sort_keys_u64(rootkeys, rootsorted, B, st));
     u32 *gid_at_root = best;         // free after the flow rounds
     ulk_launch(B, st, K_BasinRegroup{rootsorted, Lr, gid_at_root, out.g_root, out.g_lab, out.g_L, lab_hist});
     CHK(ulk_exclusive_scan_i32(lab_hist, out.bs, R + 1, st));
-    if (nfg * 8 < V) ulk_launch_list(fgl, nfg, dm, st, K_ClearHalo{lab, dm, out.bas});   // short list (pass A): clear its halo only
-    else CHK(ulk_memset(out.bas, 0xff, (size_t)V * sizeof(i32), st));
-    ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_AssignBasin{bp, gid_at_root, out.bas});
+    // every list voxel gets its basin id (-1 outside the regions); a stencil kernel never reads the
+    // basin of a foreground voxel outside the list (a foreground neighbour is in the same component)
+    ulk_launch_rkn<4>(rl, m, st, K_AssignBasin{bp, gid_at_root, out.bas});
     A.release(rootkeys); A.release(rootsorted);
 
     // ---- per-basin accumulators, join keys (area attribute), bottleneck lower bound: one pass
@@ -503,8 +447,8 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     if (need_stats) { out.bbmin = A.get<i32>(3 * (i64)B); out.bbmax = A.get<i32>(3 * (i64)B); out.csum = A.get<i64>(3 * (i64)B); }
     i32 *hp = nullptr;
     out.mw = mw;
-    if (need_join) { out.jk = A.get<u32>(V); hp = A.get<i32>(V); }
-    i32 *xl = A.get<i32>(nfg);       // voxels on a boundary between basins of one region
+    if (need_join) { out.jk = A.get<u32>(n); hp = A.get<i32>(m); }
+    i32 *xl = A.get<i32>(m);         // voxels on a boundary between basins of one region
     u32 *Tk = nullptr;
     if (need_k3) { out.b_k3 = A.get<u32>(B); Tk = A.get<u32>(B); }
     CHKA(A);
@@ -518,12 +462,12 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
         ulk_fill<i32>(out.bbmax, -0x7fffffff, 3 * (i64)B, st);
         CHK(ulk_memset(out.csum, 0, (size_t)B * 3 * sizeof(i64), st));
     }
-    ulk_launch_list_phx<1>("BasinAccum", fgl, nfg, dm, st, K_BasinAccum{out.bas, lab, mw, pk, dm, out.b_size, out.b_top, ncross,
+    ulk_launch_rkx<1>("BasinAccum", rl, fg.fgl, m, dm, st, K_BasinAccum{out.bas, mw, pk, po, fg, out.b_size, out.b_top, ncross,
                                         need_stats ? 1 : 0, out.bbmin, out.bbmax, out.csum,
                                         need_join ? 1 : 0, out.g_L, out.jk, hp, ctr + 0,
                                         need_k3 ? 1 : 0, out.b_k3, Tk, xl, ctr + 1, out.g_lab});
-    ulk_launch(nflow, st, K_FlowTop{flow_root, flow_key, out.bas, ct, dm, out.b_top, Tk});
-    A.release(flow_root); A.release(flow_key);
+    ulk_launch(nflow, st, K_FlowTop{flow_root, flow_key, flow_src, out.bas, ct, fg, out.b_top, Tk});
+    A.release(flow_root); A.release(flow_key); A.release(flow_src);
     u64 h_ncross = 0;
     CHK(ulk_read(&h_ncross, ncross, 1, st));
     CHK(ulk_read(hc, ctr, 4, st));
@@ -535,13 +479,14 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
         int it = 0;
         while (nhp > 0) {
             CHK(ulk_memset(ctr + 2, 0, sizeof(i32), st));
-            ulk_launch(nhp, st, K_PlateauRelax{hp, lab, mw, pk, fmark, ct, dm, out.jk, ctr + 2});
+            ulk_launch(nhp, st, K_PlateauRelax{hp, lab, mw, pk, fmark, ct, fg, out.jk, ctr + 2});
             CHK(ulk_read(hc, ctr, 4, st));
             if (!hc[2]) break;
             if (++it > 1000000) ULK_FAIL(-4, "plateau relaxation did not converge");
         }
         A.release(hp);
     }
+    A.release(po);
 
     // ---- region adjacency graph (hash of basin pairs)
     u64 cap = 1024;
@@ -557,7 +502,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
     CHK(ulk_memset(T.cnt, 0, cap * 4, st));
     CHK(ulk_memset(T.shi, 0, cap * 8, st));
     CHK(ulk_memset(T.slo, 0, cap * 8, st));
-    ulk_launch_list_phx<1>("RagInsert", xl, nxl, dm, st, K_RagInsert{out.bas, lab, ct, dm, T, fixscale});
+    ulk_launch_rkx<1>("RagInsert", xl, fg.fgl, nxl, dm, st, K_RagInsert{out.bas, out.g_lab, ct, fg, T, fixscale});
     A.release(xl);
     i32 *eflag = A.get<i32>((i64)cap + 1), *epre = A.get<i32>((i64)cap + 1);
     CHKA(A);
@@ -612,25 +557,25 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
         CHKA(A);
         ulk_launch(B, st, K_K3Need{Tk, out.b_k3, nroot, ctr + 0, needlist});
         CHK(ulk_read(hc, ctr, 1, st));
-        const i32 *kl = fgl;
-        i64 nkl = hc[0] > 0 ? nfg : 0;
+        const i32 *kl = rl;
+        i64 nkl = hc[0] > 0 ? m : 0;
         i32 *klist = nullptr, *nkl_dev = nullptr;
         if (hc[0] > 0 && hc[0] < B && !getenv("ULK_K3_ALL")) {
-            klist = A.get<i32>(nfg); nkl_dev = A.get<i32>(1);
+            klist = A.get<i32>(m); nkl_dev = A.get<i32>(1);
             CHKA(A);
 #ifdef ULK_EMU
-            CHK(ulk_select_list_split_i32(fgl, nfg, out.bas, nroot, klist, nkl_dev, st));
+            CHK(ulk_select_list_split_i32(rl, m, out.bas, nroot, klist, nkl_dev, st));
 #else
             CHK(ulk_memset(nkl_dev, 0, sizeof(i32), st));
-            ulk_launch_warp((i64)hc[0] * 32, st, K_K3Collect{needlist, hc[0], out.bas, out.bbmin, out.bbmax, dm, klist, nkl_dev});
+            ulk_launch_warp((i64)hc[0] * 32, st, K_K3Collect{needlist, hc[0], out.bas, out.bbmin, out.bbmax, fg, klist, nkl_dev});
 #endif
-            i32 n = 0;
-            CHK(ulk_read(&n, nkl_dev, 1, st));
-            kl = klist; nkl = n;
+            i32 nk = 0;
+            CHK(ulk_read(&nk, nkl_dev, 1, st));
+            kl = klist; nkl = nk;
         }
         if (stats) stats->k3_voxels += nkl;
-        ulk_launch_list_ph<4>(kl, nkl, dm, st, K_K3Init{out.bas, out.b_k3, P3});
-        ulk_launch_list_phx<4>("K3Union", kl, nkl, dm, st, K_K3Union{out.bas, dm, out.b_k3, P3});
+        ulk_launch_rk<4>(kl, fg.fgl, nkl, dm, st, K_K3Init{out.bas, out.b_k3, fg.fgl, P3});
+        ulk_launch_rkx<4>("K3Union", kl, fg.fgl, nkl, dm, st, K_K3Union{out.bas, fg, out.b_k3, P3});
         // basins that edges <= K0 leave split (rare) go on with Boruvka rounds on THEIR voxels only
         const i32 *cur = kl;
         i64 ncur = nkl;
@@ -638,21 +583,21 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkDims &dm, const i3
         for (int it = 0; nkl > 0; ++it) {
             CHK(ulk_memset(nroot, 0, (size_t)B * sizeof(i32), st));
             CHK(ulk_memset(ctr, 0, sizeof(i32), st));
-            ulk_launch_list_multi(cur, ncur, st, K_K3FlattenCount{out.bas, P3, nroot, ctr + 0});
+            ulk_launch_rk_multi(cur, ncur, st, K_K3FlattenCount{out.bas, P3, nroot, ctr + 0});
             CHK(ulk_read(hc, ctr, 1, st));
             if (hc[0] == 0) break;
             if (stats) stats->k3_rounds += 1;
             if (it == 0) {
-                sub = A.get<i32>(nfg); nsub_dev = A.get<i32>(1);
+                sub = A.get<i32>(nkl); nsub_dev = A.get<i32>(1);
                 CHKA(A);
                 CHK(ulk_select_list_split_i32(kl, nkl, out.bas, nroot, sub, nsub_dev, st));
                 i32 nsub = 0;
                 CHK(ulk_read(&nsub, nsub_dev, 1, st));
                 cur = sub; ncur = nsub;
-                ulk_launch_list(cur, ncur, dm, st, K_FillAt<u32>{best, ULK_NONE32});     // K_K3Hook resets what it used
+                ulk_launch(ncur, st, K_FillAt<u32>{cur, best, ULK_NONE32});     // K_K3Hook resets what it used
             }
-            ulk_launch_list(cur, ncur, dm, st, K_K3FindBest{out.bas, dm, nroot, P3, best});
-            ulk_launch_list(cur, ncur, dm, st, K_K3Hook{out.bas, dm, P3, best, out.b_k3});
+            ulk_launch_rk1(cur, fg.fgl, ncur, dm, st, K_K3FindBest{out.bas, fg, nroot, P3, best});
+            ulk_launch_rk1(cur, fg.fgl, ncur, dm, st, K_K3Hook{out.bas, fg, P3, best, out.b_k3});
             if (it > 100000) ULK_FAIL(-4, "bottleneck rounds did not converge");
         }
         if (sub) { A.release(sub); A.release(nsub_dev); }
@@ -701,7 +646,17 @@ template <class T> static T *keep_alloc(i64 n)
     return (T *)p;
 }
 
-int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const void *ctp, int ct_dtype,
+// the caller asked for the region-label volume: all zero when no region exists
+static int empty_labels(ulk_stream_t st, ulk_frame_nodes *F, i64 V, int keep_labels)
+{
+    if (!keep_labels) return 0;
+    F->labels = keep_alloc<i32>(V);
+    if (!F->labels) ULK_FAIL(-3, "device allocation failed");
+    CHK(ulk_memset(F->labels, 0, (size_t)V * sizeof(i32), st));
+    return ulk_sync(st);
+}
+
+int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const void *ctp, int ct_dtype,
                            const int64_t shape[3], const ulk_seg_params *prm, int keep_labels,
                            ulk_frame_nodes **result)
 {
@@ -710,8 +665,8 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     if (dm.V <= 0) ULK_FAIL(-1, "empty frame");
     if (dm.D > 65535 || dm.H > 65535) ULK_FAIL(-1, "frame too large: depth and height are limited to 65535");
     if (dm.V > 1431655000ll) ULK_FAIL(-1, "frame too large: %lld voxels (edge keys are 32-bit)", (long long)dm.V);
-    if (prm->ws_hierarchy != 0 && prm->ws_hierarchy != 1)
-        ULK_FAIL(-1, "ws_hierarchy=%d is not supported (0 area, 1 dynamics)", prm->ws_hierarchy);
+    if (prm->ws_hierarchy < 0 || prm->ws_hierarchy > 2)
+        ULK_FAIL(-1, "ws_hierarchy=%d is not supported (0 area, 1 dynamics, 2 volume)", prm->ws_hierarchy);
     const i64 V = dm.V;
     ulk_seg_stats stats_local;
     memset(&stats_local, 0, sizeof(stats_local));
@@ -721,48 +676,56 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     F->shape[0] = dm.D; F->shape[1] = dm.H; F->shape[2] = dm.W;
     *result = F;
 
-    // ---- K1 threshold; contours are staged only when their dtype is not already float32
-    UlkCt ct;
-    ct.f = nullptr; ct.d = nullptr;
-    float *ctf = nullptr; double *ctd = nullptr;
-    if (ct_dtype == ULK_F32) ct.f = (const float *)ctp;
-    else if (ulk_ct_is_f32(ct_dtype)) { ctf = A.get<float>(V); ct.f = ctf; }
-    else { ctd = A.get<double>(V); ct.d = ctd; }
-    i32 *P = A.get<i32>(V);
+    // ---- K1 threshold -> foreground words -> ranks
+    const i32 SG = (dm.W + 31) / 32;
+    const i64 nt = (i64)dm.D * dm.H * SG;
+    u32 *words = A.get<u32>(nt);
+    i32 *off = A.get<i32>(nt);
+    UlkOW *ow = A.get<UlkOW>(nt);
     u32 *cmax = A.get<u32>(1);
     CHKA(A);
     CHK(ulk_memset(cmax, 0, 4, st));
-    // ---- the foreground voxel list (raster order): every later voxel kernel runs on it
-    i32 *fgl = A.get<i32>(V);
-    i32 *nfg_dev = A.get<i32>(1);
-    CHKA(A);
-    i32 *cnt = A.get<i32>(V);            // sizes at the roots, later the component code at the roots
-    CHKA(A);
-    bool ccl_done = false;
-    // float32 contours are never staged: K_Threshold does not read them at all, the bound on the
-    // edge weights comes from K_MinEdge (region voxels only)
-    const bool late_cmax = ct_dtype == ULK_F32 && !getenv("ULK_CMAX_EARLY");
-    CHK(threshold_and_list(st, A, dm, K_Threshold{fg, fg_dtype, prm->threshold, ctp, ct_dtype, ctf, ctd, P, cmax, late_cmax ? 1 : 0}, fgl, nfg_dev, cnt, &ccl_done));
-    // ---- connected components (4/6-connected): union of runs, flatten + sizes + root list
-    i32 nfg = 0;
-    CHK(ulk_read(&nfg, nfg_dev, 1, st));
+    CHK(threshold_words(st, dm, fgp, fg_dtype, prm->threshold, SG, nt, words));
+    CHK(ulk_exclusive_scan_popc_u32(words, off, nt, st));
+    i32 h_last_off = 0; u32 h_last_w = 0;
+    CHK(ulk_read(&h_last_off, off + (nt - 1), 1, st));
+    CHK(ulk_read(&h_last_w, words + (nt - 1), 1, st));
+    const i32 nfg = h_last_off + __builtin_popcount(h_last_w);
     stats_local.n_foreground = nfg;
-    i32 *lab2 = P;                       // region labels are written in place over the component forest (-1 stays on the background)
+    F->fix_shift = ulk_fix_shift_for(0);
+    if (nfg == 0) { F->n_nodes = 0; F->stats = stats_local; return empty_labels(st, F, V, keep_labels); }
+    // ---- rank space: the foreground list, its contour values, the component forest
+    i32 *fgl = A.get<i32>(nfg);
+    i32 *P = A.get<i32>(nfg);
+    i32 *cnt = A.get<i32>(nfg);          // sizes at the roots, later the component code at the roots
+    UlkCt ct;
+    ct.f = nullptr; ct.d = nullptr;
+    float *ctf = nullptr; double *ctd = nullptr;
+    if (ulk_ct_is_f32(ct_dtype)) { ctf = A.get<float>(nfg); ct.f = ctf; }
+    else { ctd = A.get<double>(nfg); ct.d = ctd; }
+    CHKA(A);
+    expand_words(st, K_Expand{words, off, dm, SG, ctp, ct_dtype, ow, fgl, ctf, ctd, P, cmax}, nt);
+    A.release(words); A.release(off);
+    UlkFg fg;
+    fg.ow = ow; fg.fgl = fgl; fg.n = nfg; fg.S = SG; fg.SH = SG * dm.H; fg.dm = dm;
+    // ---- connected components (4/6-connected): union of runs, flatten + sizes + root list
+    UlkFastDiv fS, fH;
+    fS.init((u32)SG); fH.init((u32)dm.H);
+    ulk_launch(nt, st, K_CclWords{fg, fS, fH, P, cnt});
+    i32 *lab2 = P;                       // region labels are written in place over the component forest
     i32 *ctr = A.get<i32>(4);
     u32 *roots0 = A.get<u32>(nfg);
     CHKA(A);
-    if (!ccl_done) ulk_launch_list_phx<2>("CclUnion", fgl, nfg, dm, st, K_CclUnion{P, dm, cnt});
     CHK(ulk_memset(ctr, 0, 4 * sizeof(i32), st));
-    ulk_launch_list_multi(fgl, nfg, st, K_FlattenCount{P, cnt, (i32 *)roots0, ctr});
+    ulk_launch_rk_multi(nullptr, nfg, st, K_FlattenCount{P, cnt, (i32 *)roots0, ctr});
     i32 hc[4];
     u32 h_cmax = 0;
     CHK(ulk_read(hc, ctr, 4, st));
     CHK(ulk_read(&h_cmax, cmax, 1, st));
     const i32 n_roots = hc[0];
     const i32 max_area_i = prm->max_area > 2147483646.0 ? 2147483646 : (i32)prm->max_area;
-    int fix_shift = ulk_fix_shift_for(h_cmax);
+    const int fix_shift = ulk_fix_shift_for(h_cmax);
     F->fix_shift = fix_shift;
-    if (n_roots == 0) { F->n_nodes = 0; F->stats = stats_local; return 0; }
     // ---- per-component decisions on the (sorted) root list: small-object removal
     //      (hierarchy.py:64-73), components above max_area, consecutive numbering
     u32 *roots = A.get<u32>(n_roots);
@@ -782,7 +745,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     i32 n_cc = 0, n_big = 0;
     CHK(ulk_read(&n_cc, keeppre + n_roots, 1, st));
     CHK(ulk_read(&n_big, bigpre + n_roots, 1, st));
-    if (n_cc == 0) { F->n_nodes = 0; F->stats = stats_local; return 0; }
+    if (n_cc == 0) { F->n_nodes = 0; F->stats = stats_local; return empty_labels(st, F, V, keep_labels); }
     i32 *code = cnt;
     ulk_launch(n_roots, st, K_RootCode{roots, keep, keeppre, big, bigpre, code, cc_big, big_cc});
     A.release(roots); A.release(keep); A.release(keeppre); A.release(big); A.release(bigpre); A.release(rsize);
@@ -790,35 +753,35 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     // ---- region labels: components, oversegmented where area > max_area
     i32 R = n_cc;
     if (n_big == 0) {
-        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_LabelCc{code, cc_big, 0, lab2, nullptr, nullptr});
+        ulk_launch_rkn<4>(nullptr, nfg, st, K_LabelCc{code, cc_big, 0, lab2, nullptr, nullptr});
     } else {
         UlkArena AA;
         // the labels of the oversegmentation pass live in place too: > 0 on the components above
         // max_area, negative everywhere else
         i32 *labA = lab2;
         // pass A only ever touches the voxels of the components above max_area: its kernels run
-        // on that sub-list, collected while the labels are written (chunks of up to 32 raster-
-        // ordered voxels in arbitrary order: order only matters for coalescing)
-        i32 *fglA = AA.get<i32>(nfg);
-        i32 *nfgA_dev = AA.get<i32>(1);
+        // on that sub-list of ranks, collected while the labels are written (chunks of up to 32
+        // raster-ordered voxels in arbitrary order: order only matters for coalescing)
+        i32 *rlA = AA.get<i32>(nfg);
+        i32 *nA_dev = AA.get<i32>(1);
         CHKA(AA);
-        CHK(ulk_memset(nfgA_dev, 0, sizeof(i32), st));
+        CHK(ulk_memset(nA_dev, 0, sizeof(i32), st));
 #ifdef ULK_EMU
-        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_LabelCc{code, cc_big, 1, labA, fglA, nfgA_dev});
+        ulk_launch_rkn<4>(nullptr, nfg, st, K_LabelCc{code, cc_big, 1, labA, rlA, nA_dev});
 #else
-        ulk_launch_list_multi(fgl, nfg, st, K_LabelCc{code, cc_big, 1, labA, fglA, nfgA_dev});
+        ulk_launch_rk_multi(nullptr, nfg, st, K_LabelCc{code, cc_big, 1, labA, rlA, nA_dev});
 #endif
-        i32 nfgA = 0;
-        CHK(ulk_read(&nfgA, nfgA_dev, 1, st));
-        stats_local.pass_a_voxels = nfgA;
+        i32 nA = 0;
+        CHK(ulk_read(&nA, nA_dev, 1, st));
+        stats_local.pass_a_voxels = nA;
         VoxelStage va;
-        CHK(voxel_stage(st, AA, dm, fglA, nfgA, ct, labA, n_big, true, false, false, late_cmax ? cmax : nullptr, &fix_shift, va, &stats_local));
+        CHK(voxel_stage(st, AA, fg, rlA, nA, ct, labA, n_big, true, false, false, fix_shift, va, &stats_local));
         UlkHierScratch S;
         CHK(alloc_scratch(AA, va.B, va.Eg, S));
         UlkBasins Bv{va.b_size, va.g_L, va.b_top, nullptr, nullptr, nullptr, nullptr};
         UlkEdges Ev{va.ea, va.eb, va.wk, va.k3, va.cnt, va.shi, va.slo};
         ulk_launch(n_big, st, K_HierStage1{va.bs, va.es, Bv, Ev, S});
-        ulk_launch_list_ph<4>(fglA, nfgA, dm, st, K_Attach{va.bas, va.mw, va.jk, va.g_lab, va.bs, S.Ipar, S.Iwk, S.attach});
+        ulk_launch_rkn<4>(rlA, nA, st, K_Attach{va.bas, va.mw, va.jk, va.g_lab, va.bs, S.Ipar, S.Iwk, S.attach});
         i32 *region_of = AA.get<i32>(va.B);
         u64 *rkey_w = AA.get<u64>(va.B), *rkey_k = AA.get<u64>(va.B);
         CHKA(AA);
@@ -838,7 +801,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
         ulk_launch(nrec, st, K_Gather<u32>{rec_cc, perm0, c0});
         CHK(ulk_sort_pairs_u32(c0, c1, perm0, perm1, nrec, st));              // then by component
         ulk_launch(nrec, st, K_RankToLabel{perm1, c1, label_of_rec});
-        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_WriteLabels{n_cc, va.bas, region_of, label_of_rec, lab2});
+        ulk_launch_rkn<4>(nullptr, nfg, st, K_WriteLabels{n_cc, va.bas, region_of, label_of_rec, lab2});
         // number of valid records = regions
         i32 *nvalid = AA.get<i32>(nrec + 1), *nvpre = AA.get<i32>(nrec + 1);
         CHKA(AA);
@@ -852,22 +815,22 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     if (keep_labels) {
         F->labels = keep_alloc<i32>(V);
         if (!F->labels) return -3;
-        ulk_launch(V, st, K_CopyLabels{lab2, F->labels});
+        CHK(ulk_memset(F->labels, 0, (size_t)V * sizeof(i32), st));
+        ulk_launch(nfg, st, K_ScatterLabels{lab2, fgl, F->labels});
     }
     F->n_hier = R;
 
     // ---- pass B: the configured hierarchy on every region
     const bool area_mode = prm->ws_hierarchy == 0;
     VoxelStage vb;
-    CHK(voxel_stage(st, A, dm, fgl, nfg, ct, lab2, R, area_mode, true, true, late_cmax ? cmax : nullptr, &fix_shift, vb, &stats_local));
-    F->fix_shift = fix_shift;
+    CHK(voxel_stage(st, A, fg, nullptr, nfg, ct, lab2, R, area_mode, true, true, fix_shift, vb, &stats_local));
     UlkHierScratch S;
     CHK(alloc_scratch(A, vb.B, vb.Eg, S));
     UlkBasins Bv{vb.b_size, vb.g_L, vb.b_top, vb.b_k3, vb.bbmin, vb.bbmax, vb.csum};
     UlkEdges Ev{vb.ea, vb.eb, vb.wk, vb.k3, vb.cnt, vb.shi, vb.slo};
     ulk_launch(R, st, K_HierStage1{vb.bs, vb.es, Bv, Ev, S});
     if (area_mode)
-        ulk_launch_list_ph<4>(fgl, nfg, dm, st, K_Attach{vb.bas, vb.mw, vb.jk, vb.g_lab, vb.bs, S.Ipar, S.Iwk, S.attach});
+        ulk_launch_rkn<4>(nullptr, nfg, st, K_Attach{vb.bas, vb.mw, vb.jk, vb.g_lab, vb.bs, S.Ipar, S.Iwk, S.attach});
     i64 N2 = 2 * (i64)vb.B + 2;
     UlkNodeOut O;
     O.count = A.get<i32>(R + 1); O.nsurv = A.get<i32>(R + 1); O.rsize = A.get<i32>(R + 1);
@@ -917,7 +880,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
     UlkPaintInfo *pinfo = A.get<UlkPaintInfo>(N);
     CHKA(A);
     ulk_launch(N, st, K_PaintInfo{F->parent, F->bbox, F->mask_off, pinfo});
-    ulk_launch_list_phx<4>("MaskPaint", fgl, nfg, dm, st, K_MaskPaint{vb.bas, bnode, pinfo, dm, F->mask});
+    ulk_launch_rkx<4>("MaskPaint", nullptr, fgl, nfg, dm, st, K_MaskPaint{vb.bas, bnode, pinfo, dm, F->mask});
     // ---- overlaps: (node, emitted proper ancestor) pairs, processing.py:289-296
     i32 *depth = A.get<i32>(N + 1), *ooff = A.get<i32>(N + 1);
     CHKA(A);

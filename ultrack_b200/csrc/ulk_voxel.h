@@ -1,17 +1,107 @@
 // ulk_voxel.h -- voxel-scale kernels of the segmentation path (functor bodies).
 //
-// Every kernel is a functor launched one thread per voxel (or per list entry)
-// through ulk_launch<>.  Vocabulary follows ultrack / higra: a *region* is one
-// hierarchy's support (core/segmentation/hierarchy.py:89-90), a *basin* is a
-// catchment basin of the watershed cut of a region (altitude-0 node of
-// hg.watershed_hierarchy_by_*), the *RAG* is the basin adjacency graph.
+// Vocabulary follows ultrack / higra: a *region* is one hierarchy's support
+// (core/segmentation/hierarchy.py:89-90), a *basin* is a catchment basin of the watershed cut
+// of a region (altitude-0 node of hg.watershed_hierarchy_by_*), the *RAG* is the basin
+// adjacency graph.
+//
+// RANK SPACE.  After the threshold the frame is only ever touched through its foreground
+// voxels.  Every per-voxel array of this stage is indexed by the voxel's RANK in the raster-
+// ordered foreground list (`fgl[rank] = voxel`), never by the voxel index: a kernel's own
+// accesses are dense and coalesced whatever the foreground fraction, the arrays are n_fg long
+// instead of V, and nothing has to be cleared on the background.  Neighbours are found through
+// the foreground map `UlkFg`: one 8-byte record per 32-voxel row segment (foreground bits +
+// rank of the segment's first foreground voxel); the rank of a neighbour is one record load and
+// a population count, and the x-neighbours of rank r are simply r-1 / r+1 when fgl says so.
+// Edge keys stay voxel based (3*voxel + direction): they reproduce the enumeration order of
+// edges_from_mask (vendored/graph.py:41-57), i.e. higra's stable tie-break; rank order equals
+// voxel order, so "smaller voxel" and "smaller rank" are interchangeable.
 #pragma once
 #include "ulk_common.h"
 
 #define ULK_JK_CORE 0xFFFFFFFEu   // join key of voxels inside the regional minimum
-#define ULK_PK_OUT 0xFFFFFFFEu    // steepest-edge key of a list voxel outside every region (dropped component)
+#define ULK_PO_NONE (-1)          // steepest-edge endpoint: no in-region neighbour (a one-voxel basin seed)
+#define ULK_PO_OUT (-2)           // steepest-edge endpoint: the voxel is outside every region (dropped component)
 
-// ------------------------------------------------------------------ union-find on voxels
+#ifdef ULK_EMU
+ULK_INLINE int ulk_ffs(u32 x) { return __builtin_ffs((int)x); }
+#else
+ULK_D ULK_INLINE int ulk_ffs(u32 x) { return __ffs((int)x); }
+#endif
+
+// ------------------------------------------------------------------ foreground map
+struct alignas(8) UlkOW { u32 w; i32 o; };     // bits of a 32-voxel row segment, rank of its first foreground voxel
+struct UlkNbRaw { UlkOW e[4]; i32 vl, vr; };   // segment records at -z, -y, +y, +z; voxels of ranks r-1, r+1
+struct UlkFg {
+    const UlkOW *ow;      // [D*H*S]
+    const i32 *fgl;       // [n] voxel of rank r
+    i32 n;                // foreground voxels
+    i32 S, SH;            // segments per row, per slice
+    UlkDims dm;
+    ULK_D ULK_INLINE UlkOW load(i32 t) const
+    {
+#ifdef ULK_EMU
+        return ow[t];
+#else
+        const uint2 q = __ldg((const uint2 *)ow + t);
+        UlkOW e;
+        e.w = q.x; e.o = (i32)q.y;
+        return e;
+#endif
+    }
+    static ULK_D ULK_INLINE i32 rank_in(const UlkOW &e, int b)
+    {
+        return ((e.w >> b) & 1u) ? e.o + ulk_popc(e.w & ((1u << b) - 1u)) : -1;
+    }
+    ULK_D ULK_INLINE i32 seg(i32 z, i32 y, i32 x) const { return (z * dm.H + y) * S + (x >> 5); }
+    // rank of an arbitrary voxel (-1: background); two multiply-shift divisions + one record load
+    ULK_D ULK_INLINE i32 rank_of(i32 v) const
+    {
+        i32 z, y, x;
+        dm.coords(v, z, y, x);
+        return rank_in(load(seg(z, y, x)), x & 31);
+    }
+    // everything the six neighbour ranks of (rank r, segment t, row y, slice z) depend on; the
+    // loads are independent of each other (issue them together, convert in the next phase)
+    ULK_D ULK_INLINE UlkNbRaw nb_load(i32 r, i32 t, i32 z, i32 y, bool back, bool fwd) const
+    {
+        UlkNbRaw q;
+        for (int i = 0; i < 4; ++i) { q.e[i].w = 0; q.e[i].o = 0; }
+        q.vl = -1; q.vr = -1;
+        if (back) {
+            if (z > 0) q.e[0] = load(t - SH);
+            if (y > 0) q.e[1] = load(t - S);
+            if (r > 0) q.vl = fgl[r - 1];
+        }
+        if (fwd) {
+            if (y + 1 < dm.H) q.e[2] = load(t + S);
+            if (z + 1 < dm.D) q.e[3] = load(t + SH);
+            if (r + 1 < n) q.vr = fgl[r + 1];
+        }
+        return q;
+    }
+    // neighbour ranks in increasing edge-key order: -z, -y, -x, +x, +y, +z (-1: border or background)
+    ULK_D ULK_INLINE void nb_ranks(const UlkNbRaw &q, i32 r, i32 v, i32 x, i32 (&out)[6]) const
+    {
+        const int b = x & 31;
+        out[0] = rank_in(q.e[0], b);
+        out[1] = rank_in(q.e[1], b);
+        out[2] = (x > 0 && q.vl == v - 1) ? r - 1 : -1;
+        out[3] = (x + 1 < dm.W && q.vr == v + 1) ? r + 1 : -1;
+        out[4] = rank_in(q.e[2], b);
+        out[5] = rank_in(q.e[3], b);
+    }
+    // voxel offset of neighbour slot i (same order)
+    ULK_D ULK_INLINE i32 nb_off(int i) const
+    {
+        const i32 sy = dm.W, sz = dm.W * dm.H;
+        return i == 0 ? -sz : i == 1 ? -sy : i == 2 ? -1 : i == 3 ? 1 : i == 4 ? sy : sz;
+    }
+};
+// direction (0 = x, 1 = y, 2 = z) of neighbour slot i
+ULK_HD ULK_INLINE u32 ulk_nb_dir(int i) { return i == 0 || i == 5 ? 2u : (i == 1 || i == 4 ? 1u : 0u); }
+
+// ------------------------------------------------------------------ union-find on ranks
 ULK_D ULK_INLINE i32 ulk_vfind(const i32 *P, i32 x)
 {
     i32 p = P[x];
@@ -56,8 +146,6 @@ ULK_D ULK_INLINE void ulk_warp_append(bool flag, i32 value, i32 *list, i32 *coun
     base = __shfl_sync(0xffffffffu, base, leader);
     if (flag) list[base + __popc(m & ((1u << lane) - 1u))] = value;
 }
-#endif
-#ifndef ULK_EMU
 // lanes hold consecutive entries of a raster-ordered list, so lanes that share a key are almost
 // always neighbours: `heads` has a bit for every lane whose key differs from the lane below it;
 // returns the lane mask of the caller's run (runs need not be maximal groups -- a key that
@@ -85,13 +173,6 @@ ULK_D ULK_INLINE void ulk_vfind_multi(const i32 *P, i32 (&x)[ULK_MULTI])
             if (p[u] != x[u]) { x[u] = p[u]; more = true; }
     } while (more);
 }
-#endif
-
-// ------------------------------------------------------------------ K1: threshold + contour staging
-// processing.py:212 `foreground[time] > threshold`; vendored/hierarchy.py:158-159,350 up-casts.
-// The component forest starts with every x-run of foreground voxels inside a 32-voxel warp
-// segment already hooked to its first voxel, so K_CclUnion only has to join runs.
-#ifndef ULK_EMU
 // first lane of the chain of `linked` lanes that ends at `lane` (bit l of linked: lane l is
 // joined to lane l-1)
 ULK_D ULK_INLINE int ulk_run_start(u32 linked, int lane)
@@ -100,117 +181,134 @@ ULK_D ULK_INLINE int ulk_run_start(u32 linked, int lane)
     return 31 - __clz(stop);                               // lane 0 never has its link bit set
 }
 #endif
+// same for bit positions of a 32-voxel segment word (host + device)
+ULK_D ULK_INLINE int ulk_bit_run_start(u32 word, int b)
+{
+    const u32 linked = word & (word << 1);
+    u32 stop = ~linked & (0xffffffffu >> (31 - b));
+    int p = 31;
+    while (!((stop >> p) & 1u)) --p;
+    return p;
+}
+
+// ------------------------------------------------------------------ K1: threshold -> foreground words
+// processing.py:212 `foreground[time] > threshold`, one bit per voxel, one 32-bit word per
+// 32-voxel row segment.  Nothing else is written for the frame's V voxels.  (The functor form
+// is what the emulation and unusual dtypes run; ulk_seg.cu has the vectorised streaming kernels.)
 struct K_Threshold {
-    const void *fg; int fgt; double thr;
+    const void *fg; int fgt; double thr; UlkDims dm; i32 S; u32 *words;
+    ULK_D void operator()(i64 t) const
+    {
+        const i32 row = (i32)(t / S), sg = (i32)(t - (i64)row * S);
+        const i64 base = (i64)row * dm.W + (i64)sg * 32;
+        u32 w = 0;
+        for (int l = 0; l < 32 && sg * 32 + l < dm.W; ++l)
+            if (ulk_load_as_double(fg, fgt, base + l) > thr) w |= 1u << l;
+        words[t] = w;
+    }
+};
+// Expansion of the words into rank space: the foreground list, the contour value of every
+// foreground voxel (float32, or float64 for wide dtypes: vendored/hierarchy.py:158-159,350 up-
+// casts), the component forest with every x-run of a segment already hooked to its first voxel,
+// the interleaved (bits, first rank) records, and max |contour| over the foreground.
+struct K_Expand {
+    const u32 *words; const i32 *off; UlkDims dm; i32 S;
     const void *ct; int ctt;
-    float *ctf; double *ctd;
-    i32 *P; u32 *cmax;
-    int skip_ct;      // float32 contours are read in place later: K_MinEdge finds max |ct| over the regions
-    ULK_D ULK_INLINE bool stage(i64 v, u32 &bits) const
+    UlkOW *ow; i32 *fgl; float *ctf; double *ctd; i32 *P; u32 *cmax;
+    ULK_D ULK_INLINE u32 emit(i32 r, i32 v, i32 head) const
     {
-        double f = ulk_load_as_double(fg, fgt, v);
-        bits = 0;
-        if (ctt == ULK_F32) {       // read in place, never staged
-            if (!skip_ct) {
-                float a = fabsf(((const float *)ct)[v]);
-                if (a <= 3.0e38f) memcpy(&bits, &a, 4);
-            }
-            return f > thr;
-        }
-        double c = ulk_load_as_double(ct, ctt, v);
-        if (ctf) ctf[v] = (float)c; else if (ctd) ctd[v] = c;
-        float a = (float)(c < 0 ? -c : c);
-        if (a == a && a <= 3.0e38f) memcpy(&bits, &a, 4);
-        return f > thr;
-    }
-#ifdef ULK_EMU
-    void operator()(i64 v, i32, i32, i32 x) const
-    {
-        u32 bits;
-        bool on = stage(v, bits);
-        if (bits > *cmax) *cmax = bits;
-        bool link = on && (x & 31) != 0 && P[v - 1] >= 0;
-        P[v] = on ? (link ? P[v - 1] : (i32)v) : -1;
-    }
-#else
-    ULK_D void warp(i64 v, i32, i32, i32, bool valid) const
-    {
-        const int lane = threadIdx.x & 31;     // == x & 31
+        fgl[r] = v;
+        P[r] = head;
         u32 bits = 0;
-        bool on = valid && stage(v, bits);
-        u32 m = __reduce_max_sync(0xffffffffu, bits);
-        if (lane == 0 && m > *cmax) atomicMax(cmax, m);
-        bool prev = __shfl_up_sync(0xffffffffu, on ? 1 : 0, 1) != 0;
-        u32 linked = __ballot_sync(0xffffffffu, on && prev && lane > 0);
-        if (valid) P[v] = on ? (i32)v - (lane - ulk_run_start(linked, lane)) : -1;
+        if (ctt == ULK_F32) {
+            const float c = ((const float *)ct)[v];
+            ctf[r] = c;
+            const float a = fabsf(c);
+            if (a <= 3.0e38f) memcpy(&bits, &a, 4);
+        } else {
+            const double c = ulk_load_as_double(ct, ctt, v);
+            if (ctf) ctf[r] = (float)c; else ctd[r] = c;
+            const float a = (float)(c < 0 ? -c : c);
+            if (a == a && a <= 3.0e38f) memcpy(&bits, &a, 4);
+        }
+        return bits;
     }
-#endif
+    ULK_D void operator()(i64 t) const     // one segment per thread (emulation)
+    {
+        const u32 w = words[t];
+        const i32 o = off[t];
+        UlkOW e;
+        e.w = w; e.o = o;
+        ow[t] = e;
+        const i32 row = (i32)(t / S), sg = (i32)(t - (i64)row * S);
+        const i32 base = row * dm.W + sg * 32;
+        u32 mx = 0;
+        for (u32 m = w; m; m &= m - 1) {
+            const int b = ulk_ffs(m) - 1;
+            const i32 r = o + ulk_popc(w & ((1u << b) - 1u));
+            const int b0 = ulk_bit_run_start(w, b);
+            const u32 bits = emit(r, base + b, o + ulk_popc(w & ((1u << b0) - 1u)));
+            mx = bits > mx ? bits : mx;
+        }
+        if (mx) ulk_atomic_max(cmax, mx);
+    }
 };
 
 // ------------------------------------------------------------------ connected components (ndi.label)
-// joins the runs: an x edge only across a warp-segment boundary, a y / z edge only where the
-// edge one voxel to the left does not already join the same two runs
-struct K_CclUnion {
-    i32 *P; UlkDims dm; i32 *cnt;
-    // every neighbour is loaded up front (clamped to v at the frame border) so the loads
-    // overlap; only the sign is used, and the sign of an entry never changes
-    struct S1 { i32 v, p0, pl, py, pyl, pz, pzl; u32 h; };
-    typedef S1 S2;
-    ULK_D ULK_INLINE S1 load1(i32 v, i32 z, i32 y, i32 x, bool ok) const
+// One thread per 32-voxel row segment.  Every x-run inside a segment is already hooked to its
+// first voxel (K_Expand), so what is left is one union per run of overlap with the row above /
+// the slice above (start bits of w & w_up) and one across the segment boundary.  Size counters
+// of all run starts (the only possible roots) are zeroed.
+struct K_CclWords {
+    UlkFg fg; UlkFastDiv fS, fH; i32 *P; i32 *cnt;
+    ULK_D void operator()(i64 tt) const
     {
-        S1 s;
-        s.v = v; s.p0 = -1; s.h = 0;
-        if (!ok) return s;
-        const bool hx = x > 0, hy = y > 0, hz = z > 0;
-        const i32 uy = hy ? v - dm.W : v, uz = hz ? v - dm.W * dm.H : v;
-        s.h = (hx ? 1u : 0u) | (hy ? 2u : 0u) | (hz ? 4u : 0u) | ((x & 31) == 0 ? 8u : 0u);
-        s.p0 = P[v];
-        s.pl = P[hx ? v - 1 : v]; s.py = P[uy]; s.pyl = P[hx ? uy - 1 : uy]; s.pz = P[uz]; s.pzl = P[hx ? uz - 1 : uz];
-        return s;
+        const i32 t = (i32)tt;
+        const UlkOW e = fg.load(t);
+        const u32 w = e.w;
+        if (w == 0) return;
+        const u32 r = fS.div((u32)t), sg = (u32)t - r * (u32)fg.S;
+        const u32 zz = fH.div(r), y = r - zz * (u32)fg.dm.H;
+        for (u32 m = w & ~(w << 1); m; m &= m - 1) cnt[e.o + ulk_popc(w & ((m & (0u - m)) - 1u))] = 0;
+        if (sg > 0 && (w & 1u)) {
+            const UlkOW l = fg.load(t - 1);
+            if (l.w >> 31) ulk_vunion(P, e.o, e.o - 1);
+        }
+        if (y > 0) {
+            const UlkOW u = fg.load(t - fg.S);
+            const u32 o = w & u.w;
+            for (u32 m = o & ~(o << 1); m; m &= m - 1) {
+                const u32 below = (m & (0u - m)) - 1u;
+                ulk_vunion(P, e.o + ulk_popc(w & below), u.o + ulk_popc(u.w & below));
+            }
+        }
+        if (zz > 0) {
+            const UlkOW u = fg.load(t - fg.SH);
+            const u32 o = w & u.w;
+            for (u32 m = o & ~(o << 1); m; m &= m - 1) {
+                const u32 below = (m & (0u - m)) - 1u;
+                ulk_vunion(P, e.o + ulk_popc(w & below), u.o + ulk_popc(u.w & below));
+            }
+        }
     }
-    ULK_D ULK_INLINE S2 load2(const S1 &s, bool) const { return s; }
-    ULK_D ULK_INLINE void run(const S2 &s, bool) const
-    {
-        const i32 v = s.v;
-        if (s.p0 < 0) return;
-        if (s.p0 == v) cnt[v] = 0;      // a final root is never hooked: its size counter starts at 0
-        const bool left = (s.h & 1u) && s.pl >= 0;
-        if (left && (s.h & 8u)) ulk_vunion(P, v, v - 1);
-        if ((s.h & 2u) && s.py >= 0 && !(left && s.pyl >= 0)) ulk_vunion(P, v, v - dm.W);
-        if ((s.h & 4u) && s.pz >= 0 && !(left && s.pzl >= 0)) ulk_vunion(P, v, v - dm.W * dm.H);
-    }
-};
-struct K_Flatten {
-    i32 *P;
-    ULK_D void operator()(i64 v) const { if (P[v] >= 0) P[v] = ulk_vfind(P, (i32)v); }
 };
 // flatten, component sizes (one atomic per group of lanes with the same root) and root list
 struct K_FlattenCount {
     i32 *P; i32 *cnt; i32 *roots; i32 *nroots;
 #ifdef ULK_EMU
-    void operator()(i64 v, i32, i32, i32) const
+    void operator()(i32 r) const
     {
-        if (P[v] < 0) return;
-        i32 r = ulk_vfind(P, (i32)v);
-        P[v] = r;
-        cnt[r] += 1;
-        if (r == (i32)v) roots[(*nroots)++] = r;
+        i32 root = ulk_vfind(P, r);
+        P[r] = root;
+        cnt[root] += 1;
+        if (root == r) roots[(*nroots)++] = r;
     }
 #else
-    ULK_D void warp(i64 v, i32, i32, i32, bool valid) const
-    {
-        i32 r = -1;
-        if (valid && P[v] >= 0) { r = ulk_vfind(P, (i32)v); P[v] = r; }
-        u32 grp = __match_any_sync(0xffffffffu, r);
-        if (r < 0) return;
-        if ((threadIdx.x & 31) == __ffs(grp) - 1) atomicAdd(&cnt[r], __popc(grp));
-        if (r == (i32)v) roots[atomicAdd(nroots, 1)] = r;
-    }
     ULK_D void multi(const i32 (&v)[ULK_MULTI], const bool (&ok)[ULK_MULTI]) const
     {
         i32 r[ULK_MULTI];
 #pragma unroll
-        for (int u = 0; u < ULK_MULTI; ++u) r[u] = ok[u] ? P[v[u]] : -1;     // foreground only: P >= 0
+        for (int u = 0; u < ULK_MULTI; ++u) r[u] = ok[u] ? P[v[u]] : -1;
         ulk_vfind_multi(P, r);
 #pragma unroll
         for (int u = 0; u < ULK_MULTI; ++u) {
@@ -254,34 +352,34 @@ struct K_RootCode {
         if (big[i]) big_cc[bigpre[i]] = c;
     }
 };
-// Component labels, written in place over the flattened component forest (the background keeps
-// its -1).  mode 0 (no component above max_area): the 1-based component index, 0 if dropped.
+// Component labels, written in place over the flattened component forest.
+// mode 0 (no component above max_area): the 1-based component index, 0 if dropped.
 // mode 1: components above max_area get their 1-based index among themselves (the region labels
 // of the oversegmentation pass), the other kept components -(index + 2), dropped ones -1.
 struct K_LabelCc {
     const i32 *code; const i32 *cc_big; int mode; i32 *lab;
-    i32 *biglist; i32 *nbig;       // mode 1: the voxels of the components above max_area (32-entry chunks in raster order)
-    struct S1 { i32 v, r; };
-    struct S2 { i32 v, c; };
-    ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32, bool ok) const { S1 s; s.v = v; s.r = ok ? lab[v] : -1; return s; }
-    ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const { S2 s; s.v = a.v; s.c = a.r >= 0 ? code[a.r] : -1; return s; }
+    i32 *biglist; i32 *nbig;       // mode 1: the ranks of the voxels of the components above max_area (32-entry chunks in raster order)
+    struct S1 { i32 r, root; };
+    struct S2 { i32 r, c; };
+    ULK_D ULK_INLINE S1 load1(i32 r, bool ok) const { S1 s; s.r = r; s.root = ok ? lab[r] : -1; return s; }
+    ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const { S2 s; s.r = a.r; s.c = a.root >= 0 ? code[a.root] : -1; return s; }
     ULK_D ULK_INLINE void run(const S2 &s, bool) const
     {
         const i32 c = s.c;
         i32 g = -1;
         if (c >= 0) {
-            if (mode == 0) lab[s.v] = c;
-            else if (c == 0) lab[s.v] = -1;
+            if (mode == 0) lab[s.r] = c;
+            else if (c == 0) lab[s.r] = -1;
             else {
                 g = cc_big[c - 1];
-                lab[s.v] = g >= 0 ? g + 1 : -(c - 1) - 2;
+                lab[s.r] = g >= 0 ? g + 1 : -(c - 1) - 2;
             }
         }
         if (mode == 1) {
 #ifdef ULK_EMU
-            if (g >= 0) biglist[(*nbig)++] = s.v;
+            if (g >= 0) biglist[(*nbig)++] = s.r;
 #else
-            ulk_warp_append(g >= 0, s.v, biglist, nbig);
+            ulk_warp_append(g >= 0, s.r, biglist, nbig);
 #endif
         }
     }
@@ -318,133 +416,93 @@ struct K_LabelCc {
     }
 #endif
 };
-struct K_FlagRoots {
-    const i32 *P; i32 *flag;
-    ULK_D void operator()(i64 v) const { flag[v] = P[v] == (i32)v ? 1 : 0; }
-};
 
 // ------------------------------------------------------------------ voxel stage: steepest edges
-// For every active voxel the minimum incident edge by (weight, edge key); edge key =
-// 3*source + direction reproduces the enumeration order of edges_from_mask
-// (vendored/graph.py:41-57), i.e. higra's stable tie-break.
-// Candidates are visited in increasing edge-key order (-z, -y, -x, +x, +y, +z), so a strict
-// comparison of the weights alone yields the minimum of (weight, key).
+// For every voxel of the list the minimum incident edge by (weight, edge key); edge key =
+// 3*source voxel + direction reproduces the enumeration order of edges_from_mask
+// (vendored/graph.py:41-57), i.e. higra's stable tie-break.  Candidates are visited in
+// increasing edge-key order (-z, -y, -x, +x, +y, +z), so a strict comparison of the weights alone
+// yields the minimum of (weight, key).  Outputs: the weight (order-preserving bits), the key and
+// the RANK of the other endpoint (ULK_PO_NONE / ULK_PO_OUT otherwise).
 struct K_MinEdge {
-    const i32 *lab; UlkCt ct; UlkDims dm;
-    u32 *mw, *pk;
-    u32 *cmax;        // when set (float32 contours): max |ct| over the voxels of the regions, as float bits
-    // neighbour indices clamped to v at the frame border: all loads are issued together
-    struct S1 { i32 v, l; u32 h; i32 ln[6]; float c, cn[6]; };
-    typedef S1 S2;
-    ULK_D ULK_INLINE i32 nb(i32 v, int i, u32 h) const
-    {
-        const i32 sy = dm.W, sz = dm.W * dm.H;
-        const i32 off = i == 0 ? -sz : i == 1 ? -sy : i == 2 ? -1 : i == 3 ? 1 : i == 4 ? sy : sz;
-        return ((h >> i) & 1u) ? v + off : v;
-    }
-    ULK_D ULK_INLINE S1 load1(i32 v, i32 z, i32 y, i32 x, bool ok) const
+    const i32 *lab; UlkCt ct; UlkFg fg;
+    u32 *mw, *pk; i32 *po;
+    struct S1 { i32 r, v, x; bool ok; UlkNbRaw q; };
+    struct S2 { i32 r, v, l; bool ok; i32 rn[6], ln[6]; float c, cn[6]; };
+    ULK_D ULK_INLINE S1 load1(i32 r, i32 v, i32 z, i32 y, i32 x, bool ok) const
     {
         S1 s;
-        s.v = v; s.l = 0; s.h = 0; s.c = 0.f;
-        if (!ok) return s;
-        s.h = (z > 0 ? 1u : 0u) | (y > 0 ? 2u : 0u) | (x > 0 ? 4u : 0u) | (x + 1 < dm.W ? 8u : 0u) | (y + 1 < dm.H ? 16u : 0u) | (z + 1 < dm.D ? 32u : 0u);
-        s.l = lab[v];
-#ifdef ULK_EMU
-        for (int i = 0; i < 6; ++i) s.ln[i] = lab[nb(v, i, s.h)];
-        if (ct.f) { s.c = ct.f[v]; for (int i = 0; i < 6; ++i) s.cn[i] = ct.f[nb(v, i, s.h)]; }
-#else
-#pragma unroll
-        for (int i = 0; i < 6; ++i) s.ln[i] = lab[nb(v, i, s.h)];
-        if (ct.f) {
-            s.c = ct.f[v];
-#pragma unroll
-            for (int i = 0; i < 6; ++i) s.cn[i] = ct.f[nb(v, i, s.h)];
-        }
-#endif
-        return s;
-    }
-    ULK_D ULK_INLINE S2 load2(const S1 &s, bool) const { return s; }
-    ULK_D ULK_INLINE void run(const S2 &s, bool ok) const
-    {
-        const i32 v = s.v, l = s.l;
-        if (cmax) {
-            u32 bits = 0;
-            if (l > 0) { float a = fabsf(s.c); if (a <= 3.0e38f) memcpy(&bits, &a, 4); }
-#ifdef ULK_EMU
-            if (bits > *cmax) *cmax = bits;
-#else
-            const u32 m = __reduce_max_sync(0xffffffffu, bits);
-            if ((threadIdx.x & 31) == 0 && m > *cmax) atomicMax(cmax, m);
-#endif
-        }
-        if (l <= 0) {          // K_Hook1 reads the key instead of the label; lanes past the list end write nothing
-            if (ok) pk[v] = ULK_PK_OUT;
-            return;
-        }
-        u32 bw = ULK_NONE32, bk = ULK_NONE32;
-#ifndef ULK_EMU
-#pragma unroll
-#endif
-        for (int i = 0; i < 6; ++i) {
-            if (!((s.h >> i) & 1u) || s.ln[i] != l) continue;
-            const i32 u = nb(v, i, s.h);
-            // candidates in increasing edge-key order: the first strictly smaller weight wins
-            const i32 a = i < 3 ? u : v, b = i < 3 ? v : u;
-            const float wf = ct.f ? (i < 3 ? ulk_wsum(s.cn[i] + s.c) : ulk_wsum(s.c + s.cn[i])) : ct.w(a, b);
-            const u32 w = ulk_f2ord(wf);
-            const u32 d = i == 0 || i == 5 ? 2u : (i == 1 || i == 4 ? 1u : 0u);
-            if (w < bw) { bw = w; bk = 3u * (u32)a + d; }
-        }
-        mw[v] = bw;
-        pk[v] = bk;
-    }
-};
-ULK_HD ULK_INLINE i32 ulk_edge_other(u32 key, i32 v, const UlkDims &dm)
-{
-    i32 a = (i32)(key / 3u);
-    i32 b = a + dm.stride((int)(key % 3u));
-    return a == v ? b : a;
-}
-// first Boruvka round: every voxel hooks along its steepest edge; mutual pairs keep the
-// smaller voxel as root.  state: 0 growing, 1 minimum (basin seed)
-// reads only the steepest-edge keys (its own and the other endpoint's); the level of a root is
-// fetched by the roots alone, and `state` only exists at roots (nothing reads it elsewhere)
-struct K_Hook1 {
-    const u32 *mw, *pk; UlkDims dm;
-    i32 *bp; u8 *state; u32 *Lr; u32 *best; i32 *nbasins;
-    struct S1 { i32 v; u32 k; };
-    struct S2 { i32 v, u; u32 k, ku; };
-    ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32, bool ok) const
-    {
-        S1 s;
-        s.v = v; s.k = ULK_PK_OUT;
-        if (ok) s.k = pk[v];
+        s.r = r; s.v = v; s.x = x; s.ok = ok;
+        if (ok) s.q = fg.nb_load(r, fg.seg(z, y, x), z, y, true, true);
         return s;
     }
     ULK_D ULK_INLINE S2 load2(const S1 &a, bool ok) const
     {
         S2 s;
-        s.v = a.v; s.k = a.k; s.u = a.v; s.ku = ULK_NONE32;
-        if (ok && a.k < ULK_PK_OUT) { s.u = ulk_edge_other(a.k, a.v, dm); s.ku = pk[s.u]; }
+        s.r = a.r; s.v = a.v; s.ok = ok; s.l = 0; s.c = 0.f;
+        if (!ok) return s;
+        fg.nb_ranks(a.q, a.r, a.v, a.x, s.rn);
+        s.l = lab[a.r];
+#ifndef ULK_EMU
+#pragma unroll
+#endif
+        for (int i = 0; i < 6; ++i) s.ln[i] = s.rn[i] >= 0 ? lab[s.rn[i]] : 0;
+        if (ct.f) {
+            s.c = ct.f[a.r];
+#ifndef ULK_EMU
+#pragma unroll
+#endif
+            for (int i = 0; i < 6; ++i) s.cn[i] = s.rn[i] >= 0 ? ct.f[s.rn[i]] : 0.f;
+        }
         return s;
     }
     ULK_D ULK_INLINE void run(const S2 &s, bool ok) const
     {
         if (!ok) return;
-        const i32 v = s.v;
-        if (s.k == ULK_PK_OUT) { bp[v] = -1; return; }
-        if (s.k == ULK_NONE32) {
-            bp[v] = v; state[v] = 1; Lr[v] = ULK_NONE32; best[v] = ULK_NONE32;
+        const i32 r = s.r, v = s.v, l = s.l;
+        if (l <= 0) { po[r] = ULK_PO_OUT; return; }
+        u32 bw = ULK_NONE32, bk = ULK_NONE32;
+        i32 bo = ULK_PO_NONE;
+#ifndef ULK_EMU
+#pragma unroll
+#endif
+        for (int i = 0; i < 6; ++i) {
+            if (s.rn[i] < 0 || s.ln[i] != l) continue;
+            // candidates in increasing edge-key order: the first strictly smaller weight wins
+            const float wf = ct.f ? ulk_wsum(i < 3 ? s.cn[i] + s.c : s.c + s.cn[i]) : ct.w(r, s.rn[i]);
+            const u32 w = ulk_f2ord(wf);
+            const i32 a = i < 3 ? v + fg.nb_off(i) : v;
+            if (w < bw) { bw = w; bk = 3u * (u32)a + ulk_nb_dir(i); bo = s.rn[i]; }
+        }
+        mw[r] = bw;
+        pk[r] = bk;
+        po[r] = bo;
+    }
+};
+// first Boruvka round: every voxel hooks along its steepest edge; mutual pairs (each is the
+// other's steepest endpoint: one edge joins two neighbours, so that is the same edge) keep the
+// smaller voxel as root.  state: 0 growing, 1 minimum (basin seed); the level of a root and its
+// state only exist at roots.  Rank space only: no coordinates, no neighbour lookups.
+struct K_Hook1 {
+    const u32 *mw; const i32 *po;
+    i32 *bp; u8 *state; u32 *Lr; u32 *best; i32 *nbasins;
+    struct S1 { i32 r, o; };
+    struct S2 { i32 r, o, oo; };
+    ULK_D ULK_INLINE S1 load1(i32 r, bool ok) const { S1 s; s.r = r; s.o = ok ? po[r] : ULK_PO_OUT; return s; }
+    ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const { S2 s; s.r = a.r; s.o = a.o; s.oo = a.o >= 0 ? po[a.o] : -3; return s; }
+    ULK_D ULK_INLINE void run(const S2 &s, bool ok) const
+    {
+        if (!ok) return;
+        const i32 r = s.r;
+        if (s.o == ULK_PO_OUT) { bp[r] = -1; return; }
+        if (s.o == ULK_PO_NONE) {
+            bp[r] = r; state[r] = 1; Lr[r] = ULK_NONE32; best[r] = ULK_NONE32;
             ulk_atomic_add(nbasins, 1);
             return;
         }
-        if (s.ku == s.k && v < s.u) { bp[v] = v; state[v] = 0; Lr[v] = mw[v]; best[v] = ULK_NONE32; }
-        else bp[v] = s.u;
+        if (s.oo == r && r < s.o) { bp[r] = r; state[r] = 0; Lr[r] = mw[r]; best[r] = ULK_NONE32; }
+        else bp[r] = s.o;
     }
-};
-struct K_Compress {
-    i32 *bp;
-    ULK_D void operator()(i64 v) const { if (bp[v] >= 0) bp[v] = ulk_vfind(bp, (i32)v); }
 };
 // path compression of the hook forest, fused with the lists of the flow rounds: growing
 // roots, and candidates = voxels whose steepest weight equals their supervertex level
@@ -452,9 +510,8 @@ struct K_CompressCand {
     i32 *bp; const u32 *mw; const u32 *Lr; const u8 *state;
     i32 *cand; i32 *ncand; i32 *groots; i32 *ngroots; i32 *sroots; i32 *nsroots;
 #ifdef ULK_EMU
-    void operator()(i64 vv, i32, i32, i32) const
+    void operator()(i32 v) const
     {
-        i32 v = (i32)vv;
         if (bp[v] < 0) return;
         i32 r = ulk_vfind(bp, v);
         bp[v] = r;
@@ -487,85 +544,78 @@ struct K_CompressCand {
 // a growing supervertex looks for its minimum-key outgoing edge at its own level
 struct K_FindFlow {
     const i32 *cand; const i32 *lab; const i32 *bp; const u32 *mw; const u32 *Lr; const u8 *state;
-    UlkCt ct; UlkDims dm;
+    UlkCt ct; UlkFg fg;
     u32 *best; i32 *cand2; i32 *ncand2;
     ULK_D void operator()(i64 i) const
     {
-        i32 v = cand[i];
-        i32 r = ulk_vfind(bp, v);
-        if (state[r] != 0 || mw[v] != Lr[r]) return;
-        cand2[ulk_atomic_add(ncand2, 1)] = v;
-        i32 l = lab[v];
-        u32 lv = Lr[r];
-        i32 z, y, x;
-        dm.coords(v, z, y, x);
+        const i32 r = cand[i];
+        const i32 root = ulk_vfind(bp, r);
+        if (state[root] != 0 || mw[r] != Lr[root]) return;
+        cand2[ulk_atomic_add(ncand2, 1)] = r;
+        const i32 l = lab[r];
+        const u32 lv = Lr[root];
+        const i32 v = fg.fgl[r];
+        i32 z, y, x, rn[6];
+        fg.dm.coords(v, z, y, x);
+        fg.nb_ranks(fg.nb_load(r, fg.seg(z, y, x), z, y, true, true), r, v, x, rn);
         u32 b = ULK_NONE32;
-        for (int d = 0; d < 3; ++d) {
-            i32 st = dm.stride(d);
-            if (dm.bwd(d, z, y, x)) {
-                i32 u = v - st;
-                if (lab[u] == l && ulk_f2ord(ct.w(u, v)) == lv && ulk_vfind(bp, u) != r) {
-                    u32 k = 3u * (u32)u + d;
-                    if (k < b) b = k;
-                }
-            }
-            if (dm.fwd(d, z, y, x)) {
-                i32 u = v + st;
-                if (lab[u] == l && ulk_f2ord(ct.w(v, u)) == lv && ulk_vfind(bp, u) != r) {
-                    u32 k = 3u * (u32)v + d;
-                    if (k < b) b = k;
-                }
-            }
+        for (int j = 0; j < 6; ++j) {
+            const i32 u = rn[j];
+            if (u < 0 || lab[u] != l || ulk_f2ord(ct.w(r, u)) != lv || ulk_vfind(bp, u) == root) continue;
+            const u32 k = 3u * (u32)(j < 3 ? v + fg.nb_off(j) : v) + ulk_nb_dir(j);
+            if (k < b) b = k;
         }
-        if (b != ULK_NONE32) ulk_atomic_min(&best[r], b);
+        if (b != ULK_NONE32) ulk_atomic_min(&best[root], b);
     }
 };
 // decide, read-only part: target root of every growing supervertex (-1: becomes a minimum,
 // -2: stays root as the winner of a mutual pair)
 struct K_Decide1 {
-    const i32 *groots; const i32 *bp; const u32 *best; UlkDims dm;
-    i32 *tgt;
+    const i32 *groots; const i32 *bp; const u32 *best; UlkFg fg;
+    i32 *tgt; i32 *src_rank;       // src_rank: rank of the source voxel of the chosen edge
     ULK_D void operator()(i64 i) const
     {
-        i32 r = groots[i];
-        u32 k = best[r];
+        const i32 r = groots[i];
+        const u32 k = best[r];
         if (k == ULK_NONE32) { tgt[i] = -1; return; }
-        i32 a = (i32)(k / 3u), b = a + dm.stride((int)(k % 3u));
-        i32 ra = ulk_vfind(bp, a), rb = ulk_vfind(bp, b);
-        i32 t = ra == r ? rb : ra;
+        const i32 a = (i32)(k / 3u), b = a + fg.dm.stride((int)(k % 3u));
+        const i32 qa = fg.rank_of(a), qb = fg.rank_of(b);
+        src_rank[i] = qa;
+        const i32 ra = ulk_vfind(bp, qa), rb = ulk_vfind(bp, qb);
+        const i32 t = ra == r ? rb : ra;
         if (best[t] == k && r < t) { tgt[i] = -2; return; }
         tgt[i] = t;
     }
 };
 struct K_Decide2 {
-    const i32 *groots; const i32 *tgt;
+    const i32 *groots; const i32 *tgt; const i32 *src_rank;
     i32 *bp; u8 *state; u32 *best; u8 *fmark;
     i32 *groots2; i32 *ngroots2;
-    i32 *flow_root; u32 *flow_key; i32 *nflow; i32 *nbasins;
+    i32 *flow_root; u32 *flow_key; i32 *flow_src; i32 *nflow; i32 *nbasins;
     ULK_D void operator()(i64 i) const
     {
-        i32 r = groots[i];
-        i32 t = tgt[i];
-        u32 k = best[r];
+        const i32 r = groots[i];
+        const i32 t = tgt[i];
+        const u32 k = best[r];
         best[r] = ULK_NONE32;
         if (t == -1) { state[r] = 1; ulk_atomic_add(nbasins, 1); return; }
         if (t == -2) { groots2[ulk_atomic_add(ngroots2, 1)] = r; return; }
         bp[r] = t;
-        i32 j = ulk_atomic_add(nflow, 1);
-        flow_root[j] = r; flow_key[j] = k;
-        u32 a = k / 3u, d = k % 3u;
+        const i32 j = ulk_atomic_add(nflow, 1);
+        const u32 a = (u32)src_rank[i], d = k % 3u;
+        flow_root[j] = r; flow_key[j] = k; flow_src[j] = (i32)a;
+        // spanning-tree mark of the flow edge at its source voxel, one bit per direction
         ulk_atomic_or((u32 *)(fmark + (a & ~3u)), (1u << d) << (8u * (a & 3u)));
     }
 };
 
 // ------------------------------------------------------------------ basins
-// second path compression; every basin root appends (region label, root voxel): sorting
+// second path compression; every basin root appends (region label, root rank): sorting
 // these keys numbers the basins grouped by region, in raster order of their roots
 struct K_CompressRoots {
     i32 *bp; const i32 *lab; u64 *rootkeys; i32 *nroots;
-    ULK_D void operator()(i64 vv, i32, i32, i32) const
+    ULK_D void operator()(i32 v) const
     {
-        i32 v = (i32)vv;
         if (bp[v] < 0) return;
         i32 r = ulk_vfind(bp, v);
         bp[v] = r;
@@ -601,40 +651,26 @@ struct K_BasinRegroup {      // sorted position = global basin id
         ulk_atomic_add(&lab_hist[l - 1], 1);
     }
 };
-// bp[v] is the supervertex root of v (K_CompressCand) and bp[root] the basin root
-// (K_CompressRoots on the root list): two hops, then the basin id
-struct K_AssignBasin {     // background stays at the memset value -1
+// bp[r] is the supervertex root of r (K_CompressCand) and bp[root] the basin root
+// (K_CompressRoots on the root list): two hops, then the basin id (-1 outside the regions)
+struct K_AssignBasin {
     const i32 *bp; const u32 *gid_at_root;
     i32 *bas;
-    struct S1 { i32 v, r; };
-    struct S2 { i32 v, rr; };
-    ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32, bool ok) const { S1 s; s.v = ok ? v : -1; s.r = ok ? bp[v] : -1; return s; }
-    ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const { S2 s; s.v = a.v; s.rr = a.r < 0 ? -1 : bp[a.r]; return s; }
-    ULK_D ULK_INLINE void run(const S2 &s, bool) const { if (s.v >= 0) bas[s.v] = s.rr < 0 ? -1 : (i32)gid_at_root[s.rr]; }
-};
-// instead of a memset of the whole basin-id volume: -1 on the neighbours of the list's voxels
-// that are outside every region (the only entries outside the list a stencil kernel reads)
-struct K_ClearHalo {
-    const i32 *lab; UlkDims dm; i32 *bas;
-    ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
-    {
-        const i32 v = (i32)vv;
-        for (int d = 0; d < 3; ++d) {
-            const i32 st = dm.stride(d);
-            if (dm.bwd(d, z, y, x) && lab[v - st] <= 0) bas[v - st] = -1;
-            if (dm.fwd(d, z, y, x) && lab[v + st] <= 0) bas[v + st] = -1;
-        }
-    }
+    struct S1 { i32 r, p; };
+    struct S2 { i32 r, rr; };
+    ULK_D ULK_INLINE S1 load1(i32 r, bool ok) const { S1 s; s.r = ok ? r : -1; s.p = ok ? bp[r] : -1; return s; }
+    ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const { S2 s; s.r = a.r; s.rr = a.p < 0 ? -1 : bp[a.p]; return s; }
+    ULK_D ULK_INLINE void run(const S2 &s, bool) const { if (s.r >= 0) bas[s.r] = s.rr < 0 ? -1 : (i32)gid_at_root[s.rr]; }
 };
 // flow edges are spanning-tree edges of the basin of their supervertex
 struct K_FlowTop {
-    const i32 *flow_root; const u32 *flow_key; const i32 *bas; UlkCt ct; UlkDims dm; u64 *b_top; u32 *Tk;
+    const i32 *flow_root; const u32 *flow_key; const i32 *flow_src; const i32 *bas; UlkCt ct; UlkFg fg; u64 *b_top; u32 *Tk;
     ULK_D void operator()(i64 j) const
     {
-        u32 fk = flow_key[j];
-        i32 a = (i32)(fk / 3u), e = a + dm.stride((int)(fk % 3u));
-        i32 b = bas[flow_root[j]];
-        ulk_atomic_max(&b_top[b], ((u64)ulk_f2ord(ct.w(a, e)) << 32) | fk);
+        const u32 fk = flow_key[j];
+        const i32 a = (i32)(fk / 3u), e = a + fg.dm.stride((int)(fk % 3u));
+        const i32 b = bas[flow_root[j]];
+        ulk_atomic_max(&b_top[b], ((u64)ulk_f2ord(ct.w(flow_src[j], fg.rank_of(e))) << 32) | fk);
         if (Tk) ulk_atomic_max(&Tk[b], fk);
     }
 };
@@ -651,10 +687,10 @@ struct K_K3Need {
     }
 };
 #ifndef ULK_EMU
-// the voxels of the basins that need the check, one warp per basin scanning its bounding box
-// row by row (x-runs of a basin stay contiguous in the list, which is all K_K3Init relies on)
+// the voxels (ranks) of the basins that need the check, one warp per basin scanning its bounding
+// box row by row (x-runs of a basin stay contiguous in the list, which is all K_K3Init relies on)
 struct K_K3Collect {
-    const i32 *needlist; i64 nneed; const i32 *bas; const i32 *bbmin, *bbmax; UlkDims dm;
+    const i32 *needlist; i64 nneed; const i32 *bas; const i32 *bbmin, *bbmax; UlkFg fg;
     i32 *list; i32 *count;
     ULK_D void warp(i64 ii, bool) const
     {
@@ -666,11 +702,13 @@ struct K_K3Collect {
         const i32 z1 = bbmax[3 * b], y1 = bbmax[3 * b + 1], x1 = bbmax[3 * b + 2];
         for (i32 z = z0; z <= z1; ++z)
             for (i32 y = y0; y <= y1; ++y) {
-                const i32 row = (z * dm.H + y) * dm.W;
+                const i32 trow = (z * fg.dm.H + y) * fg.S;
                 for (i32 xb = x0; xb <= x1; xb += 32) {
                     const i32 x = xb + lane;
-                    const bool hit = x <= x1 && bas[row + x] == b;
-                    ulk_warp_append(hit, row + x, list, count);
+                    i32 r = -1;
+                    if (x <= x1) r = UlkFg::rank_in(fg.load(trow + (x >> 5)), x & 31);
+                    const bool hit = r >= 0 && bas[r] == b;
+                    ulk_warp_append(hit, r, list, count);
                 }
             }
     }
@@ -684,60 +722,62 @@ struct K_K3Collect {
 //    belong to the minimum, plateau voxels above it go to the relaxation list `hp`;
 //  * K0[basin] = max over its voxels of their smallest in-basin edge key, the lower bound of
 //    the basin's raster-key bottleneck (see K_K3*).
+// "Same region" is decided on basins (g_lab[basin] = region label): no label volume is read.
 struct K_BasinAccum {
-    const i32 *bas; const i32 *lab; const u32 *mw, *pk; UlkDims dm;
+    const i32 *bas; const u32 *mw, *pk; const i32 *po; UlkFg fg;
     i32 *b_size; u64 *b_top; u64 *ncross;
     int want_stats; i32 *bbmin, *bbmax; i64 *csum;
     int want_join; const u32 *b_L; u32 *jk; i32 *hp; i32 *nhp;
     int want_k0; u32 *K0; u32 *Tk;      // Tk: largest raster key among the basin's steepest edges
-    i32 *xl; i32 *nxl;                  // voxels with a forward edge into another basin of their region
-    const i32 *g_lab;                   // region label of a basin (the voxel's own label is not read)
-    // phase 1: the voxel's own entries and its neighbours' basins (indices clamped at the border)
-    struct S1 { i32 v, z, y, x, b, l; u32 m, k; i32 a[3], c[3]; };
-    // phase 2: what depends on them -- the basin level, the weight across the steepest edge, the
-    // labels of forward neighbours in another basin
-    struct S2 { i32 v, z, y, x, b; u64 top; u32 nc, kmin, jkv; bool plateau; };
-    ULK_D ULK_INLINE S1 load1(i32 v, i32 z, i32 y, i32 x, bool ok) const
+    i32 *xl; i32 *nxl;                  // ranks of voxels with a forward edge into another basin of their region
+    const i32 *g_lab;                   // region label of a basin
+    // phase 1: the voxel's own entries and what its neighbours' ranks depend on
+    struct S1 { i32 r, v, z, y, x, b, o; u32 m, k; UlkNbRaw q; };
+    // phase 2: the neighbours' basins, the basin level, the weight across the steepest edge
+    struct S2 { i32 r, v, z, y, x, b; u64 top; u32 nc, kmin, jkv; bool plateau; };
+    ULK_D ULK_INLINE S1 load1(i32 r, i32 v, i32 z, i32 y, i32 x, bool ok) const
     {
         S1 s;
-        s.v = v; s.z = z; s.y = y; s.x = x; s.b = -1;
+        s.r = r; s.v = v; s.z = z; s.y = y; s.x = x; s.b = -1; s.o = ULK_PO_OUT; s.m = 0; s.k = ULK_NONE32;
         if (!ok) return s;
-        const i32 sy = dm.W, sz = dm.W * dm.H;
-        s.b = bas[v];
-        s.a[0] = bas[x + 1 < dm.W ? v + 1 : v]; s.a[1] = bas[y + 1 < dm.H ? v + sy : v]; s.a[2] = bas[z + 1 < dm.D ? v + sz : v];
-        s.c[0] = s.c[1] = s.c[2] = -1;
-        if (want_k0) { s.c[0] = bas[x > 0 ? v - 1 : v]; s.c[1] = bas[y > 0 ? v - sy : v]; s.c[2] = bas[z > 0 ? v - sz : v]; }
-        s.m = mw[v]; s.k = pk[v]; s.l = 0;
+        s.b = bas[r];
+        s.m = mw[r]; s.k = pk[r]; s.o = po[r];
+        s.q = fg.nb_load(r, fg.seg(z, y, x), z, y, want_k0 != 0, true);
         return s;
     }
     ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const
     {
         S2 o;
-        o.v = a.v; o.z = a.z; o.y = a.y; o.x = a.x; o.b = a.b;
+        o.r = a.r; o.v = a.v; o.z = a.z; o.y = a.y; o.x = a.x; o.b = a.b;
         o.top = 0; o.nc = 0; o.kmin = ULK_NONE32; o.jkv = ULK_JK_CORE; o.plateau = false;
         const i32 b = a.b, v = a.v;
         if (b < 0) return o;
-        const i32 sy = dm.W, sz = dm.W * dm.H;
-        const bool f0 = a.x + 1 < dm.W, f1 = a.y + 1 < dm.H, f2 = a.z + 1 < dm.D;
-        // issue the dependent loads first
-        const bool q0 = f0 && a.a[0] != b, q1 = f1 && a.a[1] != b, q2 = f2 && a.a[2] != b;
-        const i32 l0 = q0 ? lab[v + 1] : 0, l1 = q1 ? lab[v + sy] : 0, l2 = q2 ? lab[v + sz] : 0;
-        const i32 lown = (q0 || q1 || q2) ? g_lab[b] : 0;
+        i32 rn[6], nb[6];
+        fg.nb_ranks(a.q, a.r, v, a.x, rn);
+#ifndef ULK_EMU
+#pragma unroll
+#endif
+        for (int i = 0; i < 6; ++i) nb[i] = rn[i] >= 0 ? bas[rn[i]] : -1;
         u32 bl = 0, mo = 0;
-        const bool has_edge = a.k != ULK_NONE32;
-        if (want_join) { bl = b_L[b]; if (has_edge) mo = mw[ulk_edge_other(a.k, v, dm)]; }
+        const bool has_edge = a.o >= 0;
+        if (want_join) { bl = b_L[b]; if (has_edge) mo = mw[a.o]; }
+        const bool q0 = nb[3] >= 0 && nb[3] != b, q1 = nb[4] >= 0 && nb[4] != b, q2 = nb[5] >= 0 && nb[5] != b;
+        if (q0 || q1 || q2) {
+            const i32 lown = g_lab[b];
+            if (q0 && g_lab[nb[3]] == lown) ++o.nc;
+            if (q1 && g_lab[nb[4]] == lown) ++o.nc;
+            if (q2 && g_lab[nb[5]] == lown) ++o.nc;
+        }
         o.top = has_edge ? ((u64)a.m << 32) | a.k : 0;
-        if (q0 && l0 == lown) ++o.nc;
-        if (q1 && l1 == lown) ++o.nc;
-        if (q2 && l2 == lown) ++o.nc;
+        const i32 sy = fg.dm.W, sz = fg.dm.W * fg.dm.H;
         u32 kk;
-        if (f0 && a.a[0] == b) { kk = 3u * (u32)v; if (kk < o.kmin) o.kmin = kk; }
-        if (f1 && a.a[1] == b) { kk = 3u * (u32)v + 1u; if (kk < o.kmin) o.kmin = kk; }
-        if (f2 && a.a[2] == b) { kk = 3u * (u32)v + 2u; if (kk < o.kmin) o.kmin = kk; }
+        if (nb[3] == b) { kk = 3u * (u32)v; if (kk < o.kmin) o.kmin = kk; }
+        if (nb[4] == b) { kk = 3u * (u32)v + 1u; if (kk < o.kmin) o.kmin = kk; }
+        if (nb[5] == b) { kk = 3u * (u32)v + 2u; if (kk < o.kmin) o.kmin = kk; }
         if (want_k0) {
-            if (a.x > 0 && a.c[0] == b) { kk = 3u * (u32)(v - 1); if (kk < o.kmin) o.kmin = kk; }
-            if (a.y > 0 && a.c[1] == b) { kk = 3u * (u32)(v - sy) + 1u; if (kk < o.kmin) o.kmin = kk; }
-            if (a.z > 0 && a.c[2] == b) { kk = 3u * (u32)(v - sz) + 2u; if (kk < o.kmin) o.kmin = kk; }
+            if (nb[2] == b) { kk = 3u * (u32)(v - 1); if (kk < o.kmin) o.kmin = kk; }
+            if (nb[1] == b) { kk = 3u * (u32)(v - sy) + 1u; if (kk < o.kmin) o.kmin = kk; }
+            if (nb[0] == b) { kk = 3u * (u32)(v - sz) + 2u; if (kk < o.kmin) o.kmin = kk; }
         }
         if (want_join) {
             if (a.m == bl || !has_edge) o.jkv = ULK_JK_CORE;
@@ -751,12 +791,12 @@ struct K_BasinAccum {
     {
         const i32 b = o.b;
         if (b < 0) return;
-        if (want_join) jk[o.v] = o.jkv;
+        if (want_join) jk[o.r] = o.jkv;
         b_size[b] += 1;
         if (o.top > b_top[b]) b_top[b] = o.top;
         *ncross += o.nc;
-        if (o.nc) xl[(*nxl)++] = o.v;
-        if (o.plateau) hp[(*nhp)++] = o.v;
+        if (o.nc) xl[(*nxl)++] = o.r;
+        if (o.plateau) hp[(*nhp)++] = o.r;
         if (want_k0 && o.kmin != ULK_NONE32 && o.kmin > K0[b]) K0[b] = o.kmin;
         if (want_k0 && o.top != 0 && (u32)o.top > Tk[b]) Tk[b] = (u32)o.top;
         if (want_stats) {
@@ -782,10 +822,10 @@ struct K_BasinAccum {
         const i32 b = o.b, v = o.v, x = o.x;
         u32 nct = __reduce_add_sync(0xffffffffu, o.nc);
         if (lane == 0 && nct) atomicAdd((unsigned long long *)ncross, (unsigned long long)nct);
-        if (nct) ulk_warp_append(o.nc > 0, v, xl, nxl);
+        if (nct) ulk_warp_append(o.nc > 0, o.r, xl, nxl);
         if (want_join) {
-            if (b >= 0) jk[v] = o.jkv;
-            ulk_warp_append(o.plateau, v, hp, nhp);
+            if (b >= 0) jk[o.r] = o.jkv;
+            ulk_warp_append(o.plateau, o.r, hp, nhp);
         }
         const i32 row = v - x;
         const i32 bp_ = __shfl_up_sync(0xffffffffu, b, 1), rp_ = __shfl_up_sync(0xffffffffu, row, 1);
@@ -850,35 +890,35 @@ struct K_BasinAccum {
 // ------------------------------------------------------------------ join keys (area hierarchy)
 // plateau voxels above the basin level: minimax relaxation along spanning-tree edges
 struct K_PlateauRelax {
-    const i32 *hp; const i32 *lab; const u32 *mw, *pk; const u8 *fmark; UlkCt ct; UlkDims dm;
+    const i32 *hp; const i32 *lab; const u32 *mw, *pk; const u8 *fmark; UlkCt ct; UlkFg fg;
     u32 *jk; i32 *changed;
     ULK_D void operator()(i64 i) const
     {
-        i32 v = hp[i];
-        i32 l = lab[v];
-        u32 lv = mw[v];
-        u32 cur = jk[v];
-        i32 z, y, x;
-        dm.coords(v, z, y, x);
+        const i32 r = hp[i];
+        const i32 l = lab[r];
+        const u32 lv = mw[r];
+        const u32 cur = jk[r];
+        const i32 v = fg.fgl[r];
+        i32 z, y, x, rn[6];
+        fg.dm.coords(v, z, y, x);
+        fg.nb_ranks(fg.nb_load(r, fg.seg(z, y, x), z, y, true, true), r, v, x, rn);
+        const u32 pkv = pk[r];
         u32 bestc = cur;
-        for (int d = 0; d < 3; ++d) {
-            i32 st = dm.stride(d);
-            for (int s = 0; s < 2; ++s) {
-                i32 u, src;
-                if (s == 0) { if (!dm.bwd(d, z, y, x)) continue; u = v - st; src = u; }
-                else { if (!dm.fwd(d, z, y, x)) continue; u = v + st; src = v; }
-                if (lab[u] != l) continue;
-                u32 k = 3u * (u32)src + d;
-                bool tree = pk[v] == k || pk[u] == k || ((fmark[src] >> d) & 1);
-                if (!tree) continue;
-                if (ulk_f2ord(ct.w(src, src + st)) != lv) continue;
-                u32 c;
-                if (mw[u] < lv) c = k;
-                else { u32 ju = jk[u]; c = ju > k ? ju : k; }
-                if (c < bestc) bestc = c;
-            }
+        for (int j = 0; j < 6; ++j) {
+            const i32 u = rn[j];
+            if (u < 0 || lab[u] != l) continue;
+            const u32 d = ulk_nb_dir(j);
+            const i32 srcv = j < 3 ? v + fg.nb_off(j) : v, srcr = j < 3 ? u : r;
+            const u32 k = 3u * (u32)srcv + d;
+            const bool tree = pkv == k || pk[u] == k || ((fmark[srcr] >> d) & 1);
+            if (!tree) continue;
+            if (ulk_f2ord(ct.w(r, u)) != lv) continue;
+            u32 c;
+            if (mw[u] < lv) c = k;
+            else { u32 ju = jk[u]; c = ju > k ? ju : k; }
+            if (c < bestc) bestc = c;
         }
-        if (bestc < cur) { jk[v] = bestc; *changed = 1; }
+        if (bestc < cur) { jk[r] = bestc; *changed = 1; }
     }
 };
 // late joiners climb the basin BPT: a voxel attaches to the highest ancestor of its basin
@@ -888,11 +928,11 @@ struct K_Attach {
     const i32 *Ipar; const u64 *Iwk; i32 *attach;
     struct S1 { i32 b; u32 j, m; };
     struct S2 { i32 o, node, p; u64 J; };
-    ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32, bool ok) const
+    ULK_D ULK_INLINE S1 load1(i32 r, bool ok) const
     {
         S1 s;
         s.b = -1; s.j = ULK_JK_CORE; s.m = 0;
-        if (ok) { s.b = bas[v]; s.j = jk[v]; s.m = mw[v]; }
+        if (ok) { s.b = bas[r]; s.j = jk[r]; s.m = mw[r]; }
         return s;
     }
     ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const
@@ -939,32 +979,39 @@ ULK_HD ULK_INLINE u64 ulk_hash64(u64 x)
     return x;
 }
 struct K_RagInsert {
-    const i32 *bas; const i32 *lab; UlkCt ct; UlkDims dm; UlkRagTable T; double fixscale;
-    struct S1 { i32 v, b, l; u32 f; i32 cb[3], cl[3]; };
-    typedef S1 S2;
-    ULK_D ULK_INLINE S1 load1(i32 v, i32 z, i32 y, i32 x, bool ok) const
+    const i32 *bas; const i32 *g_lab; UlkCt ct; UlkFg fg; UlkRagTable T; double fixscale;
+    struct S1 { i32 r, v, x, b; UlkNbRaw q; };
+    struct S2 { i32 r, v, b; i32 cr[3], cb[3]; };
+    ULK_D ULK_INLINE S1 load1(i32 r, i32 v, i32 z, i32 y, i32 x, bool ok) const
     {
         S1 s;
-        s.v = v; s.b = -1; s.l = 0; s.f = 0;
+        s.r = r; s.v = v; s.x = x; s.b = -1;
         if (!ok) return s;
-        s.f = (x + 1 < dm.W ? 1u : 0u) | (y + 1 < dm.H ? 2u : 0u) | (z + 1 < dm.D ? 4u : 0u);
-        const i32 u0 = (s.f & 1u) ? v + 1 : v, u1 = (s.f & 2u) ? v + dm.W : v, u2 = (s.f & 4u) ? v + dm.W * dm.H : v;
-        s.b = bas[v]; s.l = lab[v];
-        s.cb[0] = bas[u0]; s.cb[1] = bas[u1]; s.cb[2] = bas[u2];
-        s.cl[0] = lab[u0]; s.cl[1] = lab[u1]; s.cl[2] = lab[u2];
+        s.b = bas[r];
+        s.q = fg.nb_load(r, fg.seg(z, y, x), z, y, false, true);
         return s;
     }
-    ULK_D ULK_INLINE S2 load2(const S1 &s, bool) const { return s; }
+    ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const
+    {
+        S2 s;
+        s.r = a.r; s.v = a.v; s.b = a.b;
+        s.cr[0] = s.cr[1] = s.cr[2] = -1; s.cb[0] = s.cb[1] = s.cb[2] = -1;
+        if (a.b < 0) return s;
+        i32 rn[6];
+        fg.nb_ranks(a.q, a.r, a.v, a.x, rn);
+        for (int d = 0; d < 3; ++d) { s.cr[d] = rn[3 + d]; s.cb[d] = rn[3 + d] >= 0 ? bas[rn[3 + d]] : -1; }
+        return s;
+    }
     ULK_D ULK_INLINE void run(const S2 &s, bool) const
     {
-        const i32 v = s.v, b = s.b, l = s.l;
+        const i32 v = s.v, b = s.b;
         if (b < 0) return;
+        const i32 l = g_lab[b];
         for (int d = 0; d < 3; ++d) {
-            if (!((s.f >> d) & 1u) || s.cl[d] != l || s.cb[d] == b) continue;
             const i32 c = s.cb[d];
-            const i32 u = v + dm.stride(d);
+            if (c < 0 || c == b || g_lab[c] != l) continue;
             u64 key = b < c ? ((u64)(u32)b << 32) | (u32)c : ((u64)(u32)c << 32) | (u32)b;
-            float w = ct.w(v, u);
+            float w = ct.w(s.r, s.cr[d]);
             u32 ek = 3u * (u32)v + d;
             u64 h = ulk_hash64(key) & T.mask;
             for (;;) {
@@ -1014,96 +1061,103 @@ struct K_Hist {
 // alone and the basin's altitude-0 node is created by the LAST edge it accepts: the
 // bottleneck of the raster-key MST.  K0 = max over voxels of their smallest in-basin edge
 // key is a lower bound that is tight whenever edges <= K0 already connect the basin.
-// edges of a basin whose raster key is <= K0[basin].  Runs of x edges between voxels that are
-// neighbours in the (raster-ordered) voxel list and sit in one warp are hooked to their first
-// voxel at initialisation; K_K3Union joins the runs (same scheme as the component labelling).
+// Runs of x edges (key <= K0) between voxels that are neighbours in the list and sit in one warp
+// are hooked to their first voxel at initialisation; K_K3Union joins the runs (same scheme as
+// the component labelling).
 struct K_K3Init {
-    const i32 *bas; const u32 *K0; i32 *P;
-    struct S1 { i32 v, b, bl; bool ok, cons; };     // cons: the previous lane holds voxel v-1 of the same row
-    struct S2 { i32 v, b; bool ok, link; };
-    ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32 x, bool ok) const
+    const i32 *bas; const u32 *K0; const i32 *fgl; i32 *P;
+    struct S1 { i32 r, v, b, bl; bool ok, cons; };     // cons: the previous lane holds voxel v-1 of the same row
+    struct S2 { i32 r, b; bool ok, link; };
+    ULK_D ULK_INLINE S1 load1(i32 r, i32 v, i32, i32, i32 x, bool ok) const
     {
         S1 s;
-        s.v = v; s.ok = ok; s.b = -1; s.bl = -1;
+        s.r = r; s.v = v; s.ok = ok; s.b = -1; s.bl = -1;
 #ifdef ULK_EMU
-        s.cons = x > 0 && (x & 31) != 0;
+        s.cons = x > 0 && (x & 31) != 0 && r > 0 && fgl[r - 1] == v - 1;
 #else
         i32 vprev = __shfl_up_sync(0xffffffffu, v, 1);
         s.cons = (threadIdx.x & 31) > 0 && x > 0 && vprev == v - 1;
 #endif
-        if (ok) { s.b = bas[v]; s.bl = bas[x > 0 ? v - 1 : v]; }
+        if (ok) { s.b = bas[r]; s.bl = s.cons ? bas[r - 1] : -1; }
         return s;
     }
     ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const
     {
         S2 s;
-        s.v = a.v; s.b = a.b; s.ok = a.ok;
+        s.r = a.r; s.b = a.b; s.ok = a.ok;
         s.link = a.ok && a.cons && a.b >= 0 && a.bl == a.b && 3u * (u32)(a.v - 1) <= K0[a.b];
         return s;
     }
     ULK_D ULK_INLINE void run(const S2 &s, bool) const
     {
 #ifdef ULK_EMU
-        P[s.v] = s.b < 0 ? -1 : (s.link ? P[s.v - 1] : s.v);
+        P[s.r] = s.b < 0 ? -1 : (s.link ? P[s.r - 1] : s.r);
 #else
         const int lane = threadIdx.x & 31;
         u32 linked = __ballot_sync(0xffffffffu, s.link);
-        if (s.ok) P[s.v] = s.b < 0 ? -1 : s.v - (lane - ulk_run_start(linked, lane));
+        if (s.ok) P[s.r] = s.b < 0 ? -1 : s.r - (lane - ulk_run_start(linked, lane));
 #endif
     }
 };
 struct K_K3Union {
-    const i32 *bas; UlkDims dm; const u32 *K0; i32 *P;
-    struct S1 { i32 v, b, bl, by, byl, bz, bzl; u32 h; };     // h: x>0, y>0, z>0, run boundary
-    struct S2 { i32 v; u32 todo; };                             // todo: unions with -x, -y, -z
-    ULK_D ULK_INLINE S1 load1(i32 v, i32 z, i32 y, i32 x, bool ok) const
+    const i32 *bas; UlkFg fg; const u32 *K0; i32 *P;
+    struct S1 { i32 r, v, x, b; bool boundary; UlkNbRaw q; };
+    struct S2 { i32 r; i32 ul, uy, uz; };      // ranks to union with (-1: none)
+    ULK_D ULK_INLINE S1 load1(i32 r, i32 v, i32 z, i32 y, i32 x, bool ok) const
     {
         S1 s;
-        s.v = v; s.b = -1; s.h = 0;
+        s.r = r; s.v = v; s.x = x; s.b = -1;
 #ifdef ULK_EMU
-        const bool boundary = (x & 31) == 0;
+        s.boundary = (x & 31) == 0;
 #else
         i32 vprev = __shfl_up_sync(0xffffffffu, v, 1);
-        const bool boundary = (threadIdx.x & 31) == 0 || vprev != v - 1;
+        s.boundary = (threadIdx.x & 31) == 0 || vprev != v - 1;
 #endif
         if (!ok) return s;
-        const bool hx = x > 0, hy = y > 0, hz = z > 0;
-        const i32 uy = hy ? v - dm.W : v, uz = hz ? v - dm.W * dm.H : v;
-        s.h = (hx ? 1u : 0u) | (hy ? 2u : 0u) | (hz ? 4u : 0u) | (boundary ? 8u : 0u);
-        s.b = bas[v];
-        s.bl = bas[hx ? v - 1 : v]; s.by = bas[uy]; s.byl = bas[hx ? uy - 1 : uy]; s.bz = bas[uz]; s.bzl = bas[hx ? uz - 1 : uz];
+        s.b = bas[r];
+        s.q = fg.nb_load(r, fg.seg(z, y, x), z, y, true, false);
         return s;
     }
     ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const
     {
         S2 s;
-        s.v = a.v; s.todo = 0;
+        s.r = a.r; s.ul = s.uy = s.uz = -1;
         const i32 b = a.b, v = a.v;
         if (b < 0) return s;
+        i32 rn[6];
+        fg.nb_ranks(a.q, a.r, v, a.x, rn);
         const u32 kmax = K0[b];
-        const i32 uy = v - dm.W, uz = v - dm.W * dm.H;
-        const bool left = (a.h & 1u) && a.bl == b && 3u * (u32)(v - 1) <= kmax;
-        if (left && (a.h & 8u)) s.todo |= 1u;
-        // (u-1,u), (u-1,v-1) carry smaller keys than (u,v): with (v-1,v) they already join u and v
-        if ((a.h & 2u) && a.by == b && 3u * (u32)uy + 1u <= kmax && !(left && a.byl == b)) s.todo |= 2u;
-        if ((a.h & 4u) && a.bz == b && 3u * (u32)uz + 2u <= kmax && !(left && a.bzl == b)) s.todo |= 4u;
+        const i32 uy = v - fg.dm.W, uz = v - fg.dm.W * fg.dm.H;
+        const bool left = rn[2] >= 0 && bas[rn[2]] == b && 3u * (u32)(v - 1) <= kmax;
+        if (left && a.boundary) s.ul = rn[2];
+        // (u-1,u), (u-1,v-1) carry smaller keys than (u,v): with (v-1,v) they already join u and v.
+        // u-1 is the voxel of rank(u)-1 when bit (x-1) of u's segment is set
+        const int bb = a.x & 31;
+        if (rn[1] >= 0 && bas[rn[1]] == b && 3u * (u32)uy + 1u <= kmax) {
+            const bool upleft = left && bb > 0 && ((a.q.e[1].w >> (bb - 1)) & 1u) && bas[rn[1] - 1] == b;
+            if (!upleft) s.uy = rn[1];
+        }
+        if (rn[0] >= 0 && bas[rn[0]] == b && 3u * (u32)uz + 2u <= kmax) {
+            const bool upleft = left && bb > 0 && ((a.q.e[0].w >> (bb - 1)) & 1u) && bas[rn[0] - 1] == b;
+            if (!upleft) s.uz = rn[0];
+        }
         return s;
     }
     ULK_D ULK_INLINE void run(const S2 &s, bool) const
     {
-        if (s.todo & 1u) ulk_vunion(P, s.v, s.v - 1);
-        if (s.todo & 2u) ulk_vunion(P, s.v, s.v - dm.W);
-        if (s.todo & 4u) ulk_vunion(P, s.v, s.v - dm.W * dm.H);
+        if (s.ul >= 0) ulk_vunion(P, s.r, s.ul);
+        if (s.uy >= 0) ulk_vunion(P, s.r, s.uy);
+        if (s.uz >= 0) ulk_vunion(P, s.r, s.uz);
     }
 };
 struct K_K3FlattenCount {
     const i32 *bas; i32 *P; i32 *nroot; i32 *nmulti;
-    ULK_D void operator()(i64 v, i32, i32, i32) const
+    ULK_D void operator()(i32 v) const
     {
         if (P[v] < 0) return;
-        i32 r = ulk_vfind(P, (i32)v);
+        i32 r = ulk_vfind(P, v);
         P[v] = r;
-        if (r != (i32)v) return;
+        if (r != v) return;
         i32 old = ulk_atomic_add(&nroot[bas[v]], 1);
         if (old == 1) ulk_atomic_add(nmulti, 1);
     }
@@ -1126,34 +1180,35 @@ struct K_K3FlattenCount {
 #endif
 };
 struct K_K3FindBest {     // Boruvka step on the basins that are still split
-    const i32 *bas; UlkDims dm; const i32 *nroot; const i32 *P; u32 *best;
-    ULK_D void operator()(i64 vv, i32 z, i32 y, i32 x) const
+    const i32 *bas; UlkFg fg; const i32 *nroot; const i32 *P; u32 *best;
+    ULK_D void operator()(i32 r, i32 v, i32 z, i32 y, i32 x) const
     {
-        i32 v = (i32)vv;
-        i32 b = bas[v];
+        const i32 b = bas[r];
         if (b < 0 || nroot[b] <= 1) return;
-        i32 r = ulk_vfind(P, v);
+        const i32 root = ulk_vfind(P, r);
+        i32 rn[6];
+        fg.nb_ranks(fg.nb_load(r, fg.seg(z, y, x), z, y, true, true), r, v, x, rn);
         u32 k = ULK_NONE32;
-        for (int d = 0; d < 3; ++d) {
-            i32 st = dm.stride(d);
-            if (dm.bwd(d, z, y, x)) { i32 u = v - st; if (bas[u] == b && ulk_vfind(P, u) != r) { u32 kk = 3u * (u32)u + d; if (kk < k) k = kk; } }
-            if (dm.fwd(d, z, y, x)) { i32 u = v + st; if (bas[u] == b && ulk_vfind(P, u) != r) { u32 kk = 3u * (u32)v + d; if (kk < k) k = kk; } }
+        for (int j = 0; j < 6; ++j) {
+            const i32 u = rn[j];
+            if (u < 0 || bas[u] != b || ulk_vfind(P, u) == root) continue;
+            const u32 kk = 3u * (u32)(j < 3 ? v + fg.nb_off(j) : v) + ulk_nb_dir(j);
+            if (kk < k) k = kk;
         }
-        if (k != ULK_NONE32) ulk_atomic_min(&best[r], k);
+        if (k != ULK_NONE32) ulk_atomic_min(&best[root], k);
     }
 };
 struct K_K3Hook {
-    const i32 *bas; UlkDims dm; i32 *P; u32 *best; u32 *K0;
-    ULK_D void operator()(i64 vv, i32, i32, i32) const
+    const i32 *bas; UlkFg fg; i32 *P; u32 *best; u32 *K0;
+    ULK_D void operator()(i32 r, i32, i32, i32, i32) const
     {
-        i32 v = (i32)vv;
-        if (bas[v] < 0) return;
-        u32 k = best[v];
+        if (bas[r] < 0) return;
+        u32 k = best[r];
         if (k == ULK_NONE32) return;
-        best[v] = ULK_NONE32;
-        i32 a = (i32)(k / 3u), c = a + dm.stride((int)(k % 3u));
-        ulk_vunion(P, a, c);
-        ulk_atomic_max(&K0[bas[v]], k);
+        best[r] = ULK_NONE32;
+        const i32 a = (i32)(k / 3u), c = a + fg.dm.stride((int)(k % 3u));
+        ulk_vunion(P, fg.rank_of(a), fg.rank_of(c));
+        ulk_atomic_max(&K0[bas[r]], k);
     }
 };
 
@@ -1188,19 +1243,19 @@ struct K_RankToLabel {
 struct K_WriteLabels {
     i32 ncc; const i32 *basA; const i32 *region_of; const i32 *label_of_rec;
     i32 *lab;
-    struct S1 { i32 v, l, ba; };
-    struct S2 { i32 v, rec; };       // rec: index into label_of_rec, -1: label 0, -2: nothing to write
-    ULK_D ULK_INLINE S1 load1(i32 v, i32, i32, i32, bool ok) const
+    struct S1 { i32 r, l, ba; };
+    struct S2 { i32 r, rec; };       // rec: index into label_of_rec, -1: label 0, -2: nothing to write
+    ULK_D ULK_INLINE S1 load1(i32 r, bool ok) const
     {
         S1 s;
-        s.v = v; s.l = 0; s.ba = 0;
-        if (ok) { s.l = lab[v]; if (s.l > 0) s.ba = basA[v]; }
+        s.r = r; s.l = 0; s.ba = 0;
+        if (ok) { s.l = lab[r]; if (s.l > 0) s.ba = basA[r]; }
         return s;
     }
     ULK_D ULK_INLINE S2 load2(const S1 &a, bool ok) const
     {
         S2 s;
-        s.v = a.v;
+        s.r = a.r;
         if (!ok) s.rec = -2;
         else if (a.l > 0) s.rec = ncc + region_of[a.ba];
         else if (a.l <= -2) s.rec = -a.l - 2;
@@ -1210,14 +1265,14 @@ struct K_WriteLabels {
     ULK_D ULK_INLINE void run(const S2 &s, bool) const
     {
         if (s.rec == -2) return;
-        lab[s.v] = s.rec >= 0 ? label_of_rec[s.rec] : 0;
+        lab[s.r] = s.rec >= 0 ? label_of_rec[s.rec] : 0;
     }
 };
-struct K_CopyLabels {       // region labels as the caller sees them: 0 on the background
-    const i32 *lab; i32 *out;
-    ULK_D void operator()(i64 v) const { i32 l = lab[v]; out[v] = l > 0 ? l : 0; }
+struct K_ScatterLabels {    // region labels as the caller sees them (dense volume, 0 on the background: cleared before)
+    const i32 *lab; const i32 *fgl; i32 *out;
+    ULK_D void operator()(i64 r) const { i32 l = lab[r]; out[fgl[r]] = l > 0 ? l : 0; }
 };
 template <class T> struct K_FillAt {
-    T *p; T val;
-    ULK_D void operator()(i64 v, i32, i32, i32) const { p[v] = val; }
+    const i32 *list; T *p; T val;
+    ULK_D void operator()(i64 i) const { p[list[i]] = val; }
 };
