@@ -45,7 +45,7 @@ typedef struct ulk_seg_params {
     double max_area;
     double min_area_factor;
     double min_frontier;
-    int32_t ws_hierarchy;      /* 0 = area, 1 = dynamics (hg.watershed_hierarchy_by_*) */
+    int32_t ws_hierarchy;      /* 0 = area, 1 = dynamics, 2 = volume (hg.watershed_hierarchy_by_*) */
     int32_t reserved;
 } ulk_seg_params;
 

@@ -36,7 +36,7 @@ def _seg_device(lib, fg, ct, **kw):
     return h, _lib.nodes_to_host(lib, h, with_labels=True)
 
 
-@pytest.mark.parametrize("hier", ["area", "dynamics"])
+@pytest.mark.parametrize("hier", ["area", "dynamics", "volume"])
 @pytest.mark.parametrize("kind", cases.KINDS)
 @pytest.mark.parametrize("shape", [(56, 56), (10, 24, 24), (160, 160), (24, 48, 48)])
 def test_segment_parity(cuda_lib, shape, kind, hier):

@@ -12,7 +12,7 @@ def _seg(lib, fg, ct, **kw):
     return segment_frame(lib, fg, ct, keep_labels=True, **kw)
 
 
-@pytest.mark.parametrize("hier", ["area", "dynamics"])
+@pytest.mark.parametrize("hier", ["area", "dynamics", "volume"])
 @pytest.mark.parametrize("kind", cases.KINDS)
 @pytest.mark.parametrize("shape", [(56, 56), (10, 24, 24)])
 def test_segment_parity(shape, kind, hier):
@@ -26,14 +26,15 @@ def test_segment_parity(shape, kind, hier):
     assert total > 0
 
 
+@pytest.mark.parametrize("hier", ["area", "volume"])
 @pytest.mark.parametrize("min_frontier", [0.0, 0.3])
-def test_segment_parity_mock_like(min_frontier):
+def test_segment_parity_mock_like(min_frontier, hier):
     """Variant "T": bool foreground + bool contours, the tie-heavy regime of the reference's
     mock data (utils/data.py:15-32), with the reference's test config ratios."""
     from ultrack_b200 import synth
     lib = emu_lib()
     fg, ct, _ = synth.make_frame((20, 40, 40), seed=2, variant="T", radius=6.0, fill=0.45)
-    n = cases.run_and_compare(lib, _seg, fg, ct, 3, min_area=50, max_area=800, min_frontier=min_frontier)
+    n = cases.run_and_compare(lib, _seg, fg, ct, 3, min_area=50, max_area=800, min_frontier=min_frontier, ws_hierarchy=hier)
     assert n > 0
 
 

@@ -20,7 +20,7 @@ DTYPE_CODES = {
     np.dtype(np.int16): 3, np.dtype(np.float16): 4, np.dtype(np.float32): 5, np.dtype(np.float64): 6,
     np.dtype(np.int32): 7, np.dtype(np.uint32): 8, np.dtype(np.int64): 9, np.dtype(np.uint64): 10,
 }
-WS_HIERARCHY_CODES = {"area": 0, "dynamics": 1}
+WS_HIERARCHY_CODES = {"area": 0, "dynamics": 1, "volume": 2}
 
 
 class SegParams(C.Structure):

@@ -98,6 +98,7 @@ struct UlkHierScratch {     // node space [2B] unless noted
     u64 *Iwk;               // key of the merge
     u32 *IminL;             // lowest basin level below the node
     i32 *attach;            // voxels that join the node before its parent forms (area)
+    u64 *awhi, *awlo;       // fixed-point sum of those voxels' steepest-edge weights (volume; hi/lo 32-bit lanes)
     i32 *acc1;              // [B] RAG edge accepted as k-th merge (edge space offset)
     double *wprime;         // new MST weight per inner node of I
     i32 *par, *c0, *c1;     // working binary tree (T1, Tb, T2 in turn)
@@ -120,7 +121,7 @@ struct UlkHierScratch {     // node space [2B] unless noted
     i64 *ncsum;             // [3*2B]
 };
 struct UlkHierParams {
-    int kind;               // 0 area, 1 dynamics
+    int kind;               // 0 area, 1 dynamics, 2 volume
     double min_area, max_area, min_frontier;
     int fix_shift;
 };
@@ -185,6 +186,7 @@ ULK_HD inline void ulk_hier_stage1(i32 h, const i32 *bs_, const i32 *es_, const 
     auto ep = [&](i32 e, i32 &x, i32 &y) { x = ea[e] - bs; y = eb[e] - bs; };
     ulk_kruskal(b, r, ord, ep, S.uf + bs, S.rootnode + bs, S.Ipar + o, S.Ic0 + o, S.Ic1 + o, S.acc1 + bs);
     for (i32 i = 0; i < b; ++i) { S.IminL[o + i] = B.L[bs + i]; S.Iwk[o + i] = 0; S.attach[o + i] = B.size[bs + i]; }
+    for (i32 i = 0; i < 2 * b - 1; ++i) { S.awhi[o + i] = 0; S.awlo[o + i] = 0; }
     for (i32 k = 0; k < b - 1; ++k) {
         i32 x = o + b + k;
         S.Iwk[x] = E.wk[es + S.acc1[bs + k]];
@@ -195,10 +197,46 @@ ULK_HD inline void ulk_hier_stage1(i32 h, const i32 *bs_, const i32 *es_, const 
 }
 
 // new MST weights w'(x) = min over the two children of the attribute
-ULK_HD inline void ulk_hier_wprime(i32 bs, i32 b, const UlkHierScratch &S, int kind)
+// fixed-point image of a float32 edge weight (the same map for voxel sums and altitudes)
+ULK_HD ULK_INLINE i64 ulk_w_fixed(float w, double fixscale) { return (i64)((double)w * fixscale); }
+
+ULK_HD inline void ulk_hier_wprime(i32 bs, i32 b, const UlkHierScratch &S, int kind, int fix_shift = 0)
 {
     i32 o = 2 * bs;
-    if (kind == 0) {
+    if (kind == 2) {
+        // hg.attribute_volume on the voxel-level BPT: V(c) = sum over the inner nodes d below (and
+        // at) c of area(d) * (alt(parent d) - alt(d)).  For one voxel v the terms of its ancestors
+        // telescope to alt(parent c) - alt(first inner ancestor of v), and that first ancestor is
+        // created by v's steepest edge, so V(c) = area(c) * alt(x) - sum_{v in c} mw(v) with x the
+        // merge above c.  Exact in 2^-fix_shift fixed point, rounded to double once.
+        double fixscale = 1.0;
+        for (int k = 0; k < fix_shift; ++k) fixscale *= 2.0;
+        for (i32 i = 0; i < 2 * b - 1; ++i) {
+            S.area[o + i] = S.attach[o + i];
+            u128 x = ((u128)S.awhi[o + i] << 32) + (u128)S.awlo[o + i];
+            S.Xhi[o + i] = (u64)(x >> 64); S.Xlo[o + i] = (u64)x;
+        }
+        for (i32 i = 0; i < 2 * b - 2; ++i) {
+            i32 p = o + S.Ipar[o + i];
+            S.area[p] += S.area[o + i];
+            u128 x = (((u128)S.Xhi[p] << 64) | S.Xlo[p]) + (((u128)S.Xhi[o + i] << 64) | S.Xlo[o + i]);
+            S.Xhi[p] = (u64)(x >> 64); S.Xlo[p] = (u64)x;
+        }
+        double inv = 1.0;
+        for (int k = 0; k < fix_shift; ++k) inv *= 0.5;
+        for (i32 x = b; x < 2 * b - 1; ++x) {
+            const i64 ax = ulk_w_fixed(ulk_ord2f((u32)(S.Iwk[o + x] >> 32)), fixscale);
+            u128 vmin = 0;
+            for (int c = 0; c < 2; ++c) {
+                const i32 ch = o + (c ? S.Ic1[o + x] : S.Ic0[o + x]);
+                const u128 full = (u128)(u64)S.area[ch] * (u128)(u64)ax;
+                const u128 sub = ((u128)S.Xhi[ch] << 64) | S.Xlo[ch];
+                const u128 v = full > sub ? full - sub : 0;
+                if (c == 0 || v < vmin) vmin = v;
+            }
+            S.wprime[o + x] = ulk_u128_to_double(vmin) * inv;
+        }
+    } else if (kind == 0) {
         // area of each I node = voxels attached below it
         for (i32 i = 0; i < 2 * b - 1; ++i) S.area[o + i] = S.attach[o + i];
         for (i32 i = 0; i < 2 * b - 2; ++i) S.area[o + S.Ipar[o + i]] += S.area[o + i];
@@ -271,7 +309,7 @@ ULK_HD inline void ulk_hier_full(i32 h, const i32 *bs_, const i32 *es_, const Ul
 
     if (b > 1) {
         // ---- Kruskal #2: I's merges re-weighted, ties by rank1
-        ulk_hier_wprime(bs, b, S, P.kind);
+        ulk_hier_wprime(bs, b, S, P.kind, P.fix_shift);
         const double *wp = S.wprime + o;
         for (i32 k = 0; k < b - 1; ++k) ord[k] = k;
         ulk_heapsort(ord, b - 1, [&](i32 x, i32 y) {

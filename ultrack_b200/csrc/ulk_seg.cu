@@ -618,6 +618,7 @@ static int alloc_scratch(UlkArena &A, i32 B, i32 Eg, UlkHierScratch &S)
     i64 M = (Eg > B ? Eg : B) + 2;
     S.Ipar = A.get<i32>(N2); S.Ic0 = A.get<i32>(N2); S.Ic1 = A.get<i32>(N2);
     S.Iwk = A.get<u64>(N2); S.IminL = A.get<u32>(N2); S.attach = A.get<i32>(N2);
+    S.awhi = A.get<u64>(N2); S.awlo = A.get<u64>(N2);
     S.acc1 = A.get<i32>(B + 2); S.wprime = A.get<double>(N2);
     S.par = A.get<i32>(N2); S.c0 = A.get<i32>(N2); S.c1 = A.get<i32>(N2);
     S.alt = A.get<double>(N2); S.alt1 = A.get<double>(N2); S.par1 = A.get<i32>(N2);
@@ -781,7 +782,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
         UlkBasins Bv{va.b_size, va.g_L, va.b_top, nullptr, nullptr, nullptr, nullptr};
         UlkEdges Ev{va.ea, va.eb, va.wk, va.k3, va.cnt, va.shi, va.slo};
         ulk_launch(n_big, st, K_HierStage1{va.bs, va.es, Bv, Ev, S});
-        ulk_launch_rkn<4>(rlA, nA, st, K_Attach{va.bas, va.mw, va.jk, va.g_lab, va.bs, S.Ipar, S.Iwk, S.attach});
+        ulk_launch_rkn<4>(rlA, nA, st, K_Attach{va.bas, va.mw, va.jk, va.g_lab, va.bs, S.Ipar, S.Iwk, S.attach, nullptr, nullptr, 0.0});
         i32 *region_of = AA.get<i32>(va.B);
         u64 *rkey_w = AA.get<u64>(va.B), *rkey_k = AA.get<u64>(va.B);
         CHKA(AA);
@@ -821,7 +822,8 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
     F->n_hier = R;
 
     // ---- pass B: the configured hierarchy on every region
-    const bool area_mode = prm->ws_hierarchy == 0;
+    const bool area_mode = prm->ws_hierarchy == 0 || prm->ws_hierarchy == 2;    // join keys: area and volume attributes
+    const bool vol_mode = prm->ws_hierarchy == 2;
     VoxelStage vb;
     CHK(voxel_stage(st, A, fg, nullptr, nfg, ct, lab2, R, area_mode, true, true, fix_shift, vb, &stats_local));
     UlkHierScratch S;
@@ -830,7 +832,8 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
     UlkEdges Ev{vb.ea, vb.eb, vb.wk, vb.k3, vb.cnt, vb.shi, vb.slo};
     ulk_launch(R, st, K_HierStage1{vb.bs, vb.es, Bv, Ev, S});
     if (area_mode)
-        ulk_launch_rkn<4>(nullptr, nfg, st, K_Attach{vb.bas, vb.mw, vb.jk, vb.g_lab, vb.bs, S.Ipar, S.Iwk, S.attach});
+        ulk_launch_rkn<4>(nullptr, nfg, st, K_Attach{vb.bas, vb.mw, vb.jk, vb.g_lab, vb.bs, S.Ipar, S.Iwk, S.attach,
+                                                     vol_mode ? S.awhi : nullptr, vol_mode ? S.awlo : nullptr, ldexp(1.0, fix_shift)});
     i64 N2 = 2 * (i64)vb.B + 2;
     UlkNodeOut O;
     O.count = A.get<i32>(R + 1); O.nsurv = A.get<i32>(R + 1); O.rsize = A.get<i32>(R + 1);

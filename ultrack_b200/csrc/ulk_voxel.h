@@ -926,8 +926,9 @@ struct K_PlateauRelax {
 struct K_Attach {
     const i32 *bas; const u32 *mw, *jk; const i32 *b_lab; const i32 *bs;
     const i32 *Ipar; const u64 *Iwk; i32 *attach;
+    u64 *awhi, *awlo; double fixscale;      // volume attribute only (else nullptr): weight sums per attach node
     struct S1 { i32 b; u32 j, m; };
-    struct S2 { i32 o, node, p; u64 J; };
+    struct S2 { i32 o, node, p; u64 J; u32 m; bool climb; };
     ULK_D ULK_INLINE S1 load1(i32 r, bool ok) const
     {
         S1 s;
@@ -938,33 +939,64 @@ struct K_Attach {
     ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const
     {
         S2 s;
-        s.o = 0; s.node = -1; s.p = -1; s.J = 0;
-        if (a.b < 0 || a.j == ULK_JK_CORE) return s;
-        s.J = ((u64)a.m << 32) | a.j;
+        s.o = 0; s.node = -1; s.p = -1; s.J = 0; s.m = a.m; s.climb = false;
+        if (a.b < 0) return s;
+        const bool late = a.j != ULK_JK_CORE;
+        if (!late && !awhi) return s;
         const i32 st = bs[b_lab[a.b] - 1];
         s.o = 2 * st;
         s.node = a.b - st;
-        s.p = Ipar[s.o + s.node];
+        if (late) {
+            s.climb = true;
+            s.J = ((u64)a.m << 32) | a.j;
+            s.p = Ipar[s.o + s.node];
+        }
         return s;
     }
     ULK_D ULK_INLINE void run(const S2 &s, bool) const
     {
-        if (s.node < 0) return;
         const i32 o = s.o, start = s.node;
-        i32 node = start, p = s.p;
-        // the parent's merge key and the grandparent index are loaded together: one memory
-        // round trip per level of the climb
-        while (p != node) {
-            u64 w = Iwk[o + p];
-            i32 pp = Ipar[o + p];
-            if (!(w < s.J)) break;
-            node = p;
-            p = pp;
+        i32 node = start;
+        if (s.climb) {
+            i32 p = s.p;
+            // the parent's merge key and the grandparent index are loaded together: one memory
+            // round trip per level of the climb
+            while (p != node) {
+                u64 w = Iwk[o + p];
+                i32 pp = Ipar[o + p];
+                if (!(w < s.J)) break;
+                node = p;
+                p = pp;
+            }
+            if (node != start) {
+                ulk_atomic_add(&attach[o + start], -1);
+                ulk_atomic_add(&attach[o + node], 1);
+            }
         }
-        if (node != start) {
-            ulk_atomic_add(&attach[o + start], -1);
-            ulk_atomic_add(&attach[o + node], 1);
+        if (!awhi) return;          // uniform over the grid
+        // volume: the voxel's steepest-edge weight goes to the node it is attached to
+        const bool has = node >= 0 && s.m != ULK_NONE32;
+        const i64 fx = has ? (i64)((double)ulk_ord2f(s.m) * fixscale) : 0;
+        u64 hi = (u64)(fx >> 32), lo = (u64)(fx & 0xffffffffll);
+#ifdef ULK_EMU
+        if (has) { awhi[o + node] += hi; awlo[o + node] += lo; }
+#else
+        // lanes of one basin's core share the node: segmented shuffle sum towards the run's first lane
+        const int lane = threadIdx.x & 31;
+        const i32 key = has ? o + node : -1 - lane;
+        const i32 kprev = __shfl_up_sync(0xffffffffu, key, 1);
+        const u32 run = ulk_run_mask(__ballot_sync(0xffffffffu, lane == 0 || kprev != key), lane);
+        const int first = __ffs(run) - 1, last = 31 - __clz(run);
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const u64 h2 = __shfl_down_sync(0xffffffffu, hi, off), l2 = __shfl_down_sync(0xffffffffu, lo, off);
+            if (lane + off <= last) { hi += h2; lo += l2; }
         }
+        if (has && lane == first) {
+            atomicAdd((unsigned long long *)&awhi[key], (unsigned long long)hi);
+            atomicAdd((unsigned long long *)&awlo[key], (unsigned long long)lo);
+        }
+#endif
     }
 };
 
