@@ -86,13 +86,26 @@ typedef struct ulk_link_params {
     int32_t max_neighbors;
     int32_t has_scale;
     double scale[3];          /* z,y,x, applied to both centroids when has_scale != 0            */
+    /* secondary callers of compute_spatial_neighbors (processing.py:183-184,261-264):            */
+    int32_t weight_kind;      /* 0 = Node.IoU, 1 = Node.intersection (GT matching, match_gt.py:148-168) */
+    int32_t edge_must_be_positive; /* drop candidates whose weight is <= 0                        */
+    /* colour z-score gate (color_filtering_mask, processing.py:52-104); n_channels = 0: off.
+     * Device arrays of per-node statistics from ulk_node_stats, row-major [n, n_channels]:
+     * a candidate survives iff max_c |dst_mean - src_mean| / dst_std' <= z_score_threshold,
+     * dst_std' = 1 where dst_std <= 1e-6.                                                        */
+    int32_t n_channels;
+    int32_t pad0;
+    double z_score_threshold;
+    const double *src_mean;
+    const double *dst_mean;
+    const double *dst_std;
 } ulk_link_params;
 
 typedef struct ulk_links {
     int64_t n_links;
     int32_t *source;          /* [n] node index in the source frame                             */
     int32_t *target;          /* [n] node index in the target frame                             */
-    double *weight;           /* [n] IoU - distance_weight * distance                           */
+    double *weight;           /* [n] IoU (or intersection) - distance_weight * distance         */
     int64_t n_pairs;          /* candidate pairs evaluated (for the byte model)                 */
 } ulk_links;
 
@@ -157,6 +170,15 @@ ULK_API int ulk_frame_nodes_from_device(int32_t n_nodes, const int32_t shape[3],
  * frames the z column must be 0 (the reference slices `shift[:, -ndim:]`) */
 ULK_API int ulk_link_frames(const ulk_frame_nodes *src, const ulk_frame_nodes *dst, const double *dst_shift_host,
                     const ulk_link_params *params, void *stream, ulk_links **out);
+/* Per-node reductions over the node masks.  With `image` (a device [D,H,W] volume of
+ * `image_dtype`): Node.intensity_mean / Node.intensity_std (core/segmentation/node.py:280-296)
+ * and the intensity min / max of the regionprops features (processing.py:107-157) into column
+ * `channel` of the device double arrays mean / std / vmin / vmax [n_nodes, n_channels];
+ * `centroid` [n_nodes, 3] receives the float64 mean (z, y, x) of the mask coordinates.  Any
+ * output may be NULL; `image` may be NULL when only the centroid is wanted. */
+ULK_API int ulk_node_stats(const ulk_frame_nodes *nodes, const void *image, int image_dtype,
+                   int32_t channel, int32_t n_channels, double *mean, double *std, double *vmin, double *vmax,
+                   double *centroid, void *stream);
 ULK_API int ulk_links_to_host(const ulk_links *links, int32_t *source, int32_t *target, double *weight, void *stream);
 ULK_API void ulk_links_free(ulk_links *links);
 

@@ -57,3 +57,74 @@ def run_and_compare(lib, segment_fn, fg, ct, ndim: int, **kw):
     finally:
         lib.ulk_frame_nodes_free(handle)
     return len(ref["nodes"])
+
+
+def nodes_for_link(nodes, ndim, t):
+    """Device node table (numpy copy) -> the dict nodes oracle.link_oracle takes."""
+    from ultrack_b200 import _lib
+    out = []
+    lo = 3 - ndim
+    for i in range(len(nodes["area"])):
+        bb = nodes["bbox"][i].astype(np.int64)
+        out.append(dict(id=(i + 1) + (t + 1) * 1_000_000, centroid=nodes["centroid"][i][lo:].astype(np.int64),
+                        bbox=np.concatenate([bb[lo:3], bb[3 + lo:]]), mask=_lib.unpack_mask(nodes, i, ndim)))
+    return out
+
+
+def link_and_compare(lib, tabs, ndim, max_distance, max_neighbors, dw=0.0, shift=None, scale=None,
+                     weight_func="iou", positive=False, images=None, z_score_threshold=5.0,
+                     rtol=1e-5, min_links=10, max_tie_fraction=0.05):
+    """`ulk_link_frames` on two segmented frames `tabs = [(handle, nodes), (handle, nodes)]` against
+    oracle.link_oracle.link_pair, as keyed (source_id, target_id) sets; weights within `rtol`.
+    Targets with a KD-tree k-boundary distance tie are left out (their share is asserted small).
+    `images` = (channels of frame t, channels of frame t + 1) turns the colour gate on."""
+    from oracle.link_oracle import link_pair
+    from ultrack_b200.capi import link_frames, node_intensity
+    (h0, n0), (h1, n1) = tabs
+    color = frames = None
+    if images is not None:
+        m0, _ = node_intensity(lib, h0, images[0])
+        m1, s1 = node_intensity(lib, h1, images[1])
+        color = (m0, m1, s1)
+        frames = (np.stack(images[0], axis=-1), np.stack(images[1], axis=-1))
+    s, t, w, _ = link_frames(lib, h0, h1, max_distance=max_distance, max_neighbors=max_neighbors,
+                             distance_weight=dw, shift=shift, scale=scale, weight_func=weight_func,
+                             edge_must_be_positive=positive, color=color, z_score_threshold=z_score_threshold)
+    src, dst = nodes_for_link(n0, ndim, 0), nodes_for_link(n1, ndim, 1)
+    ref, _, _, _, tie = link_pair(src, dst, max_distance, max_neighbors, dw, target_shift=shift, scale=scale,
+                                  return_candidates=True, weight_func=weight_func, edge_must_be_positive=positive,
+                                  frames=frames, z_score_threshold=z_score_threshold)
+    assert tie.mean() <= max_tie_fraction, f"{tie.sum()} of {len(tie)} targets have a k-boundary tie"
+    skip = {dst[i]["id"] for i in np.nonzero(tie)[0]}
+    got = {(int(a) + 1 + 1_000_000, int(b) + 1 + 2_000_000): float(x) for a, b, x in zip(s, t, w)}
+    exp = {(int(r[1]), int(r[2])): float(r[0]) for r in ref}
+    got = {k: v for k, v in got.items() if k[1] not in skip}
+    exp = {k: v for k, v in exp.items() if k[1] not in skip}
+    assert len(exp) >= min_links, len(exp)
+    assert set(got) == set(exp), (len(got), len(exp), sorted(set(got) ^ set(exp))[:5])
+    for k in exp:
+        assert abs(got[k] - exp[k]) <= rtol * max(abs(exp[k]), 1e-300), (k, got[k], exp[k])
+    return len(exp), int(tie.sum())
+
+
+def color_images(shape, dtype, seed=5):
+    """Two image channels for frames t and t + 1: one smooth field per channel plus a small
+    frame-to-frame drift and pixel noise, so that a z-score gate of a few sigma removes some
+    candidate links and keeps others."""
+    rng = np.random.default_rng(seed)
+    base = []
+    for c in range(2):
+        f = ndi.gaussian_filter(rng.random(shape), 3.0)
+        base.append((f - f.min()) / (f.max() - f.min()))
+    out = []
+    for t in range(2):
+        chans = []
+        for c in range(2):
+            d = ndi.gaussian_filter(rng.random(shape), 4.0)
+            f = base[c] + 0.3 * t * (d - d.mean()) / d.std() * 0.05 + 0.08 * rng.random(shape)
+            if np.issubdtype(np.dtype(dtype), np.integer):
+                chans.append(np.round(np.clip(f, 0, None) * 4000).astype(dtype))
+            else:
+                chans.append(f.astype(dtype))
+        out.append(chans)
+    return out

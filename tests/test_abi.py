@@ -33,13 +33,28 @@ def test_python_binding_lists_every_declared_symbol():
     assert sorted(_lib.EXPORTS) == _declared()
 
 
-def test_struct_layouts_match_header():
+def test_struct_layouts_match_header(tmp_path):
+    """sizeof / offsetof of every ctypes mirror against the header itself, compiled by gcc."""
+    import subprocess
     from ultrack_b200 import _lib
-    assert C.sizeof(_lib.SegParams) == 48
-    assert C.sizeof(_lib.LinkParams) == 48
-    assert C.sizeof(_lib.Links) == 40
-    assert C.sizeof(_lib.SegStats) == 56
-    assert C.sizeof(_lib.FrameNodes) == 40 + 12 * 8 + 56
+    structs = {"ulk_seg_params": _lib.SegParams, "ulk_link_params": _lib.LinkParams, "ulk_links": _lib.Links,
+               "ulk_seg_stats": _lib.SegStats, "ulk_frame_nodes": _lib.FrameNodes}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', f'#include "{ROOT / "include" / "ultrack_b200.h"}"', "int main(void){"]
+    for cname, cls in structs.items():
+        lines.append(f'printf("{cname} %zu\\n", sizeof({cname}));')
+        for fname, _ in cls._fields_:
+            lines.append(f'printf("{cname}.{fname} %zu\\n", offsetof({cname}, {fname}));')
+    lines.append("return 0;}")
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-o", str(exe), str(src)], check=True)
+    out = dict(l.split() for l in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines())
+    for cname, cls in structs.items():
+        assert int(out[cname]) == C.sizeof(cls), cname
+        for fname, _ in cls._fields_:
+            assert int(out[f"{cname}.{fname}"]) == getattr(cls, fname).offset, (cname, fname)
+    assert C.sizeof(_lib.LinkParams) == 96
 
 
 def test_product_path_fails_loudly_without_gpu(monkeypatch):

@@ -230,14 +230,52 @@ def test_batch_index_windows(tmp_path, emu):
     assert _rows(cfg, q) == _rows(cfg2, q)
 
 
-def test_unsupported_options_raise(tmp_path, emu):
-    cfg = _config(tmp_path)
-    fg, ct = synth.make_timelapse((64, 64), 2, seed=1, variant="S", radius=7.0)
-    with pytest.raises(NotImplementedError):
-        segment(fg, ct, cfg, properties=["centroid"])
+def test_link_color_filter_matches_oracle(tmp_path, emu):
+    """link(config, images=...) -- color_filtering_mask, core/linking/processing.py:52-104."""
+    from tests import cases
+    cfg = _config(tmp_path, linking__z_score_threshold=0.8)
+    shape, T = (12, 40, 40), 3
+    fg, ct = synth.make_timelapse(shape, T, seed=3, variant="S", radius=5.0, motion=2.0)
     segment(fg, ct, cfg)
-    with pytest.raises(NotImplementedError):
-        link(cfg, images=[fg])
+    per_t = [cases.color_images(shape, np.float32, seed=20 + t) for t in range(T)]
+    images = [np.stack([per_t[t][t % 2][c] for t in range(T)]) for c in range(2)]     # one (T,Z,Y,X) array per channel
+    link(cfg, images=images)
+    gated = {(s, t): w for s, t, w in _rows(cfg, "select source_id,target_id,weight from links")}
+    prm = SegParams(threshold=0.5, min_area=60, max_area=2000)
+    ref = [o_seg(fg[t], ct[t], prm, time=t) for t in range(T)]
+    exp, plain = {}, 0
+    for t in range(T - 1):
+        fr = (np.stack([im[t] for im in images], axis=-1), np.stack([im[t + 1] for im in images], axis=-1))
+        for w, s, d in link_pair(ref[t]["nodes"], ref[t + 1]["nodes"], 10, 3, time=t, frames=fr, z_score_threshold=0.8):
+            exp[(int(s), int(d))] = w
+        plain += len(link_pair(ref[t]["nodes"], ref[t + 1]["nodes"], 10, 3, time=t))
+    assert set(gated) == set(exp) and 5 < len(exp) < plain
+    for k in exp:
+        assert gated[k] == pytest.approx(exp[k], rel=1e-5)
+
+
+def test_match_gt_candidate_links(tmp_path, emu):
+    """The GT matcher's compute_spatial_neighbors call (core/match_gt.py:148-168): weight =
+    intersection, positive only, rows in gt_nodes / gt_links."""
+    import scipy.ndimage as ndi
+    from ultrack_b200.match_gt import gt_frame_nodes, match_ground_truth_links
+    cfg = _config(tmp_path)
+    shape, T = (80, 80), 2
+    fg, ct = synth.make_timelapse(shape, T, seed=5, variant="S", radius=7.0, motion=2.0)
+    segment(fg, ct, cfg)
+    gt = np.stack([ndi.label(np.roll(fg[t] > 0.5, 2, axis=1))[0] for t in range(T)])
+    w, s, d = match_ground_truth_links(1, gt, cfg)
+    prm = SegParams(threshold=0.5, min_area=60, max_area=2000)
+    ref = o_seg(fg[1], ct[1], prm, time=1)
+    ndim, labels, bboxes, cens, masks, areas = gt_frame_nodes(gt[1])
+    gt_nodes = [dict(id=int(l), centroid=c, bbox=b, mask=m) for l, b, c, m in zip(labels, bboxes, cens, masks)]
+    exp = {(int(r[1]), int(r[2])): r[0] for r in link_pair(ref["nodes"], gt_nodes, 10, 3, time=1,
+                                                           weight_func="intersection", edge_must_be_positive=True)}
+    got = {(int(a), int(b)): float(x) for a, b, x in zip(s, d, w)}
+    assert got == exp and len(exp) > 5 and all(v > 0 and v == int(v) for v in exp.values())
+    rows = _rows(cfg, "select source_id,target_id,weight,selected from gt_links")
+    assert {(a, b): c for a, b, c, _ in rows} == exp
+    assert len(_rows(cfg, "select label from gt_nodes where t = 1")) == len(labels)
 
 
 def test_config_mirror_round_trip(tmp_path):

@@ -85,53 +85,56 @@ def test_golden_edge_inputs_segment_like_the_oracle():
         cases.run_and_compare(lib, _seg, mask, img, mask.ndim, min_area=4, max_area=60)
 
 
-def _nodes_for_link(nodes, ndim, t):
-    from ultrack_b200 import _lib
-    out = []
-    lo = 3 - ndim
-    for i in range(len(nodes["area"])):
-        bb = nodes["bbox"][i].astype(np.int64)
-        out.append(dict(id=(i + 1) + (t + 1) * 1_000_000, centroid=nodes["centroid"][i][lo:].astype(np.int64),
-                        bbox=np.concatenate([bb[lo:3], bb[3 + lo:]]), mask=_lib.unpack_mask(nodes, i, ndim)))
-    return out
+from tests.cases import nodes_for_link as _nodes_for_link  # noqa: E402
+
+
+def _link_tabs(lib, ndim, shape=None):
+    from ultrack_b200 import synth
+    shape = shape or ((72, 72) if ndim == 2 else (16, 40, 40))
+    tabs = []
+    for t in range(2):
+        fg, ct, _ = synth.make_frame(shape, t=t, seed=11, variant="S", radius=5.0, fill=0.35, motion=2.0)
+        tabs.append(_seg(lib, fg, ct, min_area=30, max_area=4000))
+    return tabs, shape
 
 
 @pytest.mark.parametrize("ndim,scale,dw,with_shift", [(2, None, 0.0, False), (3, None, 0.05, False),
                                                       (3, (2.0, 1.0, 1.0), 0.0, True), (2, None, 0.01, True)])
 def test_link_parity(ndim, scale, dw, with_shift):
-    from oracle.link_oracle import link_pair
-    from ultrack_b200 import synth
     lib = emu_lib()
-    shape = (72, 72) if ndim == 2 else (16, 40, 40)
-    frames_ = []
-    for t in range(2):
-        fg, ct, _ = synth.make_frame(shape, t=t, seed=11, variant="S", radius=5.0, fill=0.35, motion=2.0)
-        frames_.append(_seg(lib, fg, ct, min_area=30, max_area=4000))
-    (h0, n0), (h1, n1) = frames_
+    tabs, _ = _link_tabs(lib, ndim)
     rng = np.random.default_rng(3)
-    shift = rng.normal(0, 1.5, size=(len(n1["area"]), 3)) if with_shift else None
+    shift = rng.normal(0, 1.5, size=(len(tabs[1][1]["area"]), 3)) if with_shift else None
     if shift is not None and ndim == 2:
         shift[:, 0] = 0.0   # the host layer drops the z shift of 2-D frames (link.py)
-    max_neighbors, max_distance = 2, 9.0
-    s, t, w, npairs = link_frames(lib, h0, h1, max_distance=max_distance, max_neighbors=max_neighbors,
-                                  distance_weight=dw, shift=shift, scale=scale)
-    src, dst = _nodes_for_link(n0, ndim, 0), _nodes_for_link(n1, ndim, 1)
-    ref, cands, dist, _ = link_pair(src, dst, max_distance, max_neighbors, dw, target_shift=shift,
-                                    scale=scale, return_candidates=True)
-    # k-boundary ties of the KD-tree are heap-order dependent (hard part 5):
-    # targets whose candidate list is full are compared only when no tie sits on the boundary
-    got = {(int(a) + 1 + 1_000_000, int(b) + 1 + 2_000_000): float(x) for a, b, x in zip(s, t, w)}
-    exp = {(int(r[1]), int(r[2])): float(r[0]) for r in ref}
-    full = np.isfinite(dist).sum(axis=1) == 2 * max_neighbors
-    skip = {dst[i]["id"] for i in np.nonzero(full)[0]}
-    got = {k: v for k, v in got.items() if k[1] not in skip}
-    exp = {k: v for k, v in exp.items() if k[1] not in skip}
-    assert len(exp) > 10
-    assert set(got) == set(exp)
-    for k in exp:
-        assert abs(got[k] - exp[k]) <= 1e-5 * max(abs(exp[k]), 1e-300), (k, got[k], exp[k])
-    lib.ulk_frame_nodes_free(h0)
-    lib.ulk_frame_nodes_free(h1)
+    cases.link_and_compare(lib, tabs, ndim, 9.0, 2, dw=dw, shift=shift, scale=scale)
+    for h, _ in tabs:
+        lib.ulk_frame_nodes_free(h)
+
+
+@pytest.mark.parametrize("ndim", [2, 3])
+@pytest.mark.parametrize("positive", [False, True])
+def test_link_intersection_weight(ndim, positive):
+    """The GT matcher's call of compute_spatial_neighbors (core/match_gt.py:155-168):
+    weight = Node.intersection, edge_must_be_positive."""
+    lib = emu_lib()
+    tabs, _ = _link_tabs(lib, ndim)
+    cases.link_and_compare(lib, tabs, ndim, 9.0, 2, dw=0.5, weight_func="intersection", positive=positive)
+    for h, _ in tabs:
+        lib.ulk_frame_nodes_free(h)
+
+
+@pytest.mark.parametrize("ndim,dtype", [(2, np.float32), (3, np.uint16), (3, np.float64)])
+def test_link_color_gate(ndim, dtype):
+    """color_filtering_mask (core/linking/processing.py:52-104) with two image channels."""
+    lib = emu_lib()
+    tabs, shape = _link_tabs(lib, ndim)
+    images = cases.color_images(shape, dtype)
+    n, _ = cases.link_and_compare(lib, tabs, ndim, 9.0, 2, images=images, z_score_threshold=0.8)
+    m, _ = cases.link_and_compare(lib, tabs, ndim, 9.0, 2)
+    assert n < m            # the gate removed links
+    for h, _ in tabs:
+        lib.ulk_frame_nodes_free(h)
 
 
 def test_link_identical_frames_have_unit_weight():

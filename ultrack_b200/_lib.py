@@ -21,6 +21,7 @@ DTYPE_CODES = {
     np.dtype(np.int32): 7, np.dtype(np.uint32): 8, np.dtype(np.int64): 9, np.dtype(np.uint64): 10,
 }
 WS_HIERARCHY_CODES = {"area": 0, "dynamics": 1, "volume": 2}
+WEIGHT_KIND_CODES = {"iou": 0, "intersection": 1}
 
 
 class SegParams(C.Structure):
@@ -49,7 +50,10 @@ class FrameNodes(C.Structure):
 
 class LinkParams(C.Structure):
     _fields_ = [("max_distance", C.c_double), ("distance_weight", C.c_double),
-                ("max_neighbors", C.c_int32), ("has_scale", C.c_int32), ("scale", C.c_double * 3)]
+                ("max_neighbors", C.c_int32), ("has_scale", C.c_int32), ("scale", C.c_double * 3),
+                ("weight_kind", C.c_int32), ("edge_must_be_positive", C.c_int32),
+                ("n_channels", C.c_int32), ("pad0", C.c_int32), ("z_score_threshold", C.c_double),
+                ("src_mean", C.c_void_p), ("dst_mean", C.c_void_p), ("dst_std", C.c_void_p)]
 
 
 class Links(C.Structure):
@@ -62,7 +66,7 @@ EXPORTS = [
     "ulk_profile_enable", "ulk_profile_reset", "ulk_profile_report", "ulk_segment_frame",
     "ulk_segment_frame_host", "ulk_frame_nodes_free", "ulk_frame_nodes_to_host",
     "ulk_frame_nodes_from_host", "ulk_frame_nodes_to_device", "ulk_frame_nodes_from_device", "ulk_link_frames", "ulk_links_to_host", "ulk_links_free",
-    "ulk_labels_to_contours", "ulk_node_shifts", "ulk_synth_frame",
+    "ulk_labels_to_contours", "ulk_node_shifts", "ulk_synth_frame", "ulk_node_stats",
     "ulk_upload_begin", "ulk_segment_frame_uploaded", "ulk_upload_free",
 ]
 
@@ -96,6 +100,7 @@ def bind(lib: C.CDLL) -> C.CDLL:
     lib.ulk_frame_nodes_from_device.argtypes = [i32, C.POINTER(i32), vp, vp, vp, vp, i64, vp, vp, C.POINTER(PF)]
     lib.ulk_link_frames.argtypes = [PF, PF, vp, C.POINTER(LinkParams), vp, C.POINTER(PL)]
     lib.ulk_links_to_host.argtypes = [PL, vp, vp, vp, vp]
+    lib.ulk_node_stats.argtypes = [PF, vp, C.c_int, i32, i32, vp, vp, vp, vp, vp, vp]
     lib.ulk_links_free.argtypes = [PL]
     lib.ulk_links_free.restype = None
     lib.ulk_labels_to_contours.argtypes = [vp, i32, C.POINTER(i64), vp, vp, vp]

@@ -38,10 +38,90 @@ def segment_frame(lib, fg: np.ndarray, ct: np.ndarray, keep_labels: bool = True,
     return handle, _lib.nodes_to_host(lib, handle, with_labels=keep_labels)
 
 
+class DeviceArray:
+    """A float64 [n, c] array the library can read: a torch CUDA tensor for the CUDA library, a
+    numpy array for the host-emulation harness (whose "device" pointers are host pointers)."""
+
+    def __init__(self, lib, n: int, c: int):
+        self.shape = (int(n), int(c))
+        if getattr(lib, "_ulk_is_emu", False):
+            self._np = np.zeros(self.shape, np.float64)
+            self._t = None
+            self.ptr = self._np.ctypes.data
+        else:
+            import torch
+            self._np = None
+            self._t = torch.zeros(self.shape, dtype=torch.float64, device="cuda")
+            self.ptr = self._t.data_ptr()
+
+    def host(self) -> np.ndarray:
+        return self._np if self._np is not None else self._t.cpu().numpy()
+
+
+def _image_to_lib(lib, image):
+    """(keepalive, pointer) of one [D,H,W] image channel where the library can read it."""
+    if type(image).__module__.startswith("torch") and image.is_cuda:
+        t = image.contiguous()
+        return t, t.data_ptr()
+    image = np.ascontiguousarray(image)
+    if getattr(lib, "_ulk_is_emu", False):
+        return image, image.ctypes.data
+    import torch
+    src = image.view(np.int16) if image.dtype == np.uint16 else (image.view(np.int32) if image.dtype == np.uint32 else image)
+    t = torch.from_numpy(src).cuda()
+    return t, t.data_ptr()
+
+
+def node_stats(lib, handle, images: Sequence[np.ndarray] = (), stream: int = 0, centroid: bool = False,
+               minmax: bool = False):
+    """`ulk_node_stats` over every image channel -> dict of DeviceArrays: "mean", "std" [n, c]
+    (core/segmentation/node.py:280-296), optionally "min", "max" [n, c] and "centroid" [n, 3]."""
+    n, c = int(handle.contents.n_nodes), len(images)
+    out = {}
+    if c:
+        out["mean"], out["std"] = DeviceArray(lib, n, c), DeviceArray(lib, n, c)
+        if minmax:
+            out["min"], out["max"] = DeviceArray(lib, n, c), DeviceArray(lib, n, c)
+    if centroid:
+        out["centroid"] = DeviceArray(lib, n, 3)
+    ptr = lambda k: C.c_void_p(out[k].ptr) if k in out else None  # noqa: E731
+    for ch in range(max(c, 1)):
+        keep, img, code = None, None, 0
+        if c:
+            a = images[ch]
+            if type(a).__module__.startswith("torch"):
+                dt = np.dtype(bool) if str(a.dtype) == "torch.bool" else np.dtype(str(a.dtype).replace("torch.", ""))
+                a = a if a.is_cuda else a.numpy()
+            else:
+                a = np.asarray(a)
+                dt = a.dtype
+            keep, p = _image_to_lib(lib, a)
+            img, code = C.c_void_p(p), _lib.dtype_code(dt)
+        _lib.check(lib, lib.ulk_node_stats(handle, img, code, ch, max(c, 1), ptr("mean"), ptr("std"), ptr("min"),
+                                           ptr("max"), ptr("centroid") if ch == 0 else None, C.c_void_p(stream)))
+        del keep
+    return out
+
+
+def node_intensity(lib, handle, images: Sequence[np.ndarray], stream: int = 0):
+    """(mean, std) of `node_stats`: the inputs of the colour gate of `ulk_link_frames`."""
+    st = node_stats(lib, handle, images, stream)
+    return st["mean"], st["std"]
+
+
 def link_frames(lib, src, dst, max_distance=15.0, max_neighbors=5, distance_weight=0.0,
-                shift: Optional[np.ndarray] = None, scale: Optional[Sequence[float]] = None):
+                shift: Optional[np.ndarray] = None, scale: Optional[Sequence[float]] = None,
+                weight_func: str = "iou", edge_must_be_positive: bool = False,
+                color=None, z_score_threshold: float = 5.0):
+    """`color` = (src_mean, dst_mean, dst_std) DeviceArrays from `node_intensity` (colour gate)."""
     prm = _lib.LinkParams(float(max_distance), float(distance_weight), int(max_neighbors),
                           int(scale is not None), (C.c_double * 3)(*(scale if scale is not None else (1, 1, 1))))
+    prm.weight_kind = _lib.WEIGHT_KIND_CODES[weight_func]
+    prm.edge_must_be_positive = int(bool(edge_must_be_positive))
+    if color is not None:
+        prm.n_channels = color[0].shape[1]
+        prm.z_score_threshold = float(z_score_threshold)
+        prm.src_mean, prm.dst_mean, prm.dst_std = color[0].ptr, color[1].ptr, color[2].ptr
     out = C.POINTER(_lib.Links)()
     sh = None
     if shift is not None:

@@ -25,18 +25,34 @@ def _stale(target: Path) -> bool:
     return any((HERE / f).stat().st_mtime > mt for f in SOURCES + HEADERS)
 
 
+def _obj_stale(obj: Path, src: Path) -> bool:
+    if not obj.exists():
+        return True
+    mt = obj.stat().st_mtime
+    return src.stat().st_mtime > mt or any((HERE / h).stat().st_mtime > mt for h in HEADERS)
+
+
 def build(force: bool = False, verbose: bool = False) -> Path:
+    """One nvcc -c per source file, in parallel, then a link step (objects under csrc/build/)."""
     if not force and not _stale(LIB):
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [
-        nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-        "-fmad=false", "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC,-fvisibility=hidden",
-        "-shared", "-o", str(LIB),
-    ] + [str(HERE / s) for s in SOURCES]
+    flags = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+             "-fmad=false", "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC,-fvisibility=hidden"]
     if verbose:
-        cmd.insert(1, "-Xptxas=-v")
-    subprocess.run(cmd, check=True)
+        flags.insert(0, "-Xptxas=-v")
+    objdir = HERE / "build"
+    objdir.mkdir(exist_ok=True)
+    procs, objs = [], []
+    for s in SOURCES:
+        obj = objdir / (Path(s).stem + ".o")
+        objs.append(str(obj))
+        if force or _obj_stale(obj, HERE / s):
+            procs.append((s, subprocess.Popen([nvcc] + flags + ["-c", "-o", str(obj), str(HERE / s)])))
+    failed = [s for s, p in procs if p.wait() != 0]
+    if failed:
+        raise subprocess.CalledProcessError(1, f"nvcc -c {failed}")
+    subprocess.run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", str(LIB)] + objs, check=True)
     return LIB
 
 

@@ -4,6 +4,10 @@
 
 extern long long g_ulk_launches;
 
+// scratch slab reserved per frame voxel: the rank-space voxel stage peaks at ~56 B per FOREGROUND
+// voxel (12.5 GB at C5, 21 % foreground = 12 B per frame voxel); denser frames spill into the
+// stream-ordered pool (ulk_ws_alloc falls back to it), they do not fail
+#define ULK_WS_BYTES_PER_VOXEL 32
 #define API_CHK(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
 
 extern "C" {
@@ -51,7 +55,7 @@ int ulk_segment_frame(const void *foreground, int fg_dtype, const void *contours
     ulk_stream_t st = (ulk_stream_t)stream;
     ulk_set_alloc_stream(st);
     *out = nullptr;
-    ulk_ws_reserve((size_t)(shape[0] * shape[1] * shape[2]) * 96 + (64u << 20), st);
+    ulk_ws_reserve((size_t)(shape[0] * shape[1] * shape[2]) * ULK_WS_BYTES_PER_VOXEL + (64u << 20), st);
     int rc = ulk_segment_frame_impl(st, foreground, fg_dtype, contours, ct_dtype, shape, params, keep_labels, out);
     if (rc) { ulk_frame_nodes_free_impl(*out); *out = nullptr; ulk_sync(st); }
     return rc;
@@ -65,7 +69,7 @@ int ulk_segment_frame_host(const void *foreground, int fg_dtype, const void *con
     ulk_stream_t st = (ulk_stream_t)stream;
     ulk_set_alloc_stream(st);
     i64 V = shape[0] * shape[1] * shape[2];
-    ulk_ws_reserve((size_t)V * (96 + ulk_dtype_size(fg_dtype) + ulk_dtype_size(ct_dtype)) + (64u << 20), st);
+    ulk_ws_reserve((size_t)V * (ULK_WS_BYTES_PER_VOXEL + ulk_dtype_size(fg_dtype) + ulk_dtype_size(ct_dtype)) + (64u << 20), st);
     UlkArena A;
     u8 *dfg = A.get<u8>(V * ulk_dtype_size(fg_dtype));
     u8 *dct = A.get<u8>(V * ulk_dtype_size(ct_dtype));
@@ -278,6 +282,19 @@ int ulk_link_frames(const ulk_frame_nodes *src, const ulk_frame_nodes *dst, cons
     int rc = ulk_link_frames_impl(st, src, dst, dst_shift_host, params, out);
     if (rc && *out) { ulk_links_free(*out); *out = nullptr; }
     return rc;
+}
+
+int ulk_node_stats(const ulk_frame_nodes *nodes, const void *image, int image_dtype,
+                   int32_t channel, int32_t n_channels, double *mean, double *std, double *vmin, double *vmax,
+                   double *centroid, void *stream)
+{
+    if (!nodes) ULK_FAIL(-1, "null argument");
+    if (n_channels < 1 || channel < 0 || channel >= n_channels) ULK_FAIL(-1, "bad channel %d of %d", channel, n_channels);
+    if (nodes->n_nodes > 0 && !nodes->mask) ULK_FAIL(-1, "node table without masks");
+    if (!image && (mean || std || vmin || vmax)) ULK_FAIL(-1, "intensity statistics need an image");
+    ulk_stream_t st = (ulk_stream_t)stream;
+    ulk_set_alloc_stream(st);
+    return ulk_node_stats_impl(st, nodes, image, image_dtype, channel, n_channels, mean, std, vmin, vmax, centroid);
 }
 
 int ulk_links_to_host(const ulk_links *l, int32_t *source, int32_t *target, double *weight, void *stream)

@@ -150,6 +150,34 @@ struct K_PairIoU {
     const i32 *dbb, *darea; const i64 *doff; const u32 *dmask;
     const double *shift; i32 k; const i32 *cidx; const double *cd2; const i32 *ccount;
     double dw; double *cw; double *cdist; i64 slots;
+    int weight_kind, positive_only;        // processing.py:183-184,261-264; match_gt.py:148-168
+    int nch; double zthr; const double *smean, *dmean, *dstd;   // colour z-score gate, processing.py:52-104
+    u8 *cvalid;
+    // the candidate's weight, and whether it survives the colour gate and the positive-only rule
+    ULK_D ULK_INLINE void finish(i64 i, i64 t, i32 s, i64 inter) const
+    {
+        const double dist = sqrt(cd2[i]);
+        cdist[i] = dist;
+        double wgt = 0.0;
+        if (weight_kind == 1) wgt = (double)inter;
+        else if (inter > 0) wgt = (double)inter / (double)((i64)darea[t] + (i64)sarea[s] - inter);
+        const double pen = dw * dist;
+        wgt = wgt - pen;
+        cw[i] = wgt;
+        bool ok = !(positive_only && wgt <= 0.0);
+        if (ok && nch > 0) {
+            double worst = 0.0;
+            for (int c = 0; c < nch; ++c) {
+                double sd = dstd[t * nch + c];
+                if (sd <= 1e-6) sd = 1.0;
+                double df = (dmean[t * nch + c] - smean[(i64)s * nch + c]) / sd;
+                df = df < 0 ? -df : df;
+                if (df > worst || df != df) worst = df;
+            }
+            ok = worst <= zthr;
+        }
+        cvalid[i] = ok ? 1 : 0;
+    }
 #ifndef ULK_EMU
     // one warp per candidate pair: lanes take the (z, y) rows of the bbox overlap window
     ULK_D void warp(i64 ii, bool) const
@@ -196,12 +224,7 @@ struct K_PairIoU {
         // per-lane counts stay below 2^32 for any window that fits a frame of < 2^31 voxels
         i64 inter = (i64)__reduce_add_sync(0xffffffffu, cnt);
         if (lane != 0) return;
-        double dist = sqrt(cd2[i]);
-        cdist[i] = dist;
-        double iou = 0.0;
-        if (inter > 0) iou = (double)inter / (double)((i64)darea[t] + (i64)sarea[s] - inter);
-        double pen = dw * dist;
-        cw[i] = iou - pen;
+        finish(i, t, s, inter);
     }
 #endif
     ULK_D void operator()(i64 i) const
@@ -210,8 +233,6 @@ struct K_PairIoU {
         i32 slot = (i32)(i % k);
         if (slot >= ccount[t]) return;
         i32 s = cidx[i];
-        double dist = sqrt(cd2[i]);
-        cdist[i] = dist;
         i32 b1[6], b2[6];
         for (int d = 0; d < 6; ++d) { b1[d] = dbb[6 * t + d]; b2[d] = sbb[6 * s + d]; }
         if (shift)
@@ -243,20 +264,22 @@ struct K_PairIoU {
                     }
                 }
         }
-        double iou = 0.0;
-        if (inter > 0) iou = (double)inter / (double)((i64)darea[t] + (i64)sarea[s] - inter);
-        double pen = dw * dist;
-        cw[i] = iou - pen;
+        finish(i, t, s, inter);
     }
 };
 // processing.py:269: sorted(reverse=True)[:max_neighbors] on (weight, -dist, source_id)
 struct K_LinkTopK {
-    i32 k, maxn; const i32 *ccount; i32 *cidx; double *cw; double *cdist; i32 *nout;
+    i32 k, maxn; const i32 *ccount; i32 *cidx; double *cw; double *cdist; i32 *nout; const u8 *cvalid;
     ULK_D void operator()(i64 t) const
     {
         i32 n = ccount[t];
         i32 *ci = cidx + t * k;
         double *w = cw + t * k, *ds = cdist + t * k;
+        const u8 *ok = cvalid + t * k;
+        i32 m = 0;
+        for (i32 a = 0; a < n; ++a)
+            if (ok[a]) { ci[m] = ci[a]; w[m] = w[a]; ds[m] = ds[a]; ++m; }
+        n = m;
         for (i32 a = 1; a < n; ++a) {     // insertion sort, n <= k is small
             i32 si = ci[a]; double sw = w[a], sd = ds[a];
             i32 p = a;
@@ -282,6 +305,123 @@ struct K_LinkGather {
 };
 struct K_I32ToI64 { const i32 *a; i64 *b; ULK_D void operator()(i64 i) const { b[i] = a[i]; } };
 
+// Per-node reductions over the bit-packed masks: Node.intensity_mean / Node.intensity_std
+// (core/segmentation/node.py:280-296) of one image channel for the colour gate, plus what the
+// regionprops features of processing.py:107-157 need (intensity min / max, float centroid).
+// One warp per node, lanes over the (z, y) rows of its bbox; two passes over the mask (numpy's
+// std is the root of the mean squared deviation from the mean).
+struct UlkNodeAcc { double s, mn, mx; i64 cnt, cz, cy, cx; };
+struct K_NodeStats {
+    const i32 *bb; const i64 *moff; const u32 *mask; const void *img; int dt; i32 H, W;
+    i32 nch, ch; double *mean, *sd, *vmin, *vmax, *cen; i64 n;
+    ULK_D ULK_INLINE void pass1(const i32 *b, const u32 *m, int lane, int step, UlkNodeAcc &a) const
+    {
+        const i32 h = b[4] - b[1], w = b[5] - b[2], wpr = (w + 31) / 32;
+        const i32 nrow = (b[3] - b[0]) * h;
+        for (i32 r = lane; r < nrow; r += step) {
+            const i32 z = b[0] + r / h, y = b[1] + r % h;
+            const i64 base = ((i64)z * H + y) * W + b[2];
+            const u32 *row = m + (i64)r * wpr;
+            for (i32 q = 0; q < wpr; ++q)
+                for (u32 bits = row[q]; bits; bits &= bits - 1) {
+                    const int bit = ulk_popc((bits & (0u - bits)) - 1u);
+                    const i32 xo = q * 32 + bit;
+                    ++a.cnt; a.cz += z; a.cy += y; a.cx += b[2] + xo;
+                    if (img) {
+                        const double v = ulk_load_as_double(img, dt, base + xo);
+                        a.s += v;
+                        if (v < a.mn) a.mn = v;
+                        if (v > a.mx) a.mx = v;
+                    }
+                }
+        }
+    }
+    ULK_D ULK_INLINE double pass2(const i32 *b, const u32 *m, int lane, int step, double mu) const
+    {
+        const i32 h = b[4] - b[1], w = b[5] - b[2], wpr = (w + 31) / 32;
+        const i32 nrow = (b[3] - b[0]) * h;
+        double acc = 0.0;
+        for (i32 r = lane; r < nrow; r += step) {
+            const i32 z = b[0] + r / h, y = b[1] + r % h;
+            const i64 base = ((i64)z * H + y) * W + b[2];
+            const u32 *row = m + (i64)r * wpr;
+            for (i32 q = 0; q < wpr; ++q)
+                for (u32 bits = row[q]; bits; bits &= bits - 1) {
+                    const int bit = ulk_popc((bits & (0u - bits)) - 1u);
+                    const double d = ulk_load_as_double(img, dt, base + q * 32 + bit) - mu;
+                    acc += d * d;
+                }
+        }
+        return acc;
+    }
+    ULK_D ULK_INLINE void store(i64 i, const UlkNodeAcc &a, double mu, double q) const
+    {
+        const double c = a.cnt > 0 ? (double)a.cnt : 1.0;
+        if (cen) { cen[3 * i] = (double)a.cz / c; cen[3 * i + 1] = (double)a.cy / c; cen[3 * i + 2] = (double)a.cx / c; }
+        if (!img) return;
+        if (mean) mean[i * nch + ch] = mu;
+        if (sd) sd[i * nch + ch] = a.cnt > 0 ? sqrt(q / c) : 0.0;
+        if (vmin) vmin[i * nch + ch] = a.mn;
+        if (vmax) vmax[i * nch + ch] = a.mx;
+    }
+#ifndef ULK_EMU
+    ULK_D void warp(i64 ii, bool) const
+    {
+        const int lane = threadIdx.x & 31;
+        const i64 i = ii >> 5;
+        if (i >= n) return;
+        i32 b[6];
+        for (int d = 0; d < 6; ++d) b[d] = bb[6 * i + d];
+        const u32 *m = mask + moff[i];
+        UlkNodeAcc a{0.0, 1.0 / 0.0, -1.0 / 0.0, 0, 0, 0, 0};
+        pass1(b, m, lane, 32, a);
+        for (int o = 16; o > 0; o >>= 1) {
+            a.s += __shfl_xor_sync(0xffffffffu, a.s, o);
+            const double mn2 = __shfl_xor_sync(0xffffffffu, a.mn, o), mx2 = __shfl_xor_sync(0xffffffffu, a.mx, o);
+            a.mn = mn2 < a.mn ? mn2 : a.mn; a.mx = mx2 > a.mx ? mx2 : a.mx;
+            a.cnt += __shfl_xor_sync(0xffffffffu, a.cnt, o);
+            a.cz += __shfl_xor_sync(0xffffffffu, a.cz, o);
+            a.cy += __shfl_xor_sync(0xffffffffu, a.cy, o);
+            a.cx += __shfl_xor_sync(0xffffffffu, a.cx, o);
+        }
+        const double mu = a.cnt > 0 ? a.s / (double)a.cnt : 0.0;
+        double q = 0.0;
+        if (img && sd) {
+            q = pass2(b, m, lane, 32, mu);
+            for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+        }
+        if (lane == 0) store(i, a, mu, q);
+    }
+#endif
+    ULK_D void operator()(i64 i) const
+    {
+        i32 b[6];
+        for (int d = 0; d < 6; ++d) b[d] = bb[6 * i + d];
+        const u32 *m = mask + moff[i];
+        UlkNodeAcc a{0.0, 1.0 / 0.0, -1.0 / 0.0, 0, 0, 0, 0};
+        pass1(b, m, 0, 1, a);
+        const double mu = a.cnt > 0 ? a.s / (double)a.cnt : 0.0;
+        const double q = (img && sd) ? pass2(b, m, 0, 1, mu) : 0.0;
+        store(i, a, mu, q);
+    }
+};
+
+int ulk_node_stats_impl(ulk_stream_t st, const ulk_frame_nodes *f, const void *image, int dtype,
+                        int32_t channel, int32_t n_channels, double *mean, double *sd, double *vmin, double *vmax,
+                        double *centroid)
+{
+    const i64 n = f->n_nodes;
+    if (n <= 0) return 0;
+    K_NodeStats k{f->bbox, f->mask_off, f->mask, image, dtype, f->shape[1], f->shape[2], n_channels, channel,
+                  mean, sd, vmin, vmax, centroid, n};
+#ifdef ULK_EMU
+    ulk_launch(n, st, k);
+#else
+    ulk_launch_warp(n * 32, st, k);
+#endif
+    return ulk_sync(st);
+}
+
 int ulk_link_frames_impl(ulk_stream_t st, const ulk_frame_nodes *src, const ulk_frame_nodes *dst,
                          const double *dst_shift_host, const ulk_link_params *prm, ulk_links **out)
 {
@@ -291,6 +431,10 @@ int ulk_link_frames_impl(ulk_stream_t st, const ulk_frame_nodes *src, const ulk_
     const i32 Ns = src->n_nodes, Nd = dst->n_nodes;
     const i32 k = 2 * prm->max_neighbors;
     if (Ns <= 0 || Nd <= 0 || k <= 0 || !(prm->max_distance > 0)) return 0;
+    if (prm->weight_kind < 0 || prm->weight_kind > 1) ULK_FAIL(-1, "weight_kind=%d (0 IoU, 1 intersection)", prm->weight_kind);
+    const int nch = prm->n_channels;
+    if (nch < 0 || (nch > 0 && (!prm->src_mean || !prm->dst_mean || !prm->dst_std)))
+        ULK_FAIL(-1, "colour gate: n_channels=%d needs src_mean, dst_mean and dst_std", nch);
     UlkArena A;
     LinkGeom g;
     g.has_scale = prm->has_scale;
@@ -344,17 +488,20 @@ int ulk_link_frames_impl(ulk_stream_t st, const ulk_frame_nodes *src, const ulk_
     i64 slots = (i64)Nd * k;
     i32 *cidx = A.get<i32>(slots), *ccount = A.get<i32>(Nd), *nout = A.get<i32>(Nd + 1);
     double *cd2 = A.get<double>(slots), *cw = A.get<double>(slots), *cdist = A.get<double>(slots);
+    u8 *cvalid = A.get<u8>(slots);
     i64 *nout64 = A.get<i64>(Nd + 1), *ooff = A.get<i64>(Nd + 1);
     CHKA(A);
     ulk_launch(Nd, st, K_KnnSelect{src->centroid, dst->centroid, shift, g, sidx, cstart, k, cidx, cd2, ccount});
     K_PairIoU piou{src->bbox, src->area, src->mask_off, src->mask, dst->bbox, dst->area,
-                   dst->mask_off, dst->mask, shift, k, cidx, cd2, ccount, prm->distance_weight, cw, cdist, slots};
+                   dst->mask_off, dst->mask, shift, k, cidx, cd2, ccount, prm->distance_weight, cw, cdist, slots,
+                   prm->weight_kind, prm->edge_must_be_positive, nch, prm->z_score_threshold,
+                   prm->src_mean, prm->dst_mean, prm->dst_std, cvalid};
 #ifdef ULK_EMU
     ulk_launch(slots, st, piou);
 #else
     ulk_launch_warp(slots * 32, st, piou);
 #endif
-    ulk_launch(Nd, st, K_LinkTopK{k, prm->max_neighbors, ccount, cidx, cw, cdist, nout});
+    ulk_launch(Nd, st, K_LinkTopK{k, prm->max_neighbors, ccount, cidx, cw, cdist, nout, cvalid});
     CHK(ulk_memset(nout + Nd, 0, sizeof(i32), st));
     ulk_launch(Nd + 1, st, K_I32ToI64{nout, nout64});
     CHK(ulk_exclusive_scan_i64(nout64, ooff, (i64)Nd + 1, st));

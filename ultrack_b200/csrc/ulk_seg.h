@@ -9,6 +9,9 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fg, int fg_dtype, const 
 void ulk_frame_nodes_free_impl(ulk_frame_nodes *f);
 int ulk_link_frames_impl(ulk_stream_t st, const ulk_frame_nodes *src, const ulk_frame_nodes *dst,
                          const double *dst_shift_host, const ulk_link_params *prm, ulk_links **out);
+int ulk_node_stats_impl(ulk_stream_t st, const ulk_frame_nodes *f, const void *image, int dtype,
+                        int32_t channel, int32_t n_channels, double *mean, double *sd, double *vmin, double *vmax,
+                        double *centroid);
 int ulk_node_shifts_impl(ulk_stream_t st, const ulk_frame_nodes *nodes, const void *field, int field_dtype, int32_t n_vec,
                          const int64_t field_shape[3], double *shift_host);
 int ulk_labels_to_contours_impl(ulk_stream_t st, const int32_t *labels, int32_t n_sets, const int64_t shape[3],

@@ -201,6 +201,21 @@ def insert_links(database_path: str, weight: np.ndarray, source_id: np.ndarray, 
         conn.close()
 
 
+def insert_gt(database_path: str, gt_rows: Sequence[Tuple], weight: np.ndarray, source_id: np.ndarray,
+              target_id: np.ndarray) -> None:
+    """GTNodeDB rows (t, label, pickle, z, y, x) and the `gt_links` rows of one timepoint
+    (core/match_gt.py:103-168; compute_spatial_neighbors appends to GTLinkDB.__tablename__)."""
+    links = zip((float(w) for w in weight), (float(s) for s in source_id), (float(t) for t in target_id))
+    conn = connect(database_path)
+    try:
+        with write_lock(database_path), conn:
+            conn.execute("BEGIN IMMEDIATE")
+            conn.executemany("INSERT INTO gt_nodes (t, label, pickle, z, y, x) VALUES (?, ?, ?, ?, ?, ?)", gt_rows)
+            conn.executemany("INSERT INTO gt_links (weight, source_id, target_id) VALUES (?, ?, ?)", links)
+    finally:
+        conn.close()
+
+
 def update_shifts(database_path: str, ids: np.ndarray, shifts_zyx: np.ndarray) -> None:
     """UPDATE nodes SET z_shift, y_shift, x_shift WHERE id = ... (imgproc/flow.py:740-751)."""
     rows = [(float(s[0]), float(s[1]), float(s[2]), int(i)) for i, s in zip(ids, shifts_zyx)]

@@ -22,8 +22,11 @@ from ultrack_b200 import _lib, database, frames, sharding
 LOG = logging.getLogger(__name__)
 
 
-def link_params(config, scale: Optional[Sequence[float]], ndim: int) -> _lib.LinkParams:
-    """LinkingConfig (+ scale) -> ulk_link_params; `scale[-ndim:]` as in processing.py:215-219."""
+def link_params(config, scale: Optional[Sequence[float]], ndim: int, weight_func: str = "iou",
+                edge_must_be_positive: bool = False) -> _lib.LinkParams:
+    """LinkingConfig (+ scale) -> ulk_link_params; `scale[-ndim:]` as in processing.py:215-219.
+    `weight_func` / `edge_must_be_positive`: the two extra arguments of compute_spatial_neighbors
+    (processing.py:183-184), "iou" = Node.IoU, "intersection" = Node.intersection."""
     sc = [1.0, 1.0, 1.0]
     if scale is not None:
         # the reference keeps the last min(n_dim, len(scale)) axes of BOTH position arrays
@@ -31,13 +34,46 @@ def link_params(config, scale: Optional[Sequence[float]], ndim: int) -> _lib.Lin
         # a zero scale factor on those axes reproduces exactly
         m = min(ndim, len(scale))
         sc = [0.0] * (3 - m) + [float(v) for v in list(scale)[-m:]] if m > 0 else [0.0, 0.0, 0.0]
-    return _lib.LinkParams(float(config.max_distance), float(config.distance_weight), int(config.max_neighbors),
-                           int(scale is not None), (C.c_double * 3)(*sc))
+    prm = _lib.LinkParams(float(config.max_distance), float(config.distance_weight), int(config.max_neighbors),
+                          int(scale is not None), (C.c_double * 3)(*sc))
+    prm.weight_kind = _lib.WEIGHT_KIND_CODES[weight_func]
+    prm.edge_must_be_positive = int(bool(edge_must_be_positive))
+    return prm
+
+
+def frame_color_stats(lib, frame: frames.DeviceFrame, images: Sequence, time: int):
+    """Per-node intensity mean / std of every image channel at `time` (_compute_features,
+    processing.py:31-49) on the device node table; cached on the frame (a frame is the source of
+    one pair and the target of the previous one, with the same image)."""
+    key = (tuple(id(im) for im in images), int(time))
+    cached = getattr(frame, "_color", None)
+    if cached is not None and cached[0] == key:
+        return cached[1]
+    from ultrack_b200 import capi
+    chans = []
+    for im in images:
+        a = im[time]
+        a = a if type(a).__module__.startswith("torch") else np.asarray(a)
+        if a.ndim == frame.ndim + 1 and a.shape[-1] == 1:
+            a = a[..., 0]
+        if a.ndim != frame.ndim:
+            raise ValueError(f"image frame of shape {tuple(a.shape)} does not match {frame.ndim}-D nodes; "
+                             "pass one array per channel")
+        chans.append(a)
+    st = capi.node_stats(lib, frame.handle, chans)
+    frame._color = (key, st)
+    return st
 
 
 def link_frames_device(lib, src: frames.DeviceFrame, dst: frames.DeviceFrame, prm: _lib.LinkParams,
-                       shift: Optional[np.ndarray] = None, stream: int = 0) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
-    """One `ulk_link_frames` call -> (weight, source_id, target_id) rows."""
+                       shift: Optional[np.ndarray] = None, stream: int = 0,
+                       color=None, z_score_threshold: float = 5.0) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+    """One `ulk_link_frames` call -> (weight, source_id, target_id) rows.  `color` = (source stats,
+    target stats) from `frame_color_stats` switches the colour z-score gate on."""
+    if color is not None:
+        prm.n_channels = color[0]["mean"].shape[1]
+        prm.z_score_threshold = float(z_score_threshold)
+        prm.src_mean, prm.dst_mean, prm.dst_std = color[0]["mean"].ptr, color[1]["mean"].ptr, color[1]["std"].ptr
     out = C.POINTER(_lib.Links)()
     sh = None
     if shift is not None:
@@ -71,7 +107,7 @@ def _frame(lib, db: str, t: int, shape3, ndim: int) -> Optional[frames.DeviceFra
 
 
 def _process(time: int, config, db_path: str, scale, lib, shape3, ndim: int,
-             next_frame: Optional[frames.DeviceFrame] = None) -> None:
+             next_frame: Optional[frames.DeviceFrame] = None, images: Sequence = ()) -> None:
     """linking/processing.py:107-169 + 172-291 for the pair (time, time + 1)."""
     src = _frame(lib, db_path, time, shape3, ndim)
     dst = next_frame if next_frame is not None else _frame(lib, db_path, time + 1, shape3, ndim)
@@ -87,7 +123,12 @@ def _process(time: int, config, db_path: str, scale, lib, shape3, ndim: int,
         return
     shift = frames.load_shifts(db_path, time + 1, dst.n_nodes)
     prm = link_params(config, scale, ndim)
-    weight, source_id, target_id = link_frames_device(lib, src, dst, prm, shift)
+    color = None
+    if len(images) > 0:
+        LOG.info(f"computing filtering by color z-score from t={time}")
+        color = (frame_color_stats(lib, src, images, time), frame_color_stats(lib, dst, images, time + 1))
+    weight, source_id, target_id = link_frames_device(lib, src, dst, prm, shift, color=color,
+                                                      z_score_threshold=config.z_score_threshold)
     if len(weight) == 0:
         LOG.warning(f"No links found for time {time}. Increase `linking_config.max_distance` parameter.")
         return
@@ -104,12 +145,11 @@ def link(
 ) -> None:
     """Links candidate segments (nodes) with their neighbors on the next time.
 
-    Parameters are those of ultrack.link (linking/processing.py:294-318).  The optional colour
-    z-score filter (`images`, processing.py:52-104) is outside the accelerated path and raises.
+    Parameters are those of ultrack.link (linking/processing.py:294-318).  `images`: one array
+    (T, (Z), Y, X) per channel; per-node intensity mean / std are reduced over the device masks
+    (`ulk_node_stats`) and candidates outside `z_score_threshold` are dropped (processing.py:52-104).
     """
     LOG.info(f"Linking nodes with LinkingConfig:\n{config.linking_config}")
-    if len(images) > 0:
-        raise NotImplementedError("colour-space filtering (`images`) is not implemented by ultrack_b200")
     lib = _lib.get_lib()
     rank, world = sharding.dist_info()
     if world > 1:
@@ -134,7 +174,7 @@ def link(
         boundary = _exchange_boundary(lib, db_path, time_points, max_t + 1, world, rank, shape3, ndim)
     for time in mine:
         nxt = boundary if (boundary is not None and time == mine[-1]) else None
-        _process(time, config.linking_config, db_path, scale, lib, shape3, ndim, next_frame=nxt)
+        _process(time, config.linking_config, db_path, scale, lib, shape3, ndim, next_frame=nxt, images=images)
     sharding.barrier()
 
 
