@@ -182,6 +182,23 @@ ULK_API int ulk_node_stats(const ulk_frame_nodes *nodes, const void *image, int 
 ULK_API int ulk_links_to_host(const ulk_links *links, int32_t *source, int32_t *target, double *weight, void *stream);
 ULK_API void ulk_links_free(ulk_links *links);
 
+/* Bulk writer of the `nodes.pickle` column: pickle.dumps(Node) of every node of a
+ * frame (core/segmentation/processing.py:254-267; Node.__getstate__, node.py:270-278) in one
+ * kernel.  Blob i = head template + the node's bool mask as raw bytes + tail template, with the
+ * per-node fields patched into fixed-width holes at the offsets of `spec` (built by
+ * ultrack_b200/node.py:BlobTemplate, which documents the pickle stream).  blob_off_host[n+1] =
+ * byte offset of every blob in `out_host` (blob size = head_len + bbox volume + tail_len);
+ * ids are id_base + node index + 1 (processing.py:42-59). */
+typedef struct ulk_blob_spec {
+    int32_t head_len, tail_len, ndim, payload_start, payload_tail;
+    int32_t off_area, off_frontier, off_height, off_hidx, off_bbox, off_chunk_len;
+    int32_t off_blosc_nbytes, off_blosc_blocksize, off_blosc_cbytes, off_shape, off_raw_len;
+    int32_t toff_id, toff_time, toff_centroid;
+} ulk_blob_spec;
+ULK_API int ulk_frame_blobs_to_host(const ulk_frame_nodes *nodes, const uint8_t *head, const uint8_t *tail,
+                            const ulk_blob_spec *spec, int64_t id_base, int32_t time,
+                            const int64_t *blob_off_host, uint8_t *out_host, void *stream);
+
 /* utils/edge.py:18-96 for one frame: n_sets label images [n_sets,D,H,W] (int32, device) ->
  * foreground uint8 [D,H,W] and contours float32 [D,H,W] (sigma = None path) */
 ULK_API int ulk_labels_to_contours(const int32_t *labels, int32_t n_sets, const int64_t shape[3],

@@ -278,6 +278,41 @@ def test_match_gt_candidate_links(tmp_path, emu):
     assert len(_rows(cfg, "select label from gt_nodes where t = 1")) == len(labels)
 
 
+@pytest.mark.parametrize("shape,channels", [((64, 64), None), ((10, 32, 32), 2)])
+def test_segment_properties_features(tmp_path, emu, shape, channels):
+    """segment(..., images=, properties=) -- create_feats_callback (processing.py:107-157): float32
+    regionprops vectors in `nodes.features`, names in metadata.toml.  skimage is not installable
+    here; the expected values are regionprops' definitions restated on the unpickled masks."""
+    cfg = _config(tmp_path)
+    T = 2
+    fg, ct = synth.make_timelapse(shape, T, seed=2, variant="S", radius=6.0 if len(shape) == 2 else 5.0)
+    rng = np.random.default_rng(1)
+    img = rng.random((T,) + shape + ((channels,) if channels else ())).astype(np.float32)
+    props = ["area", "centroid", "intensity_mean", "bbox", "intensity_max", "intensity_min", "extent", "intensity_std"]
+    segment(fg, ct, cfg, images=img, properties=props)
+    nd = len(shape)
+    names = cfg.data_config.metadata["properties"]
+    suffix = lambda p: [f"{p}-{c}" for c in range(channels)] if channels else [p]    # noqa: E731
+    assert names == (["area"] + [f"centroid-{i}" for i in range(nd)] + suffix("intensity_mean")
+                     + [f"bbox-{i}" for i in range(2 * nd)] + suffix("intensity_max") + suffix("intensity_min")
+                     + ["extent"] + suffix("intensity_std"))
+    rows = _rows(cfg, "select t, pickle, features from nodes order by id")
+    assert len(rows) > 5
+    for t, blob, feats in rows:
+        node = loads_node(blob)
+        f = pickle.loads(feats)
+        assert f.dtype == np.float32 and f.shape == (len(names),)
+        idx = np.nonzero(node.mask)
+        coords = np.stack(idx, axis=1) + np.asarray(node.bbox[:nd])
+        vals = img[t][tuple(coords.T)].astype(np.float64).reshape(len(coords), -1)
+        ext = np.asarray(node.bbox[nd:]) - np.asarray(node.bbox[:nd])
+        exp = np.concatenate([[node.area], coords.mean(axis=0), vals.mean(axis=0), node.bbox, vals.max(axis=0),
+                              vals.min(axis=0), [node.area / ext.prod()], vals.std(axis=0)]).astype(np.float32)
+        assert np.allclose(f, exp, rtol=1e-5, atol=1e-6), (f, exp)
+    with pytest.raises(NotImplementedError):
+        segment(fg, ct, cfg, properties=["eccentricity"], overwrite=True)
+
+
 def test_config_mirror_round_trip(tmp_path):
     cfg = MainConfig.model_validate({"segmentation": {"ws_hierarchy": "dynamics", "min_area": 5, "max_area": 10},
                                      "data": {"working_dir": str(tmp_path)}, "tracking": {"appear_weight": -0.5}})
@@ -313,3 +348,77 @@ def test_node_blob_format():
     if flags & 0x02:
         assert cbytes == len(packed) == nbytes + 16 and blocksize == nbytes and typesize == 1
         assert np.array_equal(pickle.loads(packed[16:]), m)
+
+
+def _parse_blosc_chunk(chunk: bytes):
+    """Independent reading of the c-blosc2 chunk header (README_CHUNK_FORMAT.rst): byte 0 version,
+    1 versionlz, 2 flags (0x1 byte shuffle, 0x2 memcpyed, 0x4 bit shuffle, 0x10 don't split, bits 5-7
+    codec), 3 typesize, then little-endian uint32 nbytes, blocksize, cbytes.  flags 0x1|0x4 together
+    mark the 32-byte extended (Blosc2) header: bytes 16.. filter codes[6], udcodec, codec meta,
+    filter meta[6], reserved, blosc2 flags."""
+    import struct
+    ver, verlz, flags, typesize, nbytes, blocksize, cbytes = struct.unpack("<BBBBIII", chunk[:16])
+    extended = bool(flags & 0x01) and bool(flags & 0x04)
+    hdr = 32 if extended else 16
+    return dict(version=ver, versionlz=verlz, flags=flags, typesize=typesize, nbytes=nbytes, blocksize=blocksize,
+                cbytes=cbytes, header=hdr, memcpyed=bool(flags & 0x02), payload=chunk[hdr:hdr + nbytes])
+
+
+@pytest.mark.parametrize("shape", [(64, 64), (12, 40, 40)])
+def test_bulk_blob_writer_matches_per_node_pickle(emu, shape):
+    """`ulk_frame_blobs_to_host` (one kernel for all blobs of a frame) == dumps_node per node, as
+    unpickled objects; every mask chunk is a well-formed stored Blosc chunk."""
+    from tests.emu_harness import segment_frame
+    from ultrack_b200 import _lib
+    from ultrack_b200.node import frame_blobs
+    fg, ct, _ = synth.make_frame(shape, seed=4, variant="S", radius=5.0, fill=0.4)
+    h, nodes = segment_frame(emu, fg, ct, keep_labels=False, min_area=60, max_area=600)
+    nd = len(shape)
+    buf, off = frame_blobs(emu, h, nodes, 3, nd, 4_000_000)
+    assert len(off) == len(nodes["area"]) + 1 > 4
+    lo = 3 - nd
+    for i in range(len(nodes["area"])):
+        blob = bytes(buf[off[i]:off[i + 1]])
+        got = loads_node(blob)
+        bb = nodes["bbox"][i].astype(np.int64)
+        ref = loads_node(dumps_node(int(nodes["hidx"][i]), 4_000_000 + i + 1, 3, int(nodes["area"][i]),
+                                    float(nodes["frontier"][i]), float(nodes["height"][i]),
+                                    np.concatenate([bb[lo:3], bb[3 + lo:]]), _lib.unpack_mask(nodes, i, nd),
+                                    nodes["centroid"][i][lo:].astype(np.int64)))
+        assert list(got.__dict__) == list(ref.__dict__)
+        for k, b in ref.__dict__.items():
+            a = getattr(got, k)
+            if isinstance(b, np.ndarray):
+                assert a.dtype == b.dtype and a.shape == b.shape and np.array_equal(a, b), k
+            else:
+                assert a == b and type(a) is type(b), (k, a, b)
+        # the raw state dict (no __setstate__): mask entry is the Blosc chunk
+        class Raw:
+            def __setstate__(self, d): self.d = d
+        import io
+        class U(pickle.Unpickler):
+            def find_class(self, module, name):
+                return Raw if name == "Node" else super().find_class(module, name)
+        chunk = U(io.BytesIO(blob)).load().d["mask"]
+        c = _parse_blosc_chunk(chunk)
+        assert c["version"] == 2 and c["memcpyed"] and c["typesize"] == 1 and c["header"] == 16
+        assert c["cbytes"] == len(chunk) == c["nbytes"] + 16 and c["blocksize"] == c["nbytes"]
+        assert np.array_equal(pickle.loads(c["payload"]), got.mask)
+    emu.ulk_frame_nodes_free(h)
+
+
+def test_blosc_chunk_variants_round_trip():
+    """Stored chunks in both header forms decode: the 16-byte Blosc1 header this package writes and
+    the 32-byte extended header blosc2.pack_array itself emits (flags 0x1|0x4 set)."""
+    import struct
+    m = np.random.default_rng(2).random((5, 6, 7)) > 0.4
+    payload = pickle.dumps(m, pickle.HIGHEST_PROTOCOL)
+    n = len(payload)
+    c1 = pack_array(m)
+    assert _parse_blosc_chunk(c1)["payload"] == payload or np.array_equal(unpack_array(c1), m)
+    ext = struct.pack("<BBBBIII", 5, 1, 0x01 | 0x02 | 0x04 | 0x10, 1, n, n, n + 32) + bytes(16) + payload
+    c = _parse_blosc_chunk(ext)
+    assert c["header"] == 32 and c["memcpyed"] and c["payload"] == payload
+    assert np.array_equal(unpack_array(ext), m)
+    with pytest.raises(ValueError):
+        unpack_array(ext[:20])

@@ -56,6 +56,14 @@ class LinkParams(C.Structure):
                 ("src_mean", C.c_void_p), ("dst_mean", C.c_void_p), ("dst_std", C.c_void_p)]
 
 
+class BlobSpec(C.Structure):
+    _fields_ = [(k, C.c_int32) for k in (
+        "head_len", "tail_len", "ndim", "payload_start", "payload_tail",
+        "off_area", "off_frontier", "off_height", "off_hidx", "off_bbox", "off_chunk_len",
+        "off_blosc_nbytes", "off_blosc_blocksize", "off_blosc_cbytes", "off_shape", "off_raw_len",
+        "toff_id", "toff_time", "toff_centroid")]
+
+
 class Links(C.Structure):
     _fields_ = [("n_links", C.c_int64), ("source", C.c_void_p), ("target", C.c_void_p),
                 ("weight", C.c_void_p), ("n_pairs", C.c_int64)]
@@ -66,7 +74,7 @@ EXPORTS = [
     "ulk_profile_enable", "ulk_profile_reset", "ulk_profile_report", "ulk_segment_frame",
     "ulk_segment_frame_host", "ulk_frame_nodes_free", "ulk_frame_nodes_to_host",
     "ulk_frame_nodes_from_host", "ulk_frame_nodes_to_device", "ulk_frame_nodes_from_device", "ulk_link_frames", "ulk_links_to_host", "ulk_links_free",
-    "ulk_labels_to_contours", "ulk_node_shifts", "ulk_synth_frame", "ulk_node_stats",
+    "ulk_labels_to_contours", "ulk_node_shifts", "ulk_synth_frame", "ulk_node_stats", "ulk_frame_blobs_to_host",
     "ulk_upload_begin", "ulk_segment_frame_uploaded", "ulk_upload_free",
 ]
 
@@ -100,6 +108,7 @@ def bind(lib: C.CDLL) -> C.CDLL:
     lib.ulk_frame_nodes_from_device.argtypes = [i32, C.POINTER(i32), vp, vp, vp, vp, i64, vp, vp, C.POINTER(PF)]
     lib.ulk_link_frames.argtypes = [PF, PF, vp, C.POINTER(LinkParams), vp, C.POINTER(PL)]
     lib.ulk_links_to_host.argtypes = [PL, vp, vp, vp, vp]
+    lib.ulk_frame_blobs_to_host.argtypes = [PF, vp, vp, C.POINTER(BlobSpec), i64, i32, vp, vp, vp]
     lib.ulk_node_stats.argtypes = [PF, vp, C.c_int, i32, i32, vp, vp, vp, vp, vp, vp]
     lib.ulk_links_free.argtypes = [PL]
     lib.ulk_links_free.restype = None

@@ -315,6 +315,18 @@ void ulk_links_free(ulk_links *l)
     delete l;
 }
 
+int ulk_frame_blobs_to_host(const ulk_frame_nodes *nodes, const uint8_t *head, const uint8_t *tail,
+                            const ulk_blob_spec *spec, int64_t id_base, int32_t time,
+                            const int64_t *blob_off_host, uint8_t *out_host, void *stream)
+{
+    if (!nodes || !head || !tail || !spec || !blob_off_host || !out_host) ULK_FAIL(-1, "null argument");
+    if (spec->ndim != 2 && spec->ndim != 3) ULK_FAIL(-1, "blob spec: ndim must be 2 or 3");
+    if (nodes->n_nodes > 0 && !nodes->mask) ULK_FAIL(-1, "node table without masks");
+    ulk_stream_t st = (ulk_stream_t)stream;
+    ulk_set_alloc_stream(st);
+    return ulk_frame_blobs_impl(st, nodes, head, tail, spec, id_base, time, blob_off_host, out_host);
+}
+
 int ulk_labels_to_contours(const int32_t *labels, int32_t n_sets, const int64_t shape[3],
                            uint8_t *foreground, float *contours, void *stream)
 {

@@ -200,3 +200,104 @@ int ulk_node_shifts_impl(ulk_stream_t st, const ulk_frame_nodes *nodes, const vo
     ulk_launch(N, st, k);
     return ulk_d2h(shift_host, out, (size_t)N * 3 * sizeof(double), st);
 }
+
+// ------------------------------------------------------------------ bulk node blobs (f-2)
+// pickle.dumps(Node) of every node of a frame (core/segmentation/processing.py:254-267,
+// core/segmentation/node.py:270-278), written by the device: HEAD template + raw bool mask bytes
+// expanded from the bit-packed mask + TAIL template, fixed-width holes patched per node
+// (ultrack_b200/node.py BlobTemplate builds the templates and documents the stream).
+// One warp per node; byte j of a blob is written by lane j % 32.
+#ifdef ULK_EMU
+#define ULK_SYNCWARP()
+#else
+#define ULK_SYNCWARP() __syncwarp()
+#endif
+struct K_NodeBlobs {
+    const i32 *bbox, *centroid, *area, *hidx; const double *frontier, *height; const i64 *moff; const u32 *mask;
+    const u8 *head, *tail; ulk_blob_spec sp; i64 id_base; i32 time; const i64 *boff; u8 *out; i64 n;
+    static ULK_D ULK_INLINE void put_le(u8 *p, u64 v, int nb) { for (int k = 0; k < nb; ++k) p[k] = (u8)(v >> (8 * k)); }
+    static ULK_D ULK_INLINE void put_be_double(u8 *p, double d)
+    {
+        u64 v;
+        memcpy(&v, &d, 8);
+        for (int k = 0; k < 8; ++k) p[k] = (u8)(v >> (8 * (7 - k)));
+    }
+    ULK_D ULK_INLINE void write(i64 i, int lane, int step) const
+    {
+        const int nd = sp.ndim, lo = 3 - nd;
+        const i32 *bb = bbox + 6 * i;
+        const i32 d = bb[3] - bb[0], h = bb[4] - bb[1], w = bb[5] - bb[2];
+        const i64 vol = (i64)d * h * w;
+        u8 *o = out + boff[i];
+        for (i32 j = lane; j < sp.head_len; j += step) o[j] = head[j];
+        u8 *om = o + sp.head_len;
+        const u32 *m = mask + moff[i];
+        const i32 wpr = (w + 31) / 32;
+        const i64 rows = (i64)d * h;
+        // lanes walk the dense [d*h, w] byte image; consecutive lanes write consecutive bytes
+        for (i64 j = lane; j < vol; j += step) {
+            const i64 r = j / w;
+            const i32 x = (i32)(j - r * w);
+            om[j] = (u8)((m[r * wpr + (x >> 5)] >> (x & 31)) & 1u);
+        }
+        (void)rows;
+        u8 *ot = om + vol;
+        for (i32 j = lane; j < sp.tail_len; j += step) ot[j] = tail[j];
+        ULK_SYNCWARP();
+        if (lane != 0) return;
+        put_le(o + sp.off_area, (u64)(u32)area[i], 4);
+        put_be_double(o + sp.off_frontier, frontier ? frontier[i] : -1.0);
+        put_be_double(o + sp.off_height, height ? height[i] : -1.0);
+        put_le(o + sp.off_hidx, (u64)(u32)(hidx ? hidx[i] : -1), 4);
+        for (int k = 0; k < nd; ++k) {
+            put_le(o + sp.off_bbox + 8 * k, (u64)(i64)bb[lo + k], 8);
+            put_le(o + sp.off_bbox + 8 * (nd + k), (u64)(i64)bb[3 + lo + k], 8);
+            put_le(o + sp.off_shape + 5 * k, (u64)(u32)(bb[3 + lo + k] - bb[lo + k]), 4);
+            put_le(ot + sp.toff_centroid + 8 * k, (u64)(i64)centroid[3 * i + lo + k], 8);
+        }
+        const u64 payload = (u64)(sp.head_len - sp.payload_start) + (u64)vol + (u64)sp.payload_tail;
+        put_le(o + sp.off_chunk_len, payload + 16, 4);
+        put_le(o + sp.off_blosc_nbytes, payload, 4);
+        put_le(o + sp.off_blosc_blocksize, payload, 4);
+        put_le(o + sp.off_blosc_cbytes, payload + 16, 4);
+        put_le(o + sp.off_raw_len, (u64)vol, 4);
+        put_le(ot + sp.toff_id, (u64)(id_base + i + 1), 8);
+        put_le(ot + sp.toff_time, (u64)(u32)time, 4);
+    }
+#ifndef ULK_EMU
+    ULK_D void warp(i64 ii, bool) const
+    {
+        const i64 i = ii >> 5;
+        if (i < n) write(i, threadIdx.x & 31, 32);
+    }
+#endif
+    ULK_D void operator()(i64 i) const { write(i, 0, 1); }
+};
+
+int ulk_frame_blobs_impl(ulk_stream_t st, const ulk_frame_nodes *f, const uint8_t *head, const uint8_t *tail,
+                         const ulk_blob_spec *sp, int64_t id_base, int32_t time, const int64_t *blob_off_host,
+                         uint8_t *out_host)
+{
+    const i64 n = f->n_nodes;
+    if (n <= 0) return 0;
+    const i64 total = blob_off_host[n];
+    for (i64 i = 0; i < n; ++i)
+        if (blob_off_host[i + 1] - blob_off_host[i] >= 2147483000ll) ULK_FAIL(-1, "node %lld: mask too large for one Blosc chunk", (long long)i);
+    UlkArena A;
+    u8 *dh = A.get<u8>(sp->head_len), *dt = A.get<u8>(sp->tail_len), *dout = A.get<u8>(total);
+    i64 *doff = A.get<i64>(n + 1);
+    if (A.failed) ULK_FAIL(-3, "device allocation failed");
+    int rc = 0;
+    rc |= ulk_h2d(dh, head, (size_t)sp->head_len, st);
+    rc |= ulk_h2d(dt, tail, (size_t)sp->tail_len, st);
+    rc |= ulk_h2d(doff, blob_off_host, (size_t)(n + 1) * 8, st);
+    if (rc) return rc;
+    K_NodeBlobs k{f->bbox, f->centroid, f->area, f->hidx, f->frontier, f->height, f->mask_off, f->mask,
+                  dh, dt, *sp, id_base, time, doff, dout, n};
+#ifdef ULK_EMU
+    ulk_launch(n, st, k);
+#else
+    ulk_launch_warp(n * 32, st, k);
+#endif
+    return ulk_d2h(out_host, dout, (size_t)total, st);
+}

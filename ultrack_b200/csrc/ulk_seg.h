@@ -12,6 +12,9 @@ int ulk_link_frames_impl(ulk_stream_t st, const ulk_frame_nodes *src, const ulk_
 int ulk_node_stats_impl(ulk_stream_t st, const ulk_frame_nodes *f, const void *image, int dtype,
                         int32_t channel, int32_t n_channels, double *mean, double *sd, double *vmin, double *vmax,
                         double *centroid);
+int ulk_frame_blobs_impl(ulk_stream_t st, const ulk_frame_nodes *f, const uint8_t *head, const uint8_t *tail,
+                         const ulk_blob_spec *sp, int64_t id_base, int32_t time, const int64_t *blob_off_host,
+                         uint8_t *out_host);
 int ulk_node_shifts_impl(ulk_stream_t st, const ulk_frame_nodes *nodes, const void *field, int field_dtype, int32_t n_vec,
                          const int64_t field_shape[3], double *shift_host);
 int ulk_labels_to_contours_impl(ulk_stream_t st, const int32_t *labels, int32_t n_sets, const int64_t shape[3],

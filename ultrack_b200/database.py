@@ -13,6 +13,7 @@ Only sqlite (file and shared-cache memory) is implemented; a postgresql URL rais
 from __future__ import annotations
 
 import contextlib
+import itertools
 import fcntl
 import logging
 import os
@@ -173,6 +174,16 @@ def node_row(t: int, id: int, t_node_id: int, t_hier_id: int, z: int, y: int, x:
     return (int(t), int(id), NO_PARENT, int(hier_parent_id), int(t_node_id), int(t_hier_id),
             float(z), float(y), float(x), 0.0, 0.0, 0.0, int(area), float(frontier), float(height), 0,
             blob, features, -1.0, "UNKNOWN", "UNKNOWN", "UNKNOWN", "UNKNOWN", "UNKNOWN")
+
+
+def node_rows(t: int, ids, hier_parent_ids, t_node_ids, t_hier_ids, z, y, x, area, frontier, height, blobs,
+              features) -> List[Tuple]:
+    """`node_row` for a whole frame, column-wise (lists of Python scalars / buffers)."""
+    n = len(ids)
+    rep = itertools.repeat
+    return list(zip(rep(int(t), n), ids, rep(NO_PARENT), hier_parent_ids, t_node_ids, t_hier_ids, z, y, x,
+                    rep(0.0), rep(0.0), rep(0.0), area, frontier, height, rep(0), blobs, features, rep(-1.0),
+                    rep("UNKNOWN"), rep("UNKNOWN"), rep("UNKNOWN"), rep("UNKNOWN"), rep("UNKNOWN")))
 
 
 def insert_nodes(database_path: str, nodes: Sequence[Tuple], overlaps: Iterable[Tuple[int, int]]) -> None:

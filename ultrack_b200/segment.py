@@ -12,6 +12,7 @@ from __future__ import annotations
 import ctypes as C
 import logging
 import os
+import pickle
 import sqlite3
 import warnings
 from typing import Dict, List, Optional
@@ -20,7 +21,7 @@ import numpy as np
 
 from ultrack_b200 import _lib, database, frames, sharding
 from ultrack_b200.config import ws_hierarchy_name
-from ultrack_b200.node import dumps_node
+from ultrack_b200.node import dumps_node, frame_blobs
 
 LOG = logging.getLogger(__name__)
 
@@ -159,9 +160,13 @@ def _host_ptr(a) -> int:
     return a.ctypes.data
 
 
-def frame_rows(nodes: Dict[str, np.ndarray], time: int, ndim: int, max_segments_per_time: int):
-    """Node table -> (`nodes` rows, `overlaps` rows) exactly as _process emits them
-    (processing.py:235-300)."""
+def frame_rows(nodes: Dict[str, np.ndarray], time: int, ndim: int, max_segments_per_time: int,
+               features: Optional[np.ndarray] = None, lib=None, handle=None):
+    """Node table -> (ids, `nodes` rows, `overlaps` rows) exactly as _process emits them
+    (processing.py:235-300).  With `lib` / `handle` the pickle blobs of all nodes come from ONE
+    kernel (`node.frame_blobs`) and the rows are assembled column-wise -- no per-node Python work
+    beyond one tuple; without them (a table that only exists on the host) the blobs are pickled
+    node by node."""
     n = len(nodes["area"])
     # the reference's running index ends at n + 1 and it raises when index > max (processing.py:305-308)
     if n + 1 > max_segments_per_time:
@@ -171,24 +176,29 @@ def frame_rows(nodes: Dict[str, np.ndarray], time: int, ndim: int, max_segments_
     parent = nodes["parent"]
     hier_parent = np.where(parent >= 0, _generate_id(parent.astype(np.int64) + 1, time, max_segments_per_time),
                            database.NO_PARENT)
-    rows = []
     lo = 3 - ndim
-    for i in range(n):
-        bb = nodes["bbox"][i].astype(np.int64)
-        bbox = np.concatenate([bb[lo:3], bb[3 + lo:]])
-        cen3 = nodes["centroid"][i]
-        centroid = cen3[lo:].astype(np.int64)
-        mask = _lib.unpack_mask(nodes, i, ndim)
-        blob = dumps_node(int(nodes["hidx"][i]), int(ids[i]), time, int(nodes["area"][i]),
-                          float(nodes["frontier"][i]), float(nodes["height"][i]), bbox, mask, centroid)
-        z = int(cen3[0]) if ndim == 3 else 0
-        rows.append(database.node_row(time, int(ids[i]), int(index[i]), int(nodes["hier_id"][i]), z,
-                                      int(cen3[1]), int(cen3[2]), int(nodes["area"][i]),
-                                      float(nodes["frontier"][i]), float(nodes["height"][i]), blob,
-                                      hier_parent_id=int(hier_parent[i])))
+    if lib is not None and handle is not None:
+        buf, off = frame_blobs(lib, handle, nodes, time, ndim, (time + 1) * max_segments_per_time)
+        mv = memoryview(buf)
+        o = off.tolist()
+        blobs = [mv[o[i]:o[i + 1]] for i in range(n)]
+    else:
+        blobs = []
+        for i in range(n):
+            bb = nodes["bbox"][i].astype(np.int64)
+            blobs.append(dumps_node(int(nodes["hidx"][i]), int(ids[i]), time, int(nodes["area"][i]),
+                                    float(nodes["frontier"][i]), float(nodes["height"][i]),
+                                    np.concatenate([bb[lo:3], bb[3 + lo:]]), _lib.unpack_mask(nodes, i, ndim),
+                                    nodes["centroid"][i][lo:].astype(np.int64)))
+    cen = nodes["centroid"].astype(np.float64)
+    z = cen[:, 0].tolist() if ndim == 3 else [0.0] * n
+    feats = [None] * n if features is None else [pickle.dumps(f, protocol=pickle.HIGHEST_PROTOCOL) for f in features]
+    rows = database.node_rows(time, ids.tolist(), hier_parent.tolist(), index.tolist(), nodes["hier_id"].tolist(), z,
+                              cen[:, 1].tolist(), cen[:, 2].tolist(), nodes["area"].tolist(),
+                              nodes["frontier"].tolist(), nodes["height"].tolist(), blobs, feats)
     ov = nodes["overlaps"].astype(np.int64)
-    overlaps = [(int(a), int(b)) for a, b in zip(_generate_id(ov[:, 0] + 1, time, max_segments_per_time),
-                                                 _generate_id(ov[:, 1] + 1, time, max_segments_per_time))]
+    overlaps = list(zip(_generate_id(ov[:, 0] + 1, time, max_segments_per_time).tolist(),
+                        _generate_id(ov[:, 1] + 1, time, max_segments_per_time).tolist()))
     return ids, rows, overlaps
 
 
@@ -219,14 +229,21 @@ def _stage(time: int, foreground, contours, config, lib):
 
 
 def _process(time: int, staged, db_path: str, max_segments_per_time: int,
-             catch_duplicates_expection: bool, lib) -> None:
+             catch_duplicates_expection: bool, lib, images=None, properties: Optional[List[str]] = None) -> None:
     """processing.py:160-340 for one timepoint (`staged` comes from `_stage`)."""
     run, ndim = staged
     handle = run()
     LOG.info(f"Computing nodes of time {time}")
     try:
         nodes = _lib.nodes_to_host(lib, handle)
-        ids, rows, overlaps = frame_rows(nodes, time, ndim, max_segments_per_time)
+        feats = None
+        if properties is not None:
+            from ultrack_b200 import features
+            frame = None if images is None else images[time]
+            if frame is not None and not _is_cuda_tensor(frame):
+                frame = np.asarray(frame)
+            feats = features.frame_features(lib, handle, nodes, ndim, frame, properties)
+        ids, rows, overlaps = frame_rows(nodes, time, ndim, max_segments_per_time, feats, lib, handle)
     except Exception:
         lib.ulk_frame_nodes_free(handle)
         raise
@@ -259,14 +276,15 @@ def segment(
     """Add candidate segmentation (nodes) from `foreground` and `contours` to database.
 
     Parameters are those of ultrack.segment (processing.py:393-430).  `insertion_throttle_rate`
-    is accepted and unused: rows are inserted once per frame.  `properties` (skimage
-    regionprops features, processing.py:107-157) are outside the accelerated path and raise.
+    is accepted and unused: rows are inserted once per frame.  `properties`: the regionprops
+    features that are reductions over the node masks (`ultrack_b200.features.SUPPORTED`) are
+    computed on the device for all nodes of a frame at once; others raise NotImplementedError.
     """
     LOG.info(f"Adding nodes with SegmentationConfig:\n{config.segmentation_config}")
     if tuple(foreground.shape) != tuple(contours.shape):
         raise ValueError(f"`foreground` and `contours` shape must match. Found {foreground.shape} and {contours.shape}")
-    if properties is not None:
-        raise NotImplementedError("`properties` (skimage regionprops features) are not computed by ultrack_b200")
+    from ultrack_b200 import features
+    prop_names = features.properties_names(foreground.shape, images, properties)
     check_array_chunk(foreground)
     check_array_chunk(contours)
 
@@ -283,8 +301,10 @@ def segment(
         if overwrite:
             database.clear_all_data(db_path)
         database.create_all(db_path)
-        # `properties` is None on this path and toml drops None values (processing.py:460-467)
-        config.data_config.metadata_add({"shape": [int(s) for s in foreground.shape]})
+        meta = {"shape": [int(s) for s in foreground.shape]}
+        if prop_names is not None:       # toml drops None values (processing.py:460-467)
+            meta["properties"] = prop_names
+        config.data_config.metadata_add(meta)
     if overwrite:
         frames.STORE.clear(db_path)
     sharding.barrier()
@@ -293,6 +313,6 @@ def segment(
     staged = _stage(mine[0], foreground, contours, config.segmentation_config, lib) if mine else None
     for k, time in enumerate(mine):
         nxt = _stage(mine[k + 1], foreground, contours, config.segmentation_config, lib) if k + 1 < len(mine) else None
-        _process(time, staged, db_path, max_segments_per_time, batch_index is not None, lib)
+        _process(time, staged, db_path, max_segments_per_time, batch_index is not None, lib, images, properties)
         staged = nxt
     sharding.barrier()
