@@ -224,6 +224,172 @@ def make_config(name: str):
             "parallelism": "timepoint shards, one per GPU (reference arm: one per host core)"}
 
 
+# ----------------------------------------------------------------------------- extra legs of the GPU arm
+def run_api_leg(lib, torch, dist, rank, world, local_rank, frames_per_rank: int = 4):
+    """`e2e_api`: the PUBLIC API end to end -- ultrack_b200.segment() + link() on a C3-size
+    timelapse held in pinned host memory, rows + pickle blobs into a sqlite file on local disk
+    (what the reference's own timings include: SQL and blobs).  Timepoints are sharded over the
+    ranks exactly as a user's torchrun job would; wall clock, max over ranks."""
+    import shutil
+    import tempfile
+
+    import numpy as np
+
+    import ultrack_b200
+    from ultrack_b200 import frames as frames_mod
+    from ultrack_b200 import segment as seg_mod
+    shape, radius, _ = WORKLOADS["c3"]
+    T = frames_per_rank * world
+    dev = torch.device("cuda", local_rank)
+    fg_h = torch.empty((T,) + shape, dtype=torch.float32).pin_memory()
+    ct_h = torch.empty((T,) + shape, dtype=torch.float32).pin_memory()
+    shp = (C.c_int64 * 3)(*shape)
+    fg_d = torch.empty(shape, dtype=torch.float32, device=dev)
+    ct_d = torch.empty(shape, dtype=torch.float32, device=dev)
+    for t in range(T):
+        _lib_check(lib, lib.ulk_synth_frame(shp, t, SYNTH["seed"], radius, SYNTH["fill"], SYNTH["motion"], SYNTH["noise"],
+                                            C.c_void_p(fg_d.data_ptr()), C.c_void_p(ct_d.data_ptr()), None))
+        torch.cuda.synchronize()
+        fg_h[t].copy_(fg_d)
+        ct_h[t].copy_(ct_d)
+    del fg_d, ct_d
+    wd = [None]
+    if rank == 0:
+        wd[0] = tempfile.mkdtemp(prefix="ulk_bench_api_", dir="/tmp")
+    if world > 1:
+        dist.broadcast_object_list(wd, src=0)
+    cfg = ultrack_b200.MainConfig.model_validate({
+        "data": {"working_dir": wd[0]},
+        "segmentation": {k: SEG[k] for k in ("threshold", "min_area", "max_area", "min_area_factor", "min_frontier", "ws_hierarchy")},
+        "linking": dict(LINK)})
+    fg_np, ct_np = fg_h.numpy(), ct_h.numpy()
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    # warm-up on a throw-away database (pool growth, sqlite file creation)
+    ultrack_b200.segment(fg_np[:world], ct_np[:world], cfg, overwrite=True)
+    for k in seg_mod.TIMERS:
+        seg_mod.TIMERS[k] = 0.0
+    sync()
+    t0 = time.perf_counter()
+    ultrack_b200.segment(fg_np, ct_np, cfg, overwrite=True)
+    sync()
+    t1 = time.perf_counter()
+    ultrack_b200.link(cfg)
+    sync()
+    t2 = time.perf_counter()
+    tt = torch.tensor([t1 - t0, t2 - t1], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    out = None
+    if rank == 0:
+        import sqlite3
+        db = os.path.join(wd[0], "data.db")
+        conn = sqlite3.connect(db)
+        n_nodes = conn.execute("select count(*) from nodes").fetchone()[0]
+        n_links = conn.execute("select count(*) from links").fetchone()[0]
+        blob_bytes = conn.execute("select sum(length(pickle)) from nodes").fetchone()[0]
+        conn.close()
+        seg_s, link_s = float(tt[0]), float(tt[1])
+        V = shape[0] * shape[1] * shape[2]
+        split = {k: round(v * 1e3 / frames_per_rank, 2) for k, v in seg_mod.TIMERS.items()}
+        out = {"value": V * T / (seg_s + link_s), "unit": "voxels/s", "frames": T, "frame_shape": list(shape),
+               "segment_s": seg_s, "link_s": link_s, "nodes": n_nodes, "links": n_links, "blob_bytes": blob_bytes,
+               "db_bytes": os.path.getsize(db),
+               "rank0_ms_per_frame": dict(split, note="segment() wall split on rank 0: kernels incl. upload wait | node table D2H | "
+                                                      "blob kernel + row assembly | sqlite insert"),
+               "api": "ultrack_b200.segment(fg, ct, cfg, overwrite=True) + ultrack_b200.link(cfg): pinned host float32 "
+                      "timelapse in, nodes / overlaps / links rows with pickle blobs (stored Blosc chunks: blosc2 is not "
+                      "installable here, masks are 1 byte per bbox voxel) into sqlite on local disk"}
+    frames_mod.STORE.clear()
+    sync()
+    if rank == 0:
+        shutil.rmtree(wd[0], ignore_errors=True)
+    return out
+
+
+def _lib_check(lib, rc):
+    from ultrack_b200 import _lib
+    _lib.check(lib, rc)
+
+
+def run_h2d_ceiling(torch, dist, world, local_rank, host_bufs, reps: int = 3):
+    """Plain pinned host->device copies of one step's inputs, all ranks at once, no kernels: the
+    box's ceiling for any end-to-end number that starts from host memory."""
+    dev = torch.device("cuda", local_rank)
+    dst = [torch.empty_like(b, device=dev) for b in host_bufs]
+    nbytes = sum(b.numel() * b.element_size() for b in host_bufs)
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        for d, b in zip(dst, host_bufs):
+            d.copy_(b, non_blocking=True)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        for _ in range(reps):
+            for d, b in zip(dst, host_bufs):
+                d.copy_(b, non_blocking=True)
+        e1.record(st)
+        torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms[0]) / reps
+    return {"bytes_per_step": nbytes, "ms_per_step": ms, "gbps_per_rank": nbytes / ms / 1e6, "gbps_total": nbytes * world / ms / 1e6}
+
+
+def run_boundary_leg(lib, torch, dist, rank, world, handle, ids_len, ndim, lprm, sp):
+    """The one exchange of the sharded path: rank g+1 sends the node table of the first frame of
+    its block to rank g (frames.send_frame / recv_frame: NCCL send/recv of device buffers over
+    NVLink), and rank g links its last frame against it.  Timed on the device, max over ranks."""
+    import numpy as np
+
+    from ultrack_b200 import _lib, frames as frames_mod
+    dev = torch.device("cuda", torch.cuda.current_device())
+    mine = frames_mod.DeviceFrame(lib, handle, np.arange(ids_len, dtype=np.int64), ndim)
+    f = handle.contents
+    nbytes = int(f.n_nodes) * (10 * 4 + 2 * 8) + int(f.mask_words) * 4
+    res = {}
+    for rep in range(2):           # first round warms NCCL's p2p channels up
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0.record()
+        got = None
+        # even ranks receive first, odd ranks send first: every send has a matching receive posted
+        for phase in range(2):
+            if (rank % 2 == 0) == (phase == 0):
+                if rank + 1 < world:
+                    got = frames_mod.recv_frame(lib, rank + 1)
+            else:
+                if rank > 0:
+                    frames_mod.send_frame(mine, rank - 1)
+        e1.record()
+        n_links = 0
+        if got is not None:
+            out = C.POINTER(_lib.Links)()
+            _lib.check(lib, lib.ulk_link_frames(mine.handle, got.handle, None, C.byref(lprm), None, C.byref(out)))
+            n_links = int(out.contents.n_links)
+            lib.ulk_links_free(out)
+            got.free()
+        e2.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1), e1.elapsed_time(e2), float(n_links)], dtype=torch.float64, device=dev)
+        mx = t.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        res = {"nranks": world, "messages": world - 1, "bytes_per_message": nbytes, "exchange_ms": float(mx[0]),
+               "boundary_link_ms": float(mx[1]), "boundary_links": int(mx[2]),
+               "how": "frames.send_frame/recv_frame (torch.distributed NCCL send/recv of device buffers) + ulk_link_frames "
+                      "of the received table; CUDA events, max over ranks; second of two rounds"}
+    mine.handle = None              # the caller still owns the handle
+    return res
+
+
 # ----------------------------------------------------------------------------- GPU arm
 def main():
     ap = argparse.ArgumentParser()
@@ -234,6 +400,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-api", action="store_true", help="skip the segment()+link()+sqlite leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -392,57 +559,78 @@ def main():
         # (ulk_upload_begin of frame i+1 before ulk_segment_frame_uploaded of frame i), node
         # table + links read back to the host every step
         e2e = None
+        e2e_narrow = None
+        h2d_ceiling = {}
         if not args.no_e2e:
-            host = [(fg.cpu().pin_memory(), ct.cpu().pin_memory()) for fg, ct in frames_in]
+            def run_e2e(host, codes, prm_, prev):
+                def begin(j):
+                    up = C.c_void_p()
+                    fg, ct = host[j % 2]
+                    _lib.check(lib, lib.ulk_upload_begin(C.c_void_p(fg.data_ptr()), codes[0], C.c_void_p(ct.data_ptr()),
+                                                         codes[1], shp, C.byref(up)))
+                    return up
 
-            def begin(j):
-                up = C.c_void_p()
-                fg, ct = host[j % 2]
-                _lib.check(lib, lib.ulk_upload_begin(C.c_void_p(fg.data_ptr()), 5, C.c_void_p(ct.data_ptr()), 5, shp,
-                                                     C.byref(up)))
-                return up
+                def step_up(up, prev):
+                    h = C.POINTER(_lib.FrameNodes)()
+                    _lib.check(lib, lib.ulk_segment_frame_uploaded(up, C.byref(prm_), 0, sp, C.byref(h)))
+                    links = lnk(prev, h)
+                    n_links = int(links.contents.n_links)
+                    nodes = _lib.nodes_to_host(lib, h, stream.cuda_stream)
+                    s = np.zeros(n_links, np.int32); t = np.zeros(n_links, np.int32); w = np.zeros(n_links, np.float64)
+                    p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+                    _lib.check(lib, lib.ulk_links_to_host(links, p(s), p(t), p(w), sp))
+                    d2h = sum(v.nbytes for v in nodes.values() if isinstance(v, np.ndarray)) + s.nbytes + t.nbytes + w.nbytes
+                    lib.ulk_links_free(links)
+                    lib.ulk_frame_nodes_free(prev)
+                    return h, d2h
 
-            def step_up(up, prev):
-                h = C.POINTER(_lib.FrameNodes)()
-                _lib.check(lib, lib.ulk_segment_frame_uploaded(up, C.byref(prm), 0, sp, C.byref(h)))
-                links = lnk(prev, h)
-                n_links = int(links.contents.n_links)
-                nodes = _lib.nodes_to_host(lib, h, stream.cuda_stream)
-                s = np.zeros(n_links, np.int32); t = np.zeros(n_links, np.int32); w = np.zeros(n_links, np.float64)
-                p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
-                _lib.check(lib, lib.ulk_links_to_host(links, p(s), p(t), p(w), sp))
-                d2h = sum(v.nbytes for v in nodes.values() if isinstance(v, np.ndarray)) + s.nbytes + t.nbytes + w.nbytes
-                lib.ulk_links_free(links)
-                lib.ulk_frame_nodes_free(prev)
-                return h, d2h
-
-            ke = max(1, min(args.steps, 3))
-            up = begin(0)
-            nxt = begin(1)
-            prev, _ = step_up(up, prev)          # untimed: fills the pipeline
-            up = nxt
-            barrier()
-            e0.record(stream)
-            d2h_tot = 0
-            for i in range(ke):
-                nxt = begin(i)                   # frame i+2 of the sequence starts copying now
-                prev, d2h = step_up(up, prev)
+                ke = max(1, min(args.steps, 5))
+                up = begin(0)
+                nxt = begin(1)
+                prev, _ = step_up(up, prev)          # untimed: fills the pipeline
                 up = nxt
-                d2h_tot += d2h
-            e1.record(stream)
-            barrier()
-            lib.ulk_upload_free(up)
-            ems = e0.elapsed_time(e1)
-            e2e = (ke, ems, d2h_tot // ke)
-            del host
-    lib.ulk_frame_nodes_free(prev)
+                barrier()
+                e0.record(stream)
+                d2h_tot = 0
+                for i in range(ke):
+                    nxt = begin(i)                   # frame i+2 of the sequence starts copying now
+                    prev, d2h = step_up(up, prev)
+                    up = nxt
+                    d2h_tot += d2h
+                e1.record(stream)
+                barrier()
+                lib.ulk_upload_free(up)
+                return prev, (ke, e0.elapsed_time(e1), d2h_tot // ke)
 
-    t = torch.tensor([ms, e2e[1] if e2e else 0.0], dtype=torch.float64, device=dev)
+            # (a) the inputs as BASELINE.json's config states them: float32 + float32
+            host = [(fg.cpu().pin_memory(), ct.cpu().pin_memory()) for fg, ct in frames_in]
+            prev, e2e = run_e2e(host, (5, 5), prm, prev)
+            h2d_ceiling["f32+f32"] = run_h2d_ceiling(torch, dist, world, local_rank, list(host[0]))
+            del host
+            # (b) the dtypes the reference's own Zebrahub example feeds: bool
+            # foreground + float16 contours, 3 B/voxel instead of 8
+            host = [((fg > SEG["threshold"]).to(torch.uint8).cpu().pin_memory(), ct.to(torch.float16).cpu().pin_memory())
+                    for fg, ct in frames_in]
+            prm_u8 = seg_params(fg_dtype=np.uint8, **SEG)
+            prev, e2e_narrow = run_e2e(host, (0, 4), prm_u8, prev)
+            h2d_ceiling["u8+f16"] = run_h2d_ceiling(torch, dist, world, local_rank, list(host[0]))
+            del host
+    boundary = None
+    if world > 1:
+        boundary = run_boundary_leg(lib, torch, dist, rank, world, prev, int(prev.contents.n_nodes), 3, lprm, sp)
+    lib.ulk_frame_nodes_free(prev)
+    api = None
+    if not args.no_api:
+        del frames_in
+        torch.cuda.empty_cache()
+        api = run_api_leg(lib, torch, dist, rank, world, local_rank)
+
+    t = torch.tensor([ms, e2e[1] if e2e else 0.0, e2e_narrow[1] if e2e_narrow else 0.0], dtype=torch.float64, device=dev)
     cnt = torch.tensor([tot_links], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-    ms_max, ems_max = float(t[0]), float(t[1])
+    ms_max, ems_max, ems2_max = float(t[0]), float(t[1]), float(t[2])
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -464,9 +652,16 @@ def main():
     dom_bytes = bytes_model.kernel_bytes(dom_name, V, n_fg, n_fg_a)
     dom_avg_ms = dom_ms / dom_cnt
     traffic = None
-    tf = ROOT / "profiles" / "ncu_traffic.json"     # dram bytes per launch from `ncu --set full` captures
+    tf = ROOT / "profiles" / "ncu_traffic.json"     # dram bytes per launch from the committed ncu launch list
+    dram_step = None
     if tf.exists():
-        traffic = json.loads(tf.read_text()).get(name, {}).get(dom_name.split("<")[0])
+        tj = json.loads(tf.read_text()).get(name, {})
+        traffic = tj.get(dom_name.split("<")[0])
+        # measured DRAM bytes of one step = sum over kernels of (ncu bytes per launch x launches per step)
+        short = lambda k: k.split("<")[0].split("::")[-1]   # noqa: E731
+        seen = [(k, v) for k, v in prof.items() if short(k) in tj or k in tj]
+        if seen:
+            dram_step = sum((tj.get(k) or tj.get(short(k))) * v[0] for k, v in seen) / max(args.steps, 1)
     roofline = {
         "bound": "hbm", "kernel": dom_name, "launches": dom_cnt, "avg_ms": dom_avg_ms,
         "share_of_kernel_time": dom_ms / kern_ms if kern_ms else None,
@@ -489,17 +684,34 @@ def main():
         "gpu_launches": int(launches),
         "workspace_bytes": dict(zip(("slab", "peak_in_use", "outside_slab"), _ws_stats(lib))),
         "clocks": clk,
-        "roofline": roofline,
         "pipeline_roofline": {"algorithmic_bytes_per_step": b_frame + b_link, "achieved": pipe_gbs, "peak": peak_gbs,
                               "unit": "GB/s", "frac": pipe_gbs / peak_gbs,
+                              "dram_bytes_per_step_ncu": dram_step,
+                              "dram_over_algorithmic": (dram_step / (b_frame + b_link)) if dram_step else None,
                               "kernel_time_ms_per_step": kern_ms / args.steps,
                               "top_kernels_ms_per_step": {k: round(v[1] / args.steps, 3) for k, v in top[:80]}},
+        "roofline": roofline,
     }
     if e2e:
         ke = e2e[0]
         line["e2e"] = {"value": V * ke * world / (ems_max * 1e-3), "unit": "voxels/s", "steps": ke,
                        "ms_per_step": ems_max / ke, "h2d_bytes_per_step": 2 * 4 * V, "d2h_bytes_per_step": e2e[2],
                        "api": "ulk_upload_begin (next frame, copy stream) + ulk_segment_frame_uploaded + ulk_frame_nodes_to_host + ulk_link_frames + ulk_links_to_host, pinned host buffers; one upload per step inside the timed region"}
+    if e2e_narrow:
+        ke = e2e_narrow[0]
+        line["e2e_u8f16"] = {"value": V * ke * world / (ems2_max * 1e-3), "unit": "voxels/s", "steps": ke,
+                             "ms_per_step": ems2_max / ke, "h2d_bytes_per_step": 3 * V, "d2h_bytes_per_step": e2e_narrow[2],
+                             "inputs": "uint8 foreground + float16 contours (the reference's Zebrahub example dtypes), same API as e2e"}
+    if h2d_ceiling:
+        for key, e in (("f32+f32", line.get("e2e")), ("u8+f16", line.get("e2e_u8f16"))):
+            if e and key in h2d_ceiling:
+                h2d_ceiling[key]["e2e_fraction_of_ceiling"] = h2d_ceiling[key]["ms_per_step"] / e["ms_per_step"]
+        line["h2d_ceiling"] = dict(h2d_ceiling, how="pinned host->device cudaMemcpyAsync of one step's inputs, all ranks "
+                                                    "concurrently, no kernels; CUDA events, max over ranks")
+    if boundary:
+        line["boundary"] = boundary
+    if api:
+        line["e2e_api"] = api
     if not args.no_cpu_baseline and world == 1:
         res = run_cpu_arm(shape, radius, 3, 1)
         line["cpu_baseline"] = {"value": res["voxels_per_sec"], "unit": "voxels/s", "cores": res["cores"], "kind": "port",

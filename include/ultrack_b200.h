@@ -204,6 +204,12 @@ ULK_API int ulk_frame_blobs_to_host(const ulk_frame_nodes *nodes, const uint8_t 
 ULK_API int ulk_labels_to_contours(const int32_t *labels, int32_t n_sets, const int64_t shape[3],
                            uint8_t *foreground, float *contours, void *stream);
 
+/* the `sigma` branch of labels_to_contours (utils/edge.py:89-91), in place on a device float32
+ * [D,H,W] volume: scipy.ndimage.gaussian_filter(contours, sigma) (reflect boundary, window radius
+ * int(4 sigma + 0.5), float64 taps, float32 result per axis) then division by the global maximum.
+ * sigma: z, y, x (z ignored when D == 1). */
+ULK_API int ulk_smooth_contours(float *contours, const int64_t shape[3], const double sigma[3], void *stream);
+
 /* add_flow (imgproc/flow.py:639-751), the per-timepoint kernel: for every node of `nodes` the
  * vector field sampled at its centroid mapped into field coordinates (round half to even of
  * centroid * (field_dim - 1) / (image_dim - 1), clipped: flow.py:716-720), scaled to voxels

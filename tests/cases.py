@@ -128,3 +128,54 @@ def color_images(shape, dtype, seed=5):
                 chans.append(f.astype(dtype))
         out.append(chans)
     return out
+
+
+# ---------------------------------------------------------------------------- BASELINE.json configs
+def find_boundaries_outer(lab: np.ndarray) -> np.ndarray:
+    """skimage.segmentation.find_boundaries(lab, mode="outer") restated with scipy grey morphology
+    (skimage is not installable here): thick = dilation != erosion over the cross neighbourhood;
+    outer keeps the background side plus foreground voxels whose full 3^d neighbourhood holds two
+    different non-zero labels."""
+    nd = lab.ndim
+    cross = ndi.generate_binary_structure(nd, 1)
+    full = ndi.generate_binary_structure(nd, nd)
+    thick = ndi.grey_dilation(lab, footprint=cross) != ndi.grey_erosion(lab, footprint=cross)
+    bg = lab == 0
+    inv = lab.copy()
+    inv[bg] = np.iinfo(lab.dtype).max
+    adj = (ndi.grey_dilation(lab, footprint=full) != ndi.grey_erosion(inv, footprint=full)) & ~bg
+    return thick & (bg | adj)
+
+
+def labels_to_contours_ref(label_sets, sigma=None):
+    """utils/edge.py:78-94 for one frame, host restatement."""
+    fg = np.zeros(label_sets[0].shape, bool)
+    ct = np.zeros(label_sets[0].shape, np.float32)
+    for lb in label_sets:
+        fg |= lb > 0
+        ct += find_boundaries_outer(lb)
+    ct /= len(label_sets)
+    if sigma is not None:
+        ct = ndi.gaussian_filter(ct, sigma)
+        ct = ct / ct.max()
+    return fg, ct
+
+
+def ensemble_label_sets(labels: np.ndarray, n_sets: int = 4, seed: int = 0, merge_fraction: float = 0.1):
+    """BASELINE config 4: `n_sets` hypotheses = the base labels with independent
+    random merges (10 % of the labels take the id of their successor), so the merged contours take
+    values in {0, 1/4, 1/2, 3/4, 1}."""
+    out = []
+    n = int(labels.max())
+    for k in range(n_sets):
+        rng = np.random.default_rng(seed * 100 + k)
+        lut = np.arange(n + 1)
+        pick = rng.random(n + 1) < merge_fraction
+        pick[0] = False
+        lut[pick] = np.minimum(lut[pick] + 1, n)
+        out.append(lut[labels].astype(np.int32))
+    return out
+
+
+MOCK_CONFIG = dict(threshold=0.5, min_area=500, max_area=7500, min_frontier=0.1, ws_hierarchy="area")   # utils/data.py:35-77
+MOCK_LINK = dict(max_neighbors=10, max_distance=15.0)

@@ -117,37 +117,20 @@ def test_iou_golden(cuda_lib):
 @pytest.mark.parametrize("ndim,scale,dw,with_shift", [(2, None, 0.0, False), (3, None, 0.05, False),
                                                       (3, (2.0, 1.0, 1.0), 0.0, True), (2, None, 0.01, True)])
 def test_link_parity(cuda_lib, ndim, scale, dw, with_shift):
-    from oracle.link_oracle import link_pair
-    from tests.emu_harness import link_frames
-    from tests.test_kernel_logic_emu import _nodes_for_link
     from ultrack_b200 import synth
     shape = (160, 160) if ndim == 2 else (24, 64, 64)
     tabs = []
     for t in range(2):
         fg, ct, _ = synth.make_frame(shape, t=t, seed=11, variant="S", radius=5.0, fill=0.35, motion=2.0)
         tabs.append(_seg_host(cuda_lib, fg, ct, min_area=30, max_area=4000))
-    (h0, n0), (h1, n1) = tabs
     rng = np.random.default_rng(3)
-    shift = rng.normal(0, 1.5, size=(len(n1["area"]), 3)) if with_shift else None
+    shift = rng.normal(0, 1.5, size=(len(tabs[1][1]["area"]), 3)) if with_shift else None
     if shift is not None and ndim == 2:
         shift[:, 0] = 0.0
-    max_neighbors, max_distance = 2, 9.0
-    s, t, w, _ = link_frames(cuda_lib, h0, h1, max_distance=max_distance, max_neighbors=max_neighbors,
-                             distance_weight=dw, shift=shift, scale=scale)
-    src, dst = _nodes_for_link(n0, ndim, 0), _nodes_for_link(n1, ndim, 1)
-    ref, _, dist, _ = link_pair(src, dst, max_distance, max_neighbors, dw, target_shift=shift, scale=scale,
-                                return_candidates=True)
-    full = np.isfinite(dist).sum(axis=1) == 2 * max_neighbors   # k-boundary ties are KD-tree internals
-    skip = {dst[i]["id"] for i in np.nonzero(full)[0]}
-    got = {(int(a) + 1 + 1_000_000, int(b) + 1 + 2_000_000): float(x) for a, b, x in zip(s, t, w)}
-    exp = {(int(r[1]), int(r[2])): float(r[0]) for r in ref}
-    got = {k: v for k, v in got.items() if k[1] not in skip}
-    exp = {k: v for k, v in exp.items() if k[1] not in skip}
-    assert set(got) == set(exp) and len(exp) > 30
-    for k in exp:
-        assert abs(got[k] - exp[k]) <= RTOL * max(abs(exp[k]), 1e-300)
-    cuda_lib.ulk_frame_nodes_free(h0)
-    cuda_lib.ulk_frame_nodes_free(h1)
+    # only targets whose k-th and (k+1)-th nearest sources are equidistant are left out (< 5 %)
+    cases.link_and_compare(cuda_lib, tabs, ndim, 9.0, 2, dw=dw, shift=shift, scale=scale, rtol=RTOL, min_links=30)
+    for h, _ in tabs:
+        cuda_lib.ulk_frame_nodes_free(h)
 
 
 def test_labels_to_contours(cuda_lib):
@@ -405,3 +388,215 @@ def test_repeated_runs_stay_exact(cuda_lib):
             if rep % 10 == 0:
                 compare_nodes(nodes, ref, 3)
             cuda_lib.ulk_frame_nodes_free(h)
+
+
+# ---------------------------------------------------------------------------- r02: secondary callers, edge cases, named configs
+def _link_tabs_gpu(lib, ndim):
+    from ultrack_b200 import synth
+    shape = (160, 160) if ndim == 2 else (24, 64, 64)
+    tabs = []
+    for t in range(2):
+        fg, ct, _ = synth.make_frame(shape, t=t, seed=11, variant="S", radius=5.0, fill=0.35, motion=2.0)
+        tabs.append(_seg_host(lib, fg, ct, min_area=30, max_area=4000))
+    return tabs, shape
+
+
+@pytest.mark.parametrize("ndim", [2, 3])
+@pytest.mark.parametrize("positive", [False, True])
+def test_link_intersection_weight(cuda_lib, ndim, positive):
+    """weight_func = Node.intersection, edge_must_be_positive (core/match_gt.py:155-168)."""
+    tabs, _ = _link_tabs_gpu(cuda_lib, ndim)
+    n, ties = cases.link_and_compare(cuda_lib, tabs, ndim, 9.0, 2, dw=0.5, weight_func="intersection", positive=positive,
+                                     min_links=30)
+    for h, _ in tabs:
+        cuda_lib.ulk_frame_nodes_free(h)
+
+
+@pytest.mark.parametrize("ndim,dtype", [(2, np.float32), (3, np.uint16), (3, np.float64), (3, np.uint8)])
+def test_link_color_gate(cuda_lib, ndim, dtype):
+    """color_filtering_mask (core/linking/processing.py:52-104): ulk_node_stats + gated ulk_link_frames."""
+    tabs, shape = _link_tabs_gpu(cuda_lib, ndim)
+    images = cases.color_images(shape, dtype)
+    if dtype == np.uint8:
+        images = [[(c // 16).astype(np.uint8) for c in fr] for fr in cases.color_images(shape, np.uint16)]
+    n, _ = cases.link_and_compare(cuda_lib, tabs, ndim, 9.0, 2, images=images, z_score_threshold=0.8, min_links=20)
+    m, _ = cases.link_and_compare(cuda_lib, tabs, ndim, 9.0, 2, min_links=30)
+    assert n < m
+    for h, _ in tabs:
+        cuda_lib.ulk_frame_nodes_free(h)
+
+
+def test_segment_empty_frame_gpu(cuda_lib):
+    fg = np.zeros((16, 16), bool)
+    ct = np.zeros((16, 16), np.float32)
+    for seg in (_seg_host, _seg_device):
+        h, nodes = seg(cuda_lib, fg, ct, min_area=4, max_area=100)
+        assert len(nodes["area"]) == 0 and nodes["overlaps"].shape == (0, 2) and not nodes["labels"].any()
+        cuda_lib.ulk_frame_nodes_free(h)
+
+
+def test_segment_full_frame_single_component_gpu(cuda_lib):
+    rng = np.random.default_rng(0)
+    for shape in ((24, 24), (6, 20, 36)):
+        fg = np.ones(shape, bool)
+        ct = rng.random(shape).astype(np.float32)
+        assert cases.run_and_compare(cuda_lib, _seg_host, fg, ct, len(shape), min_area=10, max_area=120) > 0
+
+
+def test_region_too_small_raises_like_reference_gpu(cuda_lib):
+    """vendored/hierarchy.py:161-162."""
+    fg = np.zeros((12, 12), bool)
+    fg[2, 2:7] = True          # 1x5 crop: 5 elements < 8
+    fg[6:10, 6:10] = True
+    ct = np.zeros((12, 12), np.float32)
+    with pytest.raises(RuntimeError, match="Region too small. Size of 5 found."):
+        _seg_host(cuda_lib, fg, ct, min_area=4, max_area=100)
+
+
+def test_all_components_removed_gpu(cuda_lib):
+    """Every component below the small-object size (hierarchy.py:64-73): no nodes, all-zero labels."""
+    rng = np.random.default_rng(3)
+    fg = np.zeros((32, 61), bool)
+    for _ in range(12):
+        y, x = rng.integers(0, 30), rng.integers(0, 58)
+        fg[y:y + 2, x:x + 3] = True
+    ct = rng.random(fg.shape).astype(np.float32)
+    assert cases.run_and_compare(cuda_lib, _seg_host, fg, ct, 2, min_area=100, max_area=1000, min_area_factor=1.0) == 0
+
+
+def test_config1_mock_timelapse(cuda_lib, tmp_path):
+    """BASELINE configs[0]: the reference's conftest timelapse (utils/test_utils.py:106-134: ONE mock
+    frame -- bool blobs, bool boundary contours, utils/data.py:15-32 -- repeated 10x at 512x512)
+    with make_config_content's parameters (utils/data.py:35-77), through segment() + link().
+    Frame parity against the oracle, then the reference's own assertions
+    (core/linking/_test/test_link_processing.py:48-63): exactly one weight-1.0 link per target,
+    at most max_neighbors links, distances below max_distance, every node linked."""
+    from oracle.segment_oracle import SegParams, segment_frame as o_seg
+    from ultrack_b200 import MainConfig, database, link, segment, synth
+    fg, ct, _ = synth.make_frame((512, 512), seed=42, variant="T", radius=12.0, fill=0.5)
+    n = cases.run_and_compare(cuda_lib, _seg_host, fg, ct, 2, **cases.MOCK_CONFIG)
+    assert n > 50
+    T = 10
+    fgs, cts = np.stack([fg] * T), np.stack([ct] * T)
+    cfg = MainConfig.model_validate({"data": {"working_dir": str(tmp_path)}, "segmentation": dict(cases.MOCK_CONFIG),
+                                     "linking": dict(cases.MOCK_LINK)})
+    segment(fgs, cts, cfg)
+    link(cfg, scale=(1, 1))
+    ref = o_seg(fg, ct, SegParams(**cases.MOCK_CONFIG), time=0)
+    with database.connect(cfg.data_config.database_path) as conn:
+        nodes = {i: (t, y, x) for i, t, y, x in conn.execute("select id, t, y, x from nodes")}
+        links = conn.execute("select source_id, target_id, weight from links").fetchall()
+    assert len(nodes) == T * len(ref["nodes"])
+    by_target = {}
+    for s_, t_, w in links:
+        by_target.setdefault(t_, []).append(w)
+        (_, ys, xs), (_, yt, xt) = nodes[s_], nodes[t_]
+        assert np.hypot(ys - yt, xs - xt) < cases.MOCK_LINK["max_distance"]
+    for t_, ws in by_target.items():
+        assert len(ws) <= cases.MOCK_LINK["max_neighbors"] and sum(w == 1.0 for w in ws) == 1
+    assert set(by_target) == {i for i, (t, _, _) in nodes.items() if t != 0}
+    assert {s_ for s_, _, _ in links} == {i for i, (t, _, _) in nodes.items() if t != T - 1}
+
+
+def test_config2_labels_2048(cuda_lib):
+    """BASELINE configs[1] slice: int labels -> labels_to_contours on the device (no host round
+    trip) -> segment (area hierarchy) -> link with max_neighbors=5, 2048x2048, two frames, against
+    the oracle on the restated contours."""
+    import torch
+    from ultrack_b200 import labels_to_contours, synth
+    from ultrack_b200.capi import seg_params
+    from ultrack_b200.segment import segment_frame_device
+    from ultrack_b200 import _lib
+    labs = np.stack([synth.make_frame((2048, 2048), t=t, seed=3, variant="T", radius=12.0, motion=3.0)[2] for t in range(2)])
+    fg_d, ct_d = labels_to_contours(labs.astype(np.int32), device=True)
+    assert fg_d.is_cuda and ct_d.is_cuda and fg_d.dtype == torch.bool and ct_d.dtype == torch.float32
+    kw = dict(threshold=0.5, min_area=100, max_area=10000)
+    tabs = []
+    for t in range(2):
+        efg, ect = cases.labels_to_contours_ref([labs[t].astype(np.int32)])
+        assert np.array_equal(fg_d[t].cpu().numpy(), efg) and np.array_equal(ct_d[t].cpu().numpy(), ect)
+        n = cases.run_and_compare(cuda_lib, lambda lib, f, c, **k: _from_device(lib, fg_d[t], ct_d[t], **k), efg, ect, 2, **kw)
+        assert n > 1000
+        h = segment_frame_device(cuda_lib, fg_d[t], ct_d[t], seg_params(fg_dtype=bool, **kw))
+        tabs.append((h, _lib.nodes_to_host(cuda_lib, h)))
+    n, ties = cases.link_and_compare(cuda_lib, tabs, 2, 15.0, 5, min_links=1000)
+    for h, _ in tabs:
+        cuda_lib.ulk_frame_nodes_free(h)
+
+
+def _from_device(lib, f, c, **kw):
+    from ultrack_b200 import _lib
+    from ultrack_b200.capi import seg_params
+    from ultrack_b200.segment import segment_frame_device
+    h = segment_frame_device(lib, f, c, seg_params(fg_dtype=bool, **kw), keep_labels=True)
+    return h, _lib.nodes_to_host(lib, h, with_labels=True)
+
+
+@pytest.mark.parametrize("sigma", [None, 1.0])
+def test_config4_ensemble_crop(cuda_lib, sigma):
+    """BASELINE configs[3] crop: 4 label hypotheses -> contours in quarters (labels_to_contours),
+    dynamics hierarchy + frontier filter, 32x128x128, against the oracle."""
+    from ultrack_b200 import labels_to_contours, synth
+    base = synth.make_frame((32, 128, 128), seed=9, variant="T", radius=7.0)[2]
+    sets = cases.ensemble_label_sets(base, 4, seed=1)
+    fg, ct = labels_to_contours([s_[None] for s_ in sets], sigma=sigma)
+    efg, ect = cases.labels_to_contours_ref(sets, sigma)
+    assert np.array_equal(fg[0], efg)
+    if sigma is None:
+        assert np.array_equal(ct[0], ect) and set(np.unique(ct[0])) <= {0.0, 0.25, 0.5, 0.75, 1.0}
+    else:
+        assert np.allclose(ct[0], ect, rtol=1e-5, atol=1e-7)
+    n = cases.run_and_compare(cuda_lib, _seg_host, fg[0], ct[0], 3, min_area=100, max_area=5000, ws_hierarchy="dynamics",
+                              min_frontier=0.25)
+    assert n > 20
+
+
+def test_bulk_blob_writer_gpu(cuda_lib):
+    """ulk_frame_blobs_to_host on the device == the node table, field by field, after unpickling."""
+    from ultrack_b200 import _lib, synth
+    from ultrack_b200.node import frame_blobs, loads_node
+    for shape in ((96, 96), (16, 48, 48)):
+        nd = len(shape)
+        fg, ct, _ = synth.make_frame(shape, seed=4, variant="S", radius=5.0, fill=0.4)
+        h, nodes = _seg_host(cuda_lib, fg, ct, min_area=40, max_area=900)
+        buf, off = frame_blobs(cuda_lib, h, nodes, 2, nd, 3_000_000)
+        lo = 3 - nd
+        assert len(nodes["area"]) > 10
+        for i in range(len(nodes["area"])):
+            node = loads_node(bytes(buf[off[i]:off[i + 1]]))
+            bb = nodes["bbox"][i].astype(np.int64)
+            assert np.array_equal(node.bbox, np.concatenate([bb[lo:3], bb[3 + lo:]])) and node.bbox.dtype == np.int64
+            assert np.array_equal(node.mask, _lib.unpack_mask(nodes, i, nd)) and node.mask.dtype == bool
+            assert np.array_equal(node.centroid, nodes["centroid"][i][lo:])
+            assert (node.id, node.time, node.area, node._h_node_index) == (3_000_000 + i + 1, 2, nodes["area"][i], nodes["hidx"][i])
+            assert node.frontier == nodes["frontier"][i] and node.height == nodes["height"][i] and node._parent is None
+        cuda_lib.ulk_frame_nodes_free(h)
+
+
+def test_api_with_images_and_properties_gpu(cuda_lib, tmp_path):
+    """segment(images=, properties=) + link(images=) through the public API on the GPU."""
+    import pickle
+    from ultrack_b200 import MainConfig, database, link, segment, synth
+    from ultrack_b200.node import loads_node
+    cfg = MainConfig.model_validate({"data": {"working_dir": str(tmp_path)},
+                                     "segmentation": {"min_area": 60, "max_area": 2000},
+                                     "linking": {"max_distance": 10, "max_neighbors": 3, "z_score_threshold": 1.0}})
+    shape, T = (12, 48, 48), 3
+    fg, ct = synth.make_timelapse(shape, T, seed=3, variant="S", radius=5.0, motion=2.0)
+    img = np.stack([cases.color_images(shape, np.float32, seed=t)[0][0] for t in range(T)])
+    segment(fg, ct, cfg, images=img, properties=["area", "centroid", "intensity_mean", "intensity_std"])
+    link(cfg)
+    with database.connect(cfg.data_config.database_path) as conn:
+        n_plain = conn.execute("select count(*) from links").fetchone()[0]
+    link(cfg, images=[img], overwrite=True)
+    with database.connect(cfg.data_config.database_path) as conn:
+        n_gated = conn.execute("select count(*) from links").fetchone()[0]
+        rows = conn.execute("select t, pickle, features from nodes").fetchall()
+    assert 0 < n_gated < n_plain
+    for t, blob, feats in rows:
+        node = loads_node(blob)
+        f = pickle.loads(feats)
+        coords = np.stack(np.nonzero(node.mask), axis=1) + np.asarray(node.bbox[:3])
+        vals = img[t][tuple(coords.T)].astype(np.float64)
+        exp = np.concatenate([[node.area], coords.mean(axis=0), [vals.mean()], [vals.std()]]).astype(np.float32)
+        assert np.allclose(f, exp, rtol=1e-5, atol=1e-6)

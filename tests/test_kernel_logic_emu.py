@@ -166,3 +166,23 @@ def test_link_empty_side():
     assert len(s) == 0
     lib.ulk_frame_nodes_free(h0)
     lib.ulk_frame_nodes_free(h1)
+
+
+@pytest.mark.parametrize("shape,sigma", [((40, 36), 1.5), ((9, 20, 24), (0.5, 1.0, 2.0)), ((6, 18, 18), 3.0)])
+def test_smooth_contours_matches_scipy(shape, sigma):
+    """ulk_smooth_contours == scipy.ndimage.gaussian_filter + max-normalise (utils/edge.py:89-91)."""
+    import ctypes as C
+    import scipy.ndimage as ndi
+    from ultrack_b200 import _lib
+    from ultrack_b200.edge import _sigma3
+    lib = emu_lib()
+    rng = np.random.default_rng(0)
+    ct = (rng.random(shape) > 0.8).astype(np.float32) * rng.choice([0.25, 0.5, 0.75, 1.0], size=shape).astype(np.float32)
+    exp = ndi.gaussian_filter(ct, sigma)
+    exp = exp / exp.max()
+    got = np.ascontiguousarray(ct.copy())
+    shape3 = shape if len(shape) == 3 else (1,) + shape
+    _lib.check(lib, lib.ulk_smooth_contours(got.ctypes.data_as(C.c_void_p), (C.c_int64 * 3)(*shape3),
+                                            (C.c_double * 3)(*_sigma3(sigma, len(shape))), None))
+    assert np.allclose(got, exp, rtol=1e-5, atol=1e-7)
+    assert np.abs(got - exp).max() <= 2e-7

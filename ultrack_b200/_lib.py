@@ -74,7 +74,7 @@ EXPORTS = [
     "ulk_profile_enable", "ulk_profile_reset", "ulk_profile_report", "ulk_segment_frame",
     "ulk_segment_frame_host", "ulk_frame_nodes_free", "ulk_frame_nodes_to_host",
     "ulk_frame_nodes_from_host", "ulk_frame_nodes_to_device", "ulk_frame_nodes_from_device", "ulk_link_frames", "ulk_links_to_host", "ulk_links_free",
-    "ulk_labels_to_contours", "ulk_node_shifts", "ulk_synth_frame", "ulk_node_stats", "ulk_frame_blobs_to_host",
+    "ulk_labels_to_contours", "ulk_node_shifts", "ulk_synth_frame", "ulk_node_stats", "ulk_frame_blobs_to_host", "ulk_smooth_contours",
     "ulk_upload_begin", "ulk_segment_frame_uploaded", "ulk_upload_free",
 ]
 
@@ -109,6 +109,7 @@ def bind(lib: C.CDLL) -> C.CDLL:
     lib.ulk_link_frames.argtypes = [PF, PF, vp, C.POINTER(LinkParams), vp, C.POINTER(PL)]
     lib.ulk_links_to_host.argtypes = [PL, vp, vp, vp, vp]
     lib.ulk_frame_blobs_to_host.argtypes = [PF, vp, vp, C.POINTER(BlobSpec), i64, i32, vp, vp, vp]
+    lib.ulk_smooth_contours.argtypes = [vp, C.POINTER(i64), C.POINTER(dbl), vp]
     lib.ulk_node_stats.argtypes = [PF, vp, C.c_int, i32, i32, vp, vp, vp, vp, vp, vp]
     lib.ulk_links_free.argtypes = [PL]
     lib.ulk_links_free.restype = None
@@ -172,15 +173,18 @@ def dtype_code(dt) -> int:
     return DTYPE_CODES[dt]
 
 
-def nodes_to_host(lib: C.CDLL, handle, stream: int = 0, with_labels: bool = False) -> Dict[str, np.ndarray]:
-    """Copies a device node table into numpy arrays."""
+def nodes_to_host(lib: C.CDLL, handle, stream: int = 0, with_labels: bool = False,
+                  with_masks: bool = True) -> Dict[str, np.ndarray]:
+    """Copies a device node table into numpy arrays (`with_masks=False`: everything but the
+    bit-packed masks, which `segment()` does not need on the host -- the blobs are written by
+    `ulk_frame_blobs_to_host`)."""
     f = handle.contents
     n, m = int(f.n_nodes), int(f.n_overlaps)
     out = dict(
         bbox=np.zeros((n, 6), np.int32), centroid=np.zeros((n, 3), np.int32), area=np.zeros(n, np.int32),
         frontier=np.zeros(n, np.float64), height=np.zeros(n, np.float64), hier_id=np.zeros(n, np.int32),
         parent=np.zeros(n, np.int32), hidx=np.zeros(n, np.int32), mask_off=np.zeros(n + 1, np.int64),
-        mask=np.zeros(int(f.mask_words), np.uint32), overlaps=np.zeros((m, 2), np.int32),
+        mask=np.zeros(int(f.mask_words) if with_masks else 0, np.uint32), overlaps=np.zeros((m, 2), np.int32),
     )
     labels = None
     if with_labels and f.labels:
@@ -188,7 +192,7 @@ def nodes_to_host(lib: C.CDLL, handle, stream: int = 0, with_labels: bool = Fals
     p = lambda a: a.ctypes.data_as(C.c_void_p) if a is not None else None  # noqa: E731
     check(lib, lib.ulk_frame_nodes_to_host(
         handle, p(out["bbox"]), p(out["centroid"]), p(out["area"]), p(out["frontier"]), p(out["height"]),
-        p(out["hier_id"]), p(out["parent"]), p(out["hidx"]), p(out["mask_off"]), p(out["mask"]),
+        p(out["hier_id"]), p(out["parent"]), p(out["hidx"]), p(out["mask_off"]), p(out["mask"]) if with_masks else None,
         p(out["overlaps"]), p(labels), C.c_void_p(stream)))
     out["n_hier"] = int(f.n_hier)
     out["shape"] = tuple(int(s) for s in f.shape)

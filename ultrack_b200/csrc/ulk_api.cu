@@ -336,6 +336,14 @@ int ulk_labels_to_contours(const int32_t *labels, int32_t n_sets, const int64_t 
     return ulk_labels_to_contours_impl(st, labels, n_sets, shape, foreground, contours);
 }
 
+int ulk_smooth_contours(float *contours, const int64_t shape[3], const double sigma[3], void *stream)
+{
+    if (!contours || !shape || !sigma) ULK_FAIL(-1, "null argument");
+    ulk_stream_t st = (ulk_stream_t)stream;
+    ulk_set_alloc_stream(st);
+    return ulk_smooth_contours_impl(st, contours, shape, sigma);
+}
+
 int ulk_node_shifts(const ulk_frame_nodes *nodes, const void *field, int field_dtype, int32_t n_vec,
                     const int64_t field_shape[3], double *shift_host, void *stream)
 {

@@ -69,6 +69,82 @@ int ulk_labels_to_contours_impl(ulk_stream_t st, const int32_t *labels, int32_t 
     return ulk_sync(st);
 }
 
+// ------------------------------------------------------------------ contour smoothing
+// utils/edge.py:89-91: contours = ndi.gaussian_filter(contours, sigma); contours /= contours.max().
+// scipy semantics: per axis (0 first), 1-D correlation with the normalised Gaussian window of
+// radius int(4 * sigma + 0.5), boundary mode "reflect" (d c b a | a b c d | d c b a), taps
+// accumulated in float64 and every axis pass rounded to the array's float32.
+struct K_Gauss1D {
+    const float *in; float *out; const double *w; i32 r; UlkDims dm; int axis;   // axis: 0 = x, 1 = y, 2 = z
+    ULK_D void operator()(i64 vv) const
+    {
+        i32 z, y, x;
+        dm.coords((i32)vv, z, y, x);
+        const i32 n = axis == 0 ? dm.W : (axis == 1 ? dm.H : dm.D);
+        const i32 c = axis == 0 ? x : (axis == 1 ? y : z);
+        const i64 st = dm.stride(axis);
+        const float *base = in + (vv - (i64)c * st);
+        auto at = [&](i32 k) {
+            // "reflect": period 2n, mirrored about the half-sample beyond each edge
+            i32 p = k % (2 * n);
+            if (p < 0) p += 2 * n;
+            if (p >= n) p = 2 * n - 1 - p;
+            return (double)base[(i64)p * st];
+        };
+        double acc = at(c) * w[r];
+        for (i32 j = r; j >= 1; --j) acc += (at(c - j) + at(c + j)) * w[r - j];     // scipy's order: outermost pair first
+        out[vv] = (float)acc;
+    }
+};
+struct K_MaxF32 {
+    const float *p; u32 *mx;
+    ULK_D void operator()(i64 i) const
+    {
+        const float v = p[i];
+        if (v > 0.0f) { u32 b; memcpy(&b, &v, 4); if (b > *mx) ulk_atomic_max(mx, b); }
+    }
+};
+struct K_DivF32 { float *p; float d; ULK_D void operator()(i64 i) const { p[i] = p[i] / d; } };
+
+int ulk_smooth_contours_impl(ulk_stream_t st, float *contours, const int64_t shape[3], const double sigma[3])
+{
+    UlkDims dm;
+    dm.init(shape[0], shape[1], shape[2]);
+    UlkArena A;
+    float *tmp = A.get<float>(dm.V);
+    u32 *mx = A.get<u32>(1);
+    if (A.failed) ULK_FAIL(-3, "device allocation failed");
+    float *src = contours, *dst = tmp;
+    for (int ax = 2; ax >= 0; --ax) {          // scipy filters axis 0 (z) first
+        const double sg = sigma[2 - ax];
+        const i64 n = ax == 0 ? dm.W : (ax == 1 ? dm.H : dm.D);
+        if (!(sg > 0.0) || n <= 1) continue;    // 2-D frames carry a unit z axis
+        const i32 r = (i32)(4.0 * sg + 0.5);
+        std::vector<double> w((size_t)(2 * r + 1));
+        double sum = 0.0;
+        for (i32 k = -r; k <= r; ++k) { w[(size_t)(k + r)] = exp(-0.5 / (sg * sg) * (double)k * (double)k); sum += w[(size_t)(k + r)]; }
+        for (double &v : w) v /= sum;
+        double *dw = A.get<double>(2 * r + 1);
+        if (A.failed) ULK_FAIL(-3, "device allocation failed");
+        int rc = ulk_h2d(dw, w.data(), w.size() * sizeof(double), st);
+        if (rc) return rc;
+        ulk_launch(dm.V, st, K_Gauss1D{src, dst, dw, r, dm, ax});
+        float *t = src; src = dst; dst = t;
+    }
+    if (src != contours) { int rc = ulk_d2d(contours, src, (size_t)dm.V * 4, st); if (rc) return rc; }
+    int rc = ulk_memset(mx, 0, 4, st);
+    if (rc) return rc;
+    ulk_launch(dm.V, st, K_MaxF32{contours, mx});
+    u32 hb = 0;
+    rc = ulk_read(&hb, mx, 1, st);
+    if (rc) return rc;
+    float m;
+    memcpy(&m, &hb, 4);
+    // numpy divides by max() whatever it is (0 -> nan); keep that behaviour
+    ulk_launch(dm.V, st, K_DivF32{contours, m});
+    return ulk_sync(st);
+}
+
 // ------------------------------------------------------------------ synthetic frames
 ULK_HD ULK_INLINE u64 synth_mix(u64 x, u64 k)
 {

@@ -19,6 +19,7 @@ int ulk_node_shifts_impl(ulk_stream_t st, const ulk_frame_nodes *nodes, const vo
                          const int64_t field_shape[3], double *shift_host);
 int ulk_labels_to_contours_impl(ulk_stream_t st, const int32_t *labels, int32_t n_sets, const int64_t shape[3],
                                 uint8_t *foreground, float *contours);
+int ulk_smooth_contours_impl(ulk_stream_t st, float *contours, const int64_t shape[3], const double sigma[3]);
 int ulk_synth_frame_impl(ulk_stream_t st, const int64_t shape[3], int32_t t, uint64_t seed, double radius,
                          double fill, double motion, double noise, float *fg, float *ct);
 const char *ulk_error_cstr();

@@ -14,6 +14,7 @@ import logging
 import os
 import pickle
 import sqlite3
+import time as _time
 import warnings
 from typing import Dict, List, Optional
 
@@ -56,6 +57,9 @@ def check_array_chunk(array) -> None:
         if chunk_shape[0] != 1:
             warnings.warn(f"Array not chunked over time dimension. Found chunk of shape {array.chunks}."
                           "Performance will be slower.")
+
+
+_now = _time.perf_counter
 
 
 def _generate_id(index, time: int, max_segments: int):
@@ -228,14 +232,23 @@ def _stage(time: int, foreground, contours, config, lib):
     return (lambda: up.segment(prm)), fg.ndim
 
 
+# wall-clock split of _process, accumulated per process (bench.py's `e2e_api` leg reads it)
+TIMERS: Dict[str, float] = {"kernels": 0.0, "d2h": 0.0, "rows": 0.0, "sql": 0.0}
+
+
 def _process(time: int, staged, db_path: str, max_segments_per_time: int,
              catch_duplicates_expection: bool, lib, images=None, properties: Optional[List[str]] = None) -> None:
     """processing.py:160-340 for one timepoint (`staged` comes from `_stage`)."""
     run, ndim = staged
+    t0 = _now()
     handle = run()
+    t1 = _now()
+    TIMERS["kernels"] += t1 - t0
     LOG.info(f"Computing nodes of time {time}")
     try:
-        nodes = _lib.nodes_to_host(lib, handle)
+        nodes = _lib.nodes_to_host(lib, handle, with_masks=False)
+        t2 = _now()
+        TIMERS["d2h"] += t2 - t1
         feats = None
         if properties is not None:
             from ultrack_b200 import features
@@ -244,12 +257,15 @@ def _process(time: int, staged, db_path: str, max_segments_per_time: int,
                 frame = np.asarray(frame)
             feats = features.frame_features(lib, handle, nodes, ndim, frame, properties)
         ids, rows, overlaps = frame_rows(nodes, time, ndim, max_segments_per_time, feats, lib, handle)
+        t3 = _now()
+        TIMERS["rows"] += t3 - t2
     except Exception:
         lib.ulk_frame_nodes_free(handle)
         raise
     frames.STORE.put(db_path, time, frames.DeviceFrame(lib, handle, ids, ndim))
     try:
         database.insert_nodes(db_path, rows, overlaps)
+        TIMERS["sql"] += _now() - t3
     except sqlite3.IntegrityError as e:
         frames.STORE.drop(db_path, time)
         if catch_duplicates_expection:
