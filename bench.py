@@ -237,7 +237,7 @@ def run_api_leg(lib, torch, dist, rank, world, local_rank, frames_per_rank: int 
 
     import ultrack_b200
     from ultrack_b200 import frames as frames_mod
-    from ultrack_b200 import segment as seg_mod
+    seg_mod = sys.modules["ultrack_b200.segment"]      # the module (the package re-exports the function under this name)
     shape, radius, _ = WORKLOADS["c3"]
     T = frames_per_rank * world
     dev = torch.device("cuda", local_rank)
@@ -575,7 +575,7 @@ def main():
                     _lib.check(lib, lib.ulk_segment_frame_uploaded(up, C.byref(prm_), 0, sp, C.byref(h)))
                     links = lnk(prev, h)
                     n_links = int(links.contents.n_links)
-                    nodes = _lib.nodes_to_host(lib, h, stream.cuda_stream)
+                    nodes = _lib.nodes_to_host(lib, h, stream.cuda_stream, pinned=True)
                     s = np.zeros(n_links, np.int32); t = np.zeros(n_links, np.int32); w = np.zeros(n_links, np.float64)
                     p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
                     _lib.check(lib, lib.ulk_links_to_host(links, p(s), p(t), p(w), sp))

@@ -173,18 +173,36 @@ def dtype_code(dt) -> int:
     return DTYPE_CODES[dt]
 
 
+_PINNED: Dict[str, "np.ndarray"] = {}
+
+
+def _host_array(key: str, shape, dtype, pinned: bool) -> np.ndarray:
+    """Output buffer of `nodes_to_host`: fresh numpy memory, or (pinned=True) a view of a cached
+    page-locked buffer that is reused by the next call -- copies then run at PCIe speed."""
+    if not pinned:
+        return np.zeros(shape, dtype)
+    import torch
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    buf = _PINNED.get(key)
+    if buf is None or buf.nbytes < n:
+        buf = torch.empty(max(n + n // 4, 4096), dtype=torch.uint8, pin_memory=True).numpy()
+        _PINNED[key] = buf
+    return buf[:n].view(dtype).reshape(shape)
+
+
 def nodes_to_host(lib: C.CDLL, handle, stream: int = 0, with_labels: bool = False,
-                  with_masks: bool = True) -> Dict[str, np.ndarray]:
+                  with_masks: bool = True, pinned: bool = False) -> Dict[str, np.ndarray]:
     """Copies a device node table into numpy arrays (`with_masks=False`: everything but the
     bit-packed masks, which `segment()` does not need on the host -- the blobs are written by
     `ulk_frame_blobs_to_host`)."""
     f = handle.contents
     n, m = int(f.n_nodes), int(f.n_overlaps)
+    z = lambda key, shape, dt: _host_array(key, shape, dt, pinned)  # noqa: E731
     out = dict(
-        bbox=np.zeros((n, 6), np.int32), centroid=np.zeros((n, 3), np.int32), area=np.zeros(n, np.int32),
-        frontier=np.zeros(n, np.float64), height=np.zeros(n, np.float64), hier_id=np.zeros(n, np.int32),
-        parent=np.zeros(n, np.int32), hidx=np.zeros(n, np.int32), mask_off=np.zeros(n + 1, np.int64),
-        mask=np.zeros(int(f.mask_words) if with_masks else 0, np.uint32), overlaps=np.zeros((m, 2), np.int32),
+        bbox=z("bbox", (n, 6), np.int32), centroid=z("centroid", (n, 3), np.int32), area=z("area", (n,), np.int32),
+        frontier=z("frontier", (n,), np.float64), height=z("height", (n,), np.float64), hier_id=z("hier_id", (n,), np.int32),
+        parent=z("parent", (n,), np.int32), hidx=z("hidx", (n,), np.int32), mask_off=z("mask_off", (n + 1,), np.int64),
+        mask=z("mask", (int(f.mask_words) if with_masks else 0,), np.uint32), overlaps=z("overlaps", (m, 2), np.int32),
     )
     labels = None
     if with_labels and f.labels:

