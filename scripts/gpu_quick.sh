@@ -1,0 +1,13 @@
+#!/bin/bash
+# quick loop: parity tests (fail fast) + short C5 bench
+mkdir -p gpurun_out
+timeout 1800 python -m pytest tests -m gpu -q -x --timeout 900 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"
+tail -3 gpurun_out/pytest_gpu.log
+python bench.py --workload c5 --steps 8 --warmup 3 --no-cpu-baseline --no-e2e --no-api > gpurun_out/bench_quick.json 2>gpurun_out/bench_quick.err; echo "bench rc=$?"
+python - <<'PY'
+import json
+d=json.load(open('gpurun_out/bench_quick.json'))
+print('ms/step',round(d['ms_per_step'],3),'kernel ms',round(d['pipeline_roofline']['kernel_time_ms_per_step'],3),'launches',d['gpu_launches'])
+t=d['pipeline_roofline']['top_kernels_ms_per_step']
+print({k:v for k,v in list(t.items())[:22]})
+PY

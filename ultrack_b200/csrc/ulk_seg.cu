@@ -10,6 +10,7 @@
 #include "ulk_seg.h"
 #include "ulk_hier.h"
 #include "ulk_voxel.h"
+#include "ulk_front.h"
 #include <cmath>
 
 #define CHK(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
@@ -313,7 +314,7 @@ static int threshold_words(ulk_stream_t st, const UlkDims &dm, const void *fg, i
     if (vec4) {
         const u32 T = (u32)((dm.W + 127) / 128);
         const i64 nt4 = (i64)dm.D * dm.H * T;
-        static const int U4 = getenv("ULK_THR_U") ? atoi(getenv("ULK_THR_U")) : 4;
+        static const int U4 = getenv("ULK_THR_U") ? atoi(getenv("ULK_THR_U")) : 2;     // measured: 1.06 ms (U=2), 1.32 (4), 1.91 (8) at C5
         const i64 warps = (nt4 + U4 - 1) / U4;
         const unsigned grid = (unsigned)((warps + 7) / 8);
 #define ULK_THR_LAUNCH(UU, LL) ulk_threshold_kernel_v4<UU, LL><<<grid, 256, 0, st>>>(fg, thr, dm.W, (u32)S, T, (u32)nt4, words)
@@ -369,15 +370,17 @@ struct VoxelStage {
 
 // One watershed-collapse pass over a list of foreground voxels: `rl` holds the ranks of the
 // list (nullptr: every foreground voxel), m its length; every array is indexed by rank.
+// The steepest edges (mw, pk, po) come in precomputed in COMPONENT space by the front end; `redo`
+// lists the ranks whose region is smaller than their component (voxels of oversegmented
+// components in pass B): K_MinEdge runs again on those only, with the region labels.
 static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkFg &fg, const i32 *rl, i64 m, const UlkCt &ct, const i32 *lab,
                        i32 R, bool need_join, bool need_k3, bool need_stats, int fix_shift,
+                       u32 *mw, u32 *pk, i32 *po, const i32 *redo, i64 nredo,
                        VoxelStage &out, ulk_seg_stats *stats)
 {
     const double fixscale = ldexp(1.0, fix_shift);
     const UlkDims &dm = fg.dm;
     const i64 n = fg.n;
-    u32 *mw = A.get<u32>(n), *pk = A.get<u32>(n);
-    i32 *po = A.get<i32>(n);
     i32 *bp = A.get<i32>(n);
     u8 *state = A.get<u8>(n + 4);
     u32 *Lr = A.get<u32>(n), *best = A.get<u32>(n);
@@ -389,7 +392,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkFg &fg, const i32 
     CHKA(A);
     CHK(ulk_memset(fmark, 0, (size_t)n + 8, st));
     CHK(ulk_memset(ctr, 0, 8 * sizeof(i32), st));
-    ulk_launch_rkx<1>("MinEdge", rl, fg.fgl, m, dm, st, K_MinEdge{lab, ct, fg, mw, pk, po});
+    if (nredo > 0) ulk_launch_rkx<1>("MinEdge", redo, fg.fgl, nredo, dm, st, K_MinEdge{lab, ct, fg, mw, pk, po});
     ulk_launch_rkn<4>(rl, m, st, K_Hook1{mw, po, bp, state, Lr, best, ctr + 4});
     ulk_launch_rk_multi(rl, m, st, K_CompressCand{bp, mw, Lr, state, cand, ctr + 0, groots, ctr + 1, sroots, ctr + 6});
     i32 hc[8];
@@ -486,7 +489,6 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkFg &fg, const i32 
         }
         A.release(hp);
     }
-    A.release(po);
 
     // ---- region adjacency graph (hash of basin pairs)
     u64 cap = 1024;
@@ -606,7 +608,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkFg &fg, const i32 
         A.release(Tk);
         A.release(nroot);
     }
-    A.release(pk); A.release(state); A.release(Lr); A.release(best); A.release(fmark);
+    A.release(state); A.release(Lr); A.release(best); A.release(fmark);
     A.release(bp);
     if (stats) { stats->n_basins += B; stats->n_rag_edges += Eg; }
     return 0;
@@ -695,20 +697,28 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
     stats_local.n_foreground = nfg;
     F->fix_shift = ulk_fix_shift_for(0);
     if (nfg == 0) { F->n_nodes = 0; F->stats = stats_local; return empty_labels(st, F, V, keep_labels); }
-    // ---- rank space: the foreground list, its contour values, the component forest
+    // ---- rank space: the foreground list, its contour values, the component forest, and the
+    //      steepest edge of every voxel in component space (front end, ulk_front.cu)
     i32 *fgl = A.get<i32>(nfg);
     i32 *P = A.get<i32>(nfg);
     i32 *cnt = A.get<i32>(nfg);          // sizes at the roots, later the component code at the roots
+    u32 *mw = A.get<u32>(nfg), *pk = A.get<u32>(nfg);
+    i32 *po = A.get<i32>(nfg);
     UlkCt ct;
     ct.f = nullptr; ct.d = nullptr;
     float *ctf = nullptr; double *ctd = nullptr;
     if (ulk_ct_is_f32(ct_dtype)) { ctf = A.get<float>(nfg); ct.f = ctf; }
     else { ctd = A.get<double>(nfg); ct.d = ctd; }
     CHKA(A);
-    expand_words(st, K_Expand{words, off, dm, SG, ctp, ct_dtype, ow, fgl, ctf, ctd, P, cmax}, nt);
-    A.release(words); A.release(off);
     UlkFg fg;
     fg.ow = ow; fg.fgl = fgl; fg.n = nfg; fg.S = SG; fg.SH = SG * dm.H; fg.dm = dm;
+    if (ulk_front_tile_supported(ctp, ct_dtype, dm)) {
+        CHK(ulk_front_tile(st, ctp, ct_dtype, dm, SG, words, off, ow, fgl, ctf, P, mw, pk, po, cmax));
+    } else {
+        expand_words(st, K_Expand{words, off, dm, SG, ctp, ct_dtype, ow, fgl, ctf, ctd, P, cmax}, nt);
+        ulk_launch_rkx<1>("MinEdge", nullptr, fgl, nfg, dm, st, K_MinEdge{nullptr, ct, fg, mw, pk, po});
+    }
+    A.release(words); A.release(off);
     // ---- connected components (4/6-connected): union of runs, flatten + sizes + root list
     UlkFastDiv fS, fH;
     fS.init((u32)SG); fH.init((u32)dm.H);
@@ -753,8 +763,10 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
 
     // ---- region labels: components, oversegmented where area > max_area
     i32 R = n_cc;
+    i32 *rlA = nullptr;
+    i32 nA = 0;
     if (n_big == 0) {
-        ulk_launch_rkn<4>(nullptr, nfg, st, K_LabelCc{code, cc_big, 0, lab2, nullptr, nullptr});
+        ulk_launch_rkn<4>(nullptr, nfg, st, K_LabelCc{code, cc_big, 0, lab2, nullptr, nullptr, po});
     } else {
         UlkArena AA;
         // the labels of the oversegmentation pass live in place too: > 0 on the components above
@@ -763,20 +775,19 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
         // pass A only ever touches the voxels of the components above max_area: its kernels run
         // on that sub-list of ranks, collected while the labels are written (chunks of up to 32
         // raster-ordered voxels in arbitrary order: order only matters for coalescing)
-        i32 *rlA = AA.get<i32>(nfg);
+        rlA = A.get<i32>(nfg);           // kept for pass B: its steepest edges are recomputed with the region labels
         i32 *nA_dev = AA.get<i32>(1);
-        CHKA(AA);
+        CHKA(AA); CHKA(A);
         CHK(ulk_memset(nA_dev, 0, sizeof(i32), st));
 #ifdef ULK_EMU
-        ulk_launch_rkn<4>(nullptr, nfg, st, K_LabelCc{code, cc_big, 1, labA, rlA, nA_dev});
+        ulk_launch_rkn<4>(nullptr, nfg, st, K_LabelCc{code, cc_big, 1, labA, rlA, nA_dev, po});
 #else
-        ulk_launch_rk_multi(nullptr, nfg, st, K_LabelCc{code, cc_big, 1, labA, rlA, nA_dev});
+        ulk_launch_rk_multi(nullptr, nfg, st, K_LabelCc{code, cc_big, 1, labA, rlA, nA_dev, po});
 #endif
-        i32 nA = 0;
         CHK(ulk_read(&nA, nA_dev, 1, st));
         stats_local.pass_a_voxels = nA;
         VoxelStage va;
-        CHK(voxel_stage(st, AA, fg, rlA, nA, ct, labA, n_big, true, false, false, fix_shift, va, &stats_local));
+        CHK(voxel_stage(st, AA, fg, rlA, nA, ct, labA, n_big, true, false, false, fix_shift, mw, pk, po, nullptr, 0, va, &stats_local));
         UlkHierScratch S;
         CHK(alloc_scratch(AA, va.B, va.Eg, S));
         UlkBasins Bv{va.b_size, va.g_L, va.b_top, nullptr, nullptr, nullptr, nullptr};
@@ -802,7 +813,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
         ulk_launch(nrec, st, K_Gather<u32>{rec_cc, perm0, c0});
         CHK(ulk_sort_pairs_u32(c0, c1, perm0, perm1, nrec, st));              // then by component
         ulk_launch(nrec, st, K_RankToLabel{perm1, c1, label_of_rec});
-        ulk_launch_rkn<4>(nullptr, nfg, st, K_WriteLabels{n_cc, va.bas, region_of, label_of_rec, lab2});
+        ulk_launch_rkn<4>(nullptr, nfg, st, K_WriteLabels{n_cc, va.bas, region_of, label_of_rec, lab2, po});
         // number of valid records = regions
         i32 *nvalid = AA.get<i32>(nrec + 1), *nvpre = AA.get<i32>(nrec + 1);
         CHKA(AA);
@@ -825,7 +836,8 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
     const bool area_mode = prm->ws_hierarchy == 0 || prm->ws_hierarchy == 2;    // join keys: area and volume attributes
     const bool vol_mode = prm->ws_hierarchy == 2;
     VoxelStage vb;
-    CHK(voxel_stage(st, A, fg, nullptr, nfg, ct, lab2, R, area_mode, true, true, fix_shift, vb, &stats_local));
+    CHK(voxel_stage(st, A, fg, nullptr, nfg, ct, lab2, R, area_mode, true, true, fix_shift, mw, pk, po, rlA, nA, vb, &stats_local));
+    if (rlA) A.release(rlA);
     UlkHierScratch S;
     CHK(alloc_scratch(A, vb.B, vb.Eg, S));
     UlkBasins Bv{vb.b_size, vb.g_L, vb.b_top, vb.b_k3, vb.bbmin, vb.bbmax, vb.csum};

@@ -359,6 +359,7 @@ struct K_RootCode {
 struct K_LabelCc {
     const i32 *code; const i32 *cc_big; int mode; i32 *lab;
     i32 *biglist; i32 *nbig;       // mode 1: the ranks of the voxels of the components above max_area (32-entry chunks in raster order)
+    i32 *po;                       // steepest-edge endpoints: voxels of dropped components leave the graph (ULK_PO_OUT)
     struct S1 { i32 r, root; };
     struct S2 { i32 r, c; };
     ULK_D ULK_INLINE S1 load1(i32 r, bool ok) const { S1 s; s.r = r; s.root = ok ? lab[r] : -1; return s; }
@@ -367,6 +368,7 @@ struct K_LabelCc {
     {
         const i32 c = s.c;
         i32 g = -1;
+        if (c == 0) po[s.r] = ULK_PO_OUT;
         if (c >= 0) {
             if (mode == 0) lab[s.r] = c;
             else if (c == 0) lab[s.r] = -1;
@@ -401,6 +403,7 @@ struct K_LabelCc {
 #pragma unroll
         for (int u = 0; u < ULK_MULTI; ++u) {
             if (c[u] >= 0) lab[v[u]] = c[u] == 0 ? -1 : (g[u] >= 0 ? g[u] + 1 : -(c[u] - 1) - 2);
+            if (c[u] == 0) po[v[u]] = ULK_PO_OUT;
             m[u] = __ballot_sync(0xffffffffu, g[u] >= 0);
             total += __popc(m[u]);
         }
@@ -442,11 +445,12 @@ struct K_MinEdge {
         s.r = a.r; s.v = a.v; s.ok = ok; s.l = 0; s.c = 0.f;
         if (!ok) return s;
         fg.nb_ranks(a.q, a.r, a.v, a.x, s.rn);
-        s.l = lab[a.r];
+        // lab == nullptr: component space (every foreground neighbour is in the same component)
+        s.l = lab ? lab[a.r] : 1;
 #ifndef ULK_EMU
 #pragma unroll
 #endif
-        for (int i = 0; i < 6; ++i) s.ln[i] = s.rn[i] >= 0 ? lab[s.rn[i]] : 0;
+        for (int i = 0; i < 6; ++i) s.ln[i] = s.rn[i] >= 0 ? (lab ? lab[s.rn[i]] : 1) : 0;
         if (ct.f) {
             s.c = ct.f[a.r];
 #ifndef ULK_EMU
@@ -1274,7 +1278,7 @@ struct K_RankToLabel {
 // final region labels over the mode-1 component labels, in place
 struct K_WriteLabels {
     i32 ncc; const i32 *basA; const i32 *region_of; const i32 *label_of_rec;
-    i32 *lab;
+    i32 *lab; i32 *po;
     struct S1 { i32 r, l, ba; };
     struct S2 { i32 r, rec; };       // rec: index into label_of_rec, -1: label 0, -2: nothing to write
     ULK_D ULK_INLINE S1 load1(i32 r, bool ok) const
@@ -1297,7 +1301,9 @@ struct K_WriteLabels {
     ULK_D ULK_INLINE void run(const S2 &s, bool) const
     {
         if (s.rec == -2) return;
-        lab[s.r] = s.rec >= 0 ? label_of_rec[s.rec] : 0;
+        const i32 l = s.rec >= 0 ? label_of_rec[s.rec] : 0;
+        lab[s.r] = l;
+        if (l <= 0) po[s.r] = ULK_PO_OUT;
     }
 };
 struct K_ScatterLabels {    // region labels as the caller sees them (dense volume, 0 on the background: cleared before)
