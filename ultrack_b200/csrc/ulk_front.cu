@@ -25,8 +25,8 @@
 #ifndef ULK_EMU
 #include <cuda.h>
 
-#define FT_TZ 4
-#define FT_TY 16
+#define FT_TZ 8
+#define FT_TY 8
 #define FT_TX 128
 // x halo of the staged brick: 16 bytes of elements, so that the box start and the row pitch in
 // shared memory stay 16-byte aligned for every dtype (f32: 4, f16: 8, u8: 16 elements)
@@ -73,22 +73,32 @@ ulk_front_tile_kernel(const __grid_constant__ CUtensorMap tmap, const FrontArgs 
     // foreground words + rank offsets of the brick's rows and the halo rows; the brick's own
     // records also go out as the interleaved foreground map
     const i32 wx0 = x0 >> 5;
-    for (int i = tid; i < FT_ROWS * FT_WPR; i += 256) {
-        const int row = i / FT_WPR, k = i - row * FT_WPR;
-        const int lz = row / (FT_TY + 2), ly = row - lz * (FT_TY + 2);
-        const i32 z = z0 - 1 + lz, y = y0 - 1 + ly, wx = wx0 - 1 + k;
-        uint2 e = make_uint2(0u, 0u);
-        if (z >= 0 && z < D && y >= 0 && y < H && wx >= 0 && wx < S) {
-            const i64 t = ((i64)z * H + y) * S + wx;
-            e.x = a.words[t];
-            e.y = (u32)a.off[t];
-            if (lz >= 1 && lz <= FT_TZ && ly >= 1 && ly <= FT_TY && k >= 1 && k <= 4) {
+    {
+        constexpr int NIT = (FT_ROWS * FT_WPR + 255) / 256;
+        i64 tt[NIT]; u32 ww[NIT]; i32 oo[NIT]; bool own[NIT];
+        // all loads of a thread are issued before the first is used
+#pragma unroll
+        for (int u = 0; u < NIT; ++u) {
+            const int i = tid + u * 256;
+            const int row = i / FT_WPR, k = i - row * FT_WPR;
+            const int lz = row / (FT_TY + 2), ly = row - lz * (FT_TY + 2);
+            const i32 z = z0 - 1 + lz, y = y0 - 1 + ly, wx = wx0 - 1 + k;
+            const bool ok = i < FT_ROWS * FT_WPR && z >= 0 && z < D && y >= 0 && y < H && wx >= 0 && wx < S;
+            tt[u] = ok ? ((i64)z * H + y) * S + wx : -1;
+            own[u] = ok && lz >= 1 && lz <= FT_TZ && ly >= 1 && ly <= FT_TY && k >= 1 && k <= 4;
+            ww[u] = 0; oo[u] = 0;
+            if (ok) { ww[u] = a.words[tt[u]]; oo[u] = a.off[tt[u]]; }
+        }
+#pragma unroll
+        for (int u = 0; u < NIT; ++u) {
+            const int i = tid + u * 256;
+            if (i < FT_ROWS * FT_WPR) sow[i] = make_uint2(ww[u], (u32)oo[u]);
+            if (own[u]) {
                 UlkOW r;
-                r.w = e.x; r.o = (i32)e.y;
-                a.ow[t] = r;
+                r.w = ww[u]; r.o = oo[u];
+                a.ow[tt[u]] = r;
             }
         }
-        sow[i] = e;
     }
     __syncthreads();
     {   // every thread waits for the TMA bytes (phase 0)
