@@ -405,6 +405,15 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly ONE JSON line: everything libraries print on fd 1 (NCCL's version
+    # banner when a communicator comes up, ...) goes to stderr, the line is written to the real fd
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line: dict) -> None:
+        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
 
     if args.impl == "reference":
         if rank != 0:
@@ -426,7 +435,7 @@ def main():
             "cpu_baseline": cb,
             "e2e": {"value": res["voxels_per_sec"], "unit": "voxels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         }
-        print(json.dumps(line))
+        emit(line)
         return
 
     import numpy as np
@@ -719,7 +728,7 @@ def main():
                                 "links_per_sec": res["links_per_sec"],
                                 "per_core_voxels_per_sec": res["per_core_voxels_per_sec"],
                                 "reference_notebook_voxels_per_sec_per_worker": res["reference_notebook_voxels_per_sec_per_worker"]}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 

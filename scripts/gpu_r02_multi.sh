@@ -11,7 +11,7 @@ timeout 1500 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --ma
 tail -3 gpurun_out/bench_c5_n$N.err | cut -c1-300
 python - <<PY
 import json
-d=json.load(open('gpurun_out/bench_c5_n$N.json'))
+d=json.loads([l for l in open('gpurun_out/bench_c5_n$N.json') if l.startswith('{')][-1])
 print('n',d['n_gpus'],'ms/step',round(d['ms_per_step'],2),'value',d['value'])
 for k in ('e2e','e2e_u8f16','h2d_ceiling','boundary','e2e_api'): print(k, json.dumps(d.get(k))[:700])
 PY
