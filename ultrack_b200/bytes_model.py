@@ -22,6 +22,9 @@ from typing import Dict, Optional
 DENSE_BYTES_PER_VOXEL: Dict[str, float] = {
     "K_Threshold": 4 + 0.125,            # foreground in; one foreground bit out (contours are not touched here)
 }
+# the tile-resident front end reads the dense contour volume once (TMA bricks; the halo is re-read
+# from L2, not counted) and writes six rank-space arrays per foreground voxel
+FRONT_TILE = {"dense": 4 + 0.25, "fg": 6 * 4}    # contours + words / offsets in; fgl, ct, forest, mw, pk, po out
 # kernel name -> bytes per FOREGROUND voxel per launch.  Every array is rank-indexed (n_fg long);
 # an entry is what the kernel must read or write once for its own voxel.
 LIST_BYTES_PER_FG_VOXEL: Dict[str, float] = {
@@ -30,7 +33,7 @@ LIST_BYTES_PER_FG_VOXEL: Dict[str, float] = {
     "K_FlattenCount": 4 + 4,             # forest in / out
     "K_LabelCc": 4 + 4,                  # forest in, label out (in place)
     "K_WriteLabels": 4 + 4 + 4,          # label, pass-A basin in; label out
-    "K_MinEdge": 4 + 4 + 4 + 4 + 4 + 4,  # list, label, contour in; min weight, min key, other endpoint out
+    "K_MinEdge": 4 + 4 + 4 + 4 + 4 + 4,  # list, label, contour in; min weight, min key, other endpoint out (pass B: the pass-A voxels only)
     "K_Hook1": 4 + 4 + 4,                # endpoint, the endpoint's endpoint in; forest out
     "K_CompressCand": 4 + 4 + 4,         # forest in / out, weight
     "K_AssignBasin": 4 + 4 + 4,          # forest (two hops) in; basin out
@@ -52,7 +55,7 @@ def link_bytes(n_links: int, n_pairs: int, mean_mask_words: float) -> int:
 
 # list kernels of the voxel stage: launched once on the voxels of the components above max_area
 # (oversegmentation pass A) and once on the whole foreground (pass B) per frame
-TWO_PASS = {"K_MinEdge", "K_Hook1", "K_CompressCand", "K_AssignBasin", "K_BasinAccum", "K_Attach"}
+TWO_PASS = {"K_Hook1", "K_CompressCand", "K_AssignBasin", "K_BasinAccum", "K_Attach"}
 
 
 def kernel_bytes(name: str, voxels: int, n_foreground: int, pass_a_voxels: Optional[int] = None) -> Optional[float]:
@@ -61,6 +64,10 @@ def kernel_bytes(name: str, voxels: int, n_foreground: int, pass_a_voxels: Optio
     figure is the AVERAGE over the frame's two launches (pass A on `pass_a_voxels`, pass B on
     `n_foreground`), matching an average launch duration."""
     base = name.split("<")[0]
+    if base == "K_FrontTile":
+        return FRONT_TILE["dense"] * voxels + FRONT_TILE["fg"] * n_foreground
+    if base == "K_MinEdge":       # one launch per frame since the front end: the voxels of the oversegmented components
+        return LIST_BYTES_PER_FG_VOXEL[base] * (pass_a_voxels if pass_a_voxels else n_foreground)
     if base in DENSE_BYTES_PER_VOXEL:
         return DENSE_BYTES_PER_VOXEL[base] * voxels
     if base in LIST_BYTES_PER_FG_VOXEL:

@@ -793,7 +793,10 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
         UlkBasins Bv{va.b_size, va.g_L, va.b_top, nullptr, nullptr, nullptr, nullptr};
         UlkEdges Ev{va.ea, va.eb, va.wk, va.k3, va.cnt, va.shi, va.slo};
         ulk_launch(n_big, st, K_HierStage1{va.bs, va.es, Bv, Ev, S});
-        ulk_launch_rkn<4>(rlA, nA, st, K_Attach{va.bas, va.mw, va.jk, va.g_lab, va.bs, S.Ipar, S.Iwk, S.attach, nullptr, nullptr, 0.0});
+        UlkAttachInfo *ainfoA = AA.get<UlkAttachInfo>(va.B);
+        CHKA(AA);
+        ulk_launch(va.B, st, K_AttachInfo{va.g_lab, va.bs, S.Ipar, S.Iwk, ainfoA});
+        ulk_launch_rkn<4>(rlA, nA, st, K_Attach{va.bas, va.mw, va.jk, ainfoA, S.Ipar, S.Iwk, S.attach, nullptr, nullptr, 0.0});
         i32 *region_of = AA.get<i32>(va.B);
         u64 *rkey_w = AA.get<u64>(va.B), *rkey_k = AA.get<u64>(va.B);
         CHKA(AA);
@@ -843,9 +846,14 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
     UlkBasins Bv{vb.b_size, vb.g_L, vb.b_top, vb.b_k3, vb.bbmin, vb.bbmax, vb.csum};
     UlkEdges Ev{vb.ea, vb.eb, vb.wk, vb.k3, vb.cnt, vb.shi, vb.slo};
     ulk_launch(R, st, K_HierStage1{vb.bs, vb.es, Bv, Ev, S});
-    if (area_mode)
-        ulk_launch_rkn<4>(nullptr, nfg, st, K_Attach{vb.bas, vb.mw, vb.jk, vb.g_lab, vb.bs, S.Ipar, S.Iwk, S.attach,
+    if (area_mode) {
+        UlkAttachInfo *ainfo = A.get<UlkAttachInfo>(vb.B);
+        CHKA(A);
+        ulk_launch(vb.B, st, K_AttachInfo{vb.g_lab, vb.bs, S.Ipar, S.Iwk, ainfo});
+        ulk_launch_rkn<4>(nullptr, nfg, st, K_Attach{vb.bas, vb.mw, vb.jk, ainfo, S.Ipar, S.Iwk, S.attach,
                                                      vol_mode ? S.awhi : nullptr, vol_mode ? S.awlo : nullptr, ldexp(1.0, fix_shift)});
+        A.release(ainfo);
+    }
     i64 N2 = 2 * (i64)vb.B + 2;
     UlkNodeOut O;
     O.count = A.get<i32>(R + 1); O.nsurv = A.get<i32>(R + 1); O.rsize = A.get<i32>(R + 1);

@@ -927,12 +927,26 @@ struct K_PlateauRelax {
 };
 // late joiners climb the basin BPT: a voxel attaches to the highest ancestor of its basin
 // whose merge precedes its join key
+// one 16-byte record per basin: where its leaf sits in the region's tree and the first climb step
+// (parent p, its merge key and its own parent pp: most voxels stop at that first comparison)
+struct alignas(16) UlkAttachInfo { i32 o, node, p, pp; u64 pkey; u64 pad; };
+struct K_AttachInfo {
+    const i32 *b_lab; const i32 *bs; const i32 *Ipar; const u64 *Iwk; UlkAttachInfo *info;
+    ULK_D void operator()(i64 b) const
+    {
+        const i32 st = bs[b_lab[b] - 1];
+        UlkAttachInfo r;
+        r.o = 2 * st; r.node = (i32)b - st; r.p = Ipar[r.o + r.node];
+        r.pp = Ipar[r.o + r.p]; r.pkey = Iwk[r.o + r.p]; r.pad = 0;
+        info[b] = r;
+    }
+};
 struct K_Attach {
-    const i32 *bas; const u32 *mw, *jk; const i32 *b_lab; const i32 *bs;
+    const i32 *bas; const u32 *mw, *jk; const UlkAttachInfo *info;
     const i32 *Ipar; const u64 *Iwk; i32 *attach;
     u64 *awhi, *awlo; double fixscale;      // volume attribute only (else nullptr): weight sums per attach node
     struct S1 { i32 b; u32 j, m; };
-    struct S2 { i32 o, node, p; u64 J; u32 m; bool climb; };
+    struct S2 { i32 o, node, p, pp; u64 J, pkey; u32 m; bool climb; };
     ULK_D ULK_INLINE S1 load1(i32 r, bool ok) const
     {
         S1 s;
@@ -943,17 +957,24 @@ struct K_Attach {
     ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const
     {
         S2 s;
-        s.o = 0; s.node = -1; s.p = -1; s.J = 0; s.m = a.m; s.climb = false;
+        s.o = 0; s.node = -1; s.p = -1; s.pp = -1; s.J = 0; s.pkey = 0; s.m = a.m; s.climb = false;
         if (a.b < 0) return s;
         const bool late = a.j != ULK_JK_CORE;
         if (!late && !awhi) return s;
-        const i32 st = bs[b_lab[a.b] - 1];
-        s.o = 2 * st;
-        s.node = a.b - st;
+#ifdef ULK_EMU
+        const UlkAttachInfo q = info[a.b];
+#else
+        const int4 raw = __ldg((const int4 *)info + 2 * (i64)a.b);
+        UlkAttachInfo q;
+        q.o = raw.x; q.node = raw.y; q.p = raw.z; q.pp = raw.w; q.pkey = 0;
+        if (late) q.pkey = __ldg((const unsigned long long *)info + 4 * (i64)a.b + 2);
+#endif
+        s.o = q.o;
+        s.node = q.node;
         if (late) {
             s.climb = true;
             s.J = ((u64)a.m << 32) | a.j;
-            s.p = Ipar[s.o + s.node];
+            s.p = q.p; s.pp = q.pp; s.pkey = q.pkey;
         }
         return s;
     }
@@ -963,14 +984,18 @@ struct K_Attach {
         i32 node = start;
         if (s.climb) {
             i32 p = s.p;
-            // the parent's merge key and the grandparent index are loaded together: one memory
-            // round trip per level of the climb
-            while (p != node) {
-                u64 w = Iwk[o + p];
-                i32 pp = Ipar[o + p];
-                if (!(w < s.J)) break;
+            // the first step comes with the basin record; further up the parent's merge key and the
+            // grandparent index are loaded together: one memory round trip per level of the climb
+            if (p != node && s.pkey < s.J) {
                 node = p;
-                p = pp;
+                p = s.pp;
+                while (p != node) {
+                    u64 w = Iwk[o + p];
+                    i32 pp = Ipar[o + p];
+                    if (!(w < s.J)) break;
+                    node = p;
+                    p = pp;
+                }
             }
             if (node != start) {
                 ulk_atomic_add(&attach[o + start], -1);
