@@ -357,6 +357,62 @@ static int ulk_fix_shift_for(u32 cmax_bits)
     return 62 - e2;
 }
 
+// K_Attach on the WHOLE foreground (ranks 0..n-1 are contiguous): a thread takes four consecutive
+// ranks with one 128-bit load per array; the climb itself is the functor's (area attribute only --
+// the volume attribute needs the warp reduction of the list form)
+#ifndef ULK_EMU
+__global__ void __launch_bounds__(256) ulk_attach_vec4_kernel(K_Attach k, i64 n)
+{
+    const i64 g = (i64)blockIdx.x * 256 + threadIdx.x;
+    const i64 r0 = g * 4;                      // lanes past the end stay for the warp collectives below
+    i32 b[4]; u32 j[4], m[4];
+    if (r0 + 4 <= n) {
+        const int4 bq = __ldcs((const int4 *)(k.bas + r0));
+        const uint4 jq = __ldcs((const uint4 *)(k.jk + r0)), mq = __ldcs((const uint4 *)(k.mw + r0));
+        b[0] = bq.x; b[1] = bq.y; b[2] = bq.z; b[3] = bq.w;
+        j[0] = jq.x; j[1] = jq.y; j[2] = jq.z; j[3] = jq.w;
+        m[0] = mq.x; m[1] = mq.y; m[2] = mq.z; m[3] = mq.w;
+    } else {
+        for (int e = 0; e < 4; ++e) {
+            const bool ok = r0 + e < n;
+            b[e] = ok ? k.bas[r0 + e] : -1; j[e] = ok ? k.jk[r0 + e] : ULK_JK_CORE; m[e] = ok ? k.mw[r0 + e] : 0u;
+        }
+    }
+    K_Attach::S2 s[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        K_Attach::S1 a;
+        a.b = b[e]; a.j = j[e]; a.m = m[e];
+        s[e] = k.load2(a, true);
+    }
+    // the four voxels usually sit in one basin and attach to the same node: their counter updates
+    // are merged before they become atomics (the per-basin counters are heavily contended)
+    i32 pf = -1, pt = -1, pc = 0;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        if (!s[e].climb) continue;
+        const i32 node = k.climb(s[e]);
+        if (node == s[e].node) continue;
+        const i32 from = s[e].o + s[e].node, to = s[e].o + node;
+        if (from == pf && to == pt) { ++pc; continue; }
+        if (pc) { atomicAdd(&k.attach[pf], -pc); atomicAdd(&k.attach[pt], pc); }
+        pf = from; pt = to; pc = 1;
+    }
+    // ... and the last pending update of neighbouring lanes (consecutive ranks) likewise: segmented
+    // sum over runs of equal (from, to)
+    const int lane = threadIdx.x & 31;
+    const i32 fprev = __shfl_up_sync(0xffffffffu, pf, 1), tprev = __shfl_up_sync(0xffffffffu, pt, 1);
+    const u32 run = ulk_run_mask(__ballot_sync(0xffffffffu, lane == 0 || fprev != pf || tprev != pt), lane);
+    const int first = __ffs(run) - 1, last = 31 - __clz(run);
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const i32 c2 = __shfl_down_sync(0xffffffffu, pc, off);
+        if (lane + off <= last) pc += c2;
+    }
+    if (pc && lane == first) { atomicAdd(&k.attach[pf], -pc); atomicAdd(&k.attach[pt], pc); }
+}
+#endif
+
 // ------------------------------------------------------------------ voxel stage
 struct VoxelStage {
     i32 *bas = nullptr; i32 B = 0; i32 Eg = 0;
@@ -569,7 +625,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkFg &fg, const i32 
             CHK(ulk_select_list_split_i32(rl, m, out.bas, nroot, klist, nkl_dev, st));
 #else
             CHK(ulk_memset(nkl_dev, 0, sizeof(i32), st));
-            ulk_launch_warp((i64)hc[0] * 32, st, K_K3Collect{needlist, hc[0], out.bas, out.bbmin, out.bbmax, fg, klist, nkl_dev});
+            ulk_launch_warp((i64)hc[0] * 32 * ULK_K3_WARPS, st, K_K3Collect{needlist, hc[0], out.bas, out.bbmin, out.bbmax, fg, klist, nkl_dev});
 #endif
             i32 nk = 0;
             CHK(ulk_read(&nk, nkl_dev, 1, st));
@@ -850,8 +906,18 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
         UlkAttachInfo *ainfo = A.get<UlkAttachInfo>(vb.B);
         CHKA(A);
         ulk_launch(vb.B, st, K_AttachInfo{vb.g_lab, vb.bs, S.Ipar, S.Iwk, ainfo});
-        ulk_launch_rkn<4>(nullptr, nfg, st, K_Attach{vb.bas, vb.mw, vb.jk, ainfo, S.Ipar, S.Iwk, S.attach,
-                                                     vol_mode ? S.awhi : nullptr, vol_mode ? S.awlo : nullptr, ldexp(1.0, fix_shift)});
+        K_Attach ka{vb.bas, vb.mw, vb.jk, ainfo, S.Ipar, S.Iwk, S.attach,
+                    vol_mode ? S.awhi : nullptr, vol_mode ? S.awlo : nullptr, ldexp(1.0, fix_shift)};
+#ifndef ULK_EMU
+        if (!vol_mode) {
+            if (g_ulk_prof_on) ulk_prof_begin(typeid(K_Attach).name(), st);
+            ulk_attach_vec4_kernel<<<(unsigned)(((i64)nfg + 1023) / 1024), 256, 0, st>>>(ka, (i64)nfg);
+            if (g_ulk_prof_on) ulk_prof_end(st);
+            ++g_ulk_launches;
+            if (g_ulk_debug_sync) ulk_debug_after_launch("K_Attach(vec4)", st);
+        } else
+#endif
+            ulk_launch_rkn<4>(nullptr, nfg, st, ka);
         A.release(ainfo);
     }
     i64 N2 = 2 * (i64)vb.B + 2;

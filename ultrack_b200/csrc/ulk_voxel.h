@@ -690,21 +690,25 @@ struct K_K3Need {
         if (n) needlist[ulk_atomic_add(nneed, 1)] = (i32)b;
     }
 };
+#define ULK_K3_WARPS 8
 #ifndef ULK_EMU
 // the voxels (ranks) of the basins that need the check, one warp per basin scanning its bounding
 // box row by row (x-runs of a basin stay contiguous in the list, which is all K_K3Init relies on)
 struct K_K3Collect {
     const i32 *needlist; i64 nneed; const i32 *bas; const i32 *bbmin, *bbmax; UlkFg fg;
     i32 *list; i32 *count;
+    // ULK_K3_WARPS warps share a basin (slices z0 + w, z0 + w + ULK_K3_WARPS, ...): the basins that
+    // need the check are few (2 % at C5), one warp each leaves most of the GPU idle
     ULK_D void warp(i64 ii, bool) const
     {
         const int lane = threadIdx.x & 31;
-        const i64 i = ii >> 5;
+        const i64 i = ii / (32 * ULK_K3_WARPS);
         if (i >= nneed) return;
+        const i32 sub = (i32)((ii >> 5) % ULK_K3_WARPS);
         const i32 b = needlist[i];
         const i32 z0 = bbmin[3 * b], y0 = bbmin[3 * b + 1], x0 = bbmin[3 * b + 2];
         const i32 z1 = bbmax[3 * b], y1 = bbmax[3 * b + 1], x1 = bbmax[3 * b + 2];
-        for (i32 z = z0; z <= z1; ++z)
+        for (i32 z = z0 + sub; z <= z1; z += ULK_K3_WARPS)
             for (i32 y = y0; y <= y1; ++y) {
                 const i32 trow = (z * fg.dm.H + y) * fg.S;
                 for (i32 xb = x0; xb <= x1; xb += 32) {
@@ -978,30 +982,50 @@ struct K_Attach {
         }
         return s;
     }
+    // the node a late joiner attaches to: the highest ancestor of its basin whose merge precedes J
+    ULK_D ULK_INLINE i32 climb(const S2 &s) const
+    {
+        const i32 o = s.o;
+        i32 node = s.node, p = s.p;
+        // the first step comes with the basin record; further up the parent's merge key and the
+        // grandparent index are loaded together: one memory round trip per level of the climb
+        if (p != node && s.pkey < s.J) {
+            node = p;
+            p = s.pp;
+            while (p != node) {
+                u64 w = Iwk[o + p];
+                i32 pp = Ipar[o + p];
+                if (!(w < s.J)) break;
+                node = p;
+                p = pp;
+            }
+        }
+        return node;
+    }
     ULK_D ULK_INLINE void run(const S2 &s, bool) const
     {
         const i32 o = s.o, start = s.node;
         i32 node = start;
-        if (s.climb) {
-            i32 p = s.p;
-            // the first step comes with the basin record; further up the parent's merge key and the
-            // grandparent index are loaded together: one memory round trip per level of the climb
-            if (p != node && s.pkey < s.J) {
-                node = p;
-                p = s.pp;
-                while (p != node) {
-                    u64 w = Iwk[o + p];
-                    i32 pp = Ipar[o + p];
-                    if (!(w < s.J)) break;
-                    node = p;
-                    p = pp;
-                }
+        if (s.climb) node = climb(s);
+#ifdef ULK_EMU
+        if (node != start) { attach[o + start] -= 1; attach[o + node] += 1; }
+#else
+        {   // neighbouring lanes (consecutive voxels of one basin) move between the same two counters:
+            // one pair of atomics per run of equal (from, to); every thread of the grid gets here
+            const int ln = threadIdx.x & 31;
+            const i32 from = node != start ? o + start : -1 - ln, to = node != start ? o + node : -1;
+            i32 c = node != start ? 1 : 0;
+            const i32 fprev = __shfl_up_sync(0xffffffffu, from, 1), tprev = __shfl_up_sync(0xffffffffu, to, 1);
+            const u32 rn = ulk_run_mask(__ballot_sync(0xffffffffu, ln == 0 || fprev != from || tprev != to), ln);
+            const int f0 = __ffs(rn) - 1, l0 = 31 - __clz(rn);
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const i32 c2 = __shfl_down_sync(0xffffffffu, c, off);
+                if (ln + off <= l0) c += c2;
             }
-            if (node != start) {
-                ulk_atomic_add(&attach[o + start], -1);
-                ulk_atomic_add(&attach[o + node], 1);
-            }
+            if (c && ln == f0) { atomicAdd(&attach[from], -c); atomicAdd(&attach[to], c); }
         }
+#endif
         if (!awhi) return;          // uniform over the grid
         // volume: the voxel's steepest-edge weight goes to the node it is attached to
         const bool has = node >= 0 && s.m != ULK_NONE32;
