@@ -22,7 +22,8 @@ src = Path(sys.argv[2]) if len(sys.argv) > 2 else ROOT / "gpurun_out"
 prof = ROOT / "profiles"
 
 
-ALIAS = {"ulk_ccl_words_kernel": "K_CclWords", "ulk_expand_kernel": "K_ExpandForeground",
+ALIAS = {"ulk_ccl_words_kernel": "K_CclWords", "ulk_expand_kernel": "K_ExpandForeground", "ulk_front_tile_kernel": "K_FrontTile",
+         "ulk_attach_vec4_kernel": "K_Attach",
          "ulk_threshold_kernel": "K_Threshold", "ulk_threshold_kernel_v4": "K_Threshold"}
 
 
@@ -69,13 +70,19 @@ WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__t_sector_hit_rate.pct", "lts__t_sector_hit_rate.pct",
         "sm__warps_active.avg.pct_of_peak_sustained_active", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
         "l1tex__throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
-        "launch__registers_per_thread", "smsp__inst_executed.sum",
+        "launch__registers_per_thread", "smsp__inst_executed.sum", "sm__issue_active.avg.pct_of_peak_sustained_elapsed",
+        "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio",
         "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum", "l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum"]
-for f in sorted(src.glob("full_*.ncu-rep")):
-    wl = f.stem.split("_", 1)[1]
-    raw = subprocess.run(["ncu", "-i", str(f), "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+# the report itself is too large to bring back from the GPU box: its raw page is exported there
+# (full_<wl>_raw.csv); a local .ncu-rep is read through ncu when present
+for f in sorted(list(src.glob("full_*.ncu-rep")) + list(src.glob("full_*_raw.csv"))):
+    wl = f.stem.split("_")[1]
+    if f.suffix == ".csv":
+        raw = f.read_text()
+    else:
+        raw = subprocess.run(["ncu", "-i", str(f), "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     hdr, units = rows[0], rows[1]
     idx = {h: i for i, h in enumerate(hdr)}
