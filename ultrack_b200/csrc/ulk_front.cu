@@ -25,8 +25,8 @@
 #ifndef ULK_EMU
 #include <cuda.h>
 
-#define FT_TZ 8
-#define FT_TY 8
+#define FT_TZ 16
+#define FT_TY 4
 #define FT_TX 128
 // x halo of the staged brick: 16 bytes of elements, so that the box start and the row pitch in
 // shared memory stay 16-byte aligned for every dtype (f32: 4, f16: 8, u8: 16 elements)
