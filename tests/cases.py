@@ -1,8 +1,12 @@
 """Seeded inputs shared by the CPU (emulation) and GPU parity tests."""
 from __future__ import annotations
 
+from pathlib import Path
+
 import numpy as np
 import scipy.ndimage as ndi
+
+GOLDEN_DIR = Path(__file__).resolve().parent / "golden"
 
 KINDS = ("rand", "smooth", "quant", "bool", "f64", "f16", "u8")
 
@@ -179,3 +183,70 @@ def ensemble_label_sets(labels: np.ndarray, n_sets: int = 4, seed: int = 0, merg
 
 MOCK_CONFIG = dict(threshold=0.5, min_area=500, max_area=7500, min_frontier=0.1, ws_hierarchy="area")   # utils/data.py:35-77
 MOCK_LINK = dict(max_neighbors=10, max_distance=15.0)
+
+
+def golden_link_check(lib, name: str, rtol: float = 1e-5):
+    """`ulk_link_frames` (+ `ulk_node_stats` for the colour gate) against the rows the REFERENCE'S
+    own compute_spatial_neighbors produced (tests/golden/link_cases.npz, oracle/make_golden_links.py)."""
+    from scipy.spatial import KDTree
+    from tests.test_oracle_golden import golden_link_case
+    from ultrack_b200 import frames
+    from ultrack_b200.capi import link_frames, node_stats
+    src, dst, kw, rows, images = golden_link_case(name)
+    ndim = len(src[0]["centroid"])
+    shape3 = (1,) * (3 - ndim) + tuple(np.load(GOLDEN_DIR / "link_cases.npz")[f"{name}_l0"].shape)
+
+    def table(nodes):
+        n = len(nodes)
+        bbox3 = np.zeros((n, 6), np.int32)
+        cen3 = np.zeros((n, 3), np.int32)
+        for i, nd in enumerate(nodes):
+            bbox3[i, 3 - ndim:3] = nd["bbox"][:ndim]
+            bbox3[i, 6 - ndim:] = nd["bbox"][ndim:]
+            bbox3[i, 3:6 - ndim] = 1
+            cen3[i, 3 - ndim:] = nd["centroid"]
+        off, words = frames.pack_masks([nd["mask"] for nd in nodes], bbox3)
+        area = np.array([nd["mask"].sum() for nd in nodes], np.int32)
+        return frames.upload(lib, shape3, bbox3, cen3, area, off, words, np.array([nd["id"] for nd in nodes]), ndim)
+
+    ts, td = table(src), table(dst)
+    color = None
+    if images:
+        s0 = node_stats(lib, ts.handle, [im[0] for im in images])
+        s1 = node_stats(lib, td.handle, [im[1] for im in images])
+        color = (s0["mean"], s1["mean"], s1["std"])
+    shift = np.array(kw["target_shift"], np.float64)
+    if ndim == 2:
+        shift[:, 0] = 0.0
+    scale = kw["scale"]
+    sc3 = None
+    if scale is not None:
+        m = min(ndim, len(scale))
+        sc3 = [0.0] * (3 - m) + [float(v) for v in list(scale)[-m:]]        # link.link_params: short scales drop leading axes
+    s, t, w, _ = link_frames(lib, ts.handle, td.handle, max_distance=kw["max_distance"], max_neighbors=kw["max_neighbors"],
+                             distance_weight=kw["distance_weight"], shift=shift, scale=sc3, weight_func=kw["weight_func"],
+                             edge_must_be_positive=kw["edge_must_be_positive"], color=color,
+                             z_score_threshold=kw.get("z_score_threshold", 5.0))
+    got = {(int(ts.ids[a]), int(td.ids[b])): float(x) for a, b, x in zip(s, t, w)}
+    exp = {(int(r[1]), int(r[2])): float(r[0]) for r in rows}
+    # targets with a k-boundary distance tie (KD-tree heap order) are left out
+    k = 2 * kw["max_neighbors"]
+    sp = np.asarray([n["centroid"] for n in src])
+    tp = np.asarray([n["centroid"] for n in dst], dtype=np.float32) + shift[:, -ndim:]
+    if scale is not None:
+        m = min(ndim, len(scale))
+        sp, tp = sp[..., -m:] * scale[-m:], tp[..., -m:] * scale[-m:]
+    skip = set()
+    if len(src) > k:
+        d1, _ = KDTree(sp).query(tp, k=k + 1, distance_upper_bound=kw["max_distance"])
+        tie = np.isfinite(d1[:, k]) & (d1[:, k - 1] == d1[:, k])
+        assert tie.mean() <= 0.5, tie.mean()      # the 1-D "short scale" case has many exact ties
+        skip = {dst[i]["id"] for i in np.nonzero(tie)[0]}
+    got = {key: v for key, v in got.items() if key[1] not in skip}
+    exp = {key: v for key, v in exp.items() if key[1] not in skip}
+    assert set(got) == set(exp) and len(exp) > 5, (name, len(got), len(exp), sorted(set(got) ^ set(exp))[:6])
+    for key in exp:
+        assert abs(got[key] - exp[key]) <= rtol * max(abs(exp[key]), 1e-300), (key, got[key], exp[key])
+    ts.free()
+    td.free()
+    return len(exp)

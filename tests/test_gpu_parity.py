@@ -600,3 +600,11 @@ def test_api_with_images_and_properties_gpu(cuda_lib, tmp_path):
         vals = img[t][tuple(coords.T)].astype(np.float64)
         exp = np.concatenate([[node.area], coords.mean(axis=0), [vals.mean()], [vals.std()]]).astype(np.float32)
         assert np.allclose(f, exp, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("name", ["plain2d", "dw3d", "scale_shift3d", "shortscale2d", "gt_intersection3d", "positive2d",
+                                  "color2d", "color3d_u16"])
+def test_link_matches_reference_function_bodies(cuda_lib, name):
+    """ulk_link_frames / ulk_node_stats against rows produced by executing the reference's own
+    compute_spatial_neighbors + color_filtering_mask source (tests/golden/link_cases.npz)."""
+    assert cases.golden_link_check(cuda_lib, name, rtol=RTOL) > 5

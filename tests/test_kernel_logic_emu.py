@@ -186,3 +186,10 @@ def test_smooth_contours_matches_scipy(shape, sigma):
                                             (C.c_double * 3)(*_sigma3(sigma, len(shape))), None))
     assert np.allclose(got, exp, rtol=1e-5, atol=1e-7)
     assert np.abs(got - exp).max() <= 2e-7
+
+
+@pytest.mark.parametrize("name", ["plain2d", "dw3d", "scale_shift3d", "shortscale2d", "gt_intersection3d", "positive2d",
+                                  "color2d", "color3d_u16"])
+def test_link_matches_reference_function_bodies(name):
+    """The link kernels against rows produced by the reference's own compute_spatial_neighbors source."""
+    assert cases.golden_link_check(emu_lib(), name) > 5

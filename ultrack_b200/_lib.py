@@ -127,9 +127,14 @@ def get_lib() -> C.CDLL:
     global _LIB
     if _LIB is None:
         if not LIB_PATH.exists():
-            raise RuntimeError(
-                f"{LIB_PATH} is missing: build it with `python -m ultrack_b200.csrc.build` "
-                "(nvcc, sm_100a). ultrack_b200 has no CPU fallback.")
+            # a fresh checkout has no binary (*.so is not tracked): build it once when nvcc is here
+            try:
+                from ultrack_b200.csrc.build import build
+                build()
+            except Exception as e:  # noqa: BLE001
+                raise RuntimeError(
+                    f"{LIB_PATH} is missing and could not be built ({e}): run `python -m ultrack_b200.csrc.build` "
+                    "(nvcc, sm_100a). ultrack_b200 has no CPU fallback.") from e
         lib = bind(C.CDLL(str(LIB_PATH)))
         if lib.ulk_device_count() <= 0:
             raise RuntimeError("ultrack_b200 needs a CUDA device (B200, sm_100a); none is visible "

@@ -57,10 +57,25 @@ class FrameStore:
 
     def __init__(self, max_bytes: int = 64 << 30):
         self.max_bytes = max_bytes
+        self._sized = False
         self._frames: "OrderedDict[Tuple[str, int], DeviceFrame]" = OrderedDict()
         self._bytes = 0
 
+    def _size_from_device(self) -> None:
+        """Caps the store at half of what is free on the device once the first table exists (the
+        scratch slab of the segmentation call is reserved by then)."""
+        self._sized = True
+        try:
+            import torch
+            if torch.cuda.is_available():
+                free, _ = torch.cuda.mem_get_info()
+                self.max_bytes = min(self.max_bytes, int(free // 2))
+        except Exception:  # noqa: BLE001
+            pass
+
     def put(self, db: str, t: int, frame: DeviceFrame) -> None:
+        if not self._sized:
+            self._size_from_device()
         self.drop(db, t)
         self._frames[(db, t)] = frame
         self._bytes += frame.nbytes
