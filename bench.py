@@ -300,7 +300,7 @@ def run_api_leg(lib, torch, dist, rank, world, local_rank, frames_per_rank: int 
                "segment_s": seg_s, "link_s": link_s, "nodes": n_nodes, "links": n_links, "blob_bytes": blob_bytes,
                "db_bytes": os.path.getsize(db),
                "rank0_ms_per_frame": dict(split, note="segment() wall split on rank 0: kernels incl. upload wait | node table D2H | "
-                                                      "blob kernel + row assembly | sqlite insert"),
+                                                      "blob kernel + row assembly | sqlite insert (writer thread, overlapped with the next frame)"),
                "api": "ultrack_b200.segment(fg, ct, cfg, overwrite=True) + ultrack_b200.link(cfg): pinned host float32 "
                       "timelapse in, nodes / overlaps / links rows with pickle blobs (stored Blosc chunks: blosc2 is not "
                       "installable here, masks are 1 byte per bbox voxel) into sqlite on local disk"}

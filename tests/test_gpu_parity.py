@@ -608,3 +608,30 @@ def test_link_matches_reference_function_bodies(cuda_lib, name):
     """ulk_link_frames / ulk_node_stats against rows produced by executing the reference's own
     compute_spatial_neighbors + color_filtering_mask source (tests/golden/link_cases.npz)."""
     assert cases.golden_link_check(cuda_lib, name, rtol=RTOL) > 5
+
+
+def test_bench_recipe_10M_voxels_against_oracle(cuda_lib):
+    """The bench recipe and parameters on a 96x320x320 frame (9.8 M voxels, ~2000 nodes, hundreds of
+    oversegmented components): the largest input the oracle checks id by id (≈ 20 s of CPU).  The
+    frame is generated on the device (ulk_synth_frame) like the bench's own inputs."""
+    import torch
+    from oracle.compare import compare_nodes
+    from oracle.segment_oracle import SegParams, segment_frame as o_seg
+    from tests.emu_harness import seg_params
+    from ultrack_b200 import _lib
+    from ultrack_b200.segment import segment_frame_device
+    shape = (96, 320, 320)
+    fg = torch.empty(shape, dtype=torch.float32, device="cuda")
+    ct = torch.empty(shape, dtype=torch.float32, device="cuda")
+    shp = (C.c_int64 * 3)(*shape)
+    _lib.check(cuda_lib, cuda_lib.ulk_synth_frame(shp, 1, 7, 8.0, 0.3, 3.0, 1e-3, C.c_void_p(fg.data_ptr()),
+                                                  C.c_void_p(ct.data_ptr()), None))
+    torch.cuda.synchronize()
+    kw = dict(min_area=100, max_area=10000, min_frontier=0.0)
+    h = segment_frame_device(cuda_lib, fg, ct, seg_params(fg_dtype=np.float32, **kw), keep_labels=True)
+    nodes = _lib.nodes_to_host(cuda_lib, h, with_labels=True)
+    ref = o_seg(fg.cpu().numpy(), ct.cpu().numpy(), SegParams(**kw))
+    assert len(ref["nodes"]) > 1000 and nodes["stats"]["pass_a_voxels"] > 0
+    assert np.array_equal(nodes["labels"], ref["labels"])
+    compare_nodes(nodes, ref, 3)
+    cuda_lib.ulk_frame_nodes_free(h)

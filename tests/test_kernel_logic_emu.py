@@ -193,3 +193,19 @@ def test_smooth_contours_matches_scipy(shape, sigma):
 def test_link_matches_reference_function_bodies(name):
     """The link kernels against rows produced by the reference's own compute_spatial_neighbors source."""
     assert cases.golden_link_check(emu_lib(), name) > 5
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_segment_parity_fuzz(seed):
+    """Seeded random cases over shape, fill, contour kind, hierarchy attribute and every config
+    field the path reads (min_area, min_area_factor, max_area, min_frontier, threshold)."""
+    rng = np.random.default_rng(1000 + seed)
+    nd = int(rng.integers(2, 4))
+    shape = tuple(int(v) for v in (rng.integers(20, 64, 2) if nd == 2 else rng.integers(6, 26, 3)))
+    kind = cases.KINDS[int(rng.integers(0, len(cases.KINDS)))]
+    fg, ct = cases.blob_frame(shape, seed, kind, fill=float(rng.uniform(0.15, 0.8)))
+    hier = ("area", "dynamics", "volume")[int(rng.integers(0, 3))]
+    min_area = int(rng.integers(4, 60))
+    kw = dict(min_area=min_area, max_area=int(min_area * rng.uniform(1.5, 30)), ws_hierarchy=hier,
+              min_area_factor=float(rng.choice([1.0, 2.0, 4.0, 8.0])), min_frontier=float(rng.choice([0.0, 0.0, 0.1, 0.3])))
+    cases.run_and_compare(emu_lib(), _seg, fg, ct, nd, **kw)

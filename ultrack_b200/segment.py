@@ -237,7 +237,7 @@ TIMERS: Dict[str, float] = {"kernels": 0.0, "d2h": 0.0, "rows": 0.0, "sql": 0.0}
 
 
 def _process(time: int, staged, db_path: str, max_segments_per_time: int,
-             catch_duplicates_expection: bool, lib, images=None, properties: Optional[List[str]] = None) -> None:
+             writer: "_RowWriter", lib, images=None, properties: Optional[List[str]] = None) -> None:
     """processing.py:160-340 for one timepoint (`staged` comes from `_stage`)."""
     run, ndim = staged
     t0 = _now()
@@ -263,17 +263,63 @@ def _process(time: int, staged, db_path: str, max_segments_per_time: int,
         lib.ulk_frame_nodes_free(handle)
         raise
     frames.STORE.put(db_path, time, frames.DeviceFrame(lib, handle, ids, ndim))
-    try:
-        database.insert_nodes(db_path, rows, overlaps)
-        TIMERS["sql"] += _now() - t3
-    except sqlite3.IntegrityError as e:
-        frames.STORE.drop(db_path, time)
-        if catch_duplicates_expection:
-            LOG.warning(f"IntegrityError: {e}\nSkipping batch {time}.\n"
-                        "Cannot guarantee image was entirely processed.\nSEGMENTS MIGHT BE MISSING!")
-            return
-        raise ValueError("Duplicated nodes found. Set `overwrite=True` to overwrite existing data.") from e
-    LOG.info(f"DONE with time {time}.")
+    writer.put(time, rows, overlaps)
+
+
+class _RowWriter:
+    """Inserts the rows of finished frames from a background thread, so that the sqlite insert of
+    frame t (the largest host cost of `segment()`: tens of MB of blobs per frame) overlaps the
+    upload and the kernels of frame t + 1.  sqlite3 and ctypes both release the GIL while they
+    work.  One frame is queued at most (its blob buffer stays alive in the queue); errors surface
+    in `close()` / the next `put()` with the reference's messages (processing.py:320-334)."""
+
+    def __init__(self, db_path: str, catch_duplicates: bool):
+        import queue
+        import threading
+        self.db_path, self.catch = db_path, catch_duplicates
+        self.q: "queue.Queue" = queue.Queue(maxsize=1)
+        self.error: Optional[BaseException] = None
+        self.thread = threading.Thread(target=self._run, name="ultrack_b200-row-writer", daemon=True)
+        self.thread.start()
+
+    def _run(self) -> None:
+        while True:
+            item = self.q.get()
+            if item is None:
+                return
+            time, rows, overlaps = item
+            if self.error is not None:
+                continue                      # drain: a previous frame failed
+            t0 = _now()
+            try:
+                database.insert_nodes(self.db_path, rows, overlaps)
+                LOG.info(f"DONE with time {time}.")
+            except sqlite3.IntegrityError as e:
+                frames.STORE.drop(self.db_path, time)
+                if self.catch:
+                    LOG.warning(f"IntegrityError: {e}\nSkipping batch {time}.\n"
+                                "Cannot guarantee image was entirely processed.\nSEGMENTS MIGHT BE MISSING!")
+                else:
+                    err = ValueError("Duplicated nodes found. Set `overwrite=True` to overwrite existing data.")
+                    err.__cause__ = e
+                    self.error = err
+            except BaseException as e:  # noqa: BLE001
+                frames.STORE.drop(self.db_path, time)
+                self.error = e
+            TIMERS["sql"] += _now() - t0
+
+    def put(self, time: int, rows, overlaps) -> None:
+        if self.error is not None:
+            self.close()
+        self.q.put((time, rows, overlaps))
+
+    def close(self) -> None:
+        if self.thread.is_alive():
+            self.q.put(None)
+            self.thread.join()
+        if self.error is not None:
+            err, self.error = self.error, None
+            raise err
 
 
 @rename_argument("detection", "foreground")
@@ -327,8 +373,12 @@ def segment(
     # the host->device copy of the next frame overlaps the kernels of the current one
     mine = sharding.owned(time_points, length, world, rank)
     staged = _stage(mine[0], foreground, contours, config.segmentation_config, lib) if mine else None
-    for k, time in enumerate(mine):
-        nxt = _stage(mine[k + 1], foreground, contours, config.segmentation_config, lib) if k + 1 < len(mine) else None
-        _process(time, staged, db_path, max_segments_per_time, batch_index is not None, lib, images, properties)
-        staged = nxt
+    writer = _RowWriter(db_path, catch_duplicates=batch_index is not None)
+    try:
+        for k, time in enumerate(mine):
+            nxt = _stage(mine[k + 1], foreground, contours, config.segmentation_config, lib) if k + 1 < len(mine) else None
+            _process(time, staged, db_path, max_segments_per_time, writer, lib, images, properties)
+            staged = nxt
+    finally:
+        writer.close()
     sharding.barrier()
