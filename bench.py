@@ -563,6 +563,8 @@ def main():
         n_fg_a = int(f.stats.pass_a_voxels)
         stats["n_foreground"], stats["pass_a_voxels"] = n_fg, n_fg_a
         stats["k3_voxels"] = int(f.stats.k3_voxels)
+        stats["flow_rounds"], stats["k3_rounds"] = int(f.stats.flow_rounds), int(f.stats.k3_rounds)
+        stats["plateau_voxels"] = int(f.stats.plateau_voxels)
 
         # ---- e2e: the same steps from pinned HOST buffers through the ingest API segment() uses
         # (ulk_upload_begin of frame i+1 before ulk_segment_frame_uploaded of frame i), node

@@ -152,3 +152,7 @@ template <class T> struct K_Fill {
 template <class T> int ulk_fill(T *p, T v, i64 n, ulk_stream_t s) { ulk_launch(n, s, K_Fill<T>{p, v}); return 0; }
 
 template <class T> int ulk_read(T *host, const T *dev, i64 n, ulk_stream_t s) { return ulk_d2h(host, dev, (size_t)n * sizeof(T), s); }
+template <class T, class U> int ulk_read2(T *h1, const T *d1, i64 n1, U *h2, const U *d2, i64 n2, ulk_stream_t s)
+{
+    return ulk_d2h2(h1, d1, (size_t)n1 * sizeof(T), h2, d2, (size_t)n2 * sizeof(U), s);
+}

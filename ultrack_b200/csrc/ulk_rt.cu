@@ -32,6 +32,11 @@ void ulk_ws_free(void *p) { free(p); }
 void ulk_ws_stats(size_t out[3]) { out[0] = out[1] = out[2] = 0; }
 int ulk_memset(void *p, int byte, size_t bytes, ulk_stream_t) { memset(p, byte, bytes); return 0; }
 int ulk_d2h(void *dst, const void *src, size_t bytes, ulk_stream_t) { memcpy(dst, src, bytes); return 0; }
+int ulk_d2h2(void *d1, const void *s1, size_t n1, void *d2, const void *s2, size_t n2, ulk_stream_t)
+{
+    memcpy(d1, s1, n1); memcpy(d2, s2, n2);
+    return 0;
+}
 int ulk_h2d(void *dst, const void *src, size_t bytes, ulk_stream_t) { memcpy(dst, src, bytes); return 0; }
 int ulk_d2d(void *dst, const void *src, size_t bytes, ulk_stream_t) { memmove(dst, src, bytes); return 0; }
 int ulk_sync(ulk_stream_t) { return 0; }
@@ -331,6 +336,27 @@ int ulk_d2h(void *dst, const void *src, size_t bytes, ulk_stream_t s)
     ULK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s));
     ULK_CUDA(cudaStreamSynchronize(s));
     return 0;
+}
+// two small read-backs behind ONE stream synchronisation (every host round trip costs 10-30 us)
+int ulk_d2h2(void *dst1, const void *src1, size_t n1, void *dst2, const void *src2, size_t n2, ulk_stream_t s)
+{
+    const size_t o2 = (n1 + 15) / 16 * 16;
+    if (o2 + n2 <= kPinnedPage) {
+        if (!g_pinned_page && cudaHostAlloc(&g_pinned_page, kPinnedPage, cudaHostAllocDefault) != cudaSuccess) {
+            g_pinned_page = nullptr;
+            cudaGetLastError();
+        }
+        if (g_pinned_page) {
+            ULK_CUDA(cudaMemcpyAsync(g_pinned_page, src1, n1, cudaMemcpyDeviceToHost, s));
+            ULK_CUDA(cudaMemcpyAsync((char *)g_pinned_page + o2, src2, n2, cudaMemcpyDeviceToHost, s));
+            ULK_CUDA(cudaStreamSynchronize(s));
+            memcpy(dst1, g_pinned_page, n1);
+            memcpy(dst2, (char *)g_pinned_page + o2, n2);
+            return 0;
+        }
+    }
+    int rc = ulk_d2h(dst1, src1, n1, s);
+    return rc ? rc : ulk_d2h(dst2, src2, n2, s);
 }
 int ulk_h2d(void *dst, const void *src, size_t bytes, ulk_stream_t s) { ULK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s)); return 0; }
 int ulk_d2d(void *dst, const void *src, size_t bytes, ulk_stream_t s)

@@ -461,6 +461,7 @@ void ulk_ws_free(void *p);
 void ulk_ws_stats(size_t out[3]);
 int ulk_memset(void *p, int byte, size_t bytes, ulk_stream_t s);
 int ulk_d2h(void *dst, const void *src, size_t bytes, ulk_stream_t s);  // synchronises
+int ulk_d2h2(void *dst1, const void *src1, size_t n1, void *dst2, const void *src2, size_t n2, ulk_stream_t s);  // one sync
 int ulk_h2d(void *dst, const void *src, size_t bytes, ulk_stream_t s);
 int ulk_d2d(void *dst, const void *src, size_t bytes, ulk_stream_t s);
 int ulk_sync(ulk_stream_t s);

@@ -528,8 +528,7 @@ static int voxel_stage(ulk_stream_t st, UlkArena &A, const UlkFg &fg, const i32 
     ulk_launch(nflow, st, K_FlowTop{flow_root, flow_key, flow_src, out.bas, ct, fg, out.b_top, Tk});
     A.release(flow_root); A.release(flow_key); A.release(flow_src);
     u64 h_ncross = 0;
-    CHK(ulk_read(&h_ncross, ncross, 1, st));
-    CHK(ulk_read(hc, ctr, 4, st));
+    CHK(ulk_read2(&h_ncross, ncross, 1, hc, ctr, 4, st));
     const i32 nxl = hc[1];
     if (need_join) {
         // plateau voxels above their basin level: minimax relaxation along spanning-tree edges
@@ -747,8 +746,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
     CHK(threshold_words(st, dm, fgp, fg_dtype, prm->threshold, SG, nt, words));
     CHK(ulk_exclusive_scan_popc_u32(words, off, nt, st));
     i32 h_last_off = 0; u32 h_last_w = 0;
-    CHK(ulk_read(&h_last_off, off + (nt - 1), 1, st));
-    CHK(ulk_read(&h_last_w, words + (nt - 1), 1, st));
+    CHK(ulk_read2(&h_last_off, off + (nt - 1), 1, &h_last_w, words + (nt - 1), 1, st));
     const i32 nfg = h_last_off + __builtin_popcount(h_last_w);
     stats_local.n_foreground = nfg;
     F->fix_shift = ulk_fix_shift_for(0);
@@ -787,8 +785,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
     ulk_launch_rk_multi(nullptr, nfg, st, K_FlattenCount{P, cnt, (i32 *)roots0, ctr});
     i32 hc[4];
     u32 h_cmax = 0;
-    CHK(ulk_read(hc, ctr, 4, st));
-    CHK(ulk_read(&h_cmax, cmax, 1, st));
+    CHK(ulk_read2(hc, ctr, 4, &h_cmax, cmax, 1, st));
     const i32 n_roots = hc[0];
     const i32 max_area_i = prm->max_area > 2147483646.0 ? 2147483646 : (i32)prm->max_area;
     const int fix_shift = ulk_fix_shift_for(h_cmax);
@@ -810,8 +807,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
     CHK(ulk_exclusive_scan_i32(keep, keeppre, (i64)n_roots + 1, st));
     CHK(ulk_exclusive_scan_i32(big, bigpre, (i64)n_roots + 1, st));
     i32 n_cc = 0, n_big = 0;
-    CHK(ulk_read(&n_cc, keeppre + n_roots, 1, st));
-    CHK(ulk_read(&n_big, bigpre + n_roots, 1, st));
+    CHK(ulk_read2(&n_cc, keeppre + n_roots, 1, &n_big, bigpre + n_roots, 1, st));
     if (n_cc == 0) { F->n_nodes = 0; F->stats = stats_local; return empty_labels(st, F, V, keep_labels); }
     i32 *code = cnt;
     ulk_launch(n_roots, st, K_RootCode{roots, keep, keeppre, big, bigpre, code, cc_big, big_cc});
@@ -879,8 +875,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
         ulk_launch(nrec, st, K_Valid{rec_cc, nvalid});
         CHK(ulk_memset(nvalid + nrec, 0, sizeof(i32), st));
         CHK(ulk_exclusive_scan_i32(nvalid, nvpre, nrec + 1, st));
-        CHK(ulk_read(&R, nvpre + nrec, 1, st));
-        CHK(ulk_sync(st));
+        CHK(ulk_read(&R, nvpre + nrec, 1, st));      // synchronises: pass A's scratch can go
     }
     A.release(cc_big); A.release(big_cc); A.release(cnt);
     if (keep_labels) {
@@ -935,16 +930,14 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
     HP.min_frontier = prm->min_frontier; HP.fix_shift = fix_shift;
     ulk_launch(R, st, K_HierFull{vb.bs, vb.es, Bv, Ev, S, HP, O});
     ulk_launch(R, st, K_RegionSizeCheck{vb.bs, S, err});
-    u64 h_err = 0;
-    CHK(ulk_read(&h_err, err, 1, st));
-    if (h_err != ULK_NONE64) ULK_FAIL(-10, "Region too small. Size of %d found.", (int)(h_err & 0xff));
-
     // ---- node table
     i32 *noff = A.get<i32>(R + 1);
     CHKA(A);
     CHK(ulk_exclusive_scan_i32(O.count, noff, R + 1, st));
+    u64 h_err = 0;
     i32 N = 0;
-    CHK(ulk_read(&N, noff + R, 1, st));
+    CHK(ulk_read2(&h_err, err, 1, &N, noff + R, 1, st));
+    if (h_err != ULK_NONE64) ULK_FAIL(-10, "Region too small. Size of %d found.", (int)(h_err & 0xff));
     F->n_nodes = N;
     F->bbox = keep_alloc<i32>(6 * (i64)N); F->centroid = keep_alloc<i32>(3 * (i64)N);
     F->area = keep_alloc<i32>(N); F->frontier = keep_alloc<double>(N); F->height = keep_alloc<double>(N);
@@ -959,8 +952,16 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
                                    F->frontier, F->height, mwords});
     CHK(ulk_memset(mwords + N, 0, sizeof(i64), st));
     CHK(ulk_exclusive_scan_i64(mwords, F->mask_off, (i64)N + 1, st));
+    // overlaps = (node, emitted proper ancestor) pairs, processing.py:289-296: their count comes
+    // back together with the mask size (one host round trip)
+    i32 *depth = A.get<i32>(N + 1), *ooff = A.get<i32>(N + 1);
+    CHKA(A);
+    ulk_launch(N, st, K_AncestorCount{F->parent, depth});
+    CHK(ulk_memset(depth + N, 0, sizeof(i32), st));
+    CHK(ulk_exclusive_scan_i32(depth, ooff, (i64)N + 1, st));
     i64 total_words = 0;
-    CHK(ulk_read(&total_words, F->mask_off + N, 1, st));
+    i32 M = 0;
+    CHK(ulk_read2(&total_words, F->mask_off + N, 1, &M, ooff + N, 1, st));
     F->mask_words = total_words;
     F->mask = keep_alloc<u32>(total_words);
     if (!F->mask) ULK_FAIL(-3, "device allocation failed");
@@ -970,14 +971,6 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
     CHKA(A);
     ulk_launch(N, st, K_PaintInfo{F->parent, F->bbox, F->mask_off, pinfo});
     ulk_launch_rkx<4>("MaskPaint", nullptr, fgl, nfg, dm, st, K_MaskPaint{vb.bas, bnode, pinfo, dm, F->mask});
-    // ---- overlaps: (node, emitted proper ancestor) pairs, processing.py:289-296
-    i32 *depth = A.get<i32>(N + 1), *ooff = A.get<i32>(N + 1);
-    CHKA(A);
-    ulk_launch(N, st, K_AncestorCount{F->parent, depth});
-    CHK(ulk_memset(depth + N, 0, sizeof(i32), st));
-    CHK(ulk_exclusive_scan_i32(depth, ooff, (i64)N + 1, st));
-    i32 M = 0;
-    CHK(ulk_read(&M, ooff + N, 1, st));
     F->n_overlaps = M;
     F->overlaps = keep_alloc<i32>(2 * (i64)M);
     if (!F->overlaps) ULK_FAIL(-3, "device allocation failed");
