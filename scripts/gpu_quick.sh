@@ -10,5 +10,5 @@ d=json.load(open('gpurun_out/bench_quick.json'))
 print('ms/step',round(d['ms_per_step'],3),'kernel ms',round(d['pipeline_roofline']['kernel_time_ms_per_step'],3),'launches',d['gpu_launches'])
 t=d['pipeline_roofline']['top_kernels_ms_per_step']
 print({k:v for k,v in list(t.items())[:22]})
-print(d['frame_stats'])
+print(d["frame_stats"]); print(d["ms_steps_rank0"], d["workspace_bytes"])
 PY
