@@ -252,7 +252,7 @@ int ulk_ws_reserve(size_t bytes, ulk_stream_t s)
     // or three frames alive at a time): one block allocated and handed back stays cached (the
     // release threshold is unlimited), so steady-state calls never grow the pool
     {
-        size_t prime = bytes / 64;
+        size_t prime = bytes / 16;        // ~2 B per frame voxel: the masks + tables of three frames at 20-30 % foreground
         if (prime < (256ull << 20)) prime = 256ull << 20;
         void *p = nullptr;
         if (cudaMallocAsync(&p, prime, g_alloc_stream) == cudaSuccess) cudaFreeAsync(p, g_alloc_stream);
