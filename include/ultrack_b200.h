@@ -210,6 +210,22 @@ ULK_API int ulk_labels_to_contours(const int32_t *labels, int32_t n_sets, const 
  * sigma: z, y, x (z ignored when D == 1). */
 ULK_API int ulk_smooth_contours(float *contours, const int64_t shape[3], const double sigma[3], void *stream);
 
+/* No counterpart in the reference: added for callers that
+ * cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).
+ * ulk_smooth_contours with NO allocation of any kind: the ping-pong volume and the maximum live in
+ * a file-scope device array of ULK_SMOOTH_STATIC_MAX_VOXELS float32 (+ 256 B), held by every GPU
+ * that loads the library until exit; the Gaussian taps travel in the kernel parameters.  Results
+ * are bit-identical to ulk_smooth_contours.  Limits: D*H*W <= ULK_SMOOTH_STATIC_MAX_VOXELS and
+ * int(4 sigma + 0.5) <= ULK_SMOOTH_STATIC_MAX_RADIUS per filtered axis; beyond them the call fails
+ * with code -12 and a message (use ulk_smooth_contours).  The call only ENQUEUES work on `stream`
+ * and does not synchronise it (no host read-back: the maximum stays on the device).  All calls on
+ * a device share the one array: calls that overlap on the GPU (different streams or host threads)
+ * race -- serialise them. */
+#define ULK_SMOOTH_STATIC_MAX_VOXELS 4194304        /* 16 MiB of float32: 2048 x 2048 or 64 x 256 x 256 */
+#define ULK_SMOOTH_STATIC_MAX_RADIUS 127            /* sigma < 31.875 */
+ULK_API int ulk_smooth_contours_static(float *contours, const int64_t shape[3], const double sigma[3], void *stream);
+ULK_API int64_t ulk_smooth_contours_static_max_voxels(void);
+
 /* add_flow (imgproc/flow.py:639-751), the per-timepoint kernel: for every node of `nodes` the
  * vector field sampled at its centroid mapped into field coordinates (round half to even of
  * centroid * (field_dim - 1) / (image_dim - 1), clipped: flow.py:716-720), scaled to voxels

@@ -188,6 +188,30 @@ def test_smooth_contours_matches_scipy(shape, sigma):
     assert np.abs(got - exp).max() <= 2e-7
 
 
+@pytest.mark.parametrize("shape,sigma", [((40, 36), 1.5), ((9, 20, 24), (0.5, 1.0, 2.0)), ((6, 18, 18), 3.0), ((12, 10), (0.0, 2.0))])
+def test_smooth_contours_static_equals_allocating_entry(shape, sigma):
+    """ulk_smooth_contours_static (fixed scratch, taps in the kernel parameters, device-side maximum)
+    gives the bits of ulk_smooth_contours, twice in a row on the shared scratch; limits are refused."""
+    import ctypes as C
+    from ultrack_b200 import _lib
+    from ultrack_b200.edge import _sigma3
+    lib = emu_lib()
+    shape3 = shape if len(shape) == 3 else (1,) + shape
+    shp, sg = (C.c_int64 * 3)(*shape3), (C.c_double * 3)(*_sigma3(sigma, len(shape)))
+    for seed in (0, 1):
+        rng = np.random.default_rng(seed)
+        ct = (rng.random(shape) > 0.8).astype(np.float32) * rng.choice([0.25, 0.5, 0.75, 1.0], size=shape).astype(np.float32)
+        ref, got = ct.copy(), ct.copy()
+        _lib.check(lib, lib.ulk_smooth_contours(ref.ctypes.data_as(C.c_void_p), shp, sg, None))
+        _lib.check(lib, lib.ulk_smooth_contours_static(got.ctypes.data_as(C.c_void_p), shp, sg, None))
+        assert np.array_equal(ref.view(np.uint32), got.view(np.uint32))
+    big = (C.c_int64 * 3)(1, 4096, 2048)
+    assert lib.ulk_smooth_contours_static(got.ctypes.data_as(C.c_void_p), big, sg, None) == -12
+    assert b"static scratch limit" in lib.ulk_last_error()
+    assert lib.ulk_smooth_contours_static(got.ctypes.data_as(C.c_void_p), shp, (C.c_double * 3)(0.0, 40.0, 1.0), None) == -12
+    assert lib.ulk_smooth_contours_static_max_voxels() == 4194304
+
+
 @pytest.mark.parametrize("name", ["plain2d", "dw3d", "scale_shift3d", "shortscale2d", "gt_intersection3d", "positive2d",
                                   "color2d", "color3d_u16"])
 def test_link_matches_reference_function_bodies(name):

@@ -76,6 +76,7 @@ EXPORTS = [
     "ulk_frame_nodes_from_host", "ulk_frame_nodes_to_device", "ulk_frame_nodes_from_device", "ulk_link_frames", "ulk_links_to_host", "ulk_links_free",
     "ulk_labels_to_contours", "ulk_node_shifts", "ulk_synth_frame", "ulk_node_stats", "ulk_frame_blobs_to_host", "ulk_smooth_contours",
     "ulk_upload_begin", "ulk_segment_frame_uploaded", "ulk_upload_free",
+    "ulk_smooth_contours_static", "ulk_smooth_contours_static_max_voxels",
 ]
 
 
@@ -110,6 +111,9 @@ def bind(lib: C.CDLL) -> C.CDLL:
     lib.ulk_links_to_host.argtypes = [PL, vp, vp, vp, vp]
     lib.ulk_frame_blobs_to_host.argtypes = [PF, vp, vp, C.POINTER(BlobSpec), i64, i32, vp, vp, vp]
     lib.ulk_smooth_contours.argtypes = [vp, C.POINTER(i64), C.POINTER(dbl), vp]
+    lib.ulk_smooth_contours_static.argtypes = [vp, C.POINTER(i64), C.POINTER(dbl), vp]
+    lib.ulk_smooth_contours_static_max_voxels.argtypes = []
+    lib.ulk_smooth_contours_static_max_voxels.restype = C.c_int64
     lib.ulk_node_stats.argtypes = [PF, vp, C.c_int, i32, i32, vp, vp, vp, vp, vp, vp]
     lib.ulk_links_free.argtypes = [PL]
     lib.ulk_links_free.restype = None

@@ -12,7 +12,7 @@ from pathlib import Path
 
 HERE = Path(__file__).resolve().parent
 ROOT = HERE.parent.parent
-SOURCES = ["ulk_rt.cu", "ulk_seg.cu", "ulk_front.cu", "ulk_link.cu", "ulk_aux.cu", "ulk_api.cu"]
+SOURCES = ["ulk_rt.cu", "ulk_seg.cu", "ulk_front.cu", "ulk_link.cu", "ulk_aux.cu", "ulk_static.cu", "ulk_api.cu"]
 HEADERS = ["ulk_rt.h", "ulk_common.h", "ulk_voxel.h", "ulk_hier.h", "ulk_seg.h", "ulk_front.h", "../../include/ultrack_b200.h"]
 LIB = HERE / "libultrack_b200.so"
 EMU_LIB = ROOT / "tests" / "emu" / "libulk_emu.so"
