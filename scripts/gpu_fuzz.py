@@ -2,7 +2,8 @@
 """Random parity cases of the CUDA library against the oracle on a GPU box (TEST TOOL, not a test:
 the committed GPU tests are deterministic).  Half of the cases use a row length that is a multiple
 of 16 so that float32 / float16 / uint8 contours take the TMA front end; the rest take the list
-kernels.  usage: python scripts/gpu_fuzz.py [n_cases] [first_seed]"""
+kernels.  usage: python scripts/gpu_fuzz.py [n_cases] [first_seed] [wide]
+("wide": 3-D cases span several front-end bricks in every direction)"""
 import sys
 from pathlib import Path
 
@@ -22,6 +23,7 @@ def _seg(lib, fg, ct, **kw):
 def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 300
     first = int(sys.argv[2]) if len(sys.argv) > 2 else 5000
+    wide = len(sys.argv) > 3 and sys.argv[3] == "wide"
     lib = _lib.get_lib()
     bad = 0
     tma = 0
@@ -31,6 +33,9 @@ def main():
         shape = [int(v) for v in (rng.integers(16, 200, 2) if nd == 2 else rng.integers(5, 48, 3))]
         if seed % 2 == 0:
             shape[-1] = max(16, (shape[-1] // 16) * 16)
+        if wide and nd == 3:
+            # several TMA bricks ([16, 4, 128]) in every direction, ragged last bricks
+            shape = [int(rng.integers(14, 40)), int(rng.integers(3, 22)), 16 * int(rng.integers(7, 20))]
         shape = tuple(shape)
         kind = cases.KINDS[int(rng.integers(0, len(cases.KINDS)))]
         fg, ct = cases.blob_frame(shape, seed, kind, fill=float(rng.uniform(0.1, 0.9)))
@@ -45,7 +50,7 @@ def main():
         except Exception as e:  # noqa: BLE001
             bad += 1
             print("FAIL", seed, shape, kind, kw, repr(e)[:300], flush=True)
-    print(f"gpu fuzz: {n} cases from seed {first}, {tma} through the TMA front end, {bad} failures")
+    print(f"gpu fuzz{' (wide)' if wide else ''}: {n} cases from seed {first}, {tma} through the TMA front end, {bad} failures")
     return 1 if bad else 0
 
 
