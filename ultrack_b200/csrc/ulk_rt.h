@@ -20,6 +20,7 @@
 #include <numeric>
 #include <vector>
 #include <cmath>
+#include <type_traits>
 #define ULK_HD
 #define ULK_D
 #define ULK_INLINE inline
@@ -39,6 +40,11 @@ typedef uint64_t u64;
 typedef uint32_t u32;
 typedef int32_t i32;
 typedef uint8_t u8;
+
+// a phased rank-space functor may declare S0 load0(r, ok): the loads that need the rank only
+// (see ulk_kernel_rk); load1 then takes the S0 as its first argument
+template <class F, class = void> struct ulk_has_load0 : std::false_type {};
+template <class F> struct ulk_has_load0<F, std::void_t<typename F::S0>> : std::true_type {};
 
 // ---------------------------------------------------------------- errors
 void ulk_set_error(const char *fmt, ...);
@@ -124,7 +130,8 @@ template <int U, class F, class DM> void ulk_launch_rk(const i32 *rl, const i32 
     for (i64 i = 0; i < m; ++i) {
         i32 r = rl ? rl[i] : (i32)i, v = fgl[r], z, y, x;
         dm.coords(v, z, y, x);
-        f.run(f.load2(f.load1(r, v, z, y, x, true), true), true);
+        if constexpr (ulk_has_load0<F>::value) f.run(f.load2(f.load1(f.load0(r, true), r, v, z, y, x, true), true), true);
+        else f.run(f.load2(f.load1(r, v, z, y, x, true), true), true);
     }
 }
 template <int UDEF, class F, class DM> void ulk_launch_rkx(const char *, const i32 *rl, const i32 *fgl, i64 m, const DM &dm, ulk_stream_t s, const F &f) { ulk_launch_rk<UDEF>(rl, fgl, m, dm, s, f); }
@@ -339,13 +346,35 @@ template <int U, class F, class DM> __global__ void __launch_bounds__(256) ulk_k
     typename F::S1 a[U];
     typename F::S2 b[U];
     bool ok[U];
+    if constexpr (ulk_has_load0<F>::value) {
+        // the entries that depend on the rank alone are requested together with the voxel index,
+        // before the coordinate arithmetic waits for it (no branch in between: rank 0 stands in
+        // for the entries past the end of the list)
+        typename F::S0 p[U];
+        i32 rr[U], vv[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-        const i64 i = base + u * 256;
-        ok[u] = i < m;
-        i32 r = 0, v = 0, z = 0, y = 0, x = 0;
-        if (ok[u]) { r = rl ? rl[i] : (i32)i; v = fgl[r]; dm.coords(v, z, y, x); }
-        a[u] = f.load1(r, v, z, y, x, ok[u]);
+        for (int u = 0; u < U; ++u) {
+            const i64 i = base + u * 256;
+            ok[u] = i < m;
+            rr[u] = ok[u] ? (rl ? rl[i] : (i32)i) : 0;
+            vv[u] = fgl[rr[u]];
+            p[u] = f.load0(rr[u], ok[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            i32 z, y, x;
+            dm.coords(vv[u], z, y, x);
+            a[u] = f.load1(p[u], rr[u], vv[u], z, y, x, ok[u]);
+        }
+    } else {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const i64 i = base + u * 256;
+            ok[u] = i < m;
+            i32 r = 0, v = 0, z = 0, y = 0, x = 0;
+            if (ok[u]) { r = rl ? rl[i] : (i32)i; v = fgl[r]; dm.coords(v, z, y, x); }
+            a[u] = f.load1(r, v, z, y, x, ok[u]);
+        }
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) b[u] = f.load2(a[u], ok[u]);

@@ -743,14 +743,24 @@ struct K_BasinAccum {
     struct S1 { i32 r, v, z, y, x, b, o; u32 m, k; UlkNbRaw q; };
     // phase 2: the neighbours' basins, the basin level, the weight across the steepest edge
     struct S2 { i32 r, v, z, y, x, b; u64 top; u32 nc, kmin, jkv; bool plateau; };
-    ULK_D ULK_INLINE S1 load1(i32 r, i32 v, i32 z, i32 y, i32 x, bool ok) const
+    // phase 0: what the rank alone addresses (requested together with the voxel index)
+    struct S0 { i32 b, o; u32 m, k; };
+    ULK_D ULK_INLINE S0 load0(i32 r, bool ok) const
+    {
+        S0 p;
+        p.b = bas[r]; p.m = mw[r]; p.k = pk[r]; p.o = po[r];
+        if (!ok) { p.b = -1; p.o = ULK_PO_OUT; p.m = 0; p.k = ULK_NONE32; }
+        return p;
+    }
+    ULK_D ULK_INLINE S1 load1(const S0 &p, i32 r, i32 v, i32 z, i32 y, i32 x, bool ok) const
     {
         S1 s;
-        s.r = r; s.v = v; s.z = z; s.y = y; s.x = x; s.b = -1; s.o = ULK_PO_OUT; s.m = 0; s.k = ULK_NONE32;
-        if (!ok) return s;
-        s.b = bas[r];
-        s.m = mw[r]; s.k = pk[r]; s.o = po[r];
-        s.q = fg.nb_load(r, fg.seg(z, y, x), z, y, want_k0 != 0, true);
+        s.r = r; s.v = v; s.z = z; s.y = y; s.x = x; s.b = p.b; s.o = p.o; s.m = p.m; s.k = p.k;
+        if (ok) s.q = fg.nb_load(r, fg.seg(z, y, x), z, y, want_k0 != 0, true);
+        else {
+            for (int i = 0; i < 4; ++i) { s.q.e[i].w = 0; s.q.e[i].o = 0; }
+            s.q.vl = -1; s.q.vr = -1;
+        }
         return s;
     }
     ULK_D ULK_INLINE S2 load2(const S1 &a, bool) const
