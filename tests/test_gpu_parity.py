@@ -52,6 +52,24 @@ def test_segment_parity(cuda_lib, shape, kind, hier):
     assert total > 0
 
 
+@pytest.mark.parametrize("shape", [(160, 160), (20, 12, 272)])
+@pytest.mark.parametrize("odd", ["tiny", "negative", "huge", "mixed"])
+def test_front_tile_contours_outside_fast_range(cuda_lib, shape, odd):
+    """The tile front end computes edge weights with a float expression that is exact for contour
+    values that are 0 or in [2^-23, 2^39); a foreground value outside that range raises a flag and
+    the edges are recomputed in the general form.  Rows are a multiple of 16 floats (TMA path)."""
+    fg, ct = cases.blob_frame(shape, 7, "smooth")
+    ct = ct.astype(np.float32)
+    rng = np.random.default_rng(11)
+    pick = rng.random(shape) < 0.03
+    vals = {"tiny": [1e-9, 3e-8, 1e-30], "negative": [-0.25, -1e-3, -0.0], "huge": [1e12, 3e20],
+            "mixed": [1e-9, -0.5, 7e11, 3e-8]}[odd]
+    ct[pick] = rng.choice(np.array(vals, np.float32), size=int(pick.sum()))
+    n = cases.run_and_compare(cuda_lib, _seg_host, fg, ct, len(shape), min_area=30, max_area=2000,
+                              ws_hierarchy="area" if odd != "mixed" else "dynamics")
+    assert n > 0
+
+
 @pytest.mark.parametrize("variant,shape,radius", [("T", (20, 40, 40), 6.0), ("T", (128, 128), 7.0),
                                                   ("S", (32, 64, 64), 6.0), ("S", (256, 256), 9.0)])
 @pytest.mark.parametrize("min_frontier", [0.0, 0.1])

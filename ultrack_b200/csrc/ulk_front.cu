@@ -109,12 +109,11 @@ ulk_front_tile_kernel(const __grid_constant__ CUtensorMap tmap, const FrontArgs 
     }
     // Edge weights: w = float32(double(a + b) / 2 + 1e-8).  For a + b == 0 or 2^-24 <= |a + b| < 2^40
     // the float expression (a + b) * 0.5f + 1e-8f is bit-identical (ulk_wsum_fast), and when every
-    // staged value is 0 or in [2^-23, 2^39) -- true for any sane contour map -- every pairwise
-    // sum is in that range: the CTA checks its brick once and the per-edge test disappears.
-    // (uint8 contours are always in range; float32 is tested on the raw bits, 4 values per load.)
-    __shared__ int s_odd;
+    // FOREGROUND contour value is 0 or in [2^-23, 2^39) -- true for any sane contour map -- every
+    // sum this kernel uses is in that range (only edges between foreground voxels count).  The
+    // kernel always takes the float expression; every voxel tests its own value and a single odd
+    // one raises a.cmax[1], upon which the caller recomputes the edges with K_MinEdge.
     __shared__ int s_wsum[8];
-    if (tid == 0) s_odd = 0;
     // ---- CTA-wide compaction of the brick's foreground voxels: thread t owns word t & 3 of row
     //      chunk t >> 2 (FT_TZ * FT_TY * 4 == 256); a block scan of the population counts gives the
     //      slot of its first voxel in the brick-local list
@@ -133,26 +132,7 @@ ulk_front_tile_kernel(const __grid_constant__ CUtensorMap tmap, const FrontArgs 
     int base = incl - mycnt, total = 0;
 #pragma unroll
     for (int wq = 0; wq < 8; ++wq) { const int t = s_wsum[wq]; if (wq < warp) base += t; total += t; }
-    if (sizeof(CT) == 4) {
-        const uint4 *p4 = (const uint4 *)sct;
-        u32 hi = 0, lo = 0xffffffffu;
-        for (int i = tid; i < FT_ROWS * TXP / 4; i += 256) {
-            const uint4 q = p4[i];
-            hi = max(max(hi, q.x), max(q.y, max(q.z, q.w)));
-            lo = min(min(lo, q.x - 1u), min(q.y - 1u, min(q.z - 1u, q.w - 1u)));     // zero wraps to the top
-        }
-        // all non-zero values in [2^-23, 2^39) as raw bits (a set sign bit exceeds the upper bound)
-        if (hi >= 0x53000000u || lo < 0x34000000u - 1u) s_odd = 1;
-    } else if (sizeof(CT) == 2) {
-        bool odd = false;
-        for (int i = tid; i < FT_ROWS * TXP; i += 256) {
-            const float f = FtConv<CT>::f(sct[i]);
-            odd |= !(f == 0.0f || (f >= 1.1920929e-7f && f < 5.49755814e11f));
-        }
-        if (odd) s_odd = 1;
-    }
-    __syncthreads();
-    const bool nice = s_odd == 0;
+    bool odd = false;
     const i32 sy = W, sz = W * H;
     u32 mx = 0;
     // bricks denser than FT_CAP voxels (> 50 % foreground) take more than one round
@@ -188,36 +168,25 @@ ulk_front_tile_kernel(const __grid_constant__ CUtensorMap tmap, const FrontArgs 
         const float s0 = FtConv<CT>::f(pc[-(FT_TY + 2) * TXP]) + c, s1 = FtConv<CT>::f(pc[-TXP]) + c;
         const float s2 = FtConv<CT>::f(pc[-1]) + c, s3 = c + FtConv<CT>::f(pc[1]);
         const float s4 = c + FtConv<CT>::f(pc[TXP]), s5 = c + FtConv<CT>::f(pc[(FT_TY + 2) * TXP]);
-        float q0, q1, q2, q3, q4, q5;
-        if (nice) {
-            q0 = s0 * 0.5f + 1e-8f; q1 = s1 * 0.5f + 1e-8f; q2 = s2 * 0.5f + 1e-8f;
-            q3 = s3 * 0.5f + 1e-8f; q4 = s4 * 0.5f + 1e-8f; q5 = s5 * 0.5f + 1e-8f;
-        } else {
-            q0 = ulk_wsum(s0); q1 = ulk_wsum(s1); q2 = ulk_wsum(s2); q3 = ulk_wsum(s3); q4 = ulk_wsum(s4); q5 = ulk_wsum(s5);
+        const float q0 = s0 * 0.5f + 1e-8f, q1 = s1 * 0.5f + 1e-8f, q2 = s2 * 0.5f + 1e-8f;
+        const float q3 = s3 * 0.5f + 1e-8f, q4 = s4 * 0.5f + 1e-8f, q5 = s5 * 0.5f + 1e-8f;
+        {
+            u32 cb;
+            memcpy(&cb, &c, 4);
+            odd |= !(cb == 0u || (cb >= 0x34000000u && cb < 0x53000000u));      // 0 or [2^-23, 2^39), sign clear
         }
         // first strictly smaller weight in key order wins: (weight, key) minimum.  Float order
-        // equals the order of the encoded bits K_MinEdge compares (weights are never NaN here:
-        // a NaN contour is not "nice" and takes the encoded compare below)
+        // equals the order of the encoded bits K_MinEdge compares (in-range weights are finite)
         int best = -1;
         u32 bw = ULK_NONE32;
-        if (nice) {
-            float bf = __int_as_float(0x7f800000);        // nice weights are finite
-            if (h0 && q0 < bf) { bf = q0; best = 0; }
-            if (h1 && q1 < bf) { bf = q1; best = 1; }
-            if (h2 && q2 < bf) { bf = q2; best = 2; }
-            if (h3 && q3 < bf) { bf = q3; best = 3; }
-            if (h4 && q4 < bf) { bf = q4; best = 4; }
-            if (h5 && q5 < bf) { bf = q5; best = 5; }
-            if (best >= 0) bw = ulk_f2ord(bf);
-        } else {
-            u32 eo;
-            if (h0 && (eo = ulk_f2ord(q0)) < bw) { bw = eo; best = 0; }
-            if (h1 && (eo = ulk_f2ord(q1)) < bw) { bw = eo; best = 1; }
-            if (h2 && (eo = ulk_f2ord(q2)) < bw) { bw = eo; best = 2; }
-            if (h3 && (eo = ulk_f2ord(q3)) < bw) { bw = eo; best = 3; }
-            if (h4 && (eo = ulk_f2ord(q4)) < bw) { bw = eo; best = 4; }
-            if (h5 && (eo = ulk_f2ord(q5)) < bw) { bw = eo; best = 5; }
-        }
+        float bf = __int_as_float(0x7f800000);
+        if (h0 && q0 < bf) { bf = q0; best = 0; }
+        if (h1 && q1 < bf) { bf = q1; best = 1; }
+        if (h2 && q2 < bf) { bf = q2; best = 2; }
+        if (h3 && q3 < bf) { bf = q3; best = 3; }
+        if (h4 && q4 < bf) { bf = q4; best = 4; }
+        if (h5 && q5 < bf) { bf = q5; best = 5; }
+        if (best >= 0) bw = ulk_f2ord(bf);
         // edge key = 3 * source voxel + direction; other endpoint = rank of the neighbour
         u32 bk = ULK_NONE32;
         i32 bo = ULK_PO_NONE;
@@ -245,6 +214,7 @@ ulk_front_tile_kernel(const __grid_constant__ CUtensorMap tmap, const FrontArgs 
     }
     mx = __reduce_max_sync(0xffffffffu, mx);
     if (lane == 0 && mx > *a.cmax) atomicMax(a.cmax, mx);
+    if (__any_sync(0xffffffffu, odd) && lane == 0) a.cmax[1] = 1u;
 }
 
 typedef CUresult (*ulk_encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,

@@ -740,9 +740,9 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
     u32 *words = A.get<u32>(nt);
     i32 *off = A.get<i32>(nt);
     UlkOW *ow = A.get<UlkOW>(nt);
-    u32 *cmax = A.get<u32>(1);
+    u32 *cmax = A.get<u32>(2);           // [0] largest |contour| bits  [1] the tile front end met a value outside its fast range
     CHKA(A);
-    CHK(ulk_memset(cmax, 0, 4, st));
+    CHK(ulk_memset(cmax, 0, 8, st));
     CHK(threshold_words(st, dm, fgp, fg_dtype, prm->threshold, SG, nt, words));
     CHK(ulk_exclusive_scan_popc_u32(words, off, nt, st));
     i32 h_last_off = 0; u32 h_last_w = 0;
@@ -784,8 +784,12 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
     CHK(ulk_memset(ctr, 0, 4 * sizeof(i32), st));
     ulk_launch_rk_multi(nullptr, nfg, st, K_FlattenCount{P, cnt, (i32 *)roots0, ctr});
     i32 hc[4];
-    u32 h_cmax = 0;
-    CHK(ulk_read2(hc, ctr, 4, &h_cmax, cmax, 1, st));
+    u32 h_cm[2] = {0, 0};
+    CHK(ulk_read2(hc, ctr, 4, h_cm, cmax, 2, st));
+    const u32 h_cmax = h_cm[0];
+    // a foreground contour value outside the tile kernel's exact float range (negative, NaN / inf,
+    // below 2^-23 or above 2^39): the steepest edges are recomputed in the general form
+    if (h_cm[1]) ulk_launch_rkx<1>("MinEdge", nullptr, fgl, nfg, dm, st, K_MinEdge{nullptr, ct, fg, mw, pk, po});
     const i32 n_roots = hc[0];
     const i32 max_area_i = prm->max_area > 2147483646.0 ? 2147483646 : (i32)prm->max_area;
     const int fix_shift = ulk_fix_shift_for(h_cmax);
