@@ -814,7 +814,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
     CHK(ulk_read2(&n_cc, keeppre + n_roots, 1, &n_big, bigpre + n_roots, 1, st));
     if (n_cc == 0) { F->n_nodes = 0; F->stats = stats_local; return empty_labels(st, F, V, keep_labels); }
     i32 *code = cnt;
-    ulk_launch(n_roots, st, K_RootCode{roots, keep, keeppre, big, bigpre, code, cc_big, big_cc});
+    ulk_launch(n_roots, st, K_RootCode{roots, keep, keeppre, big, bigpre, code, cc_big, big_cc, n_big > 0 ? 1 : 0});
     A.release(roots); A.release(keep); A.release(keeppre); A.release(big); A.release(bigpre); A.release(rsize);
 
     // ---- region labels: components, oversegmented where area > max_area
@@ -822,7 +822,7 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
     i32 *rlA = nullptr;
     i32 nA = 0;
     if (n_big == 0) {
-        ulk_launch_rkn<4>(nullptr, nfg, st, K_LabelCc{code, cc_big, 0, lab2, nullptr, nullptr, po});
+        ulk_launch_rkn<4>(nullptr, nfg, st, K_LabelCc{code, 0, lab2, nullptr, nullptr, po});
     } else {
         UlkArena AA;
         // the labels of the oversegmentation pass live in place too: > 0 on the components above
@@ -836,9 +836,9 @@ int ulk_segment_frame_impl(ulk_stream_t st, const void *fgp, int fg_dtype, const
         CHKA(AA); CHKA(A);
         CHK(ulk_memset(nA_dev, 0, sizeof(i32), st));
 #ifdef ULK_EMU
-        ulk_launch_rkn<4>(nullptr, nfg, st, K_LabelCc{code, cc_big, 1, labA, rlA, nA_dev, po});
+        ulk_launch_rkn<4>(nullptr, nfg, st, K_LabelCc{code, 1, labA, rlA, nA_dev, po});
 #else
-        ulk_launch_rk_multi(nullptr, nfg, st, K_LabelCc{code, cc_big, 1, labA, rlA, nA_dev, po});
+        ulk_launch_rk_multi(nullptr, nfg, st, K_LabelCc{code, 1, labA, rlA, nA_dev, po});
 #endif
         CHK(ulk_read(&nA, nA_dev, 1, st));
         stats_local.pass_a_voxels = nA;

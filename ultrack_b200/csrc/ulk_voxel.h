@@ -340,24 +340,28 @@ struct K_RootFlags {
 };
 // code[root] = 1-based index among the kept components (0: dropped); cc_big[index] = index
 // among the components above max_area or -1; big_cc = the inverse of cc_big
+// code at the root of every component.  final == 0: the 1-based index among the kept components
+// (0: dropped).  final == 1 (some component is above max_area): the label K_LabelCc mode 1 writes,
+// so that the voxel pass needs two dependent loads instead of three.
 struct K_RootCode {
-    const u32 *roots; const i32 *keep, *keeppre, *big, *bigpre; i32 *code; i32 *cc_big; i32 *big_cc;
+    const u32 *roots; const i32 *keep, *keeppre, *big, *bigpre; i32 *code; i32 *cc_big; i32 *big_cc; int final;
     ULK_D void operator()(i64 i) const
     {
         u32 r = roots[i];
         if (!keep[i]) { code[r] = 0; return; }
         i32 c = keeppre[i];
-        code[r] = c + 1;
         cc_big[c] = big[i] ? bigpre[i] : -1;
         if (big[i]) big_cc[bigpre[i]] = c;
+        code[r] = !final ? c + 1 : (big[i] ? bigpre[i] + 1 : -c - 2);
     }
 };
 // Component labels, written in place over the flattened component forest.
 // mode 0 (no component above max_area): the 1-based component index, 0 if dropped.
 // mode 1: components above max_area get their 1-based index among themselves (the region labels
 // of the oversegmentation pass), the other kept components -(index + 2), dropped ones -1.
+// (mode 1 reads the final label from `code`, see K_RootCode; -1 never is one)
 struct K_LabelCc {
-    const i32 *code; const i32 *cc_big; int mode; i32 *lab;
+    const i32 *code; int mode; i32 *lab;
     i32 *biglist; i32 *nbig;       // mode 1: the ranks of the voxels of the components above max_area (32-entry chunks in raster order)
     i32 *po;                       // steepest-edge endpoints: voxels of dropped components leave the graph (ULK_PO_OUT)
     struct S1 { i32 r, root; };
@@ -369,12 +373,11 @@ struct K_LabelCc {
         const i32 c = s.c;
         i32 g = -1;
         if (c == 0) po[s.r] = ULK_PO_OUT;
-        if (c >= 0) {
+        if (c != -1) {
             if (mode == 0) lab[s.r] = c;
-            else if (c == 0) lab[s.r] = -1;
             else {
-                g = cc_big[c - 1];
-                lab[s.r] = g >= 0 ? g + 1 : -(c - 1) - 2;
+                lab[s.r] = c == 0 ? -1 : c;
+                g = c > 0 ? c - 1 : -1;
             }
         }
         if (mode == 1) {
@@ -396,13 +399,13 @@ struct K_LabelCc {
 #pragma unroll
         for (int u = 0; u < ULK_MULTI; ++u) c[u] = r[u] >= 0 ? code[r[u]] : -1;
 #pragma unroll
-        for (int u = 0; u < ULK_MULTI; ++u) g[u] = c[u] > 0 ? cc_big[c[u] - 1] : -1;
+        for (int u = 0; u < ULK_MULTI; ++u) g[u] = c[u] > 0 ? c[u] - 1 : -1;
         const int lane = threadIdx.x & 31;
         u32 m[ULK_MULTI];
         i32 total = 0;
 #pragma unroll
         for (int u = 0; u < ULK_MULTI; ++u) {
-            if (c[u] >= 0) lab[v[u]] = c[u] == 0 ? -1 : (g[u] >= 0 ? g[u] + 1 : -(c[u] - 1) - 2);
+            if (c[u] != -1) lab[v[u]] = c[u] == 0 ? -1 : c[u];
             if (c[u] == 0) po[v[u]] = ULK_PO_OUT;
             m[u] = __ballot_sync(0xffffffffu, g[u] >= 0);
             total += __popc(m[u]);
@@ -1344,7 +1347,9 @@ struct K_WriteLabels {
     {
         S1 s;
         s.r = r; s.l = 0; s.ba = 0;
-        if (ok) { s.l = lab[r]; if (s.l > 0) s.ba = basA[r]; }
+        // basA is read whatever the label says (it is only used for l > 0): a load that waits for
+        // the label would serialise the entries of a thread
+        if (ok) { s.l = lab[r]; s.ba = basA[r]; }
         return s;
     }
     ULK_D ULK_INLINE S2 load2(const S1 &a, bool ok) const
