@@ -70,6 +70,40 @@ def test_front_tile_contours_outside_fast_range(cuda_lib, shape, odd):
     assert n > 0
 
 
+@pytest.mark.parametrize("dtype", [np.float32, np.float16, np.uint8])
+@pytest.mark.parametrize("thr", [0.3, -0.3, 1e-320, 2.0000000001, 1e39, float("inf")])
+def test_threshold_not_representable_in_float32(cuda_lib, dtype, thr):
+    """The vectorised threshold kernel compares in float32 against the threshold rounded down to
+    float32; the result must equal `double(v) > thr` for thresholds no float32 represents, with
+    voxels sitting exactly on either side (C ABI called directly: the Python layer would round thr)."""
+    from ultrack_b200 import _lib
+    shape = (48, 256)
+    mask, ct = cases.blob_frame(shape, 3, "smooth")
+    mask = np.asarray(mask) > 0
+    rng = np.random.default_rng(0)
+    if dtype == np.uint8:
+        near = np.array([0, 1, 2, 3, 255], np.uint8)
+    else:
+        with np.errstate(over="ignore"):
+            c = dtype(thr) if np.isfinite(dtype(thr)) else dtype(np.finfo(dtype).max)
+            near = np.array([c, np.nextafter(c, dtype(np.inf)), np.nextafter(c, dtype(-np.inf)), 0, np.finfo(dtype).max,
+                             -np.finfo(dtype).max, np.inf, -np.inf], dtype)
+    above = near[near.astype(np.float64) > thr]
+    below = near[~(near.astype(np.float64) > thr)]
+    fg = np.where(mask, rng.choice(above, size=shape) if len(above) else below[0],
+                  rng.choice(below, size=shape) if len(below) else above[0]).astype(dtype)
+    want = int((fg.astype(np.float64) > thr).sum())
+    prm = _lib.SegParams(float(thr), 30.0, 4000.0, 4.0, 0.0, 0, 0)
+    h = C.POINTER(_lib.FrameNodes)()
+    ctc = np.ascontiguousarray(ct, np.float32)
+    rc = cuda_lib.ulk_segment_frame_host(fg.ctypes.data_as(C.c_void_p), _lib.dtype_code(fg.dtype), ctc.ctypes.data_as(C.c_void_p),
+                                         _lib.dtype_code(ctc.dtype), (C.c_int64 * 3)(1, *shape), C.byref(prm), 0, None, C.byref(h))
+    _lib.check(cuda_lib, rc)
+    assert h.contents.stats.n_foreground == want
+    assert (want > 0) == (len(above) > 0)
+    cuda_lib.ulk_frame_nodes_free(h)
+
+
 @pytest.mark.parametrize("variant,shape,radius", [("T", (20, 40, 40), 6.0), ("T", (128, 128), 7.0),
                                                   ("S", (32, 64, 64), 6.0), ("S", (256, 256), 9.0)])
 @pytest.mark.parametrize("min_frontier", [0.0, 0.1])

@@ -216,35 +216,45 @@ ulk_threshold_kernel(K_Threshold k, u32 ntask)
 // W % 4 == 0 and aligned volumes: a lane loads four consecutive voxels with one vector load, a warp
 // covers four 32-voxel row segments per task; the foreground word of a segment is the OR of its
 // eight lanes' nibbles.  All U loads of a thread are issued before the first is used.
+// The comparison `double(v) > thr` of the generic kernel is done in float32 against thr rounded
+// DOWN to float32 (ulk_thr_floor_f32): every v here is exactly a float, and no float lies strictly
+// between that bound and thr, so the two comparisons agree for every v and every thr.
+static float ulk_thr_floor_f32(double thr)
+{
+    if (thr != thr) return (float)thr;                       // NaN: both comparisons are false
+    float t = (float)thr;
+    if ((double)t > thr) t = nextafterf(t, -INFINITY);
+    return t;
+}
 struct UlkLoadF32 {
     typedef float4 Raw;
     static __device__ __forceinline__ Raw load(const void *p, i64 v) { return __ldcs((const float4 *)((const float *)p + v)); }
-    static __device__ __forceinline__ u32 nib(const Raw &f, double thr)
+    static __device__ __forceinline__ u32 nib(const Raw &f, float thr)
     {
-        return ((double)f.x > thr ? 1u : 0u) | ((double)f.y > thr ? 2u : 0u) | ((double)f.z > thr ? 4u : 0u) | ((double)f.w > thr ? 8u : 0u);
+        return (f.x > thr ? 1u : 0u) | (f.y > thr ? 2u : 0u) | (f.z > thr ? 4u : 0u) | (f.w > thr ? 8u : 0u);
     }
 };
 struct UlkLoadU8 {
     typedef u32 Raw;
     static __device__ __forceinline__ Raw load(const void *p, i64 v) { return __ldcs((const u32 *)((const u8 *)p + v)); }
-    static __device__ __forceinline__ u32 nib(const Raw &q, double thr)
+    static __device__ __forceinline__ u32 nib(const Raw &q, float thr)
     {
-        return ((double)(q & 0xffu) > thr ? 1u : 0u) | ((double)((q >> 8) & 0xffu) > thr ? 2u : 0u) |
-               ((double)((q >> 16) & 0xffu) > thr ? 4u : 0u) | ((double)(q >> 24) > thr ? 8u : 0u);
+        return ((float)(q & 0xffu) > thr ? 1u : 0u) | ((float)((q >> 8) & 0xffu) > thr ? 2u : 0u) |
+               ((float)((q >> 16) & 0xffu) > thr ? 4u : 0u) | ((float)(q >> 24) > thr ? 8u : 0u);
     }
 };
 struct UlkLoadF16 {
     typedef uint2 Raw;
     static __device__ __forceinline__ Raw load(const void *p, i64 v) { return __ldcs((const uint2 *)((const uint16_t *)p + v)); }
-    static __device__ __forceinline__ u32 nib(const Raw &q, double thr)
+    static __device__ __forceinline__ u32 nib(const Raw &q, float thr)
     {
         const float a = ulk_half_to_float((uint16_t)(q.x & 0xffffu)), b = ulk_half_to_float((uint16_t)(q.x >> 16));
         const float c = ulk_half_to_float((uint16_t)(q.y & 0xffffu)), d = ulk_half_to_float((uint16_t)(q.y >> 16));
-        return ((double)a > thr ? 1u : 0u) | ((double)b > thr ? 2u : 0u) | ((double)c > thr ? 4u : 0u) | ((double)d > thr ? 8u : 0u);
+        return (a > thr ? 1u : 0u) | (b > thr ? 2u : 0u) | (c > thr ? 4u : 0u) | (d > thr ? 8u : 0u);
     }
 };
 template <int U, class L> __global__ void __launch_bounds__(256)
-ulk_threshold_kernel_v4(const void *fg, double thr, i32 W, u32 S, u32 T, u32 ntask4, u32 *words)
+ulk_threshold_kernel_v4(const void *fg, float thr, i32 W, u32 S, u32 T, u32 ntask4, u32 *words)
 {
     const int lane = threadIdx.x & 31;
     const u32 t0 = (u32)((((i64)blockIdx.x * 256 + threadIdx.x) >> 5) * U);
@@ -314,10 +324,11 @@ static int threshold_words(ulk_stream_t st, const UlkDims &dm, const void *fg, i
     if (vec4) {
         const u32 T = (u32)((dm.W + 127) / 128);
         const i64 nt4 = (i64)dm.D * dm.H * T;
+        const float thr_f = ulk_thr_floor_f32(thr);
         static const int U4 = getenv("ULK_THR_U") ? atoi(getenv("ULK_THR_U")) : 2;     // measured: 1.06 ms (U=2), 1.32 (4), 1.91 (8) at C5
         const i64 warps = (nt4 + U4 - 1) / U4;
         const unsigned grid = (unsigned)((warps + 7) / 8);
-#define ULK_THR_LAUNCH(UU, LL) ulk_threshold_kernel_v4<UU, LL><<<grid, 256, 0, st>>>(fg, thr, dm.W, (u32)S, T, (u32)nt4, words)
+#define ULK_THR_LAUNCH(UU, LL) ulk_threshold_kernel_v4<UU, LL><<<grid, 256, 0, st>>>(fg, thr_f, dm.W, (u32)S, T, (u32)nt4, words)
         if (fgt == ULK_F32) { if (U4 == 8) ULK_THR_LAUNCH(8, UlkLoadF32); else if (U4 == 2) ULK_THR_LAUNCH(2, UlkLoadF32); else ULK_THR_LAUNCH(4, UlkLoadF32); }
         else if (fgt == ULK_U8) { if (U4 == 8) ULK_THR_LAUNCH(8, UlkLoadU8); else if (U4 == 2) ULK_THR_LAUNCH(2, UlkLoadU8); else ULK_THR_LAUNCH(4, UlkLoadU8); }
         else { if (U4 == 8) ULK_THR_LAUNCH(8, UlkLoadF16); else if (U4 == 2) ULK_THR_LAUNCH(2, UlkLoadF16); else ULK_THR_LAUNCH(4, UlkLoadF16); }
