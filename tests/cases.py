@@ -91,8 +91,10 @@ def link_and_compare(lib, tabs, ndim, max_distance, max_neighbors, dw=0.0, shift
         m1, s1 = node_intensity(lib, h1, images[1])
         color = (m0, m1, s1)
         frames = (np.stack(images[0], axis=-1), np.stack(images[1], axis=-1))
+    # the C ABI takes (z, y, x) factors; 2-D frames have z = 0 everywhere
+    kscale = None if scale is None else (1.0,) * (3 - len(scale)) + tuple(scale)
     s, t, w, _ = link_frames(lib, h0, h1, max_distance=max_distance, max_neighbors=max_neighbors,
-                             distance_weight=dw, shift=shift, scale=scale, weight_func=weight_func,
+                             distance_weight=dw, shift=shift, scale=kscale, weight_func=weight_func,
                              edge_must_be_positive=positive, color=color, z_score_threshold=z_score_threshold)
     src, dst = nodes_for_link(n0, ndim, 0), nodes_for_link(n1, ndim, 1)
     ref, _, _, _, tie = link_pair(src, dst, max_distance, max_neighbors, dw, target_shift=shift, scale=scale,

@@ -8,6 +8,7 @@ oracle without a GPU.  The package itself never loads this library.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Dict, Optional, Sequence
 
 import numpy as np
@@ -21,7 +22,9 @@ _EMU = None
 def emu_lib():
     global _EMU
     if _EMU is None:
-        _EMU = _lib.bind(C.CDLL(str(build_emu())))
+        # ULK_EMU_LIB: a differently built harness (e.g. g++ -fsanitize=address,undefined, run with the
+        # sanitizer runtimes in LD_PRELOAD) instead of tests/emu/libulk_emu.so
+        _EMU = _lib.bind(C.CDLL(os.environ.get("ULK_EMU_LIB") or str(build_emu())))
         _EMU._ulk_is_emu = True
     return _EMU
 
