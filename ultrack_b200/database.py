@@ -219,9 +219,11 @@ def insert_links(database_path: str, weight: np.ndarray, source_id: np.ndarray, 
     """DataFrame[weight, source_id, target_id].to_sql('links', append) (linking/processing.py:279-289).
     The reference's frame is one float64 array, so ids reach sqlite as REAL values; the BIGINT
     column affinity stores them back as integers -- the same happens here."""
-    rows = zip((float(w) for w in weight), (float(s) for s in source_id), (float(t) for t in target_id))
+    as_floats = lambda a: np.asarray(a, dtype=np.float64).tolist()      # noqa: E731  (Python floats, one C loop per column)
+    rows = zip(as_floats(weight), as_floats(source_id), as_floats(target_id))
     conn = connect(database_path)
     try:
+        _bulk_pragmas(conn)
         with write_lock(database_path), conn:
             conn.execute("BEGIN IMMEDIATE")
             conn.executemany("INSERT INTO links (weight, source_id, target_id) VALUES (?, ?, ?)", rows)
